@@ -1,0 +1,82 @@
+"""The oracle (oracle/ddim_oracle.py) replayed against fixtures minted from the UNMODIFIED
+reference by oracle/make_golden.py.  CPU only; this is what pins the oracle."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import ddim_oracle as O
+
+# the oracle restates the same torch ops in the same order, so it reproduces the reference to the last bit on
+# the machine that minted the fixtures; a different host CPU may pick other oneDNN kernels -> fp32 noise floor
+TOL = dict(rtol=0, atol=2e-4)
+
+
+def _load(golden_dir, name):
+    return np.load(os.path.join(golden_dir, name + ".npz"))
+
+
+def test_state_dict_spec_matches_reference_layout(oracle_sd, golden_dir):
+    spec = O.state_dict_spec()
+    assert len(spec) == 389                                   # SURVEY.md §7 hard part 9
+    assert sum(int(np.prod(s)) for k, s in spec.items() if k != "temb.te") == 47_155_266
+    assert "up_modules.0.3.conv.weight" in spec and spec["up_modules.0.3.conv.weight"] == (256, 192, 4, 4)
+    assert "down_modules.1.0.norm.2.bias" not in spec
+    fp = _load(golden_dir, "weights_fingerprint")
+    for k, s in zip(fp["keys"], fp["sums"]):
+        assert float(oracle_sd[str(k)].double().sum()) == pytest.approx(float(s), rel=1e-12, abs=1e-12)
+
+
+def test_schedule(golden_dir):
+    assert np.array_equal(O.alphas_cumprod().numpy(), _load(golden_dir, "schedule")["alphas"])
+
+
+@pytest.mark.parametrize("name", ["model_b2_t64", "model_b1_t32", "model_b3_t96"])
+def test_model_forward(oracle_sd, golden_dir, name):
+    g = _load(golden_dir, name)
+    b, T, seed = (int(v) for v in g["meta"])
+    x, _, t = O.synthetic_inputs(b, T, seed)
+    assert np.array_equal(t.numpy(), g["t"])
+    out = O.OracleModel(oracle_sd)(x, t)
+    np.testing.assert_allclose(out.numpy(), g["out"], **TOL)
+
+
+@pytest.mark.parametrize("name", ["ddim_b2_t32_eta0", "ddim_b1_t64_eta1"])
+def test_generalized_steps(oracle_sd, golden_dir, name):
+    g = _load(golden_dir, name)
+    b, T, seed, nsteps = (int(v) for v in g["meta"])
+    eta = float(g["eta"])
+    sel = set(int(v) for v in g["sel"]) if bool(g["has_sel"]) else None
+    x, _, _ = O.synthetic_inputs(b, T, seed)
+    seq = O.uniform_seq(1000, nsteps)
+    gen = torch.Generator().manual_seed(seed + 1000)
+    noise = [torch.randn(x.shape, generator=gen) for _ in seq]
+    xs, x0 = O.generalized_steps(x, seq, O.OracleModel(oracle_sd), O.alphas_cumprod(), sel, noise=noise, eta=eta)
+    assert torch.equal(xs[0], x)
+    assert len(xs) - 1 == g["xs"].shape[0] and len(x0) == g["x0"].shape[0]
+    for got, want in zip(xs[1:], g["xs"]):
+        np.testing.assert_allclose(got.numpy(), want, rtol=0, atol=5e-4)
+    for got, want in zip(x0, g["x0"]):
+        np.testing.assert_allclose(got.numpy(), want, rtol=0, atol=5e-4)
+
+
+def test_loss(oracle_sd, golden_dir):
+    g = _load(golden_dir, "loss_b4_t32")
+    b, T, seed = (int(v) for v in g["meta"])
+    x0, e, t = O.synthetic_inputs(b, T, seed)
+    m = O.OracleModel(oracle_sd)
+    a = O.alphas_cumprod()
+    assert float(O.noise_estimation_loss(m, x0, t, e, a)) == pytest.approx(float(g["loss"]), rel=1e-5)
+    np.testing.assert_allclose(O.noise_estimation_loss(m, x0, t, e, a, keepdim=True).numpy(), g["per_sample"], rtol=1e-5)
+
+
+def test_ddim_coefficients_edge_cases():
+    a = O.alphas_cumprod()
+    co = O.ddim_coefficients(a, range(0, 1000, 20), eta=0.0)
+    assert len(co) == 50 and co[0]["i"] == 980 and co[-1]["j"] == -1
+    assert co[-1]["at_next"] == 1.0 and co[-1]["c2"] == 0.0          # functions/denoising.py:12: alpha[0] = 1.0
+    assert all(c["c1"] == 0.0 for c in co)
+    co1 = O.ddim_coefficients(a, range(0, 1000, 250), eta=1.0)
+    assert all(c["c1"] > 0 for c in co1[:-1]) and co1[-1]["c1"] == 0.0
+    assert O.select_index_for(1000, 10) == {999, 888, 777, 666, 555, 444, 333, 222, 111, 0}
