@@ -1,0 +1,432 @@
+// Host side of the tcgen05 implicit-GEMM kernel: tensor maps, tap programs, C-ABI entry points.
+#include <stdarg.h>
+#include <string.h>
+
+#include <mutex>
+
+#include "../../include/ddim_b200.h"
+#include "umma_gemm.cuh"
+
+using namespace ddimb;
+
+// ------------------------------------------------------------------------------------------------ errors
+static thread_local char g_err[512] = "";
+void ddimb_set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+extern "C" const char* ddimb_last_error(void) { return g_err; }
+extern "C" int ddimb_version(void) { return 100; }
+
+// ------------------------------------------------------------------------------------------------ tensor maps
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  });
+  return fn;
+}
+
+// bf16 tensor map; dims/box innermost first; strides in ELEMENTS for dims 1..rank-1
+static int make_tmap_bf16(CUtensorMap* tm, const void* ptr, int rank, const uint64_t* dims, const uint64_t* strides_elems,
+                          const uint32_t* box, int ck) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (!fn) {
+    ddimb_set_error("cuTensorMapEncodeTiled entry point unavailable (no CUDA driver?)");
+    return DDIMB_ERR_DRIVER;
+  }
+  cuuint64_t gd[5], gs[4];
+  cuuint32_t bx[5], es[5];
+  for (int i = 0; i < rank; ++i) {
+    gd[i] = dims[i];
+    bx[i] = box[i];
+    es[i] = 1;
+    if (i > 0) gs[i - 1] = strides_elems[i - 1] * 2;
+  }
+  if ((reinterpret_cast<uintptr_t>(ptr) & 15) != 0) {
+    ddimb_set_error("tensor map base %p not 16-byte aligned", ptr);
+    return DDIMB_ERR_ARG;
+  }
+  for (int i = 0; i < rank - 1; ++i)
+    if (gs[i] % 16 != 0) {
+      ddimb_set_error("tensor map stride %d = %llu bytes is not a multiple of 16", i, (unsigned long long)gs[i]);
+      return DDIMB_ERR_ARG;
+    }
+  CUtensorMapSwizzle sw = (ck == 64) ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;
+  CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(ptr), gd, gs, bx, es,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    ddimb_set_error("cuTensorMapEncodeTiled failed: CUresult %d (rank %d dims %llu,%llu,%llu box %u,%u,%u)", (int)r, rank,
+                    (unsigned long long)dims[0], (unsigned long long)(rank > 1 ? dims[1] : 0),
+                    (unsigned long long)(rank > 2 ? dims[2] : 0), box[0], rank > 1 ? box[1] : 0, rank > 2 ? box[2] : 0);
+    return DDIMB_ERR_TMAP;
+  }
+  return DDIMB_OK;
+}
+
+static int next_pow2_cols(int c) {
+  int v = 32;
+  while (v < c) v <<= 1;
+  return v;
+}
+
+// Fill the derived fields of GemmParams and launch.  A map is 5-D, B map is 3-D.
+static int launch_gemm(GemmParams& p, const CUtensorMap& tmA, const CUtensorMap& tmB, int ck, cudaStream_t stream) {
+  DDIMB_CHECK_ARG(ck == 32 || ck == 64);
+  DDIMB_CHECK_ARG(p.box[0] * p.box[1] * p.box[2] * p.box[3] == kTileM);
+  DDIMB_CHECK_ARG(p.n_seg % 16 == 0 && p.n_seg >= 16 && p.n_seg <= 256);
+  DDIMB_CHECK_ARG(p.n_acc % 16 == 0 && p.n_acc <= 512 && p.n_acc % p.n_seg == 0 && p.n_acc / p.n_seg <= 32);
+  DDIMB_CHECK_ARG(p.ntaps >= 1 && p.ntaps <= kMaxTaps);
+  DDIMB_CHECK_ARG(p.bias_mod % 16 == 0 && p.bias_mod >= 16);
+  if (p.stats) DDIMB_CHECK_ARG(p.bias_mod % 32 == 0 && p.num_n_tiles == 1);
+  int brows = 0;
+  for (int t = 0; t < p.ntaps; ++t) {
+    const TapDesc& tp = p.taps[t];
+    DDIMB_CHECK_ARG(tp.nseg >= 1 && tp.nchunk >= 1);
+    DDIMB_CHECK_ARG(tp.tmem_col0 % p.n_seg == 0 && tp.tmem_col0 + tp.nseg * p.n_seg <= p.n_acc);
+    if (tp.nseg * p.n_seg > brows) brows = tp.nseg * p.n_seg;
+  }
+  p.b_rows_per_stage = brows;
+  const int stage_bytes = (ck == 64 ? GemmSmem<64>::stage_bytes(brows) : GemmSmem<32>::stage_bytes(brows));
+  DDIMB_CHECK_ARG(stage_bytes % 1024 == 0);
+  const int max_smem = 232448;   // 227 KB opt-in limit per CTA on sm_100
+  int stages = (max_smem - 1024 - kGemmAuxBytes) / stage_bytes;
+  if (stages > 8) stages = 8;
+  DDIMB_CHECK_ARG(stages >= 2);
+  p.num_stages = stages;
+  p.num_acc_bufs = (2 * p.n_acc <= 512) ? 2 : 1;
+  p.tmem_cols = next_pow2_cols(p.num_acc_bufs * p.n_acc);
+  p.num_tiles = p.num_n_tiles * p.ntile[0] * p.ntile[1] * p.ntile[2] * p.ntile[3];
+  DDIMB_CHECK_ARG(p.num_tiles >= 1);
+  int smem = 1024 + stages * stage_bytes + kGemmAuxBytes;
+  if (smem < 120 * 1024) smem = 120 * 1024;   // keep one CTA per SM: TMEM is allocated without contention
+  int grid = p.num_tiles < ddimb_num_sms() ? p.num_tiles : ddimb_num_sms();
+  if (ck == 64) {
+    static bool attr = false;
+    if (!attr) { DDIMB_CUDA(cudaFuncSetAttribute(umma_gemm_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem)); attr = true; }
+    umma_gemm_kernel<64><<<grid, kGemmThreads, smem, stream>>>(tmA, tmB, p);
+  } else {
+    static bool attr = false;
+    if (!attr) { DDIMB_CUDA(cudaFuncSetAttribute(umma_gemm_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem)); attr = true; }
+    umma_gemm_kernel<32><<<grid, kGemmThreads, smem, stream>>>(tmA, tmB, p);
+  }
+  DDIMB_LAUNCH_CHECK();
+  return DDIMB_OK;
+}
+
+static void init_params(GemmParams& p) {
+  memset(&p, 0, sizeof(p));
+  for (int i = 0; i < 4; ++i) { p.box[i] = 1; p.ntile[i] = 1; p.out_dim[i] = 1; }
+  p.num_n_tiles = 1;
+}
+
+static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
+static inline int pick_ck(int c) { return (c % 64 == 0) ? 64 : 32; }
+
+// spatial tile of 128 positions inside one [T, W] image: full-width rows when W < 128, else a 128-wide strip
+static void spatial_tile(int T, int W, int* bw, int* bt) {
+  *bw = W >= kTileM ? kTileM : W;
+  *bt = kTileM / *bw;
+  (void)T;
+}
+
+// ------------------------------------------------------------------------------------------------ Conv2d 3x3 s1 p1
+// reference: models/diffusion.py:28-40 (Residual_Block.conv), evaluated on NHWC bf16.
+extern "C" int ddimb_conv3x3(const void* x, const void* w, const float* bias, const float* bias_b, int bias_b_stride, int act,
+                             const void* add, void* out, double* stats, int B, int T, int W, int Cin, int Cout,
+                             cudaStream_t stream) {
+  DDIMB_CHECK_ARG(x && w && out && B >= 1 && T >= 1);
+  DDIMB_CHECK_ARG(W >= 8 && W <= 256 && (W & (W - 1)) == 0);
+  DDIMB_CHECK_ARG(Cin % 32 == 0 && Cout % 32 == 0 && Cout <= 256 && Cin <= 256);
+  const int ck = pick_ck(Cin);
+  int bw, bt;
+  spatial_tile(T, W, &bw, &bt);
+  CUtensorMap tmA, tmB;
+  {
+    uint64_t dims[5] = {(uint64_t)Cin, (uint64_t)W, (uint64_t)T, 1, (uint64_t)B};
+    uint64_t str[4] = {(uint64_t)Cin, (uint64_t)W * Cin, (uint64_t)T * W * Cin, (uint64_t)T * W * Cin};
+    uint32_t box[5] = {(uint32_t)ck, (uint32_t)bw, (uint32_t)bt, 1, 1};
+    int r = make_tmap_bf16(&tmA, x, 5, dims, str, box, ck);
+    if (r) return r;
+  }
+  {
+    uint64_t dims[3] = {(uint64_t)9 * Cin, (uint64_t)Cout, 1};
+    uint64_t str[2] = {(uint64_t)9 * Cin, (uint64_t)9 * Cin * Cout};
+    uint32_t box[3] = {(uint32_t)ck, (uint32_t)Cout, 1};
+    int r = make_tmap_bf16(&tmB, w, 3, dims, str, box, ck);
+    if (r) return r;
+  }
+  GemmParams p;
+  init_params(p);
+  p.box[0] = bw; p.box[1] = bt;
+  p.ntile[0] = ceil_div(W, bw); p.ntile[1] = ceil_div(T, bt); p.ntile[3] = B;
+  p.n_seg = Cout; p.n_acc = Cout; p.a_batched = 1;
+  p.ntaps = 9;
+  for (int ky = 0; ky < 3; ++ky)
+    for (int kx = 0; kx < 3; ++kx) {
+      TapDesc& tp = p.taps[ky * 3 + kx];
+      tp.da[0] = (int16_t)(kx - 1); tp.da[1] = (int16_t)(ky - 1); tp.da[2] = 0; tp.da[3] = 0;
+      tp.a_c0 = 0; tp.b_k0 = (ky * 3 + kx) * Cin; tp.b_n0 = 0;
+      tp.nchunk = (int16_t)(Cin / ck); tp.nseg = 1; tp.tmem_col0 = 0;
+    }
+  p.out = out; p.add = reinterpret_cast<const __nv_bfloat16*>(add); p.bias = bias; p.bias_b = bias_b; p.stats = stats;
+  p.out_stride[0] = Cout; p.out_stride[1] = (int64_t)W * Cout; p.out_stride[3] = (int64_t)T * W * Cout;
+  p.out_dim[0] = W; p.out_dim[1] = T; p.out_dim[3] = B;
+  p.n_valid = Cout; p.bias_mod = Cout; p.bias_b_stride = bias_b_stride; p.act = act;
+  return launch_gemm(p, tmA, tmB, ck, stream);
+}
+
+// ------------------------------------------------------------------------------------------------ Conv2d 4x4 s2 p1
+// reference: models/diffusion.py:70-78 (Downsample).  The NHWC input is viewed space-to-depth as
+// (2*Cin, W/2, 2, T/2, B): kernel column kx in {1,2} is one contiguous 2*Cin slab of column pair f', kx=0 / kx=3 are
+// the upper / lower half of the neighbouring pairs; kernel row ky picks (pair row t'+dy, sub-row r).
+extern "C" int ddimb_conv_down4x4(const void* x, const void* w, const float* bias, void* out, double* stats, int B, int T, int W,
+                                  int Cin, int Cout, cudaStream_t stream) {
+  DDIMB_CHECK_ARG(x && w && out && B >= 1 && T >= 2 && T % 2 == 0);
+  DDIMB_CHECK_ARG(W >= 16 && W <= 256 && (W & (W - 1)) == 0);
+  DDIMB_CHECK_ARG(Cin % 32 == 0 && Cout % 32 == 0 && Cout <= 256 && Cin <= 256);
+  const int ck = pick_ck(Cin);
+  const int To = T / 2, Wo = W / 2;
+  int bw, bt;
+  spatial_tile(To, Wo, &bw, &bt);
+  CUtensorMap tmA, tmB;
+  {
+    uint64_t dims[5] = {(uint64_t)2 * Cin, (uint64_t)Wo, 2, (uint64_t)To, (uint64_t)B};
+    uint64_t str[4] = {(uint64_t)2 * Cin, (uint64_t)W * Cin, (uint64_t)2 * W * Cin, (uint64_t)T * W * Cin};
+    uint32_t box[5] = {(uint32_t)ck, (uint32_t)bw, 1, (uint32_t)bt, 1};
+    int r = make_tmap_bf16(&tmA, x, 5, dims, str, box, ck);
+    if (r) return r;
+  }
+  {
+    uint64_t dims[3] = {(uint64_t)16 * Cin, (uint64_t)Cout, 1};
+    uint64_t str[2] = {(uint64_t)16 * Cin, (uint64_t)16 * Cin * Cout};
+    uint32_t box[3] = {(uint32_t)ck, (uint32_t)Cout, 1};
+    int r = make_tmap_bf16(&tmB, w, 3, dims, str, box, ck);
+    if (r) return r;
+  }
+  GemmParams p;
+  init_params(p);
+  p.box[0] = bw; p.box[2] = bt;
+  p.ntile[0] = ceil_div(Wo, bw); p.ntile[2] = ceil_div(To, bt); p.ntile[3] = B;
+  p.n_seg = Cout; p.n_acc = Cout; p.a_batched = 1;
+  static const int kDy[4] = {-1, 0, 0, 1}, kR[4] = {1, 0, 1, 0};
+  int nt = 0;
+  for (int ky = 0; ky < 4; ++ky) {
+    // (dx, first channel of the pair slab, kernel column of the first Cin block, number of Cin blocks)
+    const int grp[3][4] = {{0, 0, 1, 2}, {-1, Cin, 0, 1}, {1, 0, 3, 1}};
+    for (int g = 0; g < 3; ++g) {
+      TapDesc& tp = p.taps[nt++];
+      tp.da[0] = (int16_t)grp[g][0]; tp.da[1] = (int16_t)kR[ky]; tp.da[2] = (int16_t)kDy[ky]; tp.da[3] = 0;
+      tp.a_c0 = grp[g][1]; tp.b_k0 = (ky * 4 + grp[g][2]) * Cin; tp.b_n0 = 0;
+      tp.nchunk = (int16_t)(grp[g][3] * Cin / ck); tp.nseg = 1; tp.tmem_col0 = 0;
+    }
+  }
+  p.ntaps = nt;
+  p.out = out; p.bias = bias; p.stats = stats;
+  p.out_stride[0] = Cout; p.out_stride[2] = (int64_t)Wo * Cout; p.out_stride[3] = (int64_t)To * Wo * Cout;
+  p.out_dim[0] = Wo; p.out_dim[2] = To; p.out_dim[3] = B;
+  p.n_valid = Cout; p.bias_mod = Cout; p.act = 0;
+  return launch_gemm(p, tmA, tmB, ck, stream);
+}
+
+// ------------------------------------------------------------------------------------------------ ConvTranspose2d 4x4 s2 p1
+// reference: models/diffusion.py:59-67 (Upsample) followed by the additive skip of :284.
+// Output row parity r is one launch: out[2t'+r, 2f'+s, co] = sum over (dy, dx) of in[t'+dy, f'+dx, :] . Wt[:, co, ky, kx],
+// ky = r + 1 - 2 dy, kx = s + 1 - 2 dx; accumulator columns are [s][co], i.e. the 2*Cout contiguous outputs of pixel pair f'.
+// Weight operand: w[(ky*4 + kx) * Cout + co][ci] (K-major rows).
+extern "C" int ddimb_conv_up4x4(const void* x, const void* w, const float* bias, const void* skip, void* out, double* stats, int B,
+                                int T, int W, int Cin, int Cout, cudaStream_t stream) {
+  DDIMB_CHECK_ARG(x && w && out && B >= 1 && T >= 1);
+  DDIMB_CHECK_ARG(W >= 8 && W <= 128 && (W & (W - 1)) == 0);
+  DDIMB_CHECK_ARG(Cin % 32 == 0 && Cout % 32 == 0 && Cout <= 256 && Cin <= 256);
+  const int ck = pick_ck(Cin);
+  int bw, bt;
+  spatial_tile(T, W, &bw, &bt);
+  CUtensorMap tmA, tmB;
+  {
+    uint64_t dims[5] = {(uint64_t)Cin, (uint64_t)W, (uint64_t)T, 1, (uint64_t)B};
+    uint64_t str[4] = {(uint64_t)Cin, (uint64_t)W * Cin, (uint64_t)T * W * Cin, (uint64_t)T * W * Cin};
+    uint32_t box[5] = {(uint32_t)ck, (uint32_t)bw, (uint32_t)bt, 1, 1};
+    int r = make_tmap_bf16(&tmA, x, 5, dims, str, box, ck);
+    if (r) return r;
+  }
+  {
+    uint64_t dims[3] = {(uint64_t)Cin, (uint64_t)16 * Cout, 1};
+    uint64_t str[2] = {(uint64_t)Cin, (uint64_t)16 * Cout * Cin};
+    uint32_t box[3] = {(uint32_t)ck, (uint32_t)Cout, 1};
+    int r = make_tmap_bf16(&tmB, w, 3, dims, str, box, ck);
+    if (r) return r;
+  }
+  const int To = 2 * T, Wo = 2 * W;
+  for (int r = 0; r < 2; ++r) {
+    GemmParams p;
+    init_params(p);
+    p.box[0] = bw; p.box[1] = bt;
+    p.ntile[0] = ceil_div(W, bw); p.ntile[1] = ceil_div(T, bt); p.ntile[3] = B;
+    p.n_seg = Cout; p.n_acc = 2 * Cout; p.a_batched = 1;
+    int nt = 0;
+    const int dys[2] = {0, r == 0 ? -1 : 1};
+    for (int iy = 0; iy < 2; ++iy) {
+      const int dy = dys[iy], ky = r + 1 - 2 * dy;
+      const int dxs[3] = {0, -1, 1};   // dx = 0 first: it writes both column halves
+      for (int ix = 0; ix < 3; ++ix) {
+        const int dx = dxs[ix];
+        TapDesc& tp = p.taps[nt++];
+        tp.da[0] = (int16_t)dx; tp.da[1] = (int16_t)dy; tp.da[2] = 0; tp.da[3] = 0;
+        tp.a_c0 = 0; tp.b_k0 = 0; tp.nchunk = (int16_t)(Cin / ck);
+        if (dx == 0) { tp.nseg = 2; tp.b_n0 = (ky * 4 + 1) * Cout; tp.tmem_col0 = 0; }        // s=0 -> kx=1, s=1 -> kx=2
+        else if (dx < 0) { tp.nseg = 1; tp.b_n0 = (ky * 4 + 3) * Cout; tp.tmem_col0 = 0; }    // s=0, kx=3
+        else { tp.nseg = 1; tp.b_n0 = (ky * 4 + 0) * Cout; tp.tmem_col0 = Cout; }             // s=1, kx=0
+      }
+    }
+    p.ntaps = nt;
+    p.out = out; p.add = reinterpret_cast<const __nv_bfloat16*>(skip); p.bias = bias; p.stats = stats;
+    p.out_stride[0] = 2 * Cout; p.out_stride[1] = (int64_t)2 * Wo * Cout; p.out_stride[3] = (int64_t)To * Wo * Cout;
+    p.out_base = (int64_t)r * Wo * Cout;
+    p.out_dim[0] = W; p.out_dim[1] = T; p.out_dim[3] = B;
+    p.n_valid = 2 * Cout; p.bias_mod = Cout; p.act = 0;
+    int rc = launch_gemm(p, tmA, tmB, ck, stream);
+    if (rc) return rc;
+  }
+  return DDIMB_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ nn.Linear
+// out[M, N] = act(a[M, K] . w[N, K]^T + bias), a/w bf16 row-major with leading dimensions lda/ldw (elements).
+// reference: models/diffusion.py:127-128,141,156,166; hf modeling_fnet.py:204-231.
+extern "C" int ddimb_linear(const void* a, long long lda, const void* w, long long ldw, const float* bias, int act, void* out,
+                            long long ldo, int out_f32, long long out_lo_offset, int M, int N, int K, cudaStream_t stream) {
+  DDIMB_CHECK_ARG(a && w && out && M >= 1);
+  DDIMB_CHECK_ARG(K % 32 == 0 && N % 16 == 0 && lda % 8 == 0 && ldw % 8 == 0 && ldo % 8 == 0);
+  const int ck = pick_ck(K);
+  int nseg_w = N;   // segment width: largest divisor of N that is <= 256 and a multiple of 16
+  if (N > 256) {
+    nseg_w = 256;
+    while (N % nseg_w != 0) nseg_w -= 16;
+  }
+  CUtensorMap tmA, tmB;
+  {
+    uint64_t dims[5] = {(uint64_t)K, (uint64_t)M, 1, 1, 1};
+    uint64_t str[4] = {(uint64_t)lda, (uint64_t)lda * M, (uint64_t)lda * M, (uint64_t)lda * M};
+    uint32_t box[5] = {(uint32_t)ck, kTileM, 1, 1, 1};
+    int r = make_tmap_bf16(&tmA, a, 5, dims, str, box, ck);
+    if (r) return r;
+  }
+  {
+    uint64_t dims[3] = {(uint64_t)K, (uint64_t)N, 1};
+    uint64_t str[2] = {(uint64_t)ldw, (uint64_t)ldw * N};
+    uint32_t box[3] = {(uint32_t)ck, (uint32_t)nseg_w, 1};
+    int r = make_tmap_bf16(&tmB, w, 3, dims, str, box, ck);
+    if (r) return r;
+  }
+  GemmParams p;
+  init_params(p);
+  p.box[0] = kTileM;
+  p.ntile[0] = ceil_div(M, kTileM);
+  p.num_n_tiles = N / nseg_w;
+  p.n_seg = nseg_w; p.n_acc = nseg_w; p.n_tile_stride = nseg_w;
+  p.ntaps = 1;
+  TapDesc& tp = p.taps[0];
+  tp.a_c0 = 0; tp.b_k0 = 0; tp.b_n0 = 0; tp.nchunk = (int16_t)(K / ck); tp.nseg = 1; tp.tmem_col0 = 0;
+  p.out = out; p.bias = bias;
+  p.out_stride[0] = ldo; p.out_dim[0] = M;
+  p.n_valid = N; p.bias_mod = N; p.act = act; p.out_f32 = out_f32; p.out_lo_offset = out_lo_offset;
+  return launch_gemm(p, tmA, tmB, ck, stream);
+}
+
+// ------------------------------------------------------------------------------------------------ FNet Fourier mixing
+// reference: hf modeling_fnet.py:142-177 -- Re(fftn(x, dim=(1, 2))) for x [B, S, H], restated as two real GEMMs
+//   U^T[b] = Wh . x[b]^T            Wh = [cos(2 pi h'h/H); sin(2 pi h'h/H)]   ([2H, H])
+//   Y[b]   = [Cs | -Ss] . [Uc[b]; Us[b]]                                        ([S, 2S] x [2S, H])
+// `split` = 3 runs both with split-bf16 operands (hi*hi + hi*lo + lo*hi, fp32 accumulate) for ~fp32-class twiddles:
+//   x    : bf16 [B*S][ldx], hi in columns [0,H), lo in [H,2H) (lo only read when split == 3)
+//   wh   : bf16 [2H][split*H]      = [Wh_hi | Wh_hi | Wh_lo]              (matched with x [hi | lo | hi])
+//   a2   : bf16 [S][4*Sp]          = [Cs_hi | -Ss_hi | Cs_lo | -Ss_lo], each block Sp = ceil32(S) wide, zero padded
+//   ut   : bf16 workspace [B][2H][2*Sp] (hi | lo), zero-initialised once by the caller
+//   y    : fp32 [B*S][H]
+extern "C" int ddimb_fourier_mix(const void* x, long long ldx, const void* wh, const void* a2, void* ut, float* y, int B, int S, int H,
+                                 int split, cudaStream_t stream) {
+  DDIMB_CHECK_ARG(x && wh && a2 && ut && y && B >= 1 && S >= 1 && S <= 256);
+  DDIMB_CHECK_ARG(H % 256 == 0 && (split == 1 || split == 3) && ldx % 8 == 0);
+  const int Sp = ceil_div(S, 32) * 32;
+  const int nS = ceil_div(S, 16) * 16;   // UMMA N for GEMM 1
+  // ---- GEMM 1: Ut[b][m][s] = sum_h Wh[m][h] x[b][s][h]
+  {
+    const int ck = 64;
+    CUtensorMap tmA, tmB;
+    uint64_t ad[5] = {(uint64_t)split * H, (uint64_t)2 * H, 1, 1, 1};
+    uint64_t as[4] = {(uint64_t)split * H, (uint64_t)split * H * 2 * H, (uint64_t)split * H * 2 * H, (uint64_t)split * H * 2 * H};
+    uint32_t ab[5] = {(uint32_t)ck, kTileM, 1, 1, 1};
+    int r = make_tmap_bf16(&tmA, wh, 5, ad, as, ab, ck);
+    if (r) return r;
+    uint64_t bd[3] = {(uint64_t)(split == 3 ? 2 * H : H), (uint64_t)S, (uint64_t)B};
+    uint64_t bs[2] = {(uint64_t)ldx, (uint64_t)ldx * S};
+    uint32_t bb[3] = {(uint32_t)ck, (uint32_t)nS, 1};
+    r = make_tmap_bf16(&tmB, x, 3, bd, bs, bb, ck);
+    if (r) return r;
+    GemmParams p;
+    init_params(p);
+    p.box[0] = kTileM;
+    p.ntile[0] = 2 * H / kTileM; p.ntile[3] = B;
+    p.n_seg = nS; p.n_acc = nS; p.b_batched = 1;
+    p.ntaps = split;
+    const int bk[3] = {0, H, 0};   // x: hi, lo, hi
+    for (int t = 0; t < split; ++t) {
+      TapDesc& tp = p.taps[t];
+      tp.a_c0 = t * H; tp.b_k0 = bk[t]; tp.b_n0 = 0; tp.nchunk = (int16_t)(H / ck); tp.nseg = 1; tp.tmem_col0 = 0;
+    }
+    p.out = ut;
+    p.out_stride[0] = 2 * Sp; p.out_stride[3] = (int64_t)2 * H * 2 * Sp;
+    p.out_dim[0] = 2 * H; p.out_dim[3] = B;
+    p.n_valid = S; p.bias_mod = 16; p.out_lo_offset = (split == 3) ? Sp : 0;
+    r = launch_gemm(p, tmA, tmB, ck, stream);
+    if (r) return r;
+  }
+  // ---- GEMM 2: Y[b][s'][h'] = sum_s Cs[s'][s] Uc[b][h'][s] - Ss[s'][s] Us[b][h'][s]
+  {
+    const int ck = (Sp % 64 == 0) ? 64 : 32;
+    CUtensorMap tmA, tmB;
+    uint64_t ad[5] = {(uint64_t)4 * Sp, (uint64_t)S, 1, 1, 1};
+    uint64_t as[4] = {(uint64_t)4 * Sp, (uint64_t)4 * Sp * S, (uint64_t)4 * Sp * S, (uint64_t)4 * Sp * S};
+    uint32_t ab[5] = {(uint32_t)ck, kTileM, 1, 1, 1};
+    int r = make_tmap_bf16(&tmA, a2, 5, ad, as, ab, ck);
+    if (r) return r;
+    uint64_t bd[3] = {(uint64_t)2 * Sp, (uint64_t)2 * H, (uint64_t)B};
+    uint64_t bs[2] = {(uint64_t)2 * Sp, (uint64_t)2 * Sp * 2 * H};
+    uint32_t bb[3] = {(uint32_t)ck, 256, 1};
+    r = make_tmap_bf16(&tmB, ut, 3, bd, bs, bb, ck);
+    if (r) return r;
+    GemmParams p;
+    init_params(p);
+    p.box[0] = kTileM;
+    p.ntile[0] = ceil_div(S, kTileM); p.ntile[3] = B;
+    p.num_n_tiles = H / 256; p.n_seg = 256; p.n_acc = 256; p.n_tile_stride = 256; p.b_batched = 1;
+    int nt = 0;
+    for (int half = 0; half < 2; ++half) {
+      // (A block, Ut plane): hi*hi, hi*lo, lo*hi
+      const int ablk[3] = {half, half, 2 + half}, upl[3] = {0, 1, 0};
+      for (int t = 0; t < split; ++t) {
+        TapDesc& tp = p.taps[nt++];
+        tp.a_c0 = ablk[t] * Sp; tp.b_k0 = upl[t] * Sp; tp.b_n0 = half * H; tp.nchunk = (int16_t)(Sp / ck); tp.nseg = 1; tp.tmem_col0 = 0;
+      }
+    }
+    p.ntaps = nt;
+    p.out = y; p.out_f32 = 1;
+    p.out_stride[0] = H; p.out_stride[3] = (int64_t)S * H;
+    p.out_dim[0] = S; p.out_dim[3] = B;
+    p.n_valid = H; p.bias_mod = H;
+    r = launch_gemm(p, tmA, tmB, ck, stream);
+    if (r) return r;
+  }
+  return DDIMB_OK;
+}

@@ -1,0 +1,350 @@
+// One tcgen05/TMEM/TMA kernel for every dense contraction on the denoiser path
+// (reference models/diffusion.py: Conv2d 3x3 :28-40, Conv2d 4x4 s2 :70-78, ConvTranspose2d 4x4 s2 :59-67,
+//  nn.Linear :105-109,127-128,156; hf modeling_fnet.py:142-231 Fourier mixing restated as DFT GEMMs).
+//
+// D[128 rows, n_acc cols] = sum over "taps" of A_tap[128, K_tap] * B_tap[n, K_tap]^T
+//   A rows are the 128 positions of a 5-D TMA box (c, d1, d2, d3, d4) of the NHWC/row-major activation; a tap
+//   shifts the box (da[]) and picks a channel range -- TMA out-of-bounds zero fill IS the conv zero padding.
+//   B rows are output channels of the K-major packed weight (or a per-sample operand for the DFT GEMMs).
+// Warp roles (192 threads): warp0 = TMA producer, warp1 = MMA issuer (+TMEM alloc), warps2-5 = epilogue
+// (TMEM -> registers -> bias/temb/activation/skip-add/GroupNorm partial sums -> global).
+#pragma once
+#include "common.cuh"
+
+namespace ddimb {
+
+constexpr int kMaxTaps = 16;
+constexpr int kTileM = 128;
+constexpr int kGemmThreads = 192;
+
+struct TapDesc {
+  int16_t da[4];      // coordinate shift of the A box along dims 1..4
+  int32_t a_c0;       // first A channel (dim 0) of this tap
+  int32_t b_k0;       // first B k (dim 0) of this tap
+  int32_t b_n0;       // B row of segment 0 (before the n-tile offset)
+  int16_t nchunk;     // K chunks of CK elements
+  int16_t nseg;       // N segments (each n_seg wide: one UMMA + one B box per segment)
+  int32_t tmem_col0;  // accumulator column of segment 0
+};
+
+struct GemmParams {
+  // ---- tiling
+  int32_t box[4];       // A box extents along dims 1..4, product == 128
+  int32_t ntile[4];     // tiles along dims 1..4 (dim 4 = batch)
+  int32_t num_n_tiles;  // tiles along N (Linear); 1 for convs
+  int32_t num_tiles;    // num_n_tiles * prod(ntile)
+  int32_t n_seg;        // UMMA N == rows of one B box (multiple of 16, <= 256)
+  int32_t n_acc;        // accumulator columns per tile (<= 512)
+  int32_t n_tile_stride;  // B row advance per n-tile
+  int32_t a_batched;    // A dim-4 coordinate = batch index (else 0)
+  int32_t b_batched;    // B dim-2 coordinate = batch index (else 0)
+  int32_t b_rows_per_stage;  // max nseg * n_seg
+  int32_t num_stages;
+  int32_t tmem_cols;    // power of two >= 32
+  int32_t num_acc_bufs; // 1 or 2
+  int32_t ntaps;
+  TapDesc taps[kMaxTaps];
+  // ---- epilogue
+  void* out;                // bf16 or fp32
+  const __nv_bfloat16* add; // optional bf16 tensor added after the activation, same addressing as out
+  const float* bias;        // optional [bias_mod]
+  const float* bias_b;      // optional [batch][bias_b_stride] (temb slice)
+  double* stats;            // optional [batch][8][2] (sum, sum of squares) of the stored values
+  int64_t out_stride[4];    // element strides of dims 1..4 in out/add
+  int64_t out_base;         // element offset added to every address
+  int64_t out_lo_offset;    // if != 0: also store the bf16 rounding residual at addr + out_lo_offset
+  int32_t out_dim[4];       // valid extents of dims 1..4 (rows outside are neither stored nor counted)
+  int32_t n_valid;          // valid columns in total (columns >= n_valid are not stored)
+  int32_t bias_mod;         // column c uses bias[c % bias_mod]; GroupNorm group = (c % bias_mod) / (bias_mod / 8)
+  int32_t bias_b_stride;
+  int32_t act;              // 0 none, 1 silu, 2 gelu_new
+  int32_t out_f32;          // 1: out is fp32
+};
+
+template <int CK>
+struct GemmSmem {
+  static constexpr int kABytes = kTileM * CK * 2;
+  static constexpr int kSwizzle = (CK == 64) ? 2 : 4;  // descriptor code: 2 = 128B, 4 = 64B
+  static constexpr int kSBO = 8 * CK * 2;              // 8-row group pitch
+  __host__ __device__ static int stage_bytes(int b_rows) { return kABytes + b_rows * CK * 2; }
+};
+
+constexpr int kGemmAuxBytes = 1024;  // barriers, tmem pointer, stats scratch
+
+template <int CK>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                 const __grid_constant__ GemmParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;   // swizzle atoms need 1024-B alignment
+  uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
+  const int stage_bytes = GemmSmem<CK>::stage_bytes(p.b_rows_per_stage);
+  const uint32_t aux = smem_base + p.num_stages * stage_bytes;
+  // aux layout: full[8] @0, empty[8] @64, tmem_full[2] @128, tmem_empty[2] @144, tmem_ptr @160, stats float[16] @192
+  const uint32_t bar_full = aux, bar_empty = aux + 64, bar_tfull = aux + 128, bar_tempty = aux + 144;
+  volatile uint32_t* tmem_ptr_gen = reinterpret_cast<volatile uint32_t*>(smem_gen + p.num_stages * stage_bytes + 160);
+  float* stats_smem = reinterpret_cast<float*>(smem_gen + p.num_stages * stage_bytes + 192);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    for (int s = 0; s < p.num_stages; ++s) {
+      mbar_init(bar_full + 8 * s, 1);
+      mbar_init(bar_empty + 8 * s, 1);
+    }
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(bar_tfull + 8 * b, 1);
+      mbar_init(bar_tempty + 8 * b, 4);   // one arrive per epilogue warp
+    }
+    mbar_fence_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(aux + 160, (uint32_t)p.tmem_cols);
+    tmem_relinquish();
+  }
+  if (threadIdx.x >= 64 && threadIdx.x < 64 + 16) stats_smem[threadIdx.x - 64] = 0.f;
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_gen;
+
+  const int tiles_m = p.ntile[0] * p.ntile[1] * p.ntile[2] * p.ntile[3];
+
+  if (warp == 0) {
+    // ================================================================ TMA producer
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+        int nt = tile / tiles_m, r = tile - nt * tiles_m;
+        int i1 = r % p.ntile[0]; r /= p.ntile[0];
+        int i2 = r % p.ntile[1]; r /= p.ntile[1];
+        int i3 = r % p.ntile[2]; r /= p.ntile[2];
+        int i4 = r;
+        const int c1 = i1 * p.box[0], c2 = i2 * p.box[1], c3 = i3 * p.box[2];
+        const int c4 = p.a_batched ? i4 * p.box[3] : 0;
+        const int bb = p.b_batched ? i4 : 0;
+        for (int t = 0; t < p.ntaps; ++t) {
+          const TapDesc& tp = p.taps[t];
+          const uint32_t tx = (uint32_t)(GemmSmem<CK>::kABytes + tp.nseg * p.n_seg * CK * 2);
+          for (int ch = 0; ch < tp.nchunk; ++ch) {
+            mbar_wait(bar_empty + 8 * stage, phase ^ 1, 1);
+            const uint32_t sa = smem_base + stage * stage_bytes;
+            const uint32_t sb = sa + GemmSmem<CK>::kABytes;
+            mbar_arrive_expect_tx(bar_full + 8 * stage, tx);
+            tma_load_5d(sa, &tmA, bar_full + 8 * stage, tp.a_c0 + ch * CK, c1 + tp.da[0], c2 + tp.da[1], c3 + tp.da[2], c4 + tp.da[3]);
+            for (int sg = 0; sg < tp.nseg; ++sg)
+              tma_load_3d(sb + sg * p.n_seg * CK * 2, &tmB, bar_full + 8 * stage, tp.b_k0 + ch * CK,
+                          nt * p.n_tile_stride + tp.b_n0 + sg * p.n_seg, bb);
+            if (++stage == p.num_stages) { stage = 0; phase ^= 1; }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ================================================================ MMA issuer (single thread)
+    if (lane == 0) {
+      const uint32_t idesc = make_idesc_bf16(kTileM, (uint32_t)p.n_seg);
+      int stage = 0;
+      uint32_t phase = 0;
+      int local = 0;
+      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++local) {
+        const int buf = local % p.num_acc_bufs;
+        const uint32_t use = (uint32_t)(local / p.num_acc_bufs);
+        mbar_wait(bar_tempty + 8 * buf, (use & 1) ^ 1, 2);
+        tc_fence_after();
+        const uint32_t acc0 = tmem_base + (uint32_t)(buf * p.n_acc);
+        uint32_t written = 0;
+        for (int t = 0; t < p.ntaps; ++t) {
+          const TapDesc& tp = p.taps[t];
+          for (int ch = 0; ch < tp.nchunk; ++ch) {
+            mbar_wait(bar_full + 8 * stage, phase, 3);
+            tc_fence_after();
+            const uint32_t sa = smem_base + stage * stage_bytes;
+            const uint32_t sb = sa + GemmSmem<CK>::kABytes;
+            const uint64_t adesc = make_kmajor_desc(sa, GemmSmem<CK>::kSBO, GemmSmem<CK>::kSwizzle);
+            for (int sg = 0; sg < tp.nseg; ++sg) {
+              const int col = tp.tmem_col0 + sg * p.n_seg;
+              const uint32_t bit = 1u << (col / p.n_seg);
+              const uint64_t bdesc = make_kmajor_desc(sb + sg * p.n_seg * CK * 2, GemmSmem<CK>::kSBO, GemmSmem<CK>::kSwizzle);
+#pragma unroll
+              for (int k = 0; k < CK / 16; ++k) {
+                // +32 bytes along K inside the swizzle atom == +2 in the (addr >> 4) start-address field
+                umma_bf16(acc0 + (uint32_t)col, adesc + 2 * k, bdesc + 2 * k, idesc, ((written & bit) != 0u) | (k > 0));
+              }
+              written |= bit;
+            }
+            umma_commit(bar_empty + 8 * stage);   // smem slot is free once these MMAs have read it
+            if (++stage == p.num_stages) { stage = 0; phase ^= 1; }
+          }
+        }
+        umma_commit(bar_tfull + 8 * buf);         // accumulator complete
+      }
+    }
+  } else {
+    // ================================================================ epilogue (warps 2..5, TMEM lane quarter = warp % 4)
+    const int q = warp & 3;
+    const int row = q * 32 + lane;
+    const int et = threadIdx.x - 64;   // 0..127
+    int r = row;
+    const int r1 = r % p.box[0]; r /= p.box[0];
+    const int r2 = r % p.box[1]; r /= p.box[1];
+    const int r3 = r % p.box[2]; r /= p.box[2];
+    const int r4 = r;
+    const int cg = p.bias_mod >> 3;   // channels per GroupNorm group
+    int local = 0;
+    for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++local) {
+      int nt = tile / tiles_m, rr = tile - nt * tiles_m;
+      int i1 = rr % p.ntile[0]; rr /= p.ntile[0];
+      int i2 = rr % p.ntile[1]; rr /= p.ntile[1];
+      int i3 = rr % p.ntile[2]; rr /= p.ntile[2];
+      int i4 = rr;
+      const int d1 = i1 * p.box[0] + r1, d2 = i2 * p.box[1] + r2, d3 = i3 * p.box[2] + r3, d4 = i4 * p.box[3] + r4;
+      const bool valid = d1 < p.out_dim[0] && d2 < p.out_dim[1] && d3 < p.out_dim[2] && d4 < p.out_dim[3];
+      const int64_t addr0 = p.out_base + d1 * p.out_stride[0] + d2 * p.out_stride[1] + d3 * p.out_stride[2] + d4 * p.out_stride[3];
+      const int batch = i4;
+      const float* bias_b = p.bias_b ? p.bias_b + (int64_t)batch * p.bias_b_stride : nullptr;
+
+      const int buf = local % p.num_acc_bufs;
+      const uint32_t use = (uint32_t)(local / p.num_acc_bufs);
+      mbar_wait(bar_tfull + 8 * buf, use & 1, 4);
+      tc_fence_after();
+      const uint32_t trow = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * p.n_acc);
+
+      float s1 = 0.f, s2 = 0.f;
+      int cur_group = -1;
+      for (int c0 = 0; c0 < p.n_acc; c0 += 16) {
+        uint32_t v[16];
+        tmem_ld16(trow + (uint32_t)c0, v);
+        tmem_ld_wait();
+        const int gcol = nt * p.n_acc + c0;   // global column of v[0]
+        if (gcol >= p.n_valid) break;         // uniform across the CTA
+        float f[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) f[j] = __uint_as_float(v[j]);
+        if (p.bias) {
+          const int bc = gcol % p.bias_mod;   // 16-column chunks never straddle bias_mod (multiple of 16)
+#pragma unroll
+          for (int j = 0; j < 16; j += 4) {
+            const float4 b4 = *reinterpret_cast<const float4*>(p.bias + bc + j);
+            f[j] += b4.x; f[j + 1] += b4.y; f[j + 2] += b4.z; f[j + 3] += b4.w;
+          }
+        }
+        if (bias_b) {
+          const int bc = gcol % p.bias_mod;
+#pragma unroll
+          for (int j = 0; j < 16; j += 4) {
+            const float4 b4 = *reinterpret_cast<const float4*>(bias_b + bc + j);
+            f[j] += b4.x; f[j + 1] += b4.y; f[j + 2] += b4.z; f[j + 3] += b4.w;
+          }
+        }
+        if (p.act == 1) {
+#pragma unroll
+          for (int j = 0; j < 16; ++j) f[j] = silu_fast(f[j]);
+        } else if (p.act == 2) {
+#pragma unroll
+          for (int j = 0; j < 16; ++j) f[j] = gelu_new_fast(f[j]);
+        }
+        if (p.add && valid) {
+          const uint4* ap = reinterpret_cast<const uint4*>(p.add + addr0 + gcol);
+          const uint4 a0 = ap[0], a1 = ap[1];
+          const uint32_t aw[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float2 t2 = unpack_bf16x2(aw[j]);
+            f[2 * j] += t2.x; f[2 * j + 1] += t2.y;
+          }
+        }
+        const int nrem = p.n_valid - gcol;    // columns of this chunk that exist (>= 1)
+        if (p.out_f32) {
+          if (valid) {
+            float* op = reinterpret_cast<float*>(p.out) + addr0 + gcol;
+            if (nrem >= 16) {
+#pragma unroll
+              for (int j = 0; j < 16; j += 4) *reinterpret_cast<float4*>(op + j) = make_float4(f[j], f[j + 1], f[j + 2], f[j + 3]);
+            } else {
+              for (int j = 0; j < nrem; ++j) op[j] = f[j];
+            }
+          }
+        } else {
+          uint32_t w[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) w[j] = pack_bf16x2(f[2 * j], f[2 * j + 1]);
+          if (valid) {
+            __nv_bfloat16* op = reinterpret_cast<__nv_bfloat16*>(p.out) + addr0 + gcol;
+            if (nrem >= 16) {
+              stg_v4(op, make_uint4(w[0], w[1], w[2], w[3]));
+              stg_v4(op + 8, make_uint4(w[4], w[5], w[6], w[7]));
+            } else {
+              for (int j = 0; j < nrem; ++j) op[j] = __float2bfloat16_rn(f[j]);
+            }
+            if (p.out_lo_offset != 0) {
+              // split-bf16: second plane holds bf16(x - bf16(x)) so a later GEMM can use hi*W + lo*W
+              uint32_t wl[8];
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                const float2 h = unpack_bf16x2(w[j]);
+                wl[j] = pack_bf16x2(f[2 * j] - h.x, f[2 * j + 1] - h.y);
+              }
+              __nv_bfloat16* lp = op + p.out_lo_offset;
+              if (nrem >= 16) {
+                stg_v4(lp, make_uint4(wl[0], wl[1], wl[2], wl[3]));
+                stg_v4(lp + 8, make_uint4(wl[4], wl[5], wl[6], wl[7]));
+              } else {
+                for (int j = 0; j < nrem; ++j) {
+                  const float h = __bfloat162float(__float2bfloat16_rn(f[j]));
+                  lp[j] = __float2bfloat16_rn(f[j] - h);
+                }
+              }
+            }
+          }
+        }
+        if (p.stats) {
+          // GroupNorm partial sums of what the next GroupNorm will see; groups are multiples of 4 channels wide
+#pragma unroll
+          for (int j = 0; j < 16; j += 4) {
+            const int g = ((gcol + j) % p.bias_mod) / cg;
+            if (g != cur_group) {
+              if (cur_group >= 0) {
+                s1 = warp_sum(s1); s2 = warp_sum(s2);
+                if (lane == 0) { atomicAdd(&stats_smem[2 * cur_group], s1); atomicAdd(&stats_smem[2 * cur_group + 1], s2); }
+              }
+              cur_group = g; s1 = 0.f; s2 = 0.f;
+            }
+            if (valid) {
+#pragma unroll
+              for (int jj = 0; jj < 4; ++jj) { const float x = f[j + jj]; s1 += x; s2 = fmaf(x, x, s2); }
+            }
+          }
+        }
+      }
+      // accumulator buffer can be overwritten by the MMA warp
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_tempty + 8 * buf);
+      if (p.stats) {
+        if (cur_group >= 0) {
+          s1 = warp_sum(s1); s2 = warp_sum(s2);
+          if (lane == 0) { atomicAdd(&stats_smem[2 * cur_group], s1); atomicAdd(&stats_smem[2 * cur_group + 1], s2); }
+        }
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        if (et < 16) {
+          atomicAdd(p.stats + (int64_t)batch * 16 + et, (double)stats_smem[et]);
+          stats_smem[et] = 0.f;
+        }
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, (uint32_t)p.tmem_cols);
+  }
+}
+
+}  // namespace ddimb

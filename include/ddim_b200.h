@@ -1,0 +1,112 @@
+/* libddim_b200 -- C ABI of the B200-native DDIM-audio hot path.
+ *
+ * Drop-in boundary for klae01/ddim-audio: the reference has no FFI of its own (it is pure Python over torch.nn), so
+ * these are the entry points its Python layer binds through ctypes (ddim_audio_b200/_C.py; INTEGRATION.md shows the
+ * stub a maintainer would add to the reference).  Every function
+ *   - takes raw DEVICE pointers, explicit sizes and a cudaStream_t as its last argument; no torch types;
+ *   - is asynchronous on that stream, re-entrant, and owns no device memory;
+ *   - returns 0 on success, a negative DDIMB_ERR_* code for argument/driver errors or a positive cudaError_t;
+ *     ddimb_last_error() returns a thread-local description.
+ * There is no CPU path: on a machine without an sm_100 device the launches fail with a CUDA error.
+ *
+ * Activation layout inside the network: NHWC bf16, [B][T][W][C] (the reference is NCHW fp32; conv_in / conv_out
+ * convert at the network boundary).  GroupNorm statistics: double [B][8][2] = (sum, sum of squares) per group,
+ * ACCUMULATED by the producing kernel into a buffer the caller has zeroed.
+ */
+#ifndef DDIM_B200_H_
+#define DDIM_B200_H_
+
+#include <cuda_runtime_api.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+int ddimb_version(void);
+const char* ddimb_last_error(void);
+
+/* ---- sampler / loss arithmetic (fp32, elementwise) ------------------------------------------------------------ */
+
+/* functions/denoising.py:27,41-43 -- one DDIM update, in place on xt:
+ *   x0 = (xt - sqrt(1-at) et) / sqrt(at);  xt = sqrt(at_next) x0 + c2 et + c1 z.
+ * z may be NULL (or c1 == 0): the noise term is skipped.  x0_out / xs_out (nullable) receive the snapshots of
+ * :29-34 / :45-50.  n = number of floats (multiple of 4). */
+int ddimb_ddim_step(float* xt, const float* et, const float* z, float* x0_out, float* xs_out, double at, double at_next,
+                    double c1, double c2, long long n, cudaStream_t stream);
+
+/* functions/losses.py:12-13 -- out = x0 sqrt(a[t]) + e sqrt(1 - a[t]); t is int64 [B]. */
+int ddimb_qsample(const float* x0, const float* e, const float* alphas, const long long* t, float* out, int B,
+                  long long per_sample, cudaStream_t stream);
+
+/* functions/losses.py:15-18 -- per_sample[b] = sum (e - output)^2 over one sample (double; zeroed here). */
+int ddimb_sqerr_loss(const float* e, const float* output, double* per_sample, int B, long long per_sample_elems,
+                     cudaStream_t stream);
+
+/* ---- network boundary convolutions (CUDA cores; K = 18 / N = 2 are not tensor-core shapes) -------------------- */
+
+/* models/diffusion.py:189-198 -- Conv2d(Cin=2 -> 32, k3 p1): x fp32 NCHW, w fp32 [32][Cin][3][3], out bf16 NHWC. */
+int ddimb_conv_in(const float* x, const float* w, const float* bias, void* out, double* stats, int B, int Cin, int T, int F,
+                  int Cout, cudaStream_t stream);
+/* models/diffusion.py:199-208 -- Conv2d(32 -> 2, k3 p1): x bf16 NHWC, w fp32 [2][32][3][3], out fp32 NCHW. */
+int ddimb_conv_out(const void* x, const float* w, const float* bias, float* out, int B, int T, int F, int Cin, int Cout,
+                   cudaStream_t stream);
+
+/* ---- tcgen05 / TMEM / TMA implicit-GEMM convolutions and GEMMs ------------------------------------------------ */
+
+/* models/diffusion.py:28-40,49,52 -- Conv2d 3x3 s1 p1 on NHWC bf16.  w: bf16 [Cout][9*Cin], k = (ky*3+kx)*Cin + ci.
+ * Epilogue: + bias[Cout] (nullable) + bias_b[b*bias_b_stride + co] (nullable; the temb slice of :49), act (0 none,
+ * 1 SiLU of :50,53), + add (nullable bf16, same shape as out), GroupNorm partial sums into stats (nullable). */
+int ddimb_conv3x3(const void* x, const void* w, const float* bias, const float* bias_b, int bias_b_stride, int act,
+                  const void* add, void* out, double* stats, int B, int T, int W, int Cin, int Cout, cudaStream_t stream);
+
+/* models/diffusion.py:70-78 -- Downsample Conv2d 4x4 s2 p1.  w: bf16 [Cout][16*Cin], k = (ky*4+kx)*Cin + ci.
+ * x [B][T][W][Cin] -> out [B][T/2][W/2][Cout]. */
+int ddimb_conv_down4x4(const void* x, const void* w, const float* bias, void* out, double* stats, int B, int T, int W,
+                       int Cin, int Cout, cudaStream_t stream);
+
+/* models/diffusion.py:59-67 + :284 -- Upsample ConvTranspose2d 4x4 s2 p1, then "+ skip".
+ * w: bf16 [16*Cout][Cin], row = (ky*4+kx)*Cout + co.  x [B][T][W][Cin] -> out [B][2T][2W][Cout]; skip nullable. */
+int ddimb_conv_up4x4(const void* x, const void* w, const float* bias, const void* skip, void* out, double* stats, int B,
+                     int T, int W, int Cin, int Cout, cudaStream_t stream);
+
+/* nn.Linear (models/diffusion.py:127-128,141,156,166; transformers modeling_fnet.py:204-231):
+ * out[M][N] = act(a[M][K] w[N][K]^T + bias); a, w bf16 with leading dimensions lda, ldw; act 0 none / 1 SiLU /
+ * 2 gelu_new; out bf16 or fp32 (out_f32) with leading dimension ldo; out_lo_offset != 0 also stores the bf16
+ * rounding residual at out + out_lo_offset (split-bf16 operand for ddimb_fourier_mix). */
+int ddimb_linear(const void* a, long long lda, const void* w, long long ldw, const float* bias, int act, void* out,
+                 long long ldo, int out_f32, long long out_lo_offset, int M, int N, int K, cudaStream_t stream);
+
+/* transformers modeling_fnet.py:142-177 -- y = Re(fftn(x, dim=(1,2))) for x [B][S][H] as two DFT-matrix GEMMs.
+ * Operand layouts are documented at the definition (csrc/gemm_host.cu); split = 1 (bf16) or 3 (split-bf16). */
+int ddimb_fourier_mix(const void* x, long long ldx, const void* wh, const void* a2, void* ut, float* y, int B, int S, int H,
+                      int split, cudaStream_t stream);
+
+/* ---- GroupNorm / LayerNorm / token repacks -------------------------------------------------------------------- */
+
+/* models/diffusion.py:17-26,47-56 -- GroupNorm(8, C, eps) applied from precomputed statistics.
+ * mode 0: y = gn(x); mode 1: y = silu(gn(x)); mode 2: y = res + gn(x) and accumulate stats_out of y.
+ * beta nullable (norm[2] has no bias, :26). */
+int ddimb_gn_apply(const void* x, const void* res, void* y, const double* stats_in, double* stats_out, const float* gamma,
+                   const float* beta, int mode, int B, long long positions, int C, float eps, cudaStream_t stream);
+
+/* models/diffusion.py:107-120 -- BetaEmbedding layers in fp32: out[r][n] = act(in[idx?idx[r]:r] . w[n] + bias[n]). */
+int ddimb_linear_small(const float* in, const long long* idx, const float* w, const float* bias, float* out, int rows,
+                       int K, int N, int act, cudaStream_t stream);
+
+/* models/diffusion.py:273-275,130-142 -- NHWC [B][S][W][C] -> tokens [B*S][C*W] (+ positional table te) -> LayerNorm. */
+int ddimb_tokens_ln(const void* x, const float* te, const float* gamma, const float* beta, void* out, int B, int S, int W,
+                    int C, float eps, cudaStream_t stream);
+/* models/diffusion.py:277-279,284 -- tokens fp32 [B*S][C*W] -> NHWC bf16, + skip, GroupNorm partial sums. */
+int ddimb_tokens_to_nhwc(const float* tok, const void* skip, void* out, double* stats, int B, int S, int W, int C,
+                         cudaStream_t stream);
+/* transformers modeling_fnet.py:180-188,226-231 -- y = LayerNorm_512(a + b) (b nullable); writes fp32 y and its bf16
+ * operand copy ybf [rows][ldy] (columns [0,512) hi; [512,1024) rounding residual when write_lo). */
+int ddimb_layernorm512(const float* a, const float* b, const float* gamma, const float* beta, float* y, void* ybf,
+                       long long ldy, int write_lo, int rows, float eps, cudaStream_t stream);
+/* fp32 [rows][H] -> bf16 hi (+ lo) planes of a [rows][ldy] operand buffer. */
+int ddimb_split_bf16(const float* a, void* ybf, long long ldy, int H, int write_lo, long long rows, cudaStream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DDIM_B200_H_ */
