@@ -1,0 +1,81 @@
+"""ctypes binding of libddim_b200.so (include/ddim_b200.h) -- the only door from Python to the sm_100a kernels.
+
+There is no CPU path and no fallback: importing this module without the built library raises, and every
+wrapper raises ``RuntimeError`` (with the library's own message) on a non-zero return code.  Tensors are passed
+as raw device pointers plus sizes; launches go to ``torch.cuda.current_stream()``.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libddim_b200.so")
+
+if not os.path.exists(LIB_PATH):
+    raise ImportError(
+        f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` (needs nvcc); "
+        "ddim_audio_b200 has no CPU fallback"
+    )
+lib = C.CDLL(LIB_PATH)
+
+_vp, _i, _ll, _d, _f = C.c_void_p, C.c_int, C.c_longlong, C.c_double, C.c_float
+
+# name -> argtypes (the trailing cudaStream_t is appended below); must mirror include/ddim_b200.h
+SIGNATURES = {
+    "ddimb_ddim_step": [_vp, _vp, _vp, _vp, _vp, _d, _d, _d, _d, _ll],
+    "ddimb_qsample": [_vp, _vp, _vp, _vp, _vp, _i, _ll],
+    "ddimb_sqerr_loss": [_vp, _vp, _vp, _i, _ll],
+    "ddimb_sqerr_loss_bwd": [_vp, _vp, _vp, _vp, _i, _ll],
+    "ddimb_conv_in": [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i],
+    "ddimb_conv_out": [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i],
+    "ddimb_conv3x3": [_vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _i, _i, _i, _i, _i],
+    "ddimb_conv_down4x4": [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i],
+    "ddimb_conv_up4x4": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i],
+    "ddimb_linear": [_vp, _ll, _vp, _ll, _vp, _i, _vp, _ll, _i, _ll, _i, _i, _i],
+    "ddimb_fourier_mix": [_vp, _ll, _vp, _vp, _vp, _vp, _i, _i, _i, _i],
+    "ddimb_gn_apply": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _ll, _i, _f],
+    "ddimb_linear_small": [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i],
+    "ddimb_tokens_ln": [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _f],
+    "ddimb_tokens_to_nhwc": [_vp, _vp, _vp, _vp, _i, _i, _i, _i],
+    "ddimb_layernorm512": [_vp, _vp, _vp, _vp, _vp, _vp, _ll, _i, _i, _f],
+    "ddimb_split_bf16": [_vp, _vp, _ll, _i, _i, _ll],
+}
+EXPORTS = ["ddimb_version", "ddimb_last_error"] + list(SIGNATURES)
+
+lib.ddimb_version.restype = _i
+lib.ddimb_last_error.restype = C.c_char_p
+for _name, _args in SIGNATURES.items():
+    _fn = getattr(lib, _name)
+    _fn.argtypes = _args + [_vp]
+    _fn.restype = _i
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def ptr(t, dtype=None):
+    """Device pointer of a contiguous CUDA tensor (None -> NULL)."""
+    if t is None:
+        return None
+    if not t.is_cuda:
+        raise RuntimeError("ddim_audio_b200: expected a CUDA tensor (there is no CPU path)")
+    if dtype is not None and t.dtype != dtype:
+        raise RuntimeError(f"ddim_audio_b200: expected {dtype}, got {t.dtype}")
+    if not t.is_contiguous():
+        raise RuntimeError("ddim_audio_b200: expected a contiguous tensor")
+    return t.data_ptr()
+
+
+def call(name: str, *args) -> None:
+    rc = getattr(lib, name)(*args, _stream())
+    if rc != 0:
+        msg = lib.ddimb_last_error().decode(errors="replace")
+        raise RuntimeError(f"{name} failed (code {rc}): {msg}")
+
+
+def version() -> int:
+    return int(lib.ddimb_version())

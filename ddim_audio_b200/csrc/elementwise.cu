@@ -115,6 +115,31 @@ extern "C" int ddimb_sqerr_loss(const float* e, const float* output, double* per
   return DDIMB_OK;
 }
 
+// backward of the reduction above: grad_output = -2 (e - output) * g[b]
+__global__ void __launch_bounds__(256) sqerr_bwd_kernel(const float4* __restrict__ e, const float4* __restrict__ o,
+                                                        const float* __restrict__ g, float4* __restrict__ go, int64_t per4) {
+  const int b = blockIdx.y;
+  const int64_t base = (int64_t)b * per4;
+  const float s = -2.0f * g[b];
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < per4; i += (int64_t)gridDim.x * blockDim.x) {
+    const float4 a = e[base + i], c = o[base + i];
+    go[base + i] = make_float4(s * (a.x - c.x), s * (a.y - c.y), s * (a.z - c.z), s * (a.w - c.w));
+  }
+}
+
+extern "C" int ddimb_sqerr_loss_bwd(const float* e, const float* output, const float* g, float* grad_output, int B,
+                                    long long per_sample_elems, cudaStream_t stream) {
+  DDIMB_CHECK_ARG(e && output && g && grad_output && B >= 1 && per_sample_elems % 4 == 0);
+  const int64_t per4 = per_sample_elems / 4;
+  int bx = (int)((per4 + 255) / 256);
+  const int cap = ddimb_num_sms() * 8 / B + 1;
+  if (bx > cap) bx = cap;
+  sqerr_bwd_kernel<<<dim3(bx, B), 256, 0, stream>>>(reinterpret_cast<const float4*>(e), reinterpret_cast<const float4*>(output), g,
+                                                    reinterpret_cast<float4*>(grad_output), per4);
+  DDIMB_LAUNCH_CHECK();
+  return DDIMB_OK;
+}
+
 // ------------------------------------------------------------------------------------------------ GroupNorm family
 // reference models/diffusion.py:17-26 (GroupNorm(8, C, eps=1e-6)), :42-56 (where each one sits in Residual_Block).
 // x is NHWC bf16 [B][P][C]; stats[b][g] = (sum, sumsq) over the C/8 channels x P positions of group g.
@@ -298,8 +323,9 @@ extern "C" int ddimb_conv_in(const float* x, const float* w, const float* bias, 
 // ------------------------------------------------------------------------------------------------ conv_out
 // reference models/diffusion.py:199-208: Conv2d(32 -> 2, k3 p1); reads NHWC bf16, writes the fp32 NCHW epsilon.
 template <int CI, int CO>
-__global__ void __launch_bounds__(128) conv_out_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ w,
-                                                      const float* __restrict__ bias, float* __restrict__ out, int T, int F) {
+__global__ void __launch_bounds__(128) conv_out_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ x2,
+                                                      const float* __restrict__ w, const float* __restrict__ bias,
+                                                      float* __restrict__ out, int T, int F) {
   __shared__ float sw[9 * CI * CO];   // [tap][ci][co]
   const int b = blockIdx.z, t = blockIdx.y;
   for (int i = threadIdx.x; i < 9 * CI * CO; i += blockDim.x) {
@@ -320,15 +346,22 @@ __global__ void __launch_bounds__(128) conv_out_kernel(const __nv_bfloat16* __re
     for (int kx = 0; kx < 3; ++kx) {
       const int ff = f + kx - 1;
       if (ff < 0 || ff >= F) continue;
-      const uint4* xp = reinterpret_cast<const uint4*>(x + (((int64_t)b * T + tt) * F + ff) * CI);
+      const int64_t off = (((int64_t)b * T + tt) * F + ff) * CI;
+      const uint4* xp = reinterpret_cast<const uint4*>(x + off);
+      const uint4* xp2 = x2 ? reinterpret_cast<const uint4*>(x2 + off) : nullptr;
       const float* wp = sw + (ky * 3 + kx) * CI * CO;
 #pragma unroll
       for (int c8 = 0; c8 < CI / 8; ++c8) {
         const uint4 v = __ldg(xp + c8);
         const uint32_t vw[4] = {v.x, v.y, v.z, v.w};
+        uint4 v2 = make_uint4(0u, 0u, 0u, 0u);
+        if (xp2) v2 = __ldg(xp2 + c8);
+        const uint32_t vw2[4] = {v2.x, v2.y, v2.z, v2.w};
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-          const float2 p2 = unpack_bf16x2(vw[j]);
+          float2 p2 = unpack_bf16x2(vw[j]);
+          const float2 q2 = unpack_bf16x2(vw2[j]);   // the additive skip of models/diffusion.py:284 (bf16 zero when absent)
+          p2.x += q2.x; p2.y += q2.y;
           const int ci = c8 * 8 + 2 * j;
 #pragma unroll
           for (int c = 0; c < CO; ++c) {
@@ -343,10 +376,11 @@ __global__ void __launch_bounds__(128) conv_out_kernel(const __nv_bfloat16* __re
   for (int c = 0; c < CO; ++c) out[(((int64_t)b * CO + c) * T + t) * F + f] = acc[c];
 }
 
-extern "C" int ddimb_conv_out(const void* x, const float* w, const float* bias, float* out, int B, int T, int F, int Cin, int Cout,
-                              cudaStream_t stream) {
+extern "C" int ddimb_conv_out(const void* x, const void* skip, const float* w, const float* bias, float* out, int B, int T, int F,
+                              int Cin, int Cout, cudaStream_t stream) {
   DDIMB_CHECK_ARG(x && w && bias && out && B >= 1 && Cin == 32 && Cout == 2);
-  conv_out_kernel<32, 2><<<dim3((F + 127) / 128, T, B), 128, 0, stream>>>(reinterpret_cast<const __nv_bfloat16*>(x), w, bias, out, T, F);
+  conv_out_kernel<32, 2><<<dim3((F + 127) / 128, T, B), 128, 0, stream>>>(reinterpret_cast<const __nv_bfloat16*>(x),
+                                                                          reinterpret_cast<const __nv_bfloat16*>(skip), w, bias, out, T, F);
   DDIMB_LAUNCH_CHECK();
   return DDIMB_OK;
 }

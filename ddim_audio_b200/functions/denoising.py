@@ -1,0 +1,86 @@
+"""DDIM sampler behind the reference's ``generalized_steps(x, seq, model, alpha, select_index, **kwargs)``
+(functions/denoising.py:10-52).
+
+Per step: one ``model(xt, t)`` call and ONE fused update kernel (``ddimb_ddim_step``: x0 prediction, the
+alpha_next combination, the eta/sigma noise term and both optional snapshots in a single pass over ``xt``)
+instead of the reference's five elementwise launches.  Snapshots leave the GPU through a side stream into
+pinned host memory, so the loop never blocks on a device->host copy (the reference's ``.to("cpu")`` does).
+
+Stated differences from the literal reference text:
+  * the working tensor is a clone -- the reference aliases (and overwrites) a CUDA fp32 ``x``, so its ``xs[0]``
+    ends up holding the final sample; here ``xs[0]`` is the untouched input;
+  * the N(0,1) draw of :42 happens only when its coefficient c1 is non-zero (eta > 0), or comes from the
+    ``noise=`` keyword (an iterable of per-step tensors) when the caller wants a reproducible stream.
+"""
+from __future__ import annotations
+
+import torch
+
+from .. import ops
+
+
+def _ddim_scalars(alpha_list, i, j, eta):
+    """functions/denoising.py:22-24,36-40 -- float64 host arithmetic, as the reference."""
+    at = alpha_list[int(i) + 1]
+    at_next = alpha_list[int(j) + 1]
+    c1 = eta * ((1 - at / at_next) * (1 - at_next) / (1 - at)) ** 0.5
+    c2 = ((1 - at_next) - c1 ** 2) ** 0.5
+    return at, at_next, c1, c2
+
+
+class _SnapshotPipe:
+    """device buffer -> pinned host tensor on a side stream."""
+
+    def __init__(self, device):
+        self.stream = torch.cuda.Stream(device=device)
+        self.device = device
+
+    def push(self, dev_tensor):
+        host = torch.empty(dev_tensor.shape, dtype=dev_tensor.dtype, pin_memory=True)
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream(self.device))
+        with torch.cuda.stream(self.stream):
+            self.stream.wait_event(ev)
+            host.copy_(dev_tensor, non_blocking=True)
+            dev_tensor.record_stream(self.stream)
+        return host
+
+    def drain(self):
+        self.stream.synchronize()
+
+
+def generalized_steps(x, seq, model, alpha, select_index, **kwargs):
+    if not torch.cuda.is_available():
+        raise RuntimeError("ddim_audio_b200.generalized_steps needs a CUDA device: there is no CPU path")
+    eta = kwargs.get("eta", 0)
+    noise = kwargs.get("noise", None)
+    noise_it = iter(noise) if noise is not None else None
+    with torch.no_grad():
+        alpha_list = [1.0] + alpha.to("cpu", torch.float32).numpy().tolist()          # :12
+        device = x.device if x.is_cuda else torch.device("cuda", torch.cuda.current_device())
+        seq = list(seq)
+        seq_next = [-1] + seq[:-1]
+        n = x.size(0)
+        xs, x0_preds = [x], []
+        xt = x.to(device=device, dtype=torch.float32, copy=True).contiguous()
+        t = torch.zeros(n, dtype=torch.int64, device=device)
+        pipe = _SnapshotPipe(device)
+        L = len(seq)
+        for index, (i, j) in enumerate(zip(reversed(seq), reversed(seq_next))):
+            t.fill_(int(i))
+            at, at_next, c1, c2 = _ddim_scalars(alpha_list, i, j, eta)
+            et = model(xt, t)
+            selected = select_index is None or index in select_index or index - L in select_index
+            z = None
+            if noise_it is not None:
+                z = next(noise_it).to(device=device, dtype=torch.float32).contiguous()
+            elif c1 != 0:
+                z = torch.randn_like(xt)
+            x0_buf = torch.empty_like(xt) if selected else None
+            xs_buf = torch.empty_like(xt) if selected else None
+            ops.ddim_step(xt, et.contiguous(), z, at, at_next, c1, c2, x0_out=x0_buf, xs_out=xs_buf)
+            if selected:
+                x0_preds.append(pipe.push(x0_buf))                                     # :29-34
+                xs.append(pipe.push(xs_buf))                                           # :45-50
+        pipe.drain()
+    return xs, x0_preds

@@ -1,0 +1,347 @@
+"""B200-native denoiser behind the reference's ``Model(config).forward(input, t)`` (models/diffusion.py:170-294).
+
+The module tree exists to own the parameters under the reference's 389 ``state_dict`` keys (and to consume the
+RNG in the reference's construction order, so ``torch.manual_seed(s); Model(config)`` initialises identically);
+no ``torch.nn`` forward is ever called.  ``forward`` drives the sm_100a kernels of libddim_b200 through
+``ddim_audio_b200.ops``: activations live in HBM as NHWC bf16, GroupNorm statistics are produced by the
+kernel that writes a tensor, convolutions / Linears / the FNet Fourier mixing are tcgen05 GEMMs.
+There is no CPU path: a non-CUDA input raises.
+"""
+from __future__ import annotations
+
+import math
+from typing import List
+
+import torch
+import torch.nn as nn
+
+from .. import ops
+
+GN_GROUPS = 8        # models/diffusion.py:19
+GN_EPS = 1e-6        # models/diffusion.py:20
+
+
+def _group_norm(channels: int) -> nn.GroupNorm:
+    return nn.GroupNorm(GN_GROUPS, channels, eps=GN_EPS, affine=True)
+
+
+class Residual_Block(nn.Module):
+    """Parameter holder for models/diffusion.py:12-56 (3 GroupNorms, conv0 without bias, conv1 with bias;
+    norm[2] has zero-initialised weight and no bias)."""
+
+    def __init__(self, *, channels, kernel_size=3):
+        super().__init__()
+        if kernel_size != 3:
+            raise NotImplementedError("ddim_audio_b200: Residual_Block kernels exist for kernel_size=3 only (audio.yml:49)")
+        self.channels = channels
+        self.norm = nn.Sequential(_group_norm(channels), _group_norm(channels), _group_norm(channels))
+        nn.init.zeros_(self.norm[2].weight)
+        self.norm[2].register_parameter("bias", None)
+        self.conv = nn.Sequential(
+            nn.Conv2d(channels, channels, kernel_size, 1, kernel_size // 2, bias=False),
+            nn.Conv2d(channels, channels, kernel_size, 1, kernel_size // 2, bias=True),
+        )
+
+
+class Upsample(nn.Module):
+    """models/diffusion.py:59-67."""
+
+    def __init__(self, *, in_channels, out_channels):
+        super().__init__()
+        self.conv = nn.ConvTranspose2d(in_channels, out_channels, kernel_size=4, stride=2, padding=1)
+
+
+class Downsample(nn.Module):
+    """models/diffusion.py:70-78."""
+
+    def __init__(self, *, in_channels, out_channels):
+        super().__init__()
+        self.conv = nn.Conv2d(in_channels, out_channels, kernel_size=4, stride=2, padding=1)
+
+
+def sinusoid_table(length: int, channel: int) -> torch.Tensor:
+    """models/diffusion.py:81-92 applied to a zero table: sin on even columns, cos on odd ones (fp32, host)."""
+    pos = torch.arange(length, dtype=torch.float32).unsqueeze(1)
+    freq = torch.exp(torch.arange(0, channel, 2, dtype=torch.float32) * (-math.log(10000.0) / channel))
+    ang = pos * freq
+    table = torch.zeros(length, channel, dtype=torch.float32)
+    table[:, 0::2] = torch.sin(ang)
+    table[:, 1::2] = torch.cos(ang)
+    return table
+
+
+class BetaEmbedding(nn.Module):
+    """models/diffusion.py:95-120: sinusoid table buffer ``te`` + three Linears named ``weight.{0,1,2}``."""
+
+    def __init__(self, seq_length, channel_sz):
+        super().__init__()
+        pos_ch, emb_ch = 128, 512
+        self.register_buffer("te", sinusoid_table(seq_length, pos_ch))
+        self.weight = nn.Sequential(nn.Linear(pos_ch, emb_ch), nn.Linear(emb_ch, emb_ch), nn.Linear(emb_ch, channel_sz))
+
+
+class TransformerEmbedding(nn.Module):
+    """models/diffusion.py:123-145."""
+
+    def __init__(self, in_channels, config):
+        super().__init__()
+        self.LayerNorm = nn.LayerNorm(in_channels, eps=config.kwargs.layer_norm_eps)
+        self.projection = nn.Linear(in_channels, config.channels)
+        self.dropout_p = float(config.kwargs.hidden_dropout_prob)
+
+
+class _Node(nn.Module):
+    """Bare container used to spell the HF FNetEncoder key names (hf modeling_fnet.py:180-286)."""
+
+
+def _fnet_layer(hidden: int, ffn: int, eps: float) -> nn.Module:
+    lay = _Node()
+    lay.fourier = _Node()
+    lay.fourier.output = _Node()
+    lay.fourier.output.LayerNorm = nn.LayerNorm(hidden, eps=eps)
+    lay.intermediate = _Node()
+    lay.intermediate.dense = nn.Linear(hidden, ffn)
+    lay.output = _Node()
+    lay.output.dense = nn.Linear(ffn, hidden)
+    lay.output.LayerNorm = nn.LayerNorm(hidden, eps=eps)
+    return lay
+
+
+class Transformer_Module(nn.Module):
+    """models/diffusion.py:148-167.  The reference ``exec``/``eval``s config strings to build HF's FNetEncoder; the
+    only arithmetic those strings can select here is FNet with gelu_new, so they are checked, not executed."""
+
+    def __init__(self, io_channels, config):
+        super().__init__()
+        kw = config.kwargs
+        if "FNetEncoder" not in str(getattr(config, "module", "FNetEncoder")):
+            raise NotImplementedError("ddim_audio_b200: transformers.module must be FNetEncoder (audio.yml:31)")
+        if getattr(kw, "hidden_act", "gelu_new") != "gelu_new":
+            raise NotImplementedError("ddim_audio_b200: FNet hidden_act must be gelu_new (audio.yml:37)")
+        if kw.hidden_size != 512 or config.channels != kw.hidden_size:
+            raise NotImplementedError("ddim_audio_b200: FNet kernels are built for hidden_size == channels == 512 (audio.yml:34,41)")
+        self.embedding = TransformerEmbedding(io_channels, config)
+        self.encoder = _Node()
+        self.encoder.layer = nn.ModuleList(
+            [_fnet_layer(kw.hidden_size, kw.intermediate_size, kw.layer_norm_eps) for _ in range(kw.num_hidden_layers)]
+        )
+        self.compute_out = nn.Linear(config.channels, io_channels)
+        self.ln_eps = float(kw.layer_norm_eps)
+        self.hidden = int(kw.hidden_size)
+
+
+def _fourier_operands(S: int, H: int, device) -> tuple:
+    """DFT matrices for ``ddimb_fourier_mix`` (layouts documented in csrc/gemm_host.cu), built in float64 on the
+    host and split into bf16 hi / lo planes: Re(F_S x F_H) = C_S (x C_H) - S_S (x S_H)."""
+    Sp = (S + 31) // 32 * 32
+    kh = torch.arange(H, dtype=torch.float64)
+    ang_h = 2.0 * math.pi * torch.outer(kh, kh) / H
+    wh = torch.cat([torch.cos(ang_h), torch.sin(ang_h)], dim=0)                     # [2H, H]
+    wh_hi = wh.to(torch.bfloat16)
+    wh_lo = (wh - wh_hi.double()).to(torch.bfloat16)
+    wh_op = torch.cat([wh_hi, wh_hi, wh_lo], dim=1).contiguous()                    # matched with x [hi | lo | hi]
+    ks = torch.arange(S, dtype=torch.float64)
+    ang_s = 2.0 * math.pi * torch.outer(ks, ks) / S
+    blocks = []
+    for m in (torch.cos(ang_s), -torch.sin(ang_s)):
+        pad = torch.zeros(S, Sp, dtype=torch.float64)
+        pad[:, :S] = m
+        blocks.append(pad)
+    hi = [b.to(torch.bfloat16) for b in blocks]
+    lo = [(b - h.double()).to(torch.bfloat16) for b, h in zip(blocks, hi)]
+    a2 = torch.cat(hi + lo, dim=1).contiguous()                                     # [S, 4*Sp]
+    return wh_op.to(device), a2.to(device), Sp
+
+
+class Model(nn.Module):
+    """Drop-in for the reference ``Model`` (models/diffusion.py:170-294): same constructor argument (the full config
+    namespace), same parameter names and shapes, same ``forward(input[B,C,T,F], t[B]) -> [B,C,T,F]`` fp32."""
+
+    def __init__(self, config):
+        self.config = config.model
+        cfg = self.config
+        assert len(cfg.ch) == len(cfg.krn) == len(cfg.res)
+        super().__init__()
+        widths = [c for n, c in zip(cfg.res, cfg.ch) for _ in range(n)]
+        self.embedding_size = widths + widths[::-1]                                 # :177-183
+        self.temb = BetaEmbedding(config.diffusion.num_diffusion_timesteps, sum(self.embedding_size))
+        self.down_modules = nn.ModuleList([nn.Conv2d(cfg.channels, cfg.ch[0], 3, 1, 1)])
+        ups: List[nn.Module] = [nn.Conv2d(cfg.ch[0], cfg.channels, 3, 1, 1)]
+        prev = None
+        for c, k, n in zip(cfg.ch, cfg.krn, cfg.res):
+            # construction order (down stage, then up stage, per level) fixes the RNG stream of the default init
+            stage = [] if prev is None else [Downsample(in_channels=prev, out_channels=c)]
+            stage += [Residual_Block(channels=c, kernel_size=k) for _ in range(n)]
+            self.down_modules.append(nn.ModuleList(stage))
+            stage = [] if prev is None else [Upsample(in_channels=c, out_channels=prev)]
+            stage += [Residual_Block(channels=c, kernel_size=k) for _ in range(n)]
+            ups.append(nn.ModuleList(stage[::-1]))
+            prev = c
+        self.up_modules = nn.ModuleList(ups[::-1])                                  # index 0 = deepest level (:226-227)
+        self.levels = len(cfg.ch)
+        self.token_f = cfg.f_size // (2 ** (self.levels - 1))
+        self.transformer = Transformer_Module(cfg.ch[-1] * self.token_f, cfg.transformers)
+        if cfg.dtype:
+            self._apply_type_string(cfg.dtype)
+        self._packed = None
+        self._packed_key = None
+        self._consts = {}
+
+    # ------------------------------------------------------------------ dtype strings (audio.yml:26,42)
+    def _apply_type_string(self, s: str):
+        if not str(s).endswith("FloatTensor"):
+            raise NotImplementedError(f"ddim_audio_b200: parameters are fp32 masters; unsupported model.dtype {s!r}")
+        self.type(s)            # 'torch.cuda.FloatTensor' also moves the module to the GPU, as in the reference
+
+    # ------------------------------------------------------------------ kernel-ready weights
+    def _pack_key(self):
+        return tuple((p.data_ptr(), p._version) for p in self.parameters())
+
+    @torch.no_grad()
+    def _pack(self):
+        """bf16 K-major operand copies of every GEMM weight (layouts: include/ddim_b200.h)."""
+        bf = torch.bfloat16
+        pk = {}
+
+        def c3(w):      # [Co, Ci, 3, 3] -> [Co, (ky*3+kx)*Ci + ci]
+            return w.detach().permute(0, 2, 3, 1).reshape(w.shape[0], -1).to(bf).contiguous()
+
+        def rb(m):
+            return dict(g0=m.norm[0].weight, b0=m.norm[0].bias, g1=m.norm[1].weight, b1=m.norm[1].bias, g2=m.norm[2].weight,
+                        w0=c3(m.conv[0].weight), w1=c3(m.conv[1].weight), cb1=m.conv[1].bias, C=m.channels)
+
+        down = []
+        for stage in list(self.down_modules)[1:]:
+            ent = dict(down=None, blocks=[])
+            for m in stage:
+                if isinstance(m, Downsample):
+                    w = m.conv.weight.detach()                                       # [Co, Ci, 4, 4]
+                    ent["down"] = dict(w=w.permute(0, 2, 3, 1).reshape(w.shape[0], -1).to(bf).contiguous(), b=m.conv.bias)
+                else:
+                    ent["blocks"].append(rb(m))
+            down.append(ent)
+        up = []
+        for stage in list(self.up_modules)[:-1]:
+            ent = dict(up=None, blocks=[])
+            for m in stage:
+                if isinstance(m, Upsample):
+                    w = m.conv.weight.detach()                                       # [Ci, Co, 4, 4] -> [(ky*4+kx)*Co + co, ci]
+                    ent["up"] = dict(w=w.permute(2, 3, 1, 0).reshape(-1, w.shape[0]).to(bf).contiguous(), b=m.conv.bias)
+                else:
+                    ent["blocks"].append(rb(m))
+            up.append(ent)
+        pk["down"], pk["up"] = down, up
+        tr = self.transformer
+        pk["proj_w"] = tr.embedding.projection.weight.detach().to(bf).contiguous()
+        pk["out_w"] = tr.compute_out.weight.detach().to(bf).contiguous()
+        pk["fnet"] = [dict(w1=l.intermediate.dense.weight.detach().to(bf).contiguous(),
+                           w2=l.output.dense.weight.detach().to(bf).contiguous()) for l in tr.encoder.layer]
+        return pk
+
+    def _const(self, key, build):
+        if key not in self._consts:
+            self._consts[key] = build()
+        return self._consts[key]
+
+    # ------------------------------------------------------------------ forward
+    def _res_block(self, h, st_h, pb, temb, temb_off, temb_stride, stats, nxt):
+        """models/diffusion.py:42-56 as 5 launches; returns (h', stats of h')."""
+        a = ops.gn_apply(h, st_h, pb["g0"], pb["b0"], 1, GN_EPS)                                      # silu(GN0(h))
+        s0 = stats[nxt()]
+        tb = temb[:, temb_off:]
+        c0 = ops.conv3x3(a, pb["w0"], bias_b=tb, bias_b_stride=temb_stride, act=1, stats=s0)
+        n1 = ops.gn_apply(c0, s0, pb["g1"], pb["b1"], 0, GN_EPS, out=a)                               # GN1(silu(conv0 + temb))
+        s1 = stats[nxt()]
+        c1 = ops.conv3x3(n1, pb["w1"], bias=pb["cb1"], act=1, stats=s1, out=c0)                        # silu(conv1 + bias)
+        s2 = stats[nxt()]
+        out = ops.gn_apply(c1, s1, pb["g2"], None, 2, GN_EPS, res=h, stats_out=s2, out=n1)             # h + GN2(.)
+        return out, s2
+
+    @torch.no_grad()
+    def _forward_impl(self, x, t):
+        if not x.is_cuda:
+            raise RuntimeError("ddim_audio_b200.Model.forward needs CUDA tensors: there is no CPU path")
+        cfg = self.config
+        B, Cin, T, F = x.shape
+        nl = self.levels
+        if Cin != cfg.channels or F != cfg.f_size or T % (2 ** (nl - 1)) != 0:
+            raise RuntimeError(f"ddim_audio_b200: unsupported input shape {tuple(x.shape)} (need C={cfg.channels}, F={cfg.f_size}, T % {2 ** (nl - 1)} == 0)")
+        key = self._pack_key()
+        if self._packed is None or key != self._packed_key:
+            self._packed, self._packed_key = self._pack(), key
+        pk = self._packed
+        dev = x.device
+        x = x.contiguous().float()
+        t = t.to(device=dev, dtype=torch.int64).contiguous()
+
+        # ---- timestep embedding (:107-120), fp32
+        lin = self.temb.weight
+        e = ops.linear_small(self.temb.te, lin[0].weight, lin[0].bias, act=1, idx=t)
+        e = ops.linear_small(e, lin[1].weight, lin[1].bias, act=1)
+        temb = ops.linear_small(e, lin[2].weight, lin[2].bias, act=0)               # [B, sum(embedding_size)]
+        temb_stride = temb.shape[1]
+        offs = [0]
+        for w in self.embedding_size:
+            offs.append(offs[-1] + w)
+        rb_i = 0
+
+        n_stats = 2 + 2 * (nl - 1) + 3 * len(self.embedding_size)
+        stats = torch.zeros((n_stats, B, GN_GROUPS, 2), dtype=torch.float64, device=dev)
+        counter = [0]
+
+        def nxt():
+            counter[0] += 1
+            return counter[0] - 1
+
+        # ---- down path (:254-264)
+        conv0 = self.down_modules[0]
+        st = stats[nxt()]
+        h = ops.conv_in(x, conv0.weight, conv0.bias, st)
+        hidden = [h]
+        for l, ent in enumerate(pk["down"]):
+            if ent["down"] is not None:
+                st = stats[nxt()]
+                h = ops.conv_down4x4(h, ent["down"]["w"], ent["down"]["b"], st)
+            for pb in ent["blocks"]:
+                h, st = self._res_block(h, st, pb, temb, offs[rb_i], temb_stride, stats, nxt)
+                rb_i += 1
+            hidden.append(h)
+
+        # ---- FNet bottleneck (:267-279)
+        tr = self.transformer
+        S, Wt, Cl = h.shape[1], h.shape[2], h.shape[3]
+        D, H = Cl * Wt, tr.hidden
+        rows = B * S
+        te = self._const(("te", S, D, dev), lambda: sinusoid_table(2 ** math.ceil(math.log2(S)) if S > 1 else 1, D)[:S].contiguous().to(dev))
+        tok = ops.tokens_ln(h, te, tr.embedding.LayerNorm.weight, tr.embedding.LayerNorm.bias, tr.ln_eps)
+        xr = ops.linear(tok, pk["proj_w"], tr.embedding.projection.bias, out_f32=True)          # residual stream fp32 [rows, H]
+        wh, a2, Sp = self._const(("dft", S, H, dev), lambda: _fourier_operands(S, H, dev))
+        ut = self._const(("ut", B, S, H, dev), lambda: torch.zeros((B, 2 * H, 2 * Sp), dtype=torch.bfloat16, device=dev))
+        xbf = torch.empty((rows, 2 * H), dtype=torch.bfloat16, device=dev)
+        hbf = torch.empty((rows, H), dtype=torch.bfloat16, device=dev)
+        ops.split_bf16(xr, xbf, True)
+        for lay, pw in zip(tr.encoder.layer, pk["fnet"]):
+            y = ops.fourier_mix(xbf, 2 * H, wh, a2, ut, B, S, H, 3)
+            ln = lay.fourier.output.LayerNorm
+            hr = ops.layernorm512(xr, y, ln.weight, ln.bias, tr.ln_eps, hbf, False)
+            u = ops.linear(hbf, pw["w1"], lay.intermediate.dense.bias, act=2)
+            v = ops.linear(u, pw["w2"], lay.output.dense.bias, out_f32=True)
+            ln = lay.output.LayerNorm
+            xr = ops.layernorm512(v, hr, ln.weight, ln.bias, tr.ln_eps, xbf, True)
+        tok_out = ops.linear(xbf, pk["out_w"], tr.compute_out.bias, out_f32=True, M=rows, K=H)   # [rows, D]
+        st = stats[nxt()]
+        h = ops.tokens_to_nhwc(tok_out, hidden.pop(), st)                                          # + first additive skip (:284)
+
+        # ---- up path (:282-292)
+        for ent in pk["up"]:
+            for pb in ent["blocks"]:
+                h, st = self._res_block(h, st, pb, temb, offs[rb_i], temb_stride, stats, nxt)
+                rb_i += 1
+            if ent["up"] is not None:
+                st = stats[nxt()]
+                h = ops.conv_up4x4(h, ent["up"]["w"], ent["up"]["b"], skip=hidden.pop(), stats=st)
+        conv_last = self.up_modules[-1]
+        return ops.conv_out(h, hidden.pop(), conv_last.weight, conv_last.bias)
+
+    def forward(self, input, t):
+        return self._forward_impl(input, t)

@@ -1,0 +1,161 @@
+"""Tensor-level wrappers over the C ABI (one per entry point of include/ddim_b200.h).
+
+Layout conventions: network activations are NHWC bf16 ``[B, T, W, C]``; GroupNorm statistics are
+``float64 [B, 8, 2]`` (sum, sum of squares) accumulated by the producing kernel into a zeroed buffer.
+Allocation uses torch's caching allocator (plumbing); all arithmetic happens in the library.
+"""
+from __future__ import annotations
+
+import torch
+
+from . import _C
+from ._C import call, ptr
+
+bf16, f32, f64, i64 = torch.bfloat16, torch.float32, torch.float64, torch.int64
+
+
+# ---------------------------------------------------------------------------------------- sampler / loss
+def ddim_step(xt, et, z, at, at_next, c1, c2, x0_out=None, xs_out=None):
+    """functions/denoising.py:27,41-43 in place on ``xt`` (fp32)."""
+    n = xt.numel()
+    call("ddimb_ddim_step", ptr(xt, f32), ptr(et, f32), ptr(z, f32) if z is not None else None,
+         ptr(x0_out, f32) if x0_out is not None else None, ptr(xs_out, f32) if xs_out is not None else None,
+         float(at), float(at_next), float(c1), float(c2), n)
+    return xt
+
+
+def qsample(x0, e, alphas, t):
+    """functions/losses.py:12-13."""
+    out = torch.empty_like(x0)
+    B = x0.shape[0]
+    call("ddimb_qsample", ptr(x0, f32), ptr(e, f32), ptr(alphas, f32), ptr(t, i64), ptr(out, f32), B, x0.numel() // B)
+    return out
+
+
+def sqerr_loss(e, output):
+    """functions/losses.py:15-18 -> float64 [B] per-sample sums."""
+    B = e.shape[0]
+    per = torch.empty(B, dtype=f64, device=e.device)
+    call("ddimb_sqerr_loss", ptr(e, f32), ptr(output, f32), ptr(per, f64), B, e.numel() // B)
+    return per
+
+
+def sqerr_loss_bwd(e, output, g):
+    B = e.shape[0]
+    go = torch.empty_like(output)
+    call("ddimb_sqerr_loss_bwd", ptr(e, f32), ptr(output, f32), ptr(g, f32), ptr(go, f32), B, e.numel() // B)
+    return go
+
+
+# ---------------------------------------------------------------------------------------- convolutions
+def conv_in(x, w, bias, stats=None):
+    B, Cin, T, F = x.shape
+    Cout = w.shape[0]
+    out = torch.empty((B, T, F, Cout), dtype=bf16, device=x.device)
+    call("ddimb_conv_in", ptr(x, f32), ptr(w, f32), ptr(bias, f32), ptr(out), ptr(stats, f64), B, Cin, T, F, Cout)
+    return out
+
+
+def conv_out(x, skip, w, bias):
+    B, T, F, Cin = x.shape
+    Cout = w.shape[0]
+    out = torch.empty((B, Cout, T, F), dtype=f32, device=x.device)
+    call("ddimb_conv_out", ptr(x, bf16), ptr(skip, bf16), ptr(w, f32), ptr(bias, f32), ptr(out), B, T, F, Cin, Cout)
+    return out
+
+
+def conv3x3(x, w_packed, bias=None, bias_b=None, bias_b_stride=0, act=0, add=None, stats=None, out=None):
+    """x [B,T,W,Cin] bf16; w_packed bf16 [Cout, 9*Cin]; bias_b is a (possibly offset) fp32 view whose row b starts at
+    ``bias_b.data_ptr() + 4*b*bias_b_stride``."""
+    B, T, W, Cin = x.shape
+    Cout = w_packed.shape[0]
+    if out is None:
+        out = torch.empty((B, T, W, Cout), dtype=bf16, device=x.device)
+    call("ddimb_conv3x3", ptr(x, bf16), ptr(w_packed, bf16), ptr(bias, f32), bias_b.data_ptr() if bias_b is not None else None,
+         int(bias_b_stride), int(act), ptr(add, bf16), ptr(out, bf16), ptr(stats, f64), B, T, W, Cin, Cout)
+    return out
+
+
+def conv_down4x4(x, w_packed, bias, stats=None):
+    B, T, W, Cin = x.shape
+    Cout = w_packed.shape[0]
+    out = torch.empty((B, T // 2, W // 2, Cout), dtype=bf16, device=x.device)
+    call("ddimb_conv_down4x4", ptr(x, bf16), ptr(w_packed, bf16), ptr(bias, f32), ptr(out), ptr(stats, f64), B, T, W, Cin, Cout)
+    return out
+
+
+def conv_up4x4(x, w_packed, bias, skip=None, stats=None):
+    B, T, W, Cin = x.shape
+    Cout = w_packed.shape[0] // 16
+    out = torch.empty((B, 2 * T, 2 * W, Cout), dtype=bf16, device=x.device)
+    call("ddimb_conv_up4x4", ptr(x, bf16), ptr(w_packed, bf16), ptr(bias, f32), ptr(skip, bf16), ptr(out), ptr(stats, f64),
+         B, T, W, Cin, Cout)
+    return out
+
+
+# ---------------------------------------------------------------------------------------- GEMMs
+def linear(a, w, bias=None, act=0, out_f32=False, out=None, out_lo_offset=0, M=None, K=None):
+    """out[M,N] = act(a[M,K] w[N,K]^T + bias); a, w bf16 2-D (row stride = leading dimension)."""
+    M = a.shape[0] if M is None else M
+    K = w.shape[1] if K is None else K
+    N = w.shape[0]
+    if out is None:
+        out = torch.empty((M, N), dtype=f32 if out_f32 else bf16, device=a.device)
+    assert a.stride(-1) == 1 and w.stride(-1) == 1 and out.stride(-1) == 1
+    call("ddimb_linear", a.data_ptr(), a.stride(0), w.data_ptr(), w.stride(0), ptr(bias, f32), int(act), out.data_ptr(),
+         out.stride(0), 1 if out.dtype == f32 else 0, int(out_lo_offset), M, N, K)
+    return out
+
+
+def fourier_mix(xbf, ldx, wh, a2, ut, B, S, H, split):
+    """hf modeling_fnet.py:142-177 -> fp32 [B*S, H]."""
+    y = torch.empty((B * S, H), dtype=f32, device=xbf.device)
+    call("ddimb_fourier_mix", xbf.data_ptr(), int(ldx), ptr(wh, bf16), ptr(a2, bf16), ptr(ut, bf16), ptr(y), B, S, H, int(split))
+    return y
+
+
+# ---------------------------------------------------------------------------------------- norms / repacks
+def gn_apply(x, stats_in, gamma, beta, mode, eps, res=None, stats_out=None, out=None):
+    B, C = x.shape[0], x.shape[-1]
+    positions = x.numel() // (B * C)
+    if out is None:
+        out = torch.empty_like(x)
+    call("ddimb_gn_apply", ptr(x, bf16), ptr(res, bf16), ptr(out, bf16), ptr(stats_in, f64), ptr(stats_out, f64), ptr(gamma, f32),
+         ptr(beta, f32), int(mode), B, positions, C, float(eps))
+    return out
+
+
+def linear_small(inp, w, bias, act=0, idx=None):
+    rows = idx.numel() if idx is not None else inp.shape[0]
+    N, K = w.shape
+    out = torch.empty((rows, N), dtype=f32, device=w.device)
+    call("ddimb_linear_small", ptr(inp, f32), ptr(idx, i64), ptr(w, f32), ptr(bias, f32), ptr(out), rows, K, N, int(act))
+    return out
+
+
+def tokens_ln(x, te, gamma, beta, eps):
+    B, S, W, Cc = x.shape
+    out = torch.empty((B * S, Cc * W), dtype=bf16, device=x.device)
+    call("ddimb_tokens_ln", ptr(x, bf16), ptr(te, f32), ptr(gamma, f32), ptr(beta, f32), ptr(out), B, S, W, Cc, float(eps))
+    return out
+
+
+def tokens_to_nhwc(tok, skip, stats=None):
+    B, S, W, Cc = skip.shape
+    out = torch.empty_like(skip)
+    call("ddimb_tokens_to_nhwc", ptr(tok, f32), ptr(skip, bf16), ptr(out), ptr(stats, f64), B, S, W, Cc)
+    return out
+
+
+def layernorm512(a, b, gamma, beta, eps, ybf, write_lo):
+    rows = a.shape[0]
+    y = torch.empty_like(a)
+    call("ddimb_layernorm512", ptr(a, f32), ptr(b, f32), ptr(gamma, f32), ptr(beta, f32), ptr(y), ptr(ybf, bf16), ybf.stride(0),
+         1 if write_lo else 0, rows, float(eps))
+    return y
+
+
+def split_bf16(a, ybf, write_lo):
+    rows, H = a.shape
+    call("ddimb_split_bf16", ptr(a, f32), ptr(ybf, bf16), ybf.stride(0), H, 1 if write_lo else 0, rows)
+    return ybf

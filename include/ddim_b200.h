@@ -42,14 +42,19 @@ int ddimb_qsample(const float* x0, const float* e, const float* alphas, const lo
 int ddimb_sqerr_loss(const float* e, const float* output, double* per_sample, int B, long long per_sample_elems,
                      cudaStream_t stream);
 
+/* backward of ddimb_sqerr_loss: grad_output = -2 (e - output) g[b]; g is fp32 [B]. */
+int ddimb_sqerr_loss_bwd(const float* e, const float* output, const float* g, float* grad_output, int B,
+                         long long per_sample_elems, cudaStream_t stream);
+
 /* ---- network boundary convolutions (CUDA cores; K = 18 / N = 2 are not tensor-core shapes) -------------------- */
 
 /* models/diffusion.py:189-198 -- Conv2d(Cin=2 -> 32, k3 p1): x fp32 NCHW, w fp32 [32][Cin][3][3], out bf16 NHWC. */
 int ddimb_conv_in(const float* x, const float* w, const float* bias, void* out, double* stats, int B, int Cin, int T, int F,
                   int Cout, cudaStream_t stream);
-/* models/diffusion.py:199-208 -- Conv2d(32 -> 2, k3 p1): x bf16 NHWC, w fp32 [2][32][3][3], out fp32 NCHW. */
-int ddimb_conv_out(const void* x, const float* w, const float* bias, float* out, int B, int T, int F, int Cin, int Cout,
-                   cudaStream_t stream);
+/* models/diffusion.py:284,199-208 -- Conv2d(32 -> 2, k3 p1) of (x + skip): x, skip (nullable) bf16 NHWC,
+ * w fp32 [2][32][3][3], out fp32 NCHW. */
+int ddimb_conv_out(const void* x, const void* skip, const float* w, const float* bias, float* out, int B, int T, int F, int Cin,
+                   int Cout, cudaStream_t stream);
 
 /* ---- tcgen05 / TMEM / TMA implicit-GEMM convolutions and GEMMs ------------------------------------------------ */
 

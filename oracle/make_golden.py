@@ -94,6 +94,15 @@ def main():
         np.savez_compressed(os.path.join(OUT, name + ".npz"), loss=ref.numpy(), per_sample=refk.numpy(), t=t.numpy(),
                             meta=np.array([b, T, seed]))
 
+    # the reference's own default init under torch.manual_seed(0): the drop-in Model must consume the RNG identically
+    torch.manual_seed(0)
+    fresh_model, _ = R.load_model(None)
+    fsd = fresh_model.state_dict()
+    np.savez_compressed(os.path.join(OUT, "init_fingerprint.npz"), keys=np.array(list(fsd.keys())),
+                        sums=np.array([float(v.double().sum()) for v in fsd.values()]),
+                        abs_sums=np.array([float(v.double().abs().sum()) for v in fsd.values()]),
+                        shapes=np.array([str(tuple(v.shape)) for v in fsd.values()]))
+
     # weight fingerprint so a torch upgrade that changes the generator stream is caught, not silently absorbed
     fp = {k: float(v.double().sum()) for k, v in list(sd.items())[:: max(1, len(sd) // 24)]}
     np.savez_compressed(os.path.join(OUT, "weights_fingerprint.npz"), keys=np.array(list(fp.keys())), sums=np.array(list(fp.values())))
