@@ -2,6 +2,10 @@
 model-level one)."""
 import torch
 
+# the per-kernel references must be true fp32: torch lets cuDNN/cuBLAS use TF32 for convolutions by default
+torch.backends.cudnn.allow_tf32 = False
+torch.backends.cuda.matmul.allow_tf32 = False
+
 DEV = "cuda"
 
 
