@@ -1,0 +1,343 @@
+#!/usr/bin/env python
+"""bench.py -- DDIM sample-steps/s of the B200-native denoiser path (BASELINE.json metric), one JSON line on stdout.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
+        bench.py --gpus N --steps K --warmup W
+
+A *step* is one DDIM step (denoiser forward + fused update, functions/denoising.py:21-50) over one batch.
+Workload (config.workload): BASELINE.json configs[2]/[3] -- audio.yml sampling shape x[64, 2, 8192, 256] PER GPU
+(weak scaling: config 4's 512 samples over 8 GPUs is 64 per rank), eta = 0, uniform 1000-step schedule, synthetic
+N(0,1) input and seeded random-init weights (norm.2.weight randomised so the residual blocks are live).
+
+  value         sample-steps/s with xt resident in HBM (CUDA events, barrier + synchronize both sides, max over ranks)
+  e2e           the same through the public API ``generalized_steps`` with a pinned HOST x per call and both snapshot
+                lists read back to the host every step (select_index=None, as the reference does)
+  roofline      the kernel class with the largest share of the timed region: algorithmic bytes (or FLOPs) / CUDA-event
+                time on the launching stream (library profiler), against MEASURED_PEAKS.json
+  cpu_baseline  the CPU oracle (port of the reference path) on this box's host cores, bounded sample (rank 0, N=1 only)
+
+``--impl reference`` times the reference's CPU implementation of the path instead (the oracle port: the reference is
+Python/PyTorch and /root/reference does not travel to the GPU box), all host threads, bounded sample per step.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "ddim_sample_steps_per_sec"
+UNIT = "sample-steps/s"
+F_SIZE = 256
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--batch", type=int, default=64, help="samples per GPU (config 3: 64)")
+    ap.add_argument("--t-size", type=int, default=8192, help="time frames (audio.yml sampling.t_size: 8192)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--cpu-sample-steps", type=int, default=2)
+    return ap.parse_args()
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return dict(hbm=float(d["hbm_gbs"]), tensor=float(d.get("bf16_tflops_sustained", d["bf16_tflops"])), source="measured (MEASURED_PEAKS.json; bf16 sustained)")
+    return dict(hbm=6650.0, tensor=1400.0, source="fallback (B200_PROFILING.md)")
+
+
+def workload_name(batch, t_size):
+    return (f"audio.yml DDIM sampling step, x[{batch},2,{t_size},{F_SIZE}] per GPU, eta=0, uniform 1000-step schedule "
+            f"(BASELINE configs[2]/[3] shape)")
+
+
+# ------------------------------------------------------------------------------------------------ clocks
+class ClockSampler:
+    """nvidia-smi sampled every 200 ms while the timed region runs (B200_PROFILING.md clocks line)."""
+
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows = []
+        self.proc = None
+        self.index = index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200", "-i", str(self.index)],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons, pw = [], [], set(), []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            f = [c.strip() for c in r.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1])); pw.append(float(f[2]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ------------------------------------------------------------------------------------------------ synthetic model / schedule
+def alphas_cumprod():
+    """runners/diffusion.py:46-49,109-115: linear betas in float64, cast to fp32, cumprod in fp32."""
+    import numpy as np
+    import torch
+    betas = torch.from_numpy(np.linspace(1e-4, 2e-2, 1000, dtype=np.float64)).float()
+    return (1.0 - betas).cumprod(dim=0)
+
+
+def synthetic_state_dict():
+    """Reference default init under seed 0, then every norm.2.weight <- 0.5 randn (seed 1) so the residual blocks are not
+    the identity.  CPU fp32 state_dict with the reference's 389 keys."""
+    import torch
+    from ddim_audio_b200.config import audio_config
+    from ddim_audio_b200.models.diffusion import Model
+    torch.manual_seed(0)
+    m = Model(audio_config("torch.FloatTensor"))
+    g = torch.Generator().manual_seed(1)
+    sd = m.state_dict()
+    for k, v in sd.items():
+        if k.endswith("norm.2.weight"):
+            v.copy_(0.5 * torch.randn(v.shape, generator=g))
+    return sd
+
+
+# ------------------------------------------------------------------------------------------------ CPU legs (oracle = checker / baseline only)
+def cpu_steps(sd, t_size, nsteps, warm=True):
+    """nsteps DDIM steps of the oracle on x[1,2,t_size,256] with every host thread; returns (seconds, cores)."""
+    import torch
+    from oracle import ddim_oracle as O
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    model = O.OracleModel(sd)
+    al = alphas_cumprod()
+    g = torch.Generator().manual_seed(1234)
+    if warm:
+        O.generalized_steps(torch.randn(1, 2, 32, F_SIZE, generator=g), [999], model, al, set(), eta=0.0)
+    x = torch.randn(1, 2, t_size, F_SIZE, generator=g)
+    seq = list(range(0, 1000, 1000 // 50))[-nsteps:] if nsteps <= 50 else list(range(1000))[-nsteps:]
+    t0 = time.perf_counter()
+    O.generalized_steps(x, seq, model, al, set(), eta=0.0)
+    return time.perf_counter() - t0, cores
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    sd = synthetic_state_dict()
+    for _ in range(min(args.warmup, 1)):
+        cpu_steps(sd, min(args.t_size, 1024), 1)
+    per = []
+    for _ in range(args.steps):
+        dt, cores = cpu_steps(sd, args.t_size, 1, warm=False)
+        per.append(dt)
+    total = sum(per)
+    value = args.steps / total
+    sample = f"x[1,2,{args.t_size},{F_SIZE}] (1 of the workload's {args.batch} samples per GPU), 1 DDIM step per bench step, fp32, torch CPU ops"
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": 1e3 * total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic", "config": {"workload": workload_name(args.batch, args.t_size), "batch_per_gpu": args.batch, "t_size": args.t_size,
+                                        "f_size": F_SIZE, "reference_arm": "CPU oracle port of the reference path (the Python reference does not travel to the GPU box)"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------ the B200 arm
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the B200 arm has no CPU fallback (use --impl reference for the CPU baseline)")
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    from ddim_audio_b200 import _C, ops
+    from ddim_audio_b200.config import audio_config
+    from ddim_audio_b200.functions.denoising import ddim_loop_device, generalized_steps
+    from ddim_audio_b200.models.diffusion import Model
+
+    sd = synthetic_state_dict()
+    model = Model(audio_config("torch.FloatTensor")).to(dev)
+    model.load_state_dict(sd, strict=True)
+    model.eval()
+    al = alphas_cumprod()
+    alpha_list = [1.0] + al.numpy().tolist()
+    B, T = args.batch, args.t_size
+    K, W = args.steps, max(args.warmup, 0)
+    g = torch.Generator().manual_seed(1234 + rank)
+    x_host = torch.randn(B, 2, T, F_SIZE, generator=g).pin_memory()
+    seq_all = list(range(1000))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(v):
+        if world > 1:
+            tns = torch.tensor([v], dtype=torch.float64, device=dev)
+            dist.all_reduce(tns, op=dist.ReduceOp.MAX)
+            return float(tns.item())
+        return v
+
+    # ---------------- value: device-resident loop
+    xt = x_host.to(dev, non_blocking=True)
+    with torch.no_grad():
+        if W:
+            ddim_loop_device(xt, seq_all[-W:], model, alpha_list, 0.0)
+        clocks = ClockSampler(local)
+        barrier()
+        clocks.start()
+        _C.prof_enable(True)
+        _C.prof_report()
+        l0 = _C.launch_count()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        ddim_loop_device(xt, seq_all[-(W + K):-W] if W else seq_all[-K:], model, alpha_list, 0.0)
+        e1.record()
+        barrier()
+        launches = _C.launch_count() - l0
+        ms = max_over_ranks(e0.elapsed_time(e1))
+        prof = _C.prof_report()
+        _C.prof_enable(False)
+        clk = clocks.stop()
+    value = world * B * K / (ms * 1e-3)
+    finite = bool(torch.isfinite(xt).all().item())
+    del xt
+
+    # ---------------- roofline: dominant kernel class of the timed region
+    pk = peaks()
+    tot_ms = sum(p["ms"] for p in prof) or 1.0
+    kern = []
+    t_roof = 0.0
+    for p in sorted(prof, key=lambda q: -q["ms"]):
+        tb = p["bytes"] / (pk["hbm"] * 1e9) * 1e3
+        tf = p["flops"] / (pk["tensor"] * 1e12) * 1e3
+        bound = "hbm" if tb >= tf else "tensor"
+        t_roof += max(tb, tf)
+        kern.append({"name": p["name"], "share": round(p["ms"] / tot_ms, 4), "ms_per_call": round(p["ms"] / p["calls"], 5), "calls_per_step": p["calls"] / K,
+                     "bound": bound, "frac": round(max(tb, tf) / p["ms"], 4) if p["ms"] > 0 else None,
+                     "gbs": round(p["bytes"] / p["ms"] * 1e-6, 1), "tflops": round(p["flops"] / p["ms"] * 1e-9, 1)})
+    top = sorted(prof, key=lambda q: -q["ms"])[0]
+    tb = top["bytes"] / (pk["hbm"] * 1e9)
+    tf = top["flops"] / (pk["tensor"] * 1e12)
+    traffic = None
+    tr_path = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tr_path):
+        traffic = json.load(open(tr_path)).get(top["name"])
+    if tb >= tf:
+        ach = top["bytes"] / (top["ms"] * 1e-3) * 1e-9
+        roof = {"bound": "hbm", "achieved": ach, "peak": pk["hbm"], "unit": "GB/s", "frac": ach / pk["hbm"]}
+    else:
+        ach = top["flops"] / (top["ms"] * 1e-3) * 1e-12
+        roof = {"bound": "tensor", "achieved": ach, "peak": pk["tensor"], "unit": "TFLOP/s", "frac": ach / pk["tensor"]}
+    roof.update({"traffic": traffic, "kernel": top["name"], "share_of_step": top["ms"] / tot_ms, "launch_ms": top["ms"] / max(top["launches"], 1),
+                 "algorithmic_bytes_per_launch": top["bytes"] / max(top["launches"], 1), "algorithmic_flops_per_launch": top["flops"] / max(top["launches"], 1),
+                 "peak_source": pk["source"], "timed": "CUDA events on the launching stream around every launch of the timed region"})
+
+    # ---------------- e2e: public API, pinned host x in, both snapshot lists out, every step
+    e2e = None
+    if not args.no_e2e:
+        ald = al.to(dev)
+        cur = x_host
+        with torch.no_grad():
+            for i in range(max(W, 1)):
+                xs, x0 = generalized_steps(cur, [seq_all[-1 - i]], model, ald, None, eta=0.0)
+                cur = xs[-1]
+            barrier()
+            t0 = time.perf_counter()
+            for i in range(K):
+                xs, x0 = generalized_steps(cur, [seq_all[-1 - W - i]], model, ald, None, eta=0.0)
+                cur = xs[-1]
+            barrier()
+            dt = max_over_ranks(time.perf_counter() - t0)
+        nbytes = x_host.numel() * 4
+        e2e = {"value": world * B * K / dt, "unit": UNIT, "h2d_bytes_per_step": nbytes + 8 * B, "d2h_bytes_per_step": 2 * nbytes, "ms_per_step": 1e3 * dt / K,
+               "api": "generalized_steps(x_pinned_host, [t], model, alphas, None, eta=0) once per step"}
+
+    # ---------------- CPU baseline (oracle; rank 0 at N=1 only)
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        n = args.cpu_sample_steps
+        dt, cores = cpu_steps(sd, T, n)
+        cpu = {"value": n / dt, "unit": UNIT, "cores": cores, "kind": "port",
+               "sample": f"x[1,2,{T},{F_SIZE}] (1 of the {B} samples), {n} DDIM steps, fp32 torch CPU ops, {dt:.1f} s"}
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms / K, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": workload_name(B, T), "batch_per_gpu": B, "t_size": T, "f_size": F_SIZE, "eta": 0.0,
+                       "storage": "bf16 NHWC activations, fp32 accumulate, fp32 x/eps", "parallelism": f"batch-sharded x{world}, no collectives",
+                       "l2": "inputs larger than L2 (every activation tensor of the step exceeds 126 MB)" if B * T >= 16384 else "small debug shape: L2-resident",
+                       "snapshots": "none inside the device-timed steps (config 3 selects 10 of 1000 steps); every step in e2e"},
+            "clocks": clk, "e2e": e2e, "gpu_launches": int(launches), "roofline": roof, "cpu_baseline": cpu,
+            "step_roofline": {"t_roof_ms_per_step": t_roof / K, "frac": (t_roof / K) / (ms / K), "note": "sum over kernels of max(bytes/HBM peak, flops/tensor peak) / measured step"},
+            "kernels": kern[:12], "finite": finite,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

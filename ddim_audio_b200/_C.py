@@ -43,10 +43,15 @@ SIGNATURES = {
     "ddimb_layernorm512": [_vp, _vp, _vp, _vp, _vp, _vp, _ll, _i, _i, _f],
     "ddimb_split_bf16": [_vp, _vp, _ll, _i, _i, _ll],
 }
-EXPORTS = ["ddimb_version", "ddimb_last_error"] + list(SIGNATURES)
+EXPORTS = ["ddimb_version", "ddimb_last_error", "ddimb_launch_count", "ddimb_prof_enable", "ddimb_prof_report"] + list(SIGNATURES)
 
 lib.ddimb_version.restype = _i
 lib.ddimb_last_error.restype = C.c_char_p
+lib.ddimb_launch_count.restype = _ll
+lib.ddimb_prof_enable.argtypes = [_i]
+lib.ddimb_prof_enable.restype = _i
+lib.ddimb_prof_report.argtypes = [C.c_char_p, _i]
+lib.ddimb_prof_report.restype = _i
 for _name, _args in SIGNATURES.items():
     _fn = getattr(lib, _name)
     _fn.argtypes = _args + [_vp]
@@ -75,6 +80,26 @@ def call(name: str, *args) -> None:
     if rc != 0:
         msg = lib.ddimb_last_error().decode(errors="replace")
         raise RuntimeError(f"{name} failed (code {rc}): {msg}")
+
+
+def launch_count() -> int:
+    """Kernels launched by the library so far."""
+    return int(lib.ddimb_launch_count())
+
+
+def prof_enable(on: bool) -> None:
+    lib.ddimb_prof_enable(1 if on else 0)
+
+
+def prof_report():
+    """Per-kernel-class totals since the last report (synchronises the device): list of dicts."""
+    import json
+
+    buf = C.create_string_buffer(1 << 16)
+    n = lib.ddimb_prof_report(buf, len(buf))
+    if n < 0:
+        raise RuntimeError("ddimb_prof_report failed: " + lib.ddimb_last_error().decode(errors="replace"))
+    return json.loads(buf.value.decode())
 
 
 def version() -> int:

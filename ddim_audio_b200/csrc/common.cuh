@@ -29,9 +29,20 @@
   } while (0)
 
 void ddimb_set_error(const char* fmt, ...);
+// runtime.cu: launch counter and the optional per-launch CUDA-event profiler (bench.py's roofline leg)
+void ddimb_count_launch();
+struct DdimbProfScope {
+  int slot;
+  cudaStream_t stream;
+  DdimbProfScope(cudaStream_t s, const char* name, int p0, int p1, double bytes, double flops);
+  ~DdimbProfScope();
+};
+// name[p0,p1] identifies a kernel class; bytes / flops are the ALGORITHMIC figures of this one call
+#define DDIMB_PROF(stream, name, p0, p1, bytes, flops) DdimbProfScope prof_scope__(stream, name, p0, p1, (double)(bytes), (double)(flops))
 
 #define DDIMB_LAUNCH_CHECK()                                                                   \
   do {                                                                                         \
+    ddimb_count_launch();                                                                      \
     cudaError_t e__ = cudaGetLastError();                                                      \
     if (e__ != cudaSuccess) {                                                                  \
       ddimb_set_error("%s:%d: kernel launch -> %s", __FILE__, __LINE__, cudaGetErrorString(e__)); \

@@ -38,6 +38,8 @@ __global__ void __launch_bounds__(256) ddim_step_kernel(float4* __restrict__ xt,
 extern "C" int ddimb_ddim_step(float* xt, const float* et, const float* z, float* x0_out, float* xs_out, double at, double at_next,
                                double c1, double c2, long long n, cudaStream_t stream) {
   DDIMB_CHECK_ARG(xt && et && n > 0 && n % 4 == 0);
+  DDIMB_PROF(stream, "ddim_step", (z && c1 != 0.0) ? 1 : 0, (x0_out ? 1 : 0) + (xs_out ? 1 : 0),
+             4.0 * n * (3 + ((z && c1 != 0.0) ? 1 : 0) + (x0_out ? 1 : 0) + (xs_out ? 1 : 0)), 6.0 * n);
   const int64_t n4 = n / 4;
   int64_t blocks = (n4 + 255) / 256;
   const int64_t cap = (int64_t)ddimb_num_sms() * 16;
@@ -70,6 +72,7 @@ __global__ void __launch_bounds__(256) qsample_kernel(const float4* __restrict__
 extern "C" int ddimb_qsample(const float* x0, const float* e, const float* alphas, const long long* t, float* out, int B,
                              long long per_sample, cudaStream_t stream) {
   DDIMB_CHECK_ARG(x0 && e && alphas && t && out && B >= 1 && per_sample % 4 == 0);
+  DDIMB_PROF(stream, "qsample", 0, 0, 12.0 * B * per_sample, 3.0 * B * per_sample);
   const int64_t per4 = per_sample / 4;
   int bx = (int)((per4 + 255) / 256);
   const int cap = ddimb_num_sms() * 8 / B + 1;
@@ -105,6 +108,7 @@ __global__ void __launch_bounds__(256) sqerr_kernel(const float4* __restrict__ e
 extern "C" int ddimb_sqerr_loss(const float* e, const float* output, double* per_sample, int B, long long per_sample_elems,
                                 cudaStream_t stream) {
   DDIMB_CHECK_ARG(e && output && per_sample && B >= 1 && per_sample_elems % 4 == 0);
+  DDIMB_PROF(stream, "sqerr_loss", 0, 0, 8.0 * B * per_sample_elems, 3.0 * B * per_sample_elems);
   DDIMB_CUDA(cudaMemsetAsync(per_sample, 0, sizeof(double) * B, stream));
   const int64_t per4 = per_sample_elems / 4;
   int bx = (int)((per4 + 255) / 256);
@@ -130,6 +134,7 @@ __global__ void __launch_bounds__(256) sqerr_bwd_kernel(const float4* __restrict
 extern "C" int ddimb_sqerr_loss_bwd(const float* e, const float* output, const float* g, float* grad_output, int B,
                                     long long per_sample_elems, cudaStream_t stream) {
   DDIMB_CHECK_ARG(e && output && g && grad_output && B >= 1 && per_sample_elems % 4 == 0);
+  DDIMB_PROF(stream, "sqerr_loss_bwd", 0, 0, 12.0 * B * per_sample_elems, 2.0 * B * per_sample_elems);
   const int64_t per4 = per_sample_elems / 4;
   int bx = (int)((per4 + 255) / 256);
   const int cap = ddimb_num_sms() * 8 / B + 1;
@@ -227,6 +232,7 @@ extern "C" int ddimb_gn_apply(const void* x, const void* res, void* y, const dou
   DDIMB_CHECK_ARG(x && y && stats_in && gamma && B >= 1 && positions >= 1);
   DDIMB_CHECK_ARG(C % 32 == 0 && C <= 256 && mode >= 0 && mode <= 2);
   DDIMB_CHECK_ARG(mode != 2 || res);
+  DDIMB_PROF(stream, "gn_apply", C, mode, 2.0 * B * positions * C * (mode == 2 ? 3 : 2), 0.0);
   GnArgs a;
   a.x = reinterpret_cast<const __nv_bfloat16*>(x); a.res = reinterpret_cast<const __nv_bfloat16*>(res);
   a.y = reinterpret_cast<__nv_bfloat16*>(y);
@@ -314,6 +320,7 @@ __global__ void __launch_bounds__(128) conv_in_kernel(const float* __restrict__ 
 extern "C" int ddimb_conv_in(const float* x, const float* w, const float* bias, void* out, double* stats, int B, int Cin, int T, int F,
                              int Cout, cudaStream_t stream) {
   DDIMB_CHECK_ARG(x && w && bias && out && B >= 1 && Cin >= 1 && Cin <= 8 && Cout == 32);
+  DDIMB_PROF(stream, "conv_in", Cin, Cout, (double)B * T * F * (4.0 * Cin + 2.0 * Cout), 18.0 * Cin * Cout * B * T * F);
   const int smem = (9 * Cin * Cout + Cout) * 4;
   conv_in_kernel<32><<<dim3((F + 127) / 128, T, B), 128, smem, stream>>>(x, w, bias, reinterpret_cast<__nv_bfloat16*>(out), stats, Cin, T, F);
   DDIMB_LAUNCH_CHECK();
@@ -379,6 +386,7 @@ __global__ void __launch_bounds__(128) conv_out_kernel(const __nv_bfloat16* __re
 extern "C" int ddimb_conv_out(const void* x, const void* skip, const float* w, const float* bias, float* out, int B, int T, int F,
                               int Cin, int Cout, cudaStream_t stream) {
   DDIMB_CHECK_ARG(x && w && bias && out && B >= 1 && Cin == 32 && Cout == 2);
+  DDIMB_PROF(stream, "conv_out", Cin, Cout, (double)B * T * F * (2.0 * Cin * (skip ? 2 : 1) + 4.0 * Cout), 18.0 * Cin * Cout * B * T * F);
   conv_out_kernel<32, 2><<<dim3((F + 127) / 128, T, B), 128, 0, stream>>>(reinterpret_cast<const __nv_bfloat16*>(x),
                                                                           reinterpret_cast<const __nv_bfloat16*>(skip), w, bias, out, T, F);
   DDIMB_LAUNCH_CHECK();
@@ -417,6 +425,7 @@ __global__ void __launch_bounds__(256) linear_small_kernel(const float* __restri
 extern "C" int ddimb_linear_small(const float* in, const long long* idx, const float* w, const float* bias, float* out, int rows, int K,
                                   int N, int act, cudaStream_t stream) {
   DDIMB_CHECK_ARG(in && w && bias && out && rows >= 1 && K % 32 == 0 && K <= 512 && N >= 1);
+  DDIMB_PROF(stream, "linear_small", N, K, 4.0 * ((double)N * K + (double)rows * (K + N)), 2.0 * rows * N * K);
   linear_small_kernel<<<(N + 7) / 8, 256, 0, stream>>>(in, reinterpret_cast<const int64_t*>(idx), w, bias, out, rows, K, N, act);
   DDIMB_LAUNCH_CHECK();
   return DDIMB_OK;
@@ -469,6 +478,7 @@ __global__ void __launch_bounds__(256) tokens_ln_kernel(const __nv_bfloat16* __r
 extern "C" int ddimb_tokens_ln(const void* x, const float* te, const float* gamma, const float* beta, void* out, int B, int S, int W,
                                int C, float eps, cudaStream_t stream) {
   DDIMB_CHECK_ARG(x && te && gamma && beta && out && W == 8 && C % 32 == 0 && C <= 256);
+  DDIMB_PROF(stream, "tokens_ln", C, W, (double)B * S * W * C * 4.0 + (double)S * W * C * 4.0, 0.0);
   tokens_ln_kernel<8><<<B * S, C, 0, stream>>>(reinterpret_cast<const __nv_bfloat16*>(x), te, gamma, beta,
                                                 reinterpret_cast<__nv_bfloat16*>(out), S, C, eps);
   DDIMB_LAUNCH_CHECK();
@@ -506,6 +516,7 @@ __global__ void __launch_bounds__(256) tokens_to_nhwc_kernel(const float* __rest
 extern "C" int ddimb_tokens_to_nhwc(const float* tok, const void* skip, void* out, double* stats, int B, int S, int W, int C,
                                     cudaStream_t stream) {
   DDIMB_CHECK_ARG(tok && skip && out && W == 8 && C % 32 == 0 && C <= 256 && ((C >> 3) & ((C >> 3) - 1)) == 0);
+  DDIMB_PROF(stream, "tokens_to_nhwc", C, W, (double)B * S * W * C * 8.0, 0.0);
   tokens_to_nhwc_kernel<8><<<B * S, C, 0, stream>>>(tok, reinterpret_cast<const __nv_bfloat16*>(skip), reinterpret_cast<__nv_bfloat16*>(out),
                                                     stats, S, C);
   DDIMB_LAUNCH_CHECK();
@@ -565,6 +576,7 @@ __global__ void __launch_bounds__(256) layernorm512_kernel(const float* __restri
 extern "C" int ddimb_layernorm512(const float* a, const float* b, const float* gamma, const float* beta, float* y, void* ybf,
                                   long long ldy, int write_lo, int rows, float eps, cudaStream_t stream) {
   DDIMB_CHECK_ARG(a && gamma && beta && y && ybf && rows >= 1 && ldy % 4 == 0 && ldy >= (write_lo ? 1024 : 512));
+  DDIMB_PROF(stream, "layernorm512", write_lo, b ? 1 : 0, 512.0 * rows * (4.0 * (b ? 2 : 1) + 4.0 + (write_lo ? 4.0 : 2.0)), 0.0);
   layernorm512_kernel<<<(rows + 7) / 8, 256, 0, stream>>>(a, b, gamma, beta, y, reinterpret_cast<__nv_bfloat16*>(ybf), ldy, write_lo, rows, eps);
   DDIMB_LAUNCH_CHECK();
   return DDIMB_OK;
@@ -587,6 +599,7 @@ __global__ void __launch_bounds__(256) split_bf16_kernel(const float4* __restric
 
 extern "C" int ddimb_split_bf16(const float* a, void* ybf, long long ldy, int H, int write_lo, long long rows, cudaStream_t stream) {
   DDIMB_CHECK_ARG(a && ybf && rows >= 1 && H % 4 == 0 && ldy % 4 == 0);
+  DDIMB_PROF(stream, "split_bf16", H, write_lo, (double)rows * H * (4.0 + (write_lo ? 4.0 : 2.0)), 0.0);
   const int64_t n4 = rows * H / 4;
   int64_t blocks = (n4 + 255) / 256;
   const int64_t cap = (int64_t)ddimb_num_sms() * 8;

@@ -1,5 +1,5 @@
 // Host side of the tcgen05 implicit-GEMM kernel: tensor maps, tap programs, C-ABI entry points.
-#include <stdarg.h>
+#include <math.h>
 #include <string.h>
 
 #include <mutex>
@@ -8,17 +8,6 @@
 #include "umma_gemm.cuh"
 
 using namespace ddimb;
-
-// ------------------------------------------------------------------------------------------------ errors
-static thread_local char g_err[512] = "";
-void ddimb_set_error(const char* fmt, ...) {
-  va_list ap;
-  va_start(ap, fmt);
-  vsnprintf(g_err, sizeof(g_err), fmt, ap);
-  va_end(ap);
-}
-extern "C" const char* ddimb_last_error(void) { return g_err; }
-extern "C" int ddimb_version(void) { return 100; }
 
 // ------------------------------------------------------------------------------------------------ tensor maps
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
@@ -146,6 +135,8 @@ extern "C" int ddimb_conv3x3(const void* x, const void* w, const float* bias, co
                              const void* add, void* out, double* stats, int B, int T, int W, int Cin, int Cout,
                              cudaStream_t stream) {
   DDIMB_CHECK_ARG(x && w && out && B >= 1 && T >= 1);
+  const double npos = (double)B * T * W;
+  DDIMB_PROF(stream, "conv3x3", Cin, W, npos * (Cin + Cout + (add ? Cout : 0)) * 2 + 18.0 * Cin * Cout, 18.0 * Cin * Cout * npos);
   DDIMB_CHECK_ARG(W >= 8 && W <= 256 && (W & (W - 1)) == 0);
   DDIMB_CHECK_ARG(Cin % 32 == 0 && Cout % 32 == 0 && Cout <= 256 && Cin <= 256);
   const int ck = pick_ck(Cin);
@@ -193,6 +184,8 @@ extern "C" int ddimb_conv3x3(const void* x, const void* w, const float* bias, co
 extern "C" int ddimb_conv_down4x4(const void* x, const void* w, const float* bias, void* out, double* stats, int B, int T, int W,
                                   int Cin, int Cout, cudaStream_t stream) {
   DDIMB_CHECK_ARG(x && w && out && B >= 1 && T >= 2 && T % 2 == 0);
+  const double npos = (double)B * (T / 2) * (W / 2);
+  DDIMB_PROF(stream, "conv_down4x4", Cin, W, npos * (4.0 * Cin + Cout) * 2 + 32.0 * Cin * Cout, 32.0 * Cin * Cout * npos);
   DDIMB_CHECK_ARG(W >= 16 && W <= 256 && (W & (W - 1)) == 0);
   DDIMB_CHECK_ARG(Cin % 32 == 0 && Cout % 32 == 0 && Cout <= 256 && Cin <= 256);
   const int ck = pick_ck(Cin);
@@ -247,6 +240,8 @@ extern "C" int ddimb_conv_down4x4(const void* x, const void* w, const float* bia
 extern "C" int ddimb_conv_up4x4(const void* x, const void* w, const float* bias, const void* skip, void* out, double* stats, int B,
                                 int T, int W, int Cin, int Cout, cudaStream_t stream) {
   DDIMB_CHECK_ARG(x && w && out && B >= 1 && T >= 1);
+  const double npos = (double)B * T * W;
+  DDIMB_PROF(stream, "conv_up4x4", Cin, W, npos * (Cin + 4.0 * Cout * (skip ? 2 : 1)) * 2 + 32.0 * Cin * Cout, 32.0 * Cin * Cout * npos);
   DDIMB_CHECK_ARG(W >= 8 && W <= 128 && (W & (W - 1)) == 0);
   DDIMB_CHECK_ARG(Cin % 32 == 0 && Cout % 32 == 0 && Cout <= 256 && Cin <= 256);
   const int ck = pick_ck(Cin);
@@ -307,6 +302,7 @@ extern "C" int ddimb_conv_up4x4(const void* x, const void* w, const float* bias,
 extern "C" int ddimb_linear(const void* a, long long lda, const void* w, long long ldw, const float* bias, int act, void* out,
                             long long ldo, int out_f32, long long out_lo_offset, int M, int N, int K, cudaStream_t stream) {
   DDIMB_CHECK_ARG(a && w && out && M >= 1);
+  DDIMB_PROF(stream, "linear", N, K, 2.0 * M * K + 2.0 * N * K + (double)M * N * (out_f32 ? 4 : (out_lo_offset ? 4 : 2)), 2.0 * M * N * K);
   DDIMB_CHECK_ARG(K % 32 == 0 && N % 16 == 0 && lda % 8 == 0 && ldw % 8 == 0 && ldo % 8 == 0);
   const int ck = pick_ck(K);
   int nseg_w = N;   // segment width: largest divisor of N that is <= 256 and a multiple of 16
@@ -357,6 +353,8 @@ extern "C" int ddimb_linear(const void* a, long long lda, const void* w, long lo
 extern "C" int ddimb_fourier_mix(const void* x, long long ldx, const void* wh, const void* a2, void* ut, float* y, int B, int S, int H,
                                  int split, cudaStream_t stream) {
   DDIMB_CHECK_ARG(x && wh && a2 && ut && y && B >= 1 && S >= 1 && S <= 256);
+  // FLOPs are counted as an FFT of S*H points per sample (5 N log2 N), whatever the DFT-GEMMs spend
+  DDIMB_PROF(stream, "fourier_mix", S, H, (double)B * S * H * (2.0 * (split == 3 ? 2 : 1) + 4.0), 5.0 * B * S * H * log2((double)S * H));
   DDIMB_CHECK_ARG(H % 256 == 0 && (split == 1 || split == 3) && ldx % 8 == 0);
   const int Sp = ceil_div(S, 32) * 32;
   const int nS = ceil_div(S, 16) * 16;   // UMMA N for GEMM 1

@@ -49,38 +49,52 @@ class _SnapshotPipe:
         self.stream.synchronize()
 
 
+def ddim_loop_device(xt, seq, model, alpha_list, eta=0.0, select_index=None, noise=None, on_snapshot=None):
+    """The loop body of functions/denoising.py:21-50 on a DEVICE-resident fp32 ``xt`` (updated in place).
+
+    ``on_snapshot(x0_buf, xs_buf)`` receives device copies of the two tensors the reference appends at :29-34 and
+    :45-50 for the selected steps (``select_index`` None = every step; negative indices allowed); with
+    ``on_snapshot=None`` no snapshot is taken.  Returns ``xt``."""
+    device = xt.device
+    seq = list(seq)
+    seq_next = [-1] + seq[:-1]
+    noise_it = iter(noise) if noise is not None else None
+    t = torch.empty(xt.size(0), dtype=torch.int64, device=device)
+    L = len(seq)
+    for index, (i, j) in enumerate(zip(reversed(seq), reversed(seq_next))):
+        t.fill_(int(i))
+        at, at_next, c1, c2 = _ddim_scalars(alpha_list, i, j, eta)
+        et = model(xt, t)
+        selected = on_snapshot is not None and (select_index is None or index in select_index or index - L in select_index)
+        z = None
+        if noise_it is not None:
+            z = next(noise_it).to(device=device, dtype=torch.float32).contiguous()
+        elif c1 != 0:
+            z = torch.randn_like(xt)
+        x0_buf = torch.empty_like(xt) if selected else None
+        xs_buf = torch.empty_like(xt) if selected else None
+        ops.ddim_step(xt, et.contiguous(), z, at, at_next, c1, c2, x0_out=x0_buf, xs_out=xs_buf)
+        if selected:
+            on_snapshot(x0_buf, xs_buf)
+    return xt
+
+
 def generalized_steps(x, seq, model, alpha, select_index, **kwargs):
     if not torch.cuda.is_available():
         raise RuntimeError("ddim_audio_b200.generalized_steps needs a CUDA device: there is no CPU path")
     eta = kwargs.get("eta", 0)
     noise = kwargs.get("noise", None)
-    noise_it = iter(noise) if noise is not None else None
     with torch.no_grad():
         alpha_list = [1.0] + alpha.to("cpu", torch.float32).numpy().tolist()          # :12
         device = x.device if x.is_cuda else torch.device("cuda", torch.cuda.current_device())
-        seq = list(seq)
-        seq_next = [-1] + seq[:-1]
-        n = x.size(0)
         xs, x0_preds = [x], []
-        xt = x.to(device=device, dtype=torch.float32, copy=True).contiguous()
-        t = torch.zeros(n, dtype=torch.int64, device=device)
+        xt = x.to(device=device, dtype=torch.float32, copy=True, non_blocking=True).contiguous()
         pipe = _SnapshotPipe(device)
-        L = len(seq)
-        for index, (i, j) in enumerate(zip(reversed(seq), reversed(seq_next))):
-            t.fill_(int(i))
-            at, at_next, c1, c2 = _ddim_scalars(alpha_list, i, j, eta)
-            et = model(xt, t)
-            selected = select_index is None or index in select_index or index - L in select_index
-            z = None
-            if noise_it is not None:
-                z = next(noise_it).to(device=device, dtype=torch.float32).contiguous()
-            elif c1 != 0:
-                z = torch.randn_like(xt)
-            x0_buf = torch.empty_like(xt) if selected else None
-            xs_buf = torch.empty_like(xt) if selected else None
-            ops.ddim_step(xt, et.contiguous(), z, at, at_next, c1, c2, x0_out=x0_buf, xs_out=xs_buf)
-            if selected:
-                x0_preds.append(pipe.push(x0_buf))                                     # :29-34
-                xs.append(pipe.push(xs_buf))                                           # :45-50
+
+        def snap(x0_buf, xs_buf):
+            x0_preds.append(pipe.push(x0_buf))                                         # :29-34
+            xs.append(pipe.push(xs_buf))                                               # :45-50
+
+        ddim_loop_device(xt, seq, model, alpha_list, eta, select_index, noise, snap)
         pipe.drain()
     return xs, x0_preds

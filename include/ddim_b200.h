@@ -24,6 +24,14 @@ extern "C" {
 
 int ddimb_version(void);
 const char* ddimb_last_error(void);
+/* Number of kernels this library has launched since it was loaded (bench.py's gpu_launches). */
+long long ddimb_launch_count(void);
+/* Opt-in profiler: while enabled every entry point below brackets its launches with two CUDA events on the caller's
+ * stream.  ddimb_prof_report synchronises the device, writes a JSON array of per-kernel-class totals
+ * {name, calls, launches, ms, bytes, flops} (bytes / flops = the algorithmic figures of DESIGN.md) into buf, clears the
+ * records and returns the text length (negative on error). */
+int ddimb_prof_enable(int on);
+int ddimb_prof_report(char* buf, int buflen);
 
 /* ---- sampler / loss arithmetic (fp32, elementwise) ------------------------------------------------------------ */
 
