@@ -167,7 +167,6 @@ struct GnArgs {
 
 __global__ void __launch_bounds__(256) gn_apply_kernel(const GnArgs a) {
   __shared__ float s_scale[256], s_shift[256];
-  __shared__ float s_red[16];
   const int b = blockIdx.y, C = a.C, cg = C >> 3;
   if (threadIdx.x < C) {
     const int c = threadIdx.x, g = c / cg;
@@ -180,7 +179,6 @@ __global__ void __launch_bounds__(256) gn_apply_kernel(const GnArgs a) {
     s_scale[c] = sc;
     s_shift[c] = (a.beta ? a.beta[c] : 0.f) - (float)mean * sc;
   }
-  if (threadIdx.x < 16) s_red[threadIdx.x] = 0.f;
   __syncthreads();
   // blockDim * 8 is a multiple of C, so a thread keeps the same 8 channels for every item it visits
   const int c0 = (threadIdx.x * 8) % C;
@@ -219,11 +217,20 @@ __global__ void __launch_bounds__(256) gn_apply_kernel(const GnArgs a) {
     stg_v4(yp + i, make_uint4(pack_bf16x2(f[0], f[1]), pack_bf16x2(f[2], f[3]), pack_bf16x2(f[4], f[5]), pack_bf16x2(f[6], f[7])));
   }
   if (a.mode == 2 && a.stats_out) {
-    const int ga = c0 / cg, gb = (c0 + 4) / cg;
-    atomicAdd(&s_red[2 * ga], sa1); atomicAdd(&s_red[2 * ga + 1], sa2);
-    atomicAdd(&s_red[2 * gb], sb1); atomicAdd(&s_red[2 * gb + 1], sb2);
+    // fixed-order block reduction (run-to-run reproducible): per-thread partials -> shared -> 16 threads sum them in thread order
+    __shared__ float s_part[256][4];
+    s_part[threadIdx.x][0] = sa1; s_part[threadIdx.x][1] = sa2; s_part[threadIdx.x][2] = sb1; s_part[threadIdx.x][3] = sb2;
     __syncthreads();
-    if (threadIdx.x < 16) atomicAdd(a.stats_out + b * 16 + threadIdx.x, (double)s_red[threadIdx.x]);
+    if (threadIdx.x < 16) {
+      const int g = threadIdx.x >> 1, which = threadIdx.x & 1;
+      float acc = 0.f;
+      for (int t = 0; t < (int)blockDim.x; ++t) {
+        const int tc = (t * 8) % C;
+        if (tc / cg == g) acc += s_part[t][which];
+        if ((tc + 4) / cg == g) acc += s_part[t][2 + which];
+      }
+      atomicAdd(a.stats_out + b * 16 + threadIdx.x, (double)acc);
+    }
   }
 }
 

@@ -70,14 +70,16 @@ static int next_pow2_cols(int c) {
 }
 
 // Fill the derived fields of GemmParams and launch.  A map is 5-D, B map is 3-D.
-static int launch_gemm(GemmParams& p, const CUtensorMap& tmA, const CUtensorMap& tmB, int ck, cudaStream_t stream) {
+static int launch_gemm(GemmParams& p, const CUtensorMap& tmA, const CUtensorMap& tmB, int ck, cudaStream_t stream, bool conv = false) {
+  const int nacc_t = conv ? p.n_acc : 0, cmod_t = conv ? p.bias_mod : 0;
   DDIMB_CHECK_ARG(ck == 32 || ck == 64);
   DDIMB_CHECK_ARG(p.box[0] * p.box[1] * p.box[2] * p.box[3] == kTileM);
   DDIMB_CHECK_ARG(p.n_seg % 16 == 0 && p.n_seg >= 16 && p.n_seg <= 256);
   DDIMB_CHECK_ARG(p.n_acc % 16 == 0 && p.n_acc <= 512 && p.n_acc % p.n_seg == 0 && p.n_acc / p.n_seg <= 32);
   DDIMB_CHECK_ARG(p.ntaps >= 1 && p.ntaps <= kMaxTaps);
   DDIMB_CHECK_ARG(p.bias_mod % 16 == 0 && p.bias_mod >= 16);
-  if (p.stats) DDIMB_CHECK_ARG(p.bias_mod % 32 == 0 && p.num_n_tiles == 1);
+  if (conv) DDIMB_CHECK_ARG(p.bias_mod % 32 == 0 && p.num_n_tiles == 1 && p.n_valid == p.n_acc && !p.out_f32 && p.out_lo_offset == 0);
+  else DDIMB_CHECK_ARG(!p.stats && !p.add && !p.bias_b);
   int brows = 0;
   for (int t = 0; t < p.ntaps; ++t) {
     const TapDesc& tp = p.taps[t];
@@ -100,14 +102,28 @@ static int launch_gemm(GemmParams& p, const CUtensorMap& tmA, const CUtensorMap&
   int smem = 1024 + stages * stage_bytes + kGemmAuxBytes;
   if (smem < 120 * 1024) smem = 120 * 1024;   // keep one CTA per SM: TMEM is allocated without contention
   int grid = p.num_tiles < ddimb_num_sms() ? p.num_tiles : ddimb_num_sms();
-  if (ck == 64) {
-    static bool attr = false;
-    if (!attr) { DDIMB_CUDA(cudaFuncSetAttribute(umma_gemm_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem)); attr = true; }
-    umma_gemm_kernel<64><<<grid, kGemmThreads, smem, stream>>>(tmA, tmB, p);
-  } else {
-    static bool attr = false;
-    if (!attr) { DDIMB_CUDA(cudaFuncSetAttribute(umma_gemm_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem)); attr = true; }
-    umma_gemm_kernel<32><<<grid, kGemmThreads, smem, stream>>>(tmA, tmB, p);
+  // (CK, accumulator columns, channels) instantiations: every convolution shape of audio.yml (ch 32..256), plus the generic GEMM
+#define DDIMB_GEMM_CASE(CKV, NACCV, CMODV)                                                                                       \
+  if (ck == CKV && nacc_t == NACCV && cmod_t == CMODV) {                                                                         \
+    static bool attr = false;                                                                                                    \
+    if (!attr) {                                                                                                                 \
+      DDIMB_CUDA(cudaFuncSetAttribute(umma_gemm_kernel<CKV, NACCV, CMODV>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem)); \
+      attr = true;                                                                                                               \
+    }                                                                                                                            \
+    umma_gemm_kernel<CKV, NACCV, CMODV><<<grid, kGemmThreads, smem, stream>>>(tmA, tmB, p);                                      \
+    launched = true;                                                                                                             \
+  }
+  bool launched = false;
+  DDIMB_GEMM_CASE(32, 0, 0) DDIMB_GEMM_CASE(64, 0, 0)
+  DDIMB_GEMM_CASE(32, 32, 32) DDIMB_GEMM_CASE(64, 64, 64) DDIMB_GEMM_CASE(32, 96, 96) DDIMB_GEMM_CASE(64, 128, 128)
+  DDIMB_GEMM_CASE(64, 192, 192) DDIMB_GEMM_CASE(64, 256, 256)
+  DDIMB_GEMM_CASE(32, 64, 64) DDIMB_GEMM_CASE(64, 96, 96) DDIMB_GEMM_CASE(32, 128, 128)
+  DDIMB_GEMM_CASE(64, 384, 192) DDIMB_GEMM_CASE(64, 256, 128) DDIMB_GEMM_CASE(64, 192, 96) DDIMB_GEMM_CASE(32, 128, 64)
+  DDIMB_GEMM_CASE(64, 64, 32)
+#undef DDIMB_GEMM_CASE
+  if (!launched) {
+    ddimb_set_error("no tcgen05 kernel instantiation for CK=%d accumulator columns=%d channels=%d (audio.yml channel widths only)", ck, nacc_t, cmod_t);
+    return DDIMB_ERR_ARG;
   }
   DDIMB_LAUNCH_CHECK();
   return DDIMB_OK;
@@ -174,7 +190,7 @@ extern "C" int ddimb_conv3x3(const void* x, const void* w, const float* bias, co
   p.out_stride[0] = Cout; p.out_stride[1] = (int64_t)W * Cout; p.out_stride[3] = (int64_t)T * W * Cout;
   p.out_dim[0] = W; p.out_dim[1] = T; p.out_dim[3] = B;
   p.n_valid = Cout; p.bias_mod = Cout; p.bias_b_stride = bias_b_stride; p.act = act;
-  return launch_gemm(p, tmA, tmB, ck, stream);
+  return launch_gemm(p, tmA, tmB, ck, stream, true);
 }
 
 // ------------------------------------------------------------------------------------------------ Conv2d 4x4 s2 p1
@@ -229,7 +245,7 @@ extern "C" int ddimb_conv_down4x4(const void* x, const void* w, const float* bia
   p.out_stride[0] = Cout; p.out_stride[2] = (int64_t)Wo * Cout; p.out_stride[3] = (int64_t)To * Wo * Cout;
   p.out_dim[0] = Wo; p.out_dim[2] = To; p.out_dim[3] = B;
   p.n_valid = Cout; p.bias_mod = Cout; p.act = 0;
-  return launch_gemm(p, tmA, tmB, ck, stream);
+  return launch_gemm(p, tmA, tmB, ck, stream, true);
 }
 
 // ------------------------------------------------------------------------------------------------ ConvTranspose2d 4x4 s2 p1
@@ -290,7 +306,7 @@ extern "C" int ddimb_conv_up4x4(const void* x, const void* w, const float* bias,
     p.out_base = (int64_t)r * Wo * Cout;
     p.out_dim[0] = W; p.out_dim[1] = T; p.out_dim[3] = B;
     p.n_valid = 2 * Cout; p.bias_mod = Cout; p.act = 0;
-    int rc = launch_gemm(p, tmA, tmB, ck, stream);
+    int rc = launch_gemm(p, tmA, tmB, ck, stream, true);
     if (rc) return rc;
   }
   return DDIMB_OK;

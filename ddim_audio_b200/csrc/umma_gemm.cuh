@@ -69,9 +69,128 @@ struct GemmSmem {
   __host__ __device__ static int stage_bytes(int b_rows) { return kABytes + b_rows * CK * 2; }
 };
 
-constexpr int kGemmAuxBytes = 1024;  // barriers, tmem pointer, stats scratch
+constexpr int kGemmAuxBytes = 1024 + 4096;  // barriers, tmem pointer, per-warp bias copies
 
-template <int CK>
+// Mixed-radix tile counter (W tiles, T tiles, dim-3 tiles, batch, N tiles) advanced by gridDim.x per step without any
+// division: the step is decomposed once, every digit then carries at most 1.
+struct TileIter {
+  int i[5], n[5], d[5];
+  int tile, num_tiles, step;
+  __device__ __forceinline__ void init(const GemmParams& p, int first, int stride) {
+    n[0] = p.ntile[0]; n[1] = p.ntile[1]; n[2] = p.ntile[2]; n[3] = p.ntile[3]; n[4] = p.num_n_tiles;
+    int a = first, b = stride;
+#pragma unroll
+    for (int k = 0; k < 5; ++k) { i[k] = a % n[k]; a /= n[k]; d[k] = b % n[k]; b /= n[k]; }
+    tile = first; num_tiles = p.num_tiles; step = stride;
+  }
+  __device__ __forceinline__ bool valid() const { return tile < num_tiles; }
+  __device__ __forceinline__ void next() {
+    tile += step;
+    int carry = 0;
+#pragma unroll
+    for (int k = 0; k < 5; ++k) {
+      int v = i[k] + d[k] + carry;
+      carry = v >= n[k];
+      i[k] = carry ? v - n[k] : v;
+    }
+  }
+};
+
+// 32 lanes x 32 consecutive fp32 columns
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]),
+        "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]),
+        "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]),
+        "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr)
+      : "memory");
+}
+
+// Epilogue state of one thread (= one accumulator row) of a convolution: GroupNorm partial sums stay in registers across
+// tiles and are reduced (warp shuffle, then one double atomicAdd per value per warp) only when the sample changes.
+template <int CMOD>
+struct ConvEpiState {
+  float sacc[16];
+  int cur_batch;
+  __device__ __forceinline__ void reset() {
+#pragma unroll
+    for (int k = 0; k < 16; ++k) sacc[k] = 0.f;
+  }
+  __device__ __forceinline__ void flush(double* stats, int lane) {
+    if (cur_batch < 0 || stats == nullptr) return;
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+      const float v = warp_sum(sacc[k]);
+      if (lane == 0) atomicAdd(stats + (int64_t)cur_batch * 16 + k, (double)v);
+    }
+    reset();
+  }
+};
+
+// One tile of the convolution epilogue: TMEM -> registers -> + (bias + temb) -> activation -> + skip -> bf16 NHWC store,
+// GroupNorm partial sums of the stored values.  NACC accumulator columns, column c is channel c % CMOD; wb = this warp's
+// shared-memory copy of the combined per-channel bias of the current sample.
+template <int NACC, int CMOD>
+__device__ __forceinline__ void conv_epilogue_tile(uint32_t trow, const float* wb, int act, const __nv_bfloat16* add, __nv_bfloat16* out,
+                                                   int64_t addr0, bool valid, bool want_stats, ConvEpiState<CMOD>& st) {
+  constexpr int CG = CMOD / 8;   // channels per GroupNorm group (multiple of 4)
+#pragma unroll
+  for (int c0 = 0; c0 < NACC; c0 += 32) {
+    uint32_t v[32];
+    tmem_ld32(trow + (uint32_t)c0, v);
+    uint4 av[4];
+    if (add != nullptr && valid) {
+#pragma unroll
+      for (int q = 0; q < 4; ++q) av[q] = ldg_nc_v4(add + addr0 + c0 + 8 * q);
+    }
+    tmem_ld_wait();
+    float f[32];
+#pragma unroll
+    for (int j = 0; j < 32; j += 4) {
+      const float4 b4 = *reinterpret_cast<const float4*>(wb + ((c0 + j) % CMOD));
+      f[j] = __uint_as_float(v[j]) + b4.x; f[j + 1] = __uint_as_float(v[j + 1]) + b4.y;
+      f[j + 2] = __uint_as_float(v[j + 2]) + b4.z; f[j + 3] = __uint_as_float(v[j + 3]) + b4.w;
+    }
+    if (act == 1) {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) f[j] = silu_fast(f[j]);
+    }
+    if (add != nullptr && valid) {
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const uint32_t aw[4] = {av[q].x, av[q].y, av[q].z, av[q].w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const float2 t2 = unpack_bf16x2(aw[j]);
+          f[8 * q + 2 * j] += t2.x; f[8 * q + 2 * j + 1] += t2.y;
+        }
+      }
+    }
+    if (valid) {
+      __nv_bfloat16* op = out + addr0 + c0;
+#pragma unroll
+      for (int q = 0; q < 4; ++q)
+        stg_v4(op + 8 * q, make_uint4(pack_bf16x2(f[8 * q], f[8 * q + 1]), pack_bf16x2(f[8 * q + 2], f[8 * q + 3]),
+                                      pack_bf16x2(f[8 * q + 4], f[8 * q + 5]), pack_bf16x2(f[8 * q + 6], f[8 * q + 7])));
+      if (want_stats) {
+#pragma unroll
+        for (int j = 0; j < 32; j += 4) {
+          constexpr int dummy = 0; (void)dummy;
+          const int g = ((c0 + j) % CMOD) / CG;   // compile-time after unrolling
+          float s1 = (f[j] + f[j + 1]) + (f[j + 2] + f[j + 3]);
+          float s2 = fmaf(f[j], f[j], fmaf(f[j + 1], f[j + 1], fmaf(f[j + 2], f[j + 2], f[j + 3] * f[j + 3])));
+          st.sacc[2 * g] += s1; st.sacc[2 * g + 1] += s2;
+        }
+      }
+    }
+  }
+}
+
+// NACC / CMOD > 0: convolution instantiation (compile-time accumulator width and channel count, lean epilogue with
+// GroupNorm partial sums); NACC == 0: generic GEMM epilogue (Linear, Fourier mixing; runtime widths, fp32 or bf16 output).
+template <int CK, int NACC, int CMOD>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                  const __grid_constant__ GemmParams p) {
@@ -80,10 +199,10 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
   const int stage_bytes = GemmSmem<CK>::stage_bytes(p.b_rows_per_stage);
   const uint32_t aux = smem_base + p.num_stages * stage_bytes;
-  // aux layout: full[8] @0, empty[8] @64, tmem_full[2] @128, tmem_empty[2] @144, tmem_ptr @160, stats float[16] @192
+  // aux layout: full[8] @0, empty[8] @64, tmem_full[2] @128, tmem_empty[2] @144, tmem_ptr @160, per-warp bias float[4][256] @1024
   const uint32_t bar_full = aux, bar_empty = aux + 64, bar_tfull = aux + 128, bar_tempty = aux + 144;
   volatile uint32_t* tmem_ptr_gen = reinterpret_cast<volatile uint32_t*>(smem_gen + p.num_stages * stage_bytes + 160);
-  float* stats_smem = reinterpret_cast<float*>(smem_gen + p.num_stages * stage_bytes + 192);
+  float* bias_smem = reinterpret_cast<float*>(smem_gen + p.num_stages * stage_bytes + 1024);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
@@ -104,28 +223,22 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     tmem_alloc(aux + 160, (uint32_t)p.tmem_cols);
     tmem_relinquish();
   }
-  if (threadIdx.x >= 64 && threadIdx.x < 64 + 16) stats_smem[threadIdx.x - 64] = 0.f;
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_gen;
-
-  const int tiles_m = p.ntile[0] * p.ntile[1] * p.ntile[2] * p.ntile[3];
 
   if (warp == 0) {
     // ================================================================ TMA producer
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
-        int nt = tile / tiles_m, r = tile - nt * tiles_m;
-        int i1 = r % p.ntile[0]; r /= p.ntile[0];
-        int i2 = r % p.ntile[1]; r /= p.ntile[1];
-        int i3 = r % p.ntile[2]; r /= p.ntile[2];
-        int i4 = r;
-        const int c1 = i1 * p.box[0], c2 = i2 * p.box[1], c3 = i3 * p.box[2];
-        const int c4 = p.a_batched ? i4 * p.box[3] : 0;
-        const int bb = p.b_batched ? i4 : 0;
+      TileIter it;
+      for (it.init(p, blockIdx.x, gridDim.x); it.valid(); it.next()) {
+        const int c1 = it.i[0] * p.box[0], c2 = it.i[1] * p.box[1], c3 = it.i[2] * p.box[2];
+        const int c4 = p.a_batched ? it.i[3] * p.box[3] : 0;
+        const int bb = p.b_batched ? it.i[3] : 0;
+        const int nt = it.i[4];
         for (int t = 0; t < p.ntaps; ++t) {
           const TapDesc& tp = p.taps[t];
           const uint32_t tx = (uint32_t)(GemmSmem<CK>::kABytes + tp.nseg * p.n_seg * CK * 2);
@@ -187,154 +300,128 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     // ================================================================ epilogue (warps 2..5, TMEM lane quarter = warp % 4)
     const int q = warp & 3;
     const int row = q * 32 + lane;
-    const int et = threadIdx.x - 64;   // 0..127
     int r = row;
     const int r1 = r % p.box[0]; r /= p.box[0];
     const int r2 = r % p.box[1]; r /= p.box[1];
     const int r3 = r % p.box[2]; r /= p.box[2];
     const int r4 = r;
-    const int cg = p.bias_mod >> 3;   // channels per GroupNorm group
     int local = 0;
-    for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++local) {
-      int nt = tile / tiles_m, rr = tile - nt * tiles_m;
-      int i1 = rr % p.ntile[0]; rr /= p.ntile[0];
-      int i2 = rr % p.ntile[1]; rr /= p.ntile[1];
-      int i3 = rr % p.ntile[2]; rr /= p.ntile[2];
-      int i4 = rr;
-      const int d1 = i1 * p.box[0] + r1, d2 = i2 * p.box[1] + r2, d3 = i3 * p.box[2] + r3, d4 = i4 * p.box[3] + r4;
-      const bool valid = d1 < p.out_dim[0] && d2 < p.out_dim[1] && d3 < p.out_dim[2] && d4 < p.out_dim[3];
-      const int64_t addr0 = p.out_base + d1 * p.out_stride[0] + d2 * p.out_stride[1] + d3 * p.out_stride[2] + d4 * p.out_stride[3];
-      const int batch = i4;
-      const float* bias_b = p.bias_b ? p.bias_b + (int64_t)batch * p.bias_b_stride : nullptr;
-
-      const int buf = local % p.num_acc_bufs;
-      const uint32_t use = (uint32_t)(local / p.num_acc_bufs);
-      mbar_wait(bar_tfull + 8 * buf, use & 1, 4);
-      tc_fence_after();
-      const uint32_t trow = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * p.n_acc);
-
-      float s1 = 0.f, s2 = 0.f;
-      int cur_group = -1;
-      for (int c0 = 0; c0 < p.n_acc; c0 += 16) {
-        uint32_t v[16];
-        tmem_ld16(trow + (uint32_t)c0, v);
-        tmem_ld_wait();
-        const int gcol = nt * p.n_acc + c0;   // global column of v[0]
-        if (gcol >= p.n_valid) break;         // uniform across the CTA
-        float f[16];
-#pragma unroll
-        for (int j = 0; j < 16; ++j) f[j] = __uint_as_float(v[j]);
-        if (p.bias) {
-          const int bc = gcol % p.bias_mod;   // 16-column chunks never straddle bias_mod (multiple of 16)
-#pragma unroll
-          for (int j = 0; j < 16; j += 4) {
-            const float4 b4 = *reinterpret_cast<const float4*>(p.bias + bc + j);
-            f[j] += b4.x; f[j + 1] += b4.y; f[j + 2] += b4.z; f[j + 3] += b4.w;
-          }
+    TileIter it;
+    if constexpr (NACC > 0) {
+      // ---------------- convolution epilogue
+      float* wb = bias_smem + q * 256;
+      ConvEpiState<CMOD> st;
+      st.reset();
+      st.cur_batch = -1;
+      __nv_bfloat16* out = reinterpret_cast<__nv_bfloat16*>(p.out);
+      for (it.init(p, blockIdx.x, gridDim.x); it.valid(); it.next(), ++local) {
+        const int d1 = it.i[0] * p.box[0] + r1, d2 = it.i[1] * p.box[1] + r2, d3 = it.i[2] * p.box[2] + r3, d4 = it.i[3] * p.box[3] + r4;
+        const bool valid = d1 < p.out_dim[0] && d2 < p.out_dim[1] && d3 < p.out_dim[2] && d4 < p.out_dim[3];
+        const int64_t addr0 = p.out_base + d1 * p.out_stride[0] + d2 * p.out_stride[1] + d3 * p.out_stride[2] + d4 * p.out_stride[3];
+        const int batch = it.i[3];
+        if (batch != st.cur_batch) {
+          st.flush(p.stats, lane);
+          st.cur_batch = batch;
+          __syncwarp();
+          for (int c = lane; c < CMOD; c += 32)
+            wb[c] = (p.bias ? p.bias[c] : 0.f) + (p.bias_b ? p.bias_b[(int64_t)batch * p.bias_b_stride + c] : 0.f);
+          __syncwarp();
         }
-        if (bias_b) {
-          const int bc = gcol % p.bias_mod;
+        const int buf = local % p.num_acc_bufs;
+        const uint32_t use = (uint32_t)(local / p.num_acc_bufs);
+        mbar_wait(bar_tfull + 8 * buf, use & 1, 4);
+        tc_fence_after();
+        const uint32_t trow = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * NACC);
+        conv_epilogue_tile<NACC, CMOD>(trow, wb, p.act, p.add, out, addr0, valid, p.stats != nullptr, st);
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar_tempty + 8 * buf);
+      }
+      st.flush(p.stats, lane);
+    } else {
+      // ---------------- generic GEMM epilogue (Linear / Fourier mixing)
+      for (it.init(p, blockIdx.x, gridDim.x); it.valid(); it.next(), ++local) {
+        const int nt = it.i[4];
+        const int d1 = it.i[0] * p.box[0] + r1, d2 = it.i[1] * p.box[1] + r2, d3 = it.i[2] * p.box[2] + r3, d4 = it.i[3] * p.box[3] + r4;
+        const bool valid = d1 < p.out_dim[0] && d2 < p.out_dim[1] && d3 < p.out_dim[2] && d4 < p.out_dim[3];
+        const int64_t addr0 = p.out_base + d1 * p.out_stride[0] + d2 * p.out_stride[1] + d3 * p.out_stride[2] + d4 * p.out_stride[3];
+        const int buf = local % p.num_acc_bufs;
+        const uint32_t use = (uint32_t)(local / p.num_acc_bufs);
+        mbar_wait(bar_tfull + 8 * buf, use & 1, 4);
+        tc_fence_after();
+        const uint32_t trow = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * p.n_acc);
+        for (int c0 = 0; c0 < p.n_acc; c0 += 16) {
+          uint32_t v[16];
+          tmem_ld16(trow + (uint32_t)c0, v);
+          tmem_ld_wait();
+          const int gcol = nt * p.n_acc + c0;   // global column of v[0]
+          if (gcol >= p.n_valid) break;         // uniform across the CTA
+          float f[16];
 #pragma unroll
-          for (int j = 0; j < 16; j += 4) {
-            const float4 b4 = *reinterpret_cast<const float4*>(bias_b + bc + j);
-            f[j] += b4.x; f[j + 1] += b4.y; f[j + 2] += b4.z; f[j + 3] += b4.w;
-          }
-        }
-        if (p.act == 1) {
+          for (int j = 0; j < 16; ++j) f[j] = __uint_as_float(v[j]);
+          if (p.bias) {
 #pragma unroll
-          for (int j = 0; j < 16; ++j) f[j] = silu_fast(f[j]);
-        } else if (p.act == 2) {
-#pragma unroll
-          for (int j = 0; j < 16; ++j) f[j] = gelu_new_fast(f[j]);
-        }
-        if (p.add && valid) {
-          const uint4* ap = reinterpret_cast<const uint4*>(p.add + addr0 + gcol);
-          const uint4 a0 = ap[0], a1 = ap[1];
-          const uint32_t aw[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
-#pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const float2 t2 = unpack_bf16x2(aw[j]);
-            f[2 * j] += t2.x; f[2 * j + 1] += t2.y;
-          }
-        }
-        const int nrem = p.n_valid - gcol;    // columns of this chunk that exist (>= 1)
-        if (p.out_f32) {
-          if (valid) {
-            float* op = reinterpret_cast<float*>(p.out) + addr0 + gcol;
-            if (nrem >= 16) {
-#pragma unroll
-              for (int j = 0; j < 16; j += 4) *reinterpret_cast<float4*>(op + j) = make_float4(f[j], f[j + 1], f[j + 2], f[j + 3]);
-            } else {
-              for (int j = 0; j < nrem; ++j) op[j] = f[j];
+            for (int j = 0; j < 16; j += 4) {
+              const float4 b4 = *reinterpret_cast<const float4*>(p.bias + gcol + j);
+              f[j] += b4.x; f[j + 1] += b4.y; f[j + 2] += b4.z; f[j + 3] += b4.w;
             }
           }
-        } else {
-          uint32_t w[8];
+          if (p.act == 1) {
 #pragma unroll
-          for (int j = 0; j < 8; ++j) w[j] = pack_bf16x2(f[2 * j], f[2 * j + 1]);
-          if (valid) {
-            __nv_bfloat16* op = reinterpret_cast<__nv_bfloat16*>(p.out) + addr0 + gcol;
-            if (nrem >= 16) {
-              stg_v4(op, make_uint4(w[0], w[1], w[2], w[3]));
-              stg_v4(op + 8, make_uint4(w[4], w[5], w[6], w[7]));
-            } else {
-              for (int j = 0; j < nrem; ++j) op[j] = __float2bfloat16_rn(f[j]);
-            }
-            if (p.out_lo_offset != 0) {
-              // split-bf16: second plane holds bf16(x - bf16(x)) so a later GEMM can use hi*W + lo*W
-              uint32_t wl[8];
+            for (int j = 0; j < 16; ++j) f[j] = silu_fast(f[j]);
+          } else if (p.act == 2) {
 #pragma unroll
-              for (int j = 0; j < 8; ++j) {
-                const float2 h = unpack_bf16x2(w[j]);
-                wl[j] = pack_bf16x2(f[2 * j] - h.x, f[2 * j + 1] - h.y);
-              }
-              __nv_bfloat16* lp = op + p.out_lo_offset;
+            for (int j = 0; j < 16; ++j) f[j] = gelu_new_fast(f[j]);
+          }
+          const int nrem = p.n_valid - gcol;    // columns of this chunk that exist (>= 1)
+          if (p.out_f32) {
+            if (valid) {
+              float* op = reinterpret_cast<float*>(p.out) + addr0 + gcol;
               if (nrem >= 16) {
-                stg_v4(lp, make_uint4(wl[0], wl[1], wl[2], wl[3]));
-                stg_v4(lp + 8, make_uint4(wl[4], wl[5], wl[6], wl[7]));
+#pragma unroll
+                for (int j = 0; j < 16; j += 4) *reinterpret_cast<float4*>(op + j) = make_float4(f[j], f[j + 1], f[j + 2], f[j + 3]);
               } else {
-                for (int j = 0; j < nrem; ++j) {
-                  const float h = __bfloat162float(__float2bfloat16_rn(f[j]));
-                  lp[j] = __float2bfloat16_rn(f[j] - h);
+                for (int j = 0; j < nrem; ++j) op[j] = f[j];
+              }
+            }
+          } else {
+            uint32_t w[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) w[j] = pack_bf16x2(f[2 * j], f[2 * j + 1]);
+            if (valid) {
+              __nv_bfloat16* op = reinterpret_cast<__nv_bfloat16*>(p.out) + addr0 + gcol;
+              if (nrem >= 16) {
+                stg_v4(op, make_uint4(w[0], w[1], w[2], w[3]));
+                stg_v4(op + 8, make_uint4(w[4], w[5], w[6], w[7]));
+              } else {
+                for (int j = 0; j < nrem; ++j) op[j] = __float2bfloat16_rn(f[j]);
+              }
+              if (p.out_lo_offset != 0) {
+                // split-bf16: second plane holds bf16(x - bf16(x)) so a later GEMM can use hi*W + lo*W
+                uint32_t wl[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                  const float2 h = unpack_bf16x2(w[j]);
+                  wl[j] = pack_bf16x2(f[2 * j] - h.x, f[2 * j + 1] - h.y);
+                }
+                __nv_bfloat16* lp = op + p.out_lo_offset;
+                if (nrem >= 16) {
+                  stg_v4(lp, make_uint4(wl[0], wl[1], wl[2], wl[3]));
+                  stg_v4(lp + 8, make_uint4(wl[4], wl[5], wl[6], wl[7]));
+                } else {
+                  for (int j = 0; j < nrem; ++j) {
+                    const float h = __bfloat162float(__float2bfloat16_rn(f[j]));
+                    lp[j] = __float2bfloat16_rn(f[j] - h);
+                  }
                 }
               }
             }
           }
         }
-        if (p.stats) {
-          // GroupNorm partial sums of what the next GroupNorm will see; groups are multiples of 4 channels wide
-#pragma unroll
-          for (int j = 0; j < 16; j += 4) {
-            const int g = ((gcol + j) % p.bias_mod) / cg;
-            if (g != cur_group) {
-              if (cur_group >= 0) {
-                s1 = warp_sum(s1); s2 = warp_sum(s2);
-                if (lane == 0) { atomicAdd(&stats_smem[2 * cur_group], s1); atomicAdd(&stats_smem[2 * cur_group + 1], s2); }
-              }
-              cur_group = g; s1 = 0.f; s2 = 0.f;
-            }
-            if (valid) {
-#pragma unroll
-              for (int jj = 0; jj < 4; ++jj) { const float x = f[j + jj]; s1 += x; s2 = fmaf(x, x, s2); }
-            }
-          }
-        }
-      }
-      // accumulator buffer can be overwritten by the MMA warp
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(bar_tempty + 8 * buf);
-      if (p.stats) {
-        if (cur_group >= 0) {
-          s1 = warp_sum(s1); s2 = warp_sum(s2);
-          if (lane == 0) { atomicAdd(&stats_smem[2 * cur_group], s1); atomicAdd(&stats_smem[2 * cur_group + 1], s2); }
-        }
-        asm volatile("bar.sync 1, 128;" ::: "memory");
-        if (et < 16) {
-          atomicAdd(p.stats + (int64_t)batch * 16 + et, (double)stats_smem[et]);
-          stats_smem[et] = 0.f;
-        }
-        asm volatile("bar.sync 1, 128;" ::: "memory");
+        // accumulator buffer can be overwritten by the MMA warp
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar_tempty + 8 * buf);
       }
     }
   }

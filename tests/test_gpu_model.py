@@ -54,12 +54,17 @@ def test_forward_vs_oracle_t128_mixed_t(model, oracle_sd):
     assert r <= EPS_REL and m <= EPS_ABS_PER_STD * float(ref.std())
 
 
-def test_forward_is_deterministic_enough_and_batch_independent(model):
-    # samples never mix: a sample's epsilon must not depend on its batch neighbours
+def test_forward_is_reproducible_and_batch_independent(model):
+    # every reduction on the path has a fixed order except the final double-precision atomics: two runs agree (almost) bitwise
     x, _, t = O.synthetic_inputs(3, 64, 5)
     a = model(x.to(DEV), t.to(DEV))
+    a2 = model(x.to(DEV), t.to(DEV))
+    assert rel_l2(a2, a) < 1e-3
+    # samples never mix.  A different batch size changes which CTA sums which tile, i.e. the fp32
+    # summation order of the GroupNorm statistics (~1e-7), and bf16 rounding of the activations amplifies that through 32
+    # residual blocks up to the path's own rounding noise -- so the bound is the model tolerance, not zero.
     b = model(x[1:2].to(DEV), t[1:2].to(DEV))
-    assert rel_l2(a[1:2], b) < 2e-3       # atomics reorder the GroupNorm partial sums; no cross-sample term
+    assert rel_l2(a[1:2], b) < EPS_REL
 
 
 @pytest.mark.parametrize("name", ["ddim_b2_t32_eta0", "ddim_b1_t64_eta1"])
