@@ -32,6 +32,7 @@ SIGNATURES = {
     "ddimb_conv_in": [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i],
     "ddimb_conv_out": [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i],
     "ddimb_conv3x3": [_vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _i, _i, _i, _i, _i],
+    "ddimb_conv3x3_gn": [_vp, _vp, _vp, _vp, _f, _i, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _i, _i, _i, _i],
     "ddimb_conv_down4x4": [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i],
     "ddimb_conv_up4x4": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i],
     "ddimb_linear": [_vp, _ll, _vp, _ll, _vp, _i, _vp, _ll, _i, _ll, _i, _i, _i],
@@ -43,11 +44,13 @@ SIGNATURES = {
     "ddimb_layernorm512": [_vp, _vp, _vp, _vp, _vp, _vp, _ll, _i, _i, _f],
     "ddimb_split_bf16": [_vp, _vp, _ll, _i, _i, _ll],
 }
-EXPORTS = ["ddimb_version", "ddimb_last_error", "ddimb_launch_count", "ddimb_prof_enable", "ddimb_prof_report"] + list(SIGNATURES)
+EXPORTS = ["ddimb_version", "ddimb_last_error", "ddimb_launch_count", "ddimb_prof_enable", "ddimb_prof_report", "ddimb_conv3x3_wide_supported"] + list(SIGNATURES)
 
 lib.ddimb_version.restype = _i
 lib.ddimb_last_error.restype = C.c_char_p
 lib.ddimb_launch_count.restype = _ll
+lib.ddimb_conv3x3_wide_supported.argtypes = [_i, _i, _i]
+lib.ddimb_conv3x3_wide_supported.restype = _i
 lib.ddimb_prof_enable.argtypes = [_i]
 lib.ddimb_prof_enable.restype = _i
 lib.ddimb_prof_report.argtypes = [C.c_char_p, _i]

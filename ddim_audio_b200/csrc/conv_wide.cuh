@@ -1,0 +1,292 @@
+// 3x3 convolution of the two widest U-Net levels (C = 32 / 64 channels, W a multiple of 128), where the work is HBM-bound:
+// reference models/diffusion.py:42-56 -- GroupNorm (+SiLU) -> Conv2d 3x3 -> (+temb | +bias) -> SiLU, in ONE pass over x.
+//
+// A CTA walks a strip of 128 output columns down RT consecutive rows.  Every input row strip (130 positions x C channels,
+// halo columns included, TMA zero fill outside the image) is read from HBM/L2 ONCE into a ring slot; the GroupNorm affine
+// (+SiLU) of the block's first half is applied in place by four transform warps (halo positions forced back to zero, which
+// is what the reference's zero padding of the ACTIVATED tensor means); then all 9 taps are tcgen05.mma's whose A descriptors
+// simply start kx rows further into slot (t + ky - 1) -- the swizzle is a function of the absolute shared-memory address,
+// so a row-shifted start needs no re-layout (tools/umma_probe.cu).  The 9 weight tiles stay resident in shared memory.
+// Warp roles (320 threads): 0 = TMA producer, 1 = MMA issuer, 2-5 = epilogue, 6-9 = transform.
+#pragma once
+#include "umma_gemm.cuh"
+
+namespace ddimb {
+
+constexpr int kWideThreads = 320;
+constexpr int kWidePos = 130;   // positions per row strip: 128 + 2 halo columns
+
+struct WideParams {
+  int32_t B, T, W;
+  int32_t RT;             // output rows per work unit
+  int32_t units_t;        // ceil(T / RT)
+  int32_t num_units;      // B * (W / 128) * units_t
+  int32_t prologue;       // 0: x is already activated; 1: GroupNorm affine; 2: GroupNorm affine + SiLU
+  float eps;
+  const double* gn_stats; // [B][8][2] (sum, sumsq) of x
+  const float* gn_gamma;  // [C]
+  const float* gn_beta;   // [C] or null
+  // epilogue (same meaning as GemmParams)
+  __nv_bfloat16* out;
+  const __nv_bfloat16* add;
+  const float* bias;
+  const float* bias_b;
+  double* stats;
+  int32_t bias_b_stride;
+  int32_t act;
+};
+
+template <int C>
+struct WideCfg {
+  static constexpr int kRowBytes = C * 2;
+  static constexpr int kSlotBytes = ((kWidePos * kRowBytes + 1023) / 1024) * 1024;
+  static constexpr int kSlots = (C == 32) ? 8 : 6;
+  static constexpr int kAccBufs = 256 / C;          // 256 TMEM columns in use
+  static constexpr int kWBytes = 9 * C * C * 2;
+  static constexpr int kSwizzle = (C == 64) ? 2 : 4;
+  static constexpr int kSBO = 8 * kRowBytes;
+  static constexpr int kAuxBytes = 1024 + 4096 + 4 * C * 8;   // barriers | epilogue bias copies | transform scale/shift copies
+  static constexpr int kSmemBytes = 1024 + kWBytes + kSlots * kSlotBytes + kAuxBytes;
+};
+
+__device__ __forceinline__ void tma_load_4d(uint32_t dst, const void* tmap, uint32_t bar, int c0, int c1, int c2, int c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];" ::"r"(dst),
+      "l"(tmap), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+      : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+// unit -> (sample, column block, first output row); units are sample-major so a CTA's samples change rarely
+struct WideUnit {
+  int b, w0, t0, rows;
+  __device__ __forceinline__ void set(const WideParams& p, int u) {
+    const int per_b = (p.W >> 7) * p.units_t;
+    b = u / per_b;
+    const int r = u - b * per_b;
+    const int wb = r / p.units_t;
+    t0 = (r - wb * p.units_t) * p.RT;
+    w0 = wb << 7;
+    rows = min(p.RT, p.T - t0);
+  }
+};
+
+template <int C>
+__global__ void __launch_bounds__(kWideThreads, 1)
+conv3x3_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const __grid_constant__ WideParams p) {
+  using Cfg = WideCfg<C>;
+  constexpr int NS = Cfg::kSlots, NB = Cfg::kAccBufs;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
+  const uint32_t w_base = smem_base;
+  const uint32_t a_base = smem_base + Cfg::kWBytes;
+  uint8_t* a_gen = smem_gen + Cfg::kWBytes;
+  const uint32_t aux = a_base + NS * Cfg::kSlotBytes;
+  uint8_t* aux_gen = a_gen + NS * Cfg::kSlotBytes;
+  // aux: raw_full[8] @0, ready[8] @64, empty[8] @128, acc_full[8] @192, acc_empty[8] @256, wfull @320, tmem ptr @328
+  const uint32_t bar_raw = aux, bar_ready = aux + 64, bar_empty = aux + 128, bar_afull = aux + 192, bar_aempty = aux + 256, bar_w = aux + 320;
+  volatile uint32_t* tmem_ptr_gen = reinterpret_cast<volatile uint32_t*>(aux_gen + 328);
+  float* bias_smem = reinterpret_cast<float*>(aux_gen + 1024);
+  float* gn_smem = reinterpret_cast<float*>(aux_gen + 1024 + 4096);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const bool fused = p.prologue != 0;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    for (int s = 0; s < NS; ++s) {
+      mbar_init(bar_raw + 8 * s, 1);
+      mbar_init(bar_ready + 8 * s, 4);    // one arrive per transform warp
+      mbar_init(bar_empty + 8 * s, 1);
+    }
+    for (int b = 0; b < NB; ++b) {
+      mbar_init(bar_afull + 8 * b, 1);
+      mbar_init(bar_aempty + 8 * b, 4);   // one arrive per epilogue warp
+    }
+    mbar_init(bar_w, 1);
+    mbar_fence_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(aux + 328, 256u);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_gen;
+
+  if (warp == 0) {
+    // ================================================================ TMA producer
+    if (lane == 0) {
+      mbar_arrive_expect_tx(bar_w, (uint32_t)Cfg::kWBytes);
+      for (int tap = 0; tap < 9; ++tap) tma_load_3d(w_base + tap * C * C * 2, &tmB, bar_w, tap * C, 0, 0);
+      uint32_t cnt = 0;
+      WideUnit u;
+      for (int unit = blockIdx.x; unit < p.num_units; unit += gridDim.x) {
+        u.set(p, unit);
+        for (int rr = 0; rr < u.rows + 2; ++rr, ++cnt) {
+          const uint32_t slot = cnt % NS, use = cnt / NS;
+          mbar_wait(bar_empty + 8 * slot, (use & 1) ^ 1, 11);
+          mbar_arrive_expect_tx(bar_raw + 8 * slot, (uint32_t)(kWidePos * Cfg::kRowBytes));
+          tma_load_4d(a_base + slot * Cfg::kSlotBytes, &tmA, bar_raw + 8 * slot, 0, u.w0 - 1, u.t0 - 1 + rr, u.b);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ================================================================ MMA issuer (single thread)
+    if (lane == 0) {
+      const uint32_t idesc = make_idesc_bf16(kTileM, (uint32_t)C);
+      const uint32_t bar_in = fused ? bar_ready : bar_raw;
+      mbar_wait(bar_w, 0, 12);
+      tc_fence_after();
+      uint32_t cnt = 0, waited = 0, tile = 0;
+      WideUnit u;
+      for (int unit = blockIdx.x; unit < p.num_units; unit += gridDim.x) {
+        u.set(p, unit);
+        for (int ot = 0; ot < u.rows; ++ot, ++tile) {
+          // input rows cnt+ot .. cnt+ot+2 must have landed (and been transformed)
+          while (waited < cnt + ot + 3) {
+            mbar_wait(bar_in + 8 * (waited % NS), (waited / NS) & 1, 13);
+            ++waited;
+          }
+          const uint32_t buf = tile % NB, use = tile / NB;
+          mbar_wait(bar_aempty + 8 * buf, (use & 1) ^ 1, 14);
+          tc_fence_after();
+          const uint32_t acc = tmem_base + buf * C;
+#pragma unroll
+          for (int ky = 0; ky < 3; ++ky) {
+            const uint32_t slot = (cnt + ot + ky) % NS;
+#pragma unroll
+            for (int kx = 0; kx < 3; ++kx) {
+              const uint64_t adesc = make_kmajor_desc(a_base + slot * Cfg::kSlotBytes + kx * Cfg::kRowBytes, Cfg::kSBO, Cfg::kSwizzle);
+              const uint64_t bdesc = make_kmajor_desc(w_base + (ky * 3 + kx) * C * C * 2, Cfg::kSBO, Cfg::kSwizzle);
+#pragma unroll
+              for (int k = 0; k < C / 16; ++k) umma_bf16(acc, adesc + 2 * k, bdesc + 2 * k, idesc, (ky | kx | k) != 0);
+            }
+          }
+          umma_commit(bar_afull + 8 * buf);
+          umma_commit(bar_empty + 8 * ((cnt + ot) % NS));          // the oldest of the three rows is no longer needed
+          if (ot == u.rows - 1) {
+            umma_commit(bar_empty + 8 * ((cnt + ot + 1) % NS));
+            umma_commit(bar_empty + 8 * ((cnt + ot + 2) % NS));
+          }
+        }
+        cnt += u.rows + 2;
+      }
+    }
+  } else if (warp < 6) {
+    // ================================================================ epilogue (TMEM lane quarter = warp % 4)
+    const int q = warp & 3;
+    const int row = q * 32 + lane;
+    float* wb = bias_smem + q * 256;
+    ConvEpiState<C> st;
+    st.reset();
+    st.cur_batch = -1;
+    uint32_t tile = 0;
+    WideUnit u;
+    for (int unit = blockIdx.x; unit < p.num_units; unit += gridDim.x) {
+      u.set(p, unit);
+      if (u.b != st.cur_batch) {
+        st.flush(p.stats, lane);
+        st.cur_batch = u.b;
+        __syncwarp();
+        for (int c = lane; c < C; c += 32)
+          wb[c] = (p.bias ? p.bias[c] : 0.f) + (p.bias_b ? p.bias_b[(int64_t)u.b * p.bias_b_stride + c] : 0.f);
+        __syncwarp();
+      }
+      for (int ot = 0; ot < u.rows; ++ot, ++tile) {
+        const uint32_t buf = tile % NB, use = tile / NB;
+        const int64_t addr0 = ((((int64_t)u.b * p.T + (u.t0 + ot)) * p.W) + u.w0 + row) * C;
+        mbar_wait(bar_afull + 8 * buf, use & 1, 15);
+        tc_fence_after();
+        const uint32_t trow = tmem_base + ((uint32_t)(q * 32) << 16) + buf * C;
+        conv_epilogue_tile<C, C>(trow, wb, p.act, p.add, p.out, addr0, true, p.stats != nullptr, st);
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar_aempty + 8 * buf);
+      }
+    }
+    st.flush(p.stats, lane);
+  } else if (fused) {
+    // ================================================================ transform: GroupNorm affine (+SiLU) in place
+    const int tw = warp - 6, tid = tw * 32 + lane;      // 0..127
+    constexpr int CH = C / 8;                           // 16-byte chunks per position
+    const int j = tid % CH;                             // logical chunk (channels 8j .. 8j+7), fixed per thread
+    const int p0 = tid / CH;
+    constexpr int PSTEP = 128 / CH;
+    constexpr int NIT = (kWidePos + PSTEP - 1) / PSTEP;
+    float* tab = gn_smem + tw * 2 * C;                  // this warp's [scale C | shift C]
+    float sc[8], sh[8];
+    int cur_b = -1;
+    uint32_t cnt = 0;
+    WideUnit u;
+    for (int unit = blockIdx.x; unit < p.num_units; unit += gridDim.x) {
+      u.set(p, unit);
+      if (u.b != cur_b) {
+        cur_b = u.b;
+        __syncwarp();
+        for (int c = lane; c < C; c += 32) {
+          const int g = c / (C / 8);
+          const double n = (double)p.T * p.W * (C / 8);
+          const double mean = p.gn_stats[(u.b * 8 + g) * 2] / n;
+          double var = p.gn_stats[(u.b * 8 + g) * 2 + 1] / n - mean * mean;
+          if (var < 0) var = 0;
+          const float rstd = (float)(1.0 / sqrt(var + (double)p.eps));
+          const float s = p.gn_gamma[c] * rstd;
+          tab[c] = s;
+          tab[C + c] = (p.gn_beta ? p.gn_beta[c] : 0.f) - (float)mean * s;
+        }
+        __syncwarp();
+#pragma unroll
+        for (int e = 0; e < 8; ++e) { sc[e] = tab[8 * j + e]; sh[e] = tab[C + 8 * j + e]; }
+      }
+      const bool left_edge = (u.w0 == 0), right_edge = (u.w0 + 128 == p.W);
+      for (int rr = 0; rr < u.rows + 2; ++rr, ++cnt) {
+        const uint32_t slot = cnt % NS, use = cnt / NS;
+        const int t = u.t0 - 1 + rr;
+        const bool row_ok = (t >= 0) && (t < p.T);
+        uint8_t* sb = a_gen + slot * Cfg::kSlotBytes;
+        mbar_wait(bar_raw + 8 * slot, use & 1, 16);
+        uint4 v[NIT];
+        uint32_t off[NIT];
+#pragma unroll
+        for (int i = 0; i < NIT; ++i) {
+          const int pos = p0 + i * PSTEP;
+          const int sw = (C == 64) ? (pos & 7) : ((pos >> 1) & 3);
+          off[i] = (uint32_t)(pos * Cfg::kRowBytes + ((j ^ sw) << 4));
+          if (pos < kWidePos) v[i] = *reinterpret_cast<const uint4*>(sb + off[i]);
+        }
+#pragma unroll
+        for (int i = 0; i < NIT; ++i) {
+          const int pos = p0 + i * PSTEP;
+          if (pos < kWidePos) {
+            const bool zero = !row_ok || (pos == 0 && left_edge) || (pos == kWidePos - 1 && right_edge);
+            uint32_t w4[4] = {v[i].x, v[i].y, v[i].z, v[i].w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const float2 x2 = unpack_bf16x2(w4[e]);
+              float a = fmaf(x2.x, sc[2 * e], sh[2 * e]), b2 = fmaf(x2.y, sc[2 * e + 1], sh[2 * e + 1]);
+              if (p.prologue == 2) { a = silu_fast(a); b2 = silu_fast(b2); }
+              w4[e] = zero ? 0u : pack_bf16x2(a, b2);
+            }
+            *reinterpret_cast<uint4*>(sb + off[i]) = make_uint4(w4[0], w4[1], w4[2], w4[3]);
+          }
+        }
+        fence_proxy_async_smem();     // generic-proxy writes -> visible to the tensor core's async-proxy reads
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar_ready + 8 * slot);
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 256u);
+  }
+}
+
+}  // namespace ddimb

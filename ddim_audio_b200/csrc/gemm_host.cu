@@ -6,6 +6,7 @@
 
 #include "../../include/ddim_b200.h"
 #include "umma_gemm.cuh"
+#include "conv_wide.cuh"
 
 using namespace ddimb;
 
@@ -62,6 +63,8 @@ static int make_tmap_bf16(CUtensorMap* tm, const void* ptr, int rank, const uint
   }
   return DDIMB_OK;
 }
+
+static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 
 static int next_pow2_cols(int c) {
   int v = 32;
@@ -135,7 +138,6 @@ static void init_params(GemmParams& p) {
   p.num_n_tiles = 1;
 }
 
-static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 static inline int pick_ck(int c) { return (c % 64 == 0) ? 64 : 32; }
 
 // spatial tile of 128 positions inside one [T, W] image: full-width rows when W < 128, else a 128-wide strip
@@ -143,6 +145,67 @@ static void spatial_tile(int T, int W, int* bw, int* bt) {
   *bw = W >= kTileM ? kTileM : W;
   *bt = kTileM / *bw;
   (void)T;
+}
+
+// ------------------------------------------------------------------------------------------------ wide 3x3 conv (+ fused GroupNorm)
+// reference: models/diffusion.py:42-56.  Levels with C in {32, 64} and W a multiple of 128 (csrc/conv_wide.cuh).
+extern "C" int ddimb_conv3x3_wide_supported(int Cin, int Cout, int W) {
+  return (Cin == Cout && (Cin == 32 || Cin == 64) && W >= 128 && W % 128 == 0) ? 1 : 0;
+}
+
+static int launch_conv_wide(const void* x, const double* gn_stats, const float* gn_gamma, const float* gn_beta, float gn_eps, int gn_mode,
+                            const void* w, const float* bias, const float* bias_b, int bias_b_stride, int act, const void* add, void* out,
+                            double* stats, int B, int T, int W, int C, cudaStream_t stream) {
+  DDIMB_CHECK_ARG(gn_mode >= 0 && gn_mode <= 2 && (gn_mode == 0 || (gn_stats && gn_gamma)));
+  CUtensorMap tmA, tmB;
+  {
+    uint64_t dims[4] = {(uint64_t)C, (uint64_t)W, (uint64_t)T, (uint64_t)B};
+    uint64_t str[3] = {(uint64_t)C, (uint64_t)W * C, (uint64_t)T * W * C};
+    uint32_t box[4] = {(uint32_t)C, (uint32_t)kWidePos, 1, 1};
+    int r = make_tmap_bf16(&tmA, x, 4, dims, str, box, C);
+    if (r) return r;
+  }
+  {
+    uint64_t dims[3] = {(uint64_t)9 * C, (uint64_t)C, 1};
+    uint64_t str[2] = {(uint64_t)9 * C, (uint64_t)9 * C * C};
+    uint32_t box[3] = {(uint32_t)C, (uint32_t)C, 1};
+    int r = make_tmap_bf16(&tmB, w, 3, dims, str, box, C);
+    if (r) return r;
+  }
+  WideParams p;
+  memset(&p, 0, sizeof(p));
+  p.B = B; p.T = T; p.W = W;
+  int rt = 64;
+  while (rt > 8 && (long long)B * (W / 128) * ceil_div(T, rt) < 4LL * ddimb_num_sms()) rt /= 2;
+  p.RT = rt; p.units_t = ceil_div(T, rt); p.num_units = B * (W / 128) * p.units_t;
+  p.prologue = gn_mode; p.eps = gn_eps; p.gn_stats = gn_stats; p.gn_gamma = gn_gamma; p.gn_beta = gn_beta;
+  p.out = reinterpret_cast<__nv_bfloat16*>(out); p.add = reinterpret_cast<const __nv_bfloat16*>(add);
+  p.bias = bias; p.bias_b = bias_b; p.stats = stats; p.bias_b_stride = bias_b_stride; p.act = act;
+  const int grid = p.num_units < ddimb_num_sms() ? p.num_units : ddimb_num_sms();
+  if (C == 32) {
+    static bool attr = false;
+    if (!attr) { DDIMB_CUDA(cudaFuncSetAttribute(conv3x3_wide_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, WideCfg<32>::kSmemBytes)); attr = true; }
+    conv3x3_wide_kernel<32><<<grid, kWideThreads, WideCfg<32>::kSmemBytes, stream>>>(tmA, tmB, p);
+  } else {
+    static bool attr = false;
+    if (!attr) { DDIMB_CUDA(cudaFuncSetAttribute(conv3x3_wide_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, WideCfg<64>::kSmemBytes)); attr = true; }
+    conv3x3_wide_kernel<64><<<grid, kWideThreads, WideCfg<64>::kSmemBytes, stream>>>(tmA, tmB, p);
+  }
+  DDIMB_LAUNCH_CHECK();
+  return DDIMB_OK;
+}
+
+// GroupNorm(8, C) [+ SiLU] of x from precomputed statistics, then Conv2d 3x3 with the epilogue of ddimb_conv3x3 -- one kernel.
+// gn_mode 1: affine only (norm[1] before conv[1]); 2: affine + SiLU (norm[0] + silu before conv[0]).  Only the shapes
+// ddimb_conv3x3_wide_supported() accepts; other levels run ddimb_gn_apply + ddimb_conv3x3.
+extern "C" int ddimb_conv3x3_gn(const void* x, const double* gn_stats, const float* gn_gamma, const float* gn_beta, float gn_eps, int gn_mode,
+                                const void* w, const float* bias, const float* bias_b, int bias_b_stride, int act, const void* add, void* out,
+                                double* stats, int B, int T, int W, int C, cudaStream_t stream) {
+  DDIMB_CHECK_ARG(x && w && out && B >= 1 && T >= 1 && gn_mode >= 1);
+  DDIMB_CHECK_ARG(ddimb_conv3x3_wide_supported(C, C, W));
+  const double npos = (double)B * T * W;
+  DDIMB_PROF(stream, "conv3x3_gn", C, W, npos * (2 * C + (add ? C : 0)) * 2 + 18.0 * C * C, 18.0 * C * C * npos);
+  return launch_conv_wide(x, gn_stats, gn_gamma, gn_beta, gn_eps, gn_mode, w, bias, bias_b, bias_b_stride, act, add, out, stats, B, T, W, C, stream);
 }
 
 // ------------------------------------------------------------------------------------------------ Conv2d 3x3 s1 p1
@@ -155,6 +218,8 @@ extern "C" int ddimb_conv3x3(const void* x, const void* w, const float* bias, co
   DDIMB_PROF(stream, "conv3x3", Cin, W, npos * (Cin + Cout + (add ? Cout : 0)) * 2 + 18.0 * Cin * Cout, 18.0 * Cin * Cout * npos);
   DDIMB_CHECK_ARG(W >= 8 && W <= 256 && (W & (W - 1)) == 0);
   DDIMB_CHECK_ARG(Cin % 32 == 0 && Cout % 32 == 0 && Cout <= 256 && Cin <= 256);
+  if (ddimb_conv3x3_wide_supported(Cin, Cout, W))
+    return launch_conv_wide(x, nullptr, nullptr, nullptr, 0.f, 0, w, bias, bias_b, bias_b_stride, act, add, out, stats, B, T, W, Cin, stream);
   const int ck = pick_ck(Cin);
   int bw, bt;
   spatial_tile(T, W, &bw, &bt);

@@ -136,3 +136,32 @@ def test_fourier_mix(ops, B, S):
     ref = torch.fft.fftn(x.double().reshape(B, S, H), dim=(1, 2)).real.reshape(B * S, H)
     r = rel_l2(y, ref)
     assert r < 2e-4, f"fourier split-bf16 rel-l2 {r:.3e}"
+
+
+# ---------------------------------------------------------------------------------------------- wide 3x3 conv (+ fused GroupNorm)
+WIDE_CASES = [(32, 256, 8, 1), (32, 256, 70, 2), (32, 128, 33, 3), (64, 128, 16, 2), (64, 256, 9, 1), (64, 128, 130, 2), (32, 256, 1, 1)]
+
+
+@pytest.mark.parametrize("C,W,T,B", WIDE_CASES)
+@pytest.mark.parametrize("gn_mode", [1, 2])
+def test_conv3x3_gn_fused(ops, C, W, T, B, gn_mode):
+    """models/diffusion.py:47-52: conv(silu(GN(x))) / conv(GN(x)) in one kernel vs torch group_norm + conv2d in fp32."""
+    from gpu_util import group_stats
+    assert ops.conv3x3_gn_supported(C, W)
+    g = torch.Generator(device=DEV).manual_seed(C + W + T + gn_mode)
+    x = _bf(torch.randn(B, T, W, C, device=DEV, generator=g) * 1.5 + 0.3)
+    w = _bf(torch.randn(C, C, 3, 3, device=DEV, generator=g) / math.sqrt(9 * C))
+    wp = w.permute(0, 2, 3, 1).reshape(C, -1).contiguous()
+    gamma = 1.0 + 0.2 * torch.randn(C, device=DEV, generator=g)
+    beta = 0.2 * torch.randn(C, device=DEV, generator=g)
+    bias = torch.randn(C, device=DEV, generator=g) * 0.3
+    sti = group_stats(x).contiguous()
+    st = torch.zeros(B, 8, 2, dtype=torch.float64, device=DEV)
+    out = ops.conv3x3_gn(x, sti, gamma, beta, 1e-6, gn_mode, wp, bias=bias, act=1, stats=st)
+    a = F.group_norm(x.float().permute(0, 3, 1, 2), 8, gamma, beta, eps=1e-6)
+    if gn_mode == 2:
+        a = F.silu(a)
+    a = a.to(torch.bfloat16).float()          # the kernel rounds the activated operand to bf16 before the tensor core
+    ref = F.silu(F.conv2d(a, w.float(), bias, padding=1)).permute(0, 2, 3, 1)
+    assert_close_bf16(out, ref, f"conv3x3_gn C={C} W={W} T={T} B={B} mode={gn_mode}", rel=6e-3, max_rel=3e-2)
+    assert_stats(st, ref, f"conv3x3_gn stats C={C}")
