@@ -34,14 +34,16 @@ struct WideParams {
   double* stats;
   int32_t bias_b_stride;
   int32_t act;
+  int32_t dbg;            // experiment switch (DDIMB_WIDE_DBG)
 };
 
 template <int C>
 struct WideCfg {
   static constexpr int kRowBytes = C * 2;
   static constexpr int kSlotBytes = ((kWidePos * kRowBytes + 1023) / 1024) * 1024;
-  static constexpr int kSlots = (C == 32) ? 8 : 6;
-  static constexpr int kAccBufs = 256 / C;          // 256 TMEM columns in use
+  static constexpr int kSlots = (C == 32) ? 16 : 8;   // rows in flight: HBM latency x bandwidth needs > 60 KB per SM
+  static constexpr int kAccBufs = 8;                // output rows in flight in TMEM
+  static constexpr int kTmemCols = 8 * C;           // 256 / 512 columns
   static constexpr int kWBytes = 9 * C * C * 2;
   static constexpr int kSwizzle = (C == 64) ? 2 : 4;
   static constexpr int kSBO = 8 * kRowBytes;
@@ -84,9 +86,9 @@ conv3x3_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   uint8_t* a_gen = smem_gen + Cfg::kWBytes;
   const uint32_t aux = a_base + NS * Cfg::kSlotBytes;
   uint8_t* aux_gen = a_gen + NS * Cfg::kSlotBytes;
-  // aux: raw_full[8] @0, ready[8] @64, empty[8] @128, acc_full[8] @192, acc_empty[8] @256, wfull @320, tmem ptr @328
-  const uint32_t bar_raw = aux, bar_ready = aux + 64, bar_empty = aux + 128, bar_afull = aux + 192, bar_aempty = aux + 256, bar_w = aux + 320;
-  volatile uint32_t* tmem_ptr_gen = reinterpret_cast<volatile uint32_t*>(aux_gen + 328);
+  // aux: raw_full[16] @0, ready[16] @128, empty[16] @256, acc_full[8] @384, acc_empty[8] @448, wfull @512, tmem ptr @520
+  const uint32_t bar_raw = aux, bar_ready = aux + 128, bar_empty = aux + 256, bar_afull = aux + 384, bar_aempty = aux + 448, bar_w = aux + 512;
+  volatile uint32_t* tmem_ptr_gen = reinterpret_cast<volatile uint32_t*>(aux_gen + 520);
   float* bias_smem = reinterpret_cast<float*>(aux_gen + 1024);
   float* gn_smem = reinterpret_cast<float*>(aux_gen + 1024 + 4096);
 
@@ -98,7 +100,7 @@ conv3x3_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     tma_prefetch_desc(&tmB);
     for (int s = 0; s < NS; ++s) {
       mbar_init(bar_raw + 8 * s, 1);
-      mbar_init(bar_ready + 8 * s, 4);    // one arrive per transform warp
+      mbar_init(bar_ready + 8 * s, 1);    // the transform warp that owns the row
       mbar_init(bar_empty + 8 * s, 1);
     }
     for (int b = 0; b < NB; ++b) {
@@ -109,7 +111,7 @@ conv3x3_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     mbar_fence_init();
   }
   if (warp == 1) {
-    tmem_alloc(aux + 328, 256u);
+    tmem_alloc(aux + 520, (uint32_t)Cfg::kTmemCols);
     tmem_relinquish();
   }
   tc_fence_before();
@@ -121,7 +123,9 @@ conv3x3_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     // ================================================================ TMA producer
     if (lane == 0) {
       mbar_arrive_expect_tx(bar_w, (uint32_t)Cfg::kWBytes);
-      for (int tap = 0; tap < 9; ++tap) tma_load_3d(w_base + tap * C * C * 2, &tmB, bar_w, tap * C, 0, 0);
+      // per kx one B tile of 3C rows: row block j holds ky = 2 - j, i.e. the output rows (rr-2, rr-1, rr) an input row rr feeds
+      for (int ky = 0; ky < 3; ++ky)
+        for (int kx = 0; kx < 3; ++kx) tma_load_3d(w_base + (kx * 3 + (2 - ky)) * C * C * 2, &tmB, bar_w, (ky * 3 + kx) * C, 0, 0);
       uint32_t cnt = 0;
       WideUnit u;
       for (int unit = blockIdx.x; unit < p.num_units; unit += gridDim.x) {
@@ -137,43 +141,59 @@ conv3x3_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   } else if (warp == 1) {
     // ================================================================ MMA issuer (single thread)
     if (lane == 0) {
-      const uint32_t idesc = make_idesc_bf16(kTileM, (uint32_t)C);
       const uint32_t bar_in = fused ? bar_ready : bar_raw;
       mbar_wait(bar_w, 0, 12);
       tc_fence_after();
-      uint32_t cnt = 0, waited = 0, tile = 0;
+      // Input-row-major issue order: input row rr of a unit feeds output rows rr-2 (ky=2), rr-1 (ky=1) and rr (ky=0), whose
+      // accumulators are adjacent TMEM column blocks, so one MMA of N = 3C serves all three and the A tile is read from shared
+      // memory once per (kx, k) instead of three times.  Output row rr receives its FIRST contribution here (overwrite).
+      const uint32_t idesc1 = make_idesc_bf16(kTileM, (uint32_t)C), idesc2 = make_idesc_bf16(kTileM, (uint32_t)(2 * C)),
+                     idesc3 = make_idesc_bf16(kTileM, (uint32_t)(3 * C));
+      uint32_t cnt = 0, otile = 0;
       WideUnit u;
       for (int unit = blockIdx.x; unit < p.num_units; unit += gridDim.x) {
         u.set(p, unit);
-        for (int ot = 0; ot < u.rows; ++ot, ++tile) {
-          // input rows cnt+ot .. cnt+ot+2 must have landed (and been transformed)
-          while (waited < cnt + ot + 3) {
-            mbar_wait(bar_in + 8 * (waited % NS), (waited / NS) & 1, 13);
-            ++waited;
+        for (int rr = 0; rr < u.rows + 2; ++rr) {
+          const uint32_t slot = (cnt + rr) % NS;
+          mbar_wait(bar_in + 8 * slot, ((cnt + rr) / NS) & 1, 13);
+          if (rr < u.rows) {
+            const uint32_t nbuf = (otile + rr) % NB, use = (otile + rr) / NB;
+            mbar_wait(bar_aempty + 8 * nbuf, (use & 1) ^ 1, 14);
           }
-          const uint32_t buf = tile % NB, use = tile / NB;
-          mbar_wait(bar_aempty + 8 * buf, (use & 1) ^ 1, 14);
           tc_fence_after();
-          const uint32_t acc = tmem_base + buf * C;
+          // output blocks j = 0, 1, 2 <-> output rows rr-2, rr-1, rr (ky = 2, 1, 0); block 2 is a first contribution
+          const bool v0 = rr >= 2, v1 = rr >= 1 && rr - 1 < u.rows, v2 = rr < u.rows;
+          const uint32_t b0 = (otile + rr - 2) % NB, b1 = (otile + rr - 1) % NB, b2 = (otile + rr) % NB;
+          const bool m01 = v0 && v1 && b1 != 0 && !(p.dbg & 1);          // blocks 0,1 adjacent in TMEM
+          const bool m012 = m01 && v2 && b2 != 0;                        // all three adjacent
+          const uint32_t sa = a_base + slot * Cfg::kSlotBytes;
 #pragma unroll
-          for (int ky = 0; ky < 3; ++ky) {
-            const uint32_t slot = (cnt + ot + ky) % NS;
+          for (int kx = 0; kx < 3; ++kx) {
+            const uint64_t adesc = make_kmajor_desc(sa + kx * Cfg::kRowBytes, Cfg::kSBO, Cfg::kSwizzle);
+            const uint64_t bd0 = make_kmajor_desc(w_base + (kx * 3 + 0) * C * C * 2, Cfg::kSBO, Cfg::kSwizzle);
+            const uint64_t bd1 = make_kmajor_desc(w_base + (kx * 3 + 1) * C * C * 2, Cfg::kSBO, Cfg::kSwizzle);
+            const uint64_t bd2 = make_kmajor_desc(w_base + (kx * 3 + 2) * C * C * 2, Cfg::kSBO, Cfg::kSwizzle);
 #pragma unroll
-            for (int kx = 0; kx < 3; ++kx) {
-              const uint64_t adesc = make_kmajor_desc(a_base + slot * Cfg::kSlotBytes + kx * Cfg::kRowBytes, Cfg::kSBO, Cfg::kSwizzle);
-              const uint64_t bdesc = make_kmajor_desc(w_base + (ky * 3 + kx) * C * C * 2, Cfg::kSBO, Cfg::kSwizzle);
-#pragma unroll
-              for (int k = 0; k < C / 16; ++k) umma_bf16(acc, adesc + 2 * k, bdesc + 2 * k, idesc, (ky | kx | k) != 0);
+            for (int k = 0; k < C / 16; ++k) {
+              const bool init = (kx == 0 && k == 0);
+              if (m012 && !init) {
+                umma_bf16(tmem_base + b0 * C, adesc + 2 * k, bd0 + 2 * k, idesc3, 1u);
+              } else {
+                if (m01) {
+                  umma_bf16(tmem_base + b0 * C, adesc + 2 * k, bd0 + 2 * k, idesc2, 1u);
+                } else {
+                  if (v0) umma_bf16(tmem_base + b0 * C, adesc + 2 * k, bd0 + 2 * k, idesc1, 1u);
+                  if (v1) umma_bf16(tmem_base + b1 * C, adesc + 2 * k, bd1 + 2 * k, idesc1, 1u);
+                }
+                if (v2) umma_bf16(tmem_base + b2 * C, adesc + 2 * k, bd2 + 2 * k, idesc1, init ? 0u : 1u);
+              }
             }
           }
-          umma_commit(bar_afull + 8 * buf);
-          umma_commit(bar_empty + 8 * ((cnt + ot) % NS));          // the oldest of the three rows is no longer needed
-          if (ot == u.rows - 1) {
-            umma_commit(bar_empty + 8 * ((cnt + ot + 1) % NS));
-            umma_commit(bar_empty + 8 * ((cnt + ot + 2) % NS));
-          }
+          umma_commit(bar_empty + 8 * slot);                                   // this input row is consumed
+          if (rr >= 2) umma_commit(bar_afull + 8 * ((otile + rr - 2) % NB));   // output row rr-2 is complete
         }
         cnt += u.rows + 2;
+        otile += u.rows;
       }
     }
   } else if (warp < 6) {
@@ -211,12 +231,15 @@ conv3x3_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     st.flush(p.stats, lane);
   } else if (fused) {
     // ================================================================ transform: GroupNorm affine (+SiLU) in place
-    const int tw = warp - 6, tid = tw * 32 + lane;      // 0..127
+    // Each of the four warps owns every fourth row strip, so four rows are in flight and one warp's load->math->store
+    // latency chain overlaps with the others'.  Lane -> (position, 16-byte chunk) with a fixed logical chunk per lane.
+    const int tw = warp - 6;
     constexpr int CH = C / 8;                           // 16-byte chunks per position
-    const int j = tid % CH;                             // logical chunk (channels 8j .. 8j+7), fixed per thread
-    const int p0 = tid / CH;
-    constexpr int PSTEP = 128 / CH;
+    const int j = lane % CH;                            // logical chunk (channels 8j .. 8j+7), fixed per lane
+    const int p0 = lane / CH;
+    constexpr int PSTEP = 32 / CH;                      // positions per warp iteration
     constexpr int NIT = (kWidePos + PSTEP - 1) / PSTEP;
+    constexpr int BATCH = 6;                            // 16-byte loads in flight per lane
     float* tab = gn_smem + tw * 2 * C;                  // this warp's [scale C | shift C]
     float sc[8], sh[8];
     int cur_b = -1;
@@ -244,34 +267,42 @@ conv3x3_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       }
       const bool left_edge = (u.w0 == 0), right_edge = (u.w0 + 128 == p.W);
       for (int rr = 0; rr < u.rows + 2; ++rr, ++cnt) {
+        if ((int)(cnt & 3) != tw) continue;
         const uint32_t slot = cnt % NS, use = cnt / NS;
         const int t = u.t0 - 1 + rr;
         const bool row_ok = (t >= 0) && (t < p.T);
         uint8_t* sb = a_gen + slot * Cfg::kSlotBytes;
         mbar_wait(bar_raw + 8 * slot, use & 1, 16);
-        uint4 v[NIT];
-        uint32_t off[NIT];
+        if (!row_ok) {
+          // a row outside the image is all padding: zeros (TMA already filled zeros, but affine(0) != 0 must not be applied)
+        } else {
+#pragma unroll 1
+          for (int i0 = 0; i0 < NIT; i0 += BATCH) {
+            uint4 v[BATCH];
+            uint32_t off[BATCH];
 #pragma unroll
-        for (int i = 0; i < NIT; ++i) {
-          const int pos = p0 + i * PSTEP;
-          const int sw = (C == 64) ? (pos & 7) : ((pos >> 1) & 3);
-          off[i] = (uint32_t)(pos * Cfg::kRowBytes + ((j ^ sw) << 4));
-          if (pos < kWidePos) v[i] = *reinterpret_cast<const uint4*>(sb + off[i]);
-        }
-#pragma unroll
-        for (int i = 0; i < NIT; ++i) {
-          const int pos = p0 + i * PSTEP;
-          if (pos < kWidePos) {
-            const bool zero = !row_ok || (pos == 0 && left_edge) || (pos == kWidePos - 1 && right_edge);
-            uint32_t w4[4] = {v[i].x, v[i].y, v[i].z, v[i].w};
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-              const float2 x2 = unpack_bf16x2(w4[e]);
-              float a = fmaf(x2.x, sc[2 * e], sh[2 * e]), b2 = fmaf(x2.y, sc[2 * e + 1], sh[2 * e + 1]);
-              if (p.prologue == 2) { a = silu_fast(a); b2 = silu_fast(b2); }
-              w4[e] = zero ? 0u : pack_bf16x2(a, b2);
+            for (int i = 0; i < BATCH; ++i) {
+              const int pos = p0 + (i0 + i) * PSTEP;
+              const int sw = (C == 64) ? (pos & 7) : ((pos >> 1) & 3);
+              off[i] = (uint32_t)(pos * Cfg::kRowBytes + ((j ^ sw) << 4));
+              if (pos < kWidePos) v[i] = *reinterpret_cast<const uint4*>(sb + off[i]);
             }
-            *reinterpret_cast<uint4*>(sb + off[i]) = make_uint4(w4[0], w4[1], w4[2], w4[3]);
+#pragma unroll
+            for (int i = 0; i < BATCH; ++i) {
+              const int pos = p0 + (i0 + i) * PSTEP;
+              if (pos < kWidePos) {
+                const bool zero = (pos == 0 && left_edge) || (pos == kWidePos - 1 && right_edge);
+                uint32_t w4[4] = {v[i].x, v[i].y, v[i].z, v[i].w};
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                  const float2 x2 = unpack_bf16x2(w4[e]);
+                  float a = fmaf(x2.x, sc[2 * e], sh[2 * e]), b2 = fmaf(x2.y, sc[2 * e + 1], sh[2 * e + 1]);
+                  if (p.prologue == 2) { a = silu_fast(a); b2 = silu_fast(b2); }
+                  w4[e] = zero ? 0u : pack_bf16x2(a, b2);
+                }
+                *reinterpret_cast<uint4*>(sb + off[i]) = make_uint4(w4[0], w4[1], w4[2], w4[3]);
+              }
+            }
           }
         }
         fence_proxy_async_smem();     // generic-proxy writes -> visible to the tensor core's async-proxy reads
@@ -285,7 +316,7 @@ conv3x3_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, 256u);
+    tmem_dealloc(tmem_base, (uint32_t)Cfg::kTmemCols);
   }
 }
 

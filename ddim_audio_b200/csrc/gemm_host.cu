@@ -1,5 +1,6 @@
 // Host side of the tcgen05 implicit-GEMM kernel: tensor maps, tap programs, C-ABI entry points.
 #include <math.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <mutex>
@@ -181,6 +182,7 @@ static int launch_conv_wide(const void* x, const double* gn_stats, const float* 
   p.prologue = gn_mode; p.eps = gn_eps; p.gn_stats = gn_stats; p.gn_gamma = gn_gamma; p.gn_beta = gn_beta;
   p.out = reinterpret_cast<__nv_bfloat16*>(out); p.add = reinterpret_cast<const __nv_bfloat16*>(add);
   p.bias = bias; p.bias_b = bias_b; p.stats = stats; p.bias_b_stride = bias_b_stride; p.act = act;
+  { const char* e = getenv("DDIMB_WIDE_DBG"); p.dbg = e ? atoi(e) : 0; }
   const int grid = p.num_units < ddimb_num_sms() ? p.num_units : ddimb_num_sms();
   if (C == 32) {
     static bool attr = false;

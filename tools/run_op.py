@@ -31,6 +31,13 @@ if a.op == "conv3x3":
     w = (torch.randn(C, 9 * C, device=dev, generator=g) / math.sqrt(9 * C)).to(bf)
     temb = torch.randn(B, 4416, device=dev, generator=g)
     fn = lambda: ops.conv3x3(x, w, bias_b=temb, bias_b_stride=4416, act=1, stats=st)
+elif a.op == "conv3x3_gn":
+    w = (torch.randn(C, 9 * C, device=dev, generator=g) / math.sqrt(9 * C)).to(bf)
+    temb = torch.randn(B, 4416, device=dev, generator=g)
+    gam = torch.randn(C, device=dev, generator=g)
+    bet = torch.randn(C, device=dev, generator=g)
+    sti = torch.stack([x.double().reshape(B, -1, 8, C // 8).sum(dim=(1, 3)), (x.double() ** 2).reshape(B, -1, 8, C // 8).sum(dim=(1, 3))], -1).contiguous()
+    fn = lambda: ops.conv3x3_gn(x, sti, gam, bet, 1e-6, 2, w, bias_b=temb, bias_b_stride=4416, act=1, stats=st)
 elif a.op == "down":
     w = (torch.randn(Co, 16 * C, device=dev, generator=g) / math.sqrt(16 * C)).to(bf)
     b = torch.randn(Co, device=dev, generator=g)
