@@ -43,6 +43,26 @@ SIGNATURES = {
     "ddimb_tokens_to_nhwc": [_vp, _vp, _vp, _vp, _i, _i, _i, _i],
     "ddimb_layernorm512": [_vp, _vp, _vp, _vp, _vp, _vp, _ll, _i, _i, _f],
     "ddimb_split_bf16": [_vp, _vp, _ll, _i, _i, _ll],
+    # ---- training
+    "ddimb_conv3x3_wgrad": [_vp, _vp, _vp, _i, _i, _i, _i, _i],
+    "ddimb_conv_down4x4_wgrad": [_vp, _vp, _vp, _i, _i, _i, _i, _i],
+    "ddimb_conv_up4x4_wgrad": [_vp, _vp, _vp, _i, _i, _i, _i, _i],
+    "ddimb_linear_wgrad": [_vp, _ll, _vp, _ll, _vp, _i, _i, _i],
+    "ddimb_gn_bwd_reduce": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _ll, _i, _f],
+    "ddimb_gn_bwd_apply": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _ll, _i, _f],
+    "ddimb_gn_bwd_param": [_vp, _vp, _vp, _vp, _i, _ll, _i, _f],
+    "ddimb_colsum": [_vp, _i, _ll, _ll, _i, _vp],
+    "ddimb_sums_scatter": [_vp, _vp, _ll, _vp, _i, _i],
+    "ddimb_layernorm512_bwd": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _ll, _i, _vp, _vp, _i, _f],
+    "ddimb_gelu": [_vp, _vp, _vp, _ll],
+    "ddimb_add_split_bf16": [_vp, _vp, _vp, _vp, _ll, _i, _i, _ll],
+    "ddimb_dropout": [_vp, _vp, _ll, _f, C.c_ulonglong],
+    "ddimb_tokens_ln_bwd": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _f],
+    "ddimb_nhwc_to_tokens": [_vp, _vp, _i, _i, _i, _i],
+    "ddimb_linear_small_wgrad": [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i],
+    "ddimb_linear_small_dgrad": [_vp, _vp, _vp, _vp, _i, _i, _i],
+    "ddimb_conv_in_wgrad": [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i],
+    "ddimb_conv_out_wgrad": [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i],
 }
 EXPORTS = ["ddimb_version", "ddimb_last_error", "ddimb_launch_count", "ddimb_prof_enable", "ddimb_prof_report", "ddimb_conv3x3_wide_supported"] + list(SIGNATURES)
 

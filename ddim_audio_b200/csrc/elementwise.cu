@@ -162,6 +162,7 @@ struct GnArgs {
   int64_t per_sample;   // P * C
   int C;
   int mode;
+  int pre_silu;         // the normalised tensor is silu(x) (training stores pre-activations)
   float eps;
 };
 
@@ -196,7 +197,8 @@ __global__ void __launch_bounds__(256) gn_apply_kernel(const GnArgs a) {
     float f[8];
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
-      const float2 t = unpack_bf16x2(xw[j]);
+      float2 t = unpack_bf16x2(xw[j]);
+      if (a.pre_silu) { t.x = silu_fast(t.x); t.y = silu_fast(t.y); }
       f[2 * j] = fmaf(t.x, sc[2 * j], sh[2 * j]);
       f[2 * j + 1] = fmaf(t.y, sc[2 * j + 1], sh[2 * j + 1]);
     }
@@ -237,14 +239,18 @@ __global__ void __launch_bounds__(256) gn_apply_kernel(const GnArgs a) {
 extern "C" int ddimb_gn_apply(const void* x, const void* res, void* y, const double* stats_in, double* stats_out, const float* gamma,
                               const float* beta, int mode, int B, long long positions, int C, float eps, cudaStream_t stream) {
   DDIMB_CHECK_ARG(x && y && stats_in && gamma && B >= 1 && positions >= 1);
-  DDIMB_CHECK_ARG(C % 32 == 0 && C <= 256 && mode >= 0 && mode <= 2);
+  DDIMB_CHECK_ARG(C % 32 == 0 && C <= 256 && mode >= 0 && mode <= 4);
+  // modes 3 / 4 (training): the stored tensor is a pre-activation; y = gn(silu(x)) / y = res + gn(silu(x))
+  const int pre_silu = mode >= 3 ? 1 : 0;
+  if (mode == 3) mode = 0;
+  if (mode == 4) mode = 2;
   DDIMB_CHECK_ARG(mode != 2 || res);
   DDIMB_PROF(stream, "gn_apply", C, mode, 2.0 * B * positions * C * (mode == 2 ? 3 : 2), 0.0);
   GnArgs a;
   a.x = reinterpret_cast<const __nv_bfloat16*>(x); a.res = reinterpret_cast<const __nv_bfloat16*>(res);
   a.y = reinterpret_cast<__nv_bfloat16*>(y);
   a.stats_in = stats_in; a.stats_out = stats_out; a.gamma = gamma; a.beta = beta;
-  a.per_sample = positions * C; a.C = C; a.mode = mode; a.eps = eps;
+  a.per_sample = positions * C; a.C = C; a.mode = mode; a.pre_silu = pre_silu; a.eps = eps;
   const int threads = (C % 96 == 0) ? 192 : 256;   // threads * 8 must be a multiple of C
   const int64_t items = a.per_sample / 8;
   int64_t bx = (items + threads * 4 - 1) / (threads * 4);
@@ -419,11 +425,15 @@ __global__ void __launch_bounds__(256) linear_small_kernel(const float* __restri
     float acc = 0.f;
 #pragma unroll
     for (int j = 0; j < 16; ++j)
-      if (j < per) acc = fmaf(wr[j], ip[j * 32 + lane], acc);
+      if (j < per) {
+        float iv = ip[j * 32 + lane];
+        if (act & 2) iv = silu_exact(iv);
+        acc = fmaf(wr[j], iv, acc);
+      }
     acc = warp_sum(acc);
     if (lane == 0) {
       float v = acc + bv;
-      if (act == 1) v = silu_exact(v);
+      if (act & 1) v = silu_exact(v);
       out[(int64_t)r * N + n] = v;
     }
   }

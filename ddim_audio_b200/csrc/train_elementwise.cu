@@ -1,0 +1,764 @@
+// Backward-pass kernels of the HBM-bound layers (autograd of reference models/diffusion.py:12-56,81-145,189-208 and
+// hf modeling_fnet.py:180-231): GroupNorm / SiLU, LayerNorm, gelu_new, token repacks, the temb MLP, conv_in / conv_out
+// parameter gradients, dropout.  bf16 NHWC gradients, fp32 math, fp64 cross-block accumulation where a sum spans a sample.
+#include "../../include/ddim_b200.h"
+#include "common.cuh"
+
+using namespace ddimb;
+
+namespace {
+
+__device__ __forceinline__ float sigmoid_fast(float x) { return fmaf(0.5f, tanh_approx(0.5f * x), 0.5f); }
+// d/dx silu(x) = s (1 + x (1 - s)), s = sigmoid(x)
+__device__ __forceinline__ float dsilu_fast(float x) {
+  const float s = sigmoid_fast(x);
+  return s * fmaf(x, 1.0f - s, 1.0f);
+}
+__device__ __forceinline__ float dsilu_exact(float x) {
+  const float s = 1.0f / (1.0f + __expf(-x));
+  return s * fmaf(x, 1.0f - s, 1.0f);
+}
+__device__ __forceinline__ void unpack8(const uint4& v, float (&f)[8]) {
+  const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const float2 t = unpack_bf16x2(w[j]);
+    f[2 * j] = t.x; f[2 * j + 1] = t.y;
+  }
+}
+__device__ __forceinline__ uint4 pack8(const float (&f)[8]) {
+  return make_uint4(pack_bf16x2(f[0], f[1]), pack_bf16x2(f[2], f[3]), pack_bf16x2(f[4], f[5]), pack_bf16x2(f[6], f[7]));
+}
+
+// Per-(sample, channel) sums of a thread's 8 channels: every thread of a block owns the 8 channels starting at
+// (threadIdx.x * 8) % C for all items it visits (blockDim * 8 is a multiple of C).  Fixed-order block reduction, then one
+// double atomicAdd per (channel, value) per block.
+template <int NV>
+__device__ __forceinline__ void block_channel_sums(float (&acc)[NV][8], double* dst /* [C][NV] of this sample */, int C, float* s_part) {
+  // s_part: [blockDim][NV * 8]
+  float* mine = s_part + threadIdx.x * (NV * 8);
+#pragma unroll
+  for (int v = 0; v < NV; ++v)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) mine[v * 8 + j] = acc[v][j];
+  __syncthreads();
+  const int chunks = C >> 3;   // distinct 8-channel chunks; thread t owns chunk t % chunks
+  for (int o = threadIdx.x; o < C * NV; o += blockDim.x) {
+    const int c = o / NV, v = o - c * NV;
+    const int chunk = c >> 3, j = c & 7;
+    float s = 0.f;
+    for (int t = chunk; t < (int)blockDim.x; t += chunks) s += s_part[t * (NV * 8) + v * 8 + j];
+    atomicAdd(dst + (int64_t)c * NV + v, (double)s);
+  }
+}
+
+struct GnBwdArgs {
+  const __nv_bfloat16* g;    // gradient at the GroupNorm output (type B) / at the SiLU output (type A)
+  const __nv_bfloat16* z;    // type A: the GroupNorm input x;  type B: the pre-activation u (GroupNorm input is silu(u))
+  const __nv_bfloat16* add;  // optional tensor added to the result (type A: the residual-path gradient)
+  __nv_bfloat16* out;
+  const double* stats;       // [B][8][2] (sum, sumsq) of the GroupNorm input
+  double* R;                 // [B][C][2]: sum over positions of gh, gh * (GroupNorm input)
+  double* sums_out;          // optional [B][C]: sum over positions of out (type B: d bias / d temb)
+  const float* gamma;
+  const float* beta;
+  int64_t per_sample;
+  int C;
+  int type;                  // 0 = A: y = silu(gn(x));  1 = B: y = gn(silu(u))
+  float eps;
+};
+
+__device__ __forceinline__ void gn_group_stats(const double* stats, int b, int g, double n, float eps, float& mean, float& rstd) {
+  const double m = stats[(b * 8 + g) * 2] / n;
+  double var = stats[(b * 8 + g) * 2 + 1] / n - m * m;
+  if (var < 0) var = 0;
+  mean = (float)m;
+  rstd = (float)(1.0 / sqrt(var + (double)eps));
+}
+
+// Pass 1: R[b][c] = (sum gh, sum gh * zin) with  A: gh = g * silu'(gn(x)), zin = x;   B: gh = g, zin = silu(u)
+__global__ void __launch_bounds__(256) gn_bwd_reduce_kernel(const GnBwdArgs a) {
+  extern __shared__ float s_dyn[];
+  __shared__ float s_scale[256], s_shift[256];
+  const int b = blockIdx.y, C = a.C, cg = C >> 3;
+  if (a.type == 0 && threadIdx.x < C) {
+    const int c = threadIdx.x;
+    float mean, rstd;
+    gn_group_stats(a.stats, b, c / cg, (double)(a.per_sample / 8), a.eps, mean, rstd);
+    const float sc = a.gamma[c] * rstd;
+    s_scale[c] = sc;
+    s_shift[c] = (a.beta ? a.beta[c] : 0.f) - mean * sc;
+  }
+  __syncthreads();
+  const int c0 = (threadIdx.x * 8) % C;
+  float sc[8], sh[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) { sc[j] = a.type == 0 ? s_scale[c0 + j] : 1.f; sh[j] = a.type == 0 ? s_shift[c0 + j] : 0.f; }
+  const int64_t items = a.per_sample / 8;
+  const uint4* gp = reinterpret_cast<const uint4*>(a.g + (int64_t)b * a.per_sample);
+  const uint4* zp = reinterpret_cast<const uint4*>(a.z + (int64_t)b * a.per_sample);
+  float acc[2][8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) { acc[0][j] = 0.f; acc[1][j] = 0.f; }
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < items; i += (int64_t)gridDim.x * blockDim.x) {
+    float g[8], z[8];
+    unpack8(ldg_nc_v4(gp + i), g);
+    unpack8(ldg_nc_v4(zp + i), z);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float gh, zin;
+      if (a.type == 0) { gh = g[j] * dsilu_fast(fmaf(z[j], sc[j], sh[j])); zin = z[j]; }
+      else { gh = g[j]; zin = silu_fast(z[j]); }
+      acc[0][j] += gh;
+      acc[1][j] = fmaf(gh, zin, acc[1][j]);
+    }
+  }
+  block_channel_sums<2>(acc, a.R + (int64_t)b * C * 2, C, s_dyn);
+}
+
+// Pass 2: the GroupNorm input gradient  dzin = A_c gh + B_g zin + C_g  (A_c = rstd gamma_c, B_g = -rstd^2 k2, C_g = rstd (rstd mean k2 - k1),
+// k1 = mean_group(gamma gh), k2 = mean_group(gamma gh zhat)), then  A: out = dzin + add;   B: out = dzin * silu'(u), sums of out.
+__global__ void __launch_bounds__(256) gn_bwd_apply_kernel(const GnBwdArgs a) {
+  extern __shared__ float s_dyn[];
+  __shared__ float s_scale[256], s_shift[256], s_A[256], s_k[256][2], s_B[8], s_C[8];
+  const int b = blockIdx.y, C = a.C, cg = C >> 3;
+  const double n = (double)(a.per_sample / 8);
+  if (threadIdx.x < C) {
+    const int c = threadIdx.x;
+    float mean, rstd;
+    gn_group_stats(a.stats, b, c / cg, n, a.eps, mean, rstd);
+    const float gm = a.gamma[c];
+    const double r0 = a.R[((int64_t)b * C + c) * 2], r1 = a.R[((int64_t)b * C + c) * 2 + 1];
+    s_k[c][0] = (float)(gm * r0 / n);
+    s_k[c][1] = (float)(gm * (double)rstd * (r1 - (double)mean * r0) / n);
+    s_A[c] = rstd * gm;
+    s_scale[c] = gm * rstd;
+    s_shift[c] = (a.beta ? a.beta[c] : 0.f) - mean * gm * rstd;
+  }
+  __syncthreads();
+  if (threadIdx.x < 8) {
+    const int g = threadIdx.x;
+    float k1 = 0.f, k2 = 0.f;
+    for (int c = g * cg; c < (g + 1) * cg; ++c) { k1 += s_k[c][0]; k2 += s_k[c][1]; }
+    float mean, rstd;
+    gn_group_stats(a.stats, b, g, n, a.eps, mean, rstd);
+    s_B[g] = -rstd * rstd * k2;
+    s_C[g] = rstd * (rstd * mean * k2 - k1);
+  }
+  __syncthreads();
+  const int c0 = (threadIdx.x * 8) % C;
+  float sc[8], sh[8], cA[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) { sc[j] = s_scale[c0 + j]; sh[j] = s_shift[c0 + j]; cA[j] = s_A[c0 + j]; }
+  // group width is a multiple of 4: channels c0..c0+3 and c0+4..c0+7 each lie in one group
+  const float cB0 = s_B[c0 / cg], cC0 = s_C[c0 / cg], cB1 = s_B[(c0 + 4) / cg], cC1 = s_C[(c0 + 4) / cg];
+  const int64_t items = a.per_sample / 8;
+  const uint4* gp = reinterpret_cast<const uint4*>(a.g + (int64_t)b * a.per_sample);
+  const uint4* zp = reinterpret_cast<const uint4*>(a.z + (int64_t)b * a.per_sample);
+  const uint4* ap = a.add ? reinterpret_cast<const uint4*>(a.add + (int64_t)b * a.per_sample) : nullptr;
+  uint4* op = reinterpret_cast<uint4*>(a.out + (int64_t)b * a.per_sample);
+  float acc[1][8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) acc[0][j] = 0.f;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < items; i += (int64_t)gridDim.x * blockDim.x) {
+    float g[8], z[8], ad[8], o[8];
+    unpack8(ldg_nc_v4(gp + i), g);
+    unpack8(ldg_nc_v4(zp + i), z);
+    if (ap) unpack8(ldg_nc_v4(ap + i), ad);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float cB = j < 4 ? cB0 : cB1, cC = j < 4 ? cC0 : cC1;
+      if (a.type == 0) {
+        const float gh = g[j] * dsilu_fast(fmaf(z[j], sc[j], sh[j]));
+        o[j] = fmaf(cA[j], gh, fmaf(cB, z[j], cC));
+      } else {
+        const float zin = silu_fast(z[j]);
+        o[j] = fmaf(cA[j], g[j], fmaf(cB, zin, cC)) * dsilu_fast(z[j]);
+      }
+      if (ap) o[j] += ad[j];
+    }
+    const uint4 ov = pack8(o);
+    stg_v4(op + i, ov);
+    if (a.sums_out) {
+      float r[8];
+      unpack8(ov, r);   // sums of the STORED (bf16) values: what the weight-gradient GEMM of the same tensor sees
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[0][j] += r[j];
+    }
+  }
+  if (a.sums_out) block_channel_sums<1>(acc, a.sums_out + (int64_t)b * C, C, s_dyn);
+}
+
+// d gamma[c] += sum_b rstd (R1 - mean R0);  d beta[c] += sum_b R0
+__global__ void gn_bwd_param_kernel(const double* __restrict__ R, const double* __restrict__ stats, float* __restrict__ dgamma,
+                                    float* __restrict__ dbeta, int B, int C, double n, float eps) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  const int g = c / (C >> 3);
+  double dg = 0, db = 0;
+  for (int b = 0; b < B; ++b) {
+    float mean, rstd;
+    gn_group_stats(stats, b, g, n, eps, mean, rstd);
+    const double r0 = R[((int64_t)b * C + c) * 2], r1 = R[((int64_t)b * C + c) * 2 + 1];
+    dg += (double)rstd * (r1 - (double)mean * r0);
+    db += r0;
+  }
+  dgamma[c] += (float)dg;
+  if (dbeta) dbeta[c] += (float)db;
+}
+
+int gn_bwd_grid(int64_t per_sample, int B, int threads) {
+  const int64_t items = per_sample / 8;
+  int64_t bx = (items + threads * 4 - 1) / (threads * 4);
+  const int64_t cap = (int64_t)ddimb_num_sms() * 8 / B + 1;
+  if (bx > cap) bx = cap;
+  return bx < 1 ? 1 : (int)bx;
+}
+
+}  // namespace
+
+// type 0 (A): y = silu(gn(x)): g = dL/dy, z = x.   type 1 (B): y = gn(silu(u)): g = dL/dy, z = u.
+// R is double [B][C][2], zeroed by the caller.
+extern "C" int ddimb_gn_bwd_reduce(const void* g, const void* z, const double* stats, const float* gamma, const float* beta, double* R,
+                                   int type, int B, long long positions, int C, float eps, cudaStream_t stream) {
+  DDIMB_CHECK_ARG(g && z && stats && gamma && R && B >= 1 && positions >= 1 && C % 32 == 0 && C <= 256 && (type == 0 || type == 1));
+  DDIMB_PROF(stream, "gn_bwd_reduce", C, type, 4.0 * B * positions * C, 0.0);
+  GnBwdArgs a = {};
+  a.g = reinterpret_cast<const __nv_bfloat16*>(g); a.z = reinterpret_cast<const __nv_bfloat16*>(z);
+  a.stats = stats; a.R = R; a.gamma = gamma; a.beta = beta; a.per_sample = positions * C; a.C = C; a.type = type; a.eps = eps;
+  const int threads = (C % 96 == 0) ? 192 : 256;
+  gn_bwd_reduce_kernel<<<dim3(gn_bwd_grid(a.per_sample, B, threads), B), threads, threads * 16 * sizeof(float), stream>>>(a);
+  DDIMB_LAUNCH_CHECK();
+  return DDIMB_OK;
+}
+
+// out = gradient w.r.t. x (type A, + add) or w.r.t. u (type B); sums_out (nullable, double [B][C], zeroed by the caller)
+// receives the per-(sample, channel) sums of out.
+extern "C" int ddimb_gn_bwd_apply(const void* g, const void* z, const void* add, void* out, const double* stats, const double* R,
+                                  const float* gamma, const float* beta, double* sums_out, int type, int B, long long positions, int C,
+                                  float eps, cudaStream_t stream) {
+  DDIMB_CHECK_ARG(g && z && out && stats && gamma && R && B >= 1 && positions >= 1 && C % 32 == 0 && C <= 256 && (type == 0 || type == 1));
+  DDIMB_PROF(stream, "gn_bwd_apply", C, type, 2.0 * B * positions * C * (add ? 4 : 3), 0.0);
+  GnBwdArgs a = {};
+  a.g = reinterpret_cast<const __nv_bfloat16*>(g); a.z = reinterpret_cast<const __nv_bfloat16*>(z);
+  a.add = reinterpret_cast<const __nv_bfloat16*>(add); a.out = reinterpret_cast<__nv_bfloat16*>(out);
+  a.stats = stats; a.R = const_cast<double*>(R); a.sums_out = sums_out; a.gamma = gamma; a.beta = beta;
+  a.per_sample = positions * C; a.C = C; a.type = type; a.eps = eps;
+  const int threads = (C % 96 == 0) ? 192 : 256;
+  gn_bwd_apply_kernel<<<dim3(gn_bwd_grid(a.per_sample, B, threads), B), threads, threads * 8 * sizeof(float), stream>>>(a);
+  DDIMB_LAUNCH_CHECK();
+  return DDIMB_OK;
+}
+
+// dgamma / dbeta (fp32 [C], ACCUMULATED) of one GroupNorm from R and the forward statistics; dbeta nullable (norm[2] has no bias).
+extern "C" int ddimb_gn_bwd_param(const double* R, const double* stats, float* dgamma, float* dbeta, int B, long long positions, int C,
+                                  float eps, cudaStream_t stream) {
+  DDIMB_CHECK_ARG(R && stats && dgamma && B >= 1 && C % 8 == 0);
+  DDIMB_PROF(stream, "gn_bwd_param", C, 0, 16.0 * B * C, 0.0);
+  gn_bwd_param_kernel<<<(C + 63) / 64, 64, 0, stream>>>(R, stats, dgamma, dbeta, B, C, (double)positions * (C / 8), eps);
+  DDIMB_LAUNCH_CHECK();
+  return DDIMB_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ column sums (bias gradients)
+// out[c] += sum_r x[r][c]; x is bf16 or fp32 [rows][ld].  Grid-stride over row blocks, one fp32 atomicAdd per column per block.
+template <typename T>
+__global__ void __launch_bounds__(256) colsum_kernel(const T* __restrict__ x, int64_t ld, int64_t rows, int C, float* __restrict__ out,
+                                                     int rows_per_block) {
+  const int64_t r0 = (int64_t)blockIdx.x * rows_per_block;
+  const int64_t r1 = r0 + rows_per_block < rows ? r0 + rows_per_block : rows;
+  for (int c = blockIdx.y * blockDim.x + threadIdx.x; c < C; c += gridDim.y * blockDim.x) {
+    float s = 0.f;
+    for (int64_t r = r0; r < r1; ++r) {
+      if constexpr (sizeof(T) == 2) s += __bfloat162float(x[r * ld + c]);
+      else s += x[r * ld + c];
+    }
+    atomicAdd(out + c, s);
+  }
+}
+
+extern "C" int ddimb_colsum(const void* x, int is_bf16, long long ld, long long rows, int C, float* out, cudaStream_t stream) {
+  DDIMB_CHECK_ARG(x && out && rows >= 1 && C >= 1 && ld >= C);
+  DDIMB_PROF(stream, "colsum", C, is_bf16, (double)rows * C * (is_bf16 ? 2 : 4), 0.0);
+  int rpb = (int)((rows + 4 * ddimb_num_sms() - 1) / (4 * ddimb_num_sms()));
+  if (rpb < 8) rpb = 8;
+  const dim3 grid((unsigned)((rows + rpb - 1) / rpb), (unsigned)((C + 255) / 256));
+  if (is_bf16) colsum_kernel<__nv_bfloat16><<<grid, 256, 0, stream>>>(reinterpret_cast<const __nv_bfloat16*>(x), ld, rows, C, out, rpb);
+  else colsum_kernel<float><<<grid, 256, 0, stream>>>(reinterpret_cast<const float*>(x), ld, rows, C, out, rpb);
+  DDIMB_LAUNCH_CHECK();
+  return DDIMB_OK;
+}
+
+// double [B][C] per-sample sums -> fp32: out_b[b * ldb + c] += s (the temb slice gradient) and / or out_c[c] += sum_b s (a bias gradient)
+__global__ void sums_scatter_kernel(const double* __restrict__ s, float* __restrict__ out_b, int64_t ldb, float* __restrict__ out_c, int B, int C) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  double tot = 0;
+  for (int b = 0; b < B; ++b) {
+    const double v = s[(int64_t)b * C + c];
+    tot += v;
+    if (out_b) out_b[(int64_t)b * ldb + c] += (float)v;
+  }
+  if (out_c) out_c[c] += (float)tot;
+}
+
+extern "C" int ddimb_sums_scatter(const double* sums, float* out_b, long long ldb, float* out_c, int B, int C, cudaStream_t stream) {
+  DDIMB_CHECK_ARG(sums && (out_b || out_c) && B >= 1 && C >= 1);
+  DDIMB_PROF(stream, "sums_scatter", C, 0, 8.0 * B * C, 0.0);
+  sums_scatter_kernel<<<(C + 63) / 64, 64, 0, stream>>>(sums, out_b, ldb, out_c, B, C);
+  DDIMB_LAUNCH_CHECK();
+  return DDIMB_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ LayerNorm(512) backward
+// forward (hf modeling_fnet.py:180-188,226-231): y = LN(a + b).  dy = dy1 + dy2 (dy2 nullable).  One warp per row recomputes
+// mean / rstd, writes ds = dL/d(a+b) as fp32 and as bf16 operand planes (hi | lo), accumulates dgamma / dbeta.
+__global__ void __launch_bounds__(256) layernorm512_bwd_kernel(const float* __restrict__ a, const float* __restrict__ b2,
+                                                               const float* __restrict__ dy1, const float* __restrict__ dy2,
+                                                               const float* __restrict__ gamma, float* __restrict__ ds,
+                                                               __nv_bfloat16* __restrict__ dsbf, int64_t ldy, int write_lo,
+                                                               float* __restrict__ dgamma, float* __restrict__ dbeta, int rows, float eps) {
+  constexpr int H = 512;
+  const int lane = threadIdx.x & 31;
+  const int wpb = blockDim.x >> 5;
+  const float4* gp = reinterpret_cast<const float4*>(gamma);
+  float4 gm[4], dgacc[4], dbacc[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) { gm[j] = gp[j * 32 + lane]; dgacc[j] = make_float4(0, 0, 0, 0); dbacc[j] = make_float4(0, 0, 0, 0); }
+  for (int row = blockIdx.x * wpb + (threadIdx.x >> 5); row < rows; row += gridDim.x * wpb) {
+    const float4* ap = reinterpret_cast<const float4*>(a + (int64_t)row * H);
+    const float4* bp = b2 ? reinterpret_cast<const float4*>(b2 + (int64_t)row * H) : nullptr;
+    const float4* d1 = reinterpret_cast<const float4*>(dy1 + (int64_t)row * H);
+    const float4* d2 = dy2 ? reinterpret_cast<const float4*>(dy2 + (int64_t)row * H) : nullptr;
+    float4 v[4], d[4];
+    float sum = 0.f;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      v[j] = ap[j * 32 + lane];
+      if (bp) { const float4 t = bp[j * 32 + lane]; v[j].x += t.x; v[j].y += t.y; v[j].z += t.z; v[j].w += t.w; }
+      d[j] = d1[j * 32 + lane];
+      if (d2) { const float4 t = d2[j * 32 + lane]; d[j].x += t.x; d[j].y += t.y; d[j].z += t.z; d[j].w += t.w; }
+      sum += v[j].x + v[j].y + v[j].z + v[j].w;
+    }
+    const float mean = warp_sum(sum) / H;
+    float sq = 0.f;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      v[j].x -= mean; v[j].y -= mean; v[j].z -= mean; v[j].w -= mean;
+      sq += v[j].x * v[j].x + v[j].y * v[j].y + v[j].z * v[j].z + v[j].w * v[j].w;
+    }
+    const float rstd = rsqrtf(warp_sum(sq) / H + eps);
+    float m1 = 0.f, m2 = 0.f;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      v[j].x *= rstd; v[j].y *= rstd; v[j].z *= rstd; v[j].w *= rstd;   // v = xhat
+      dgacc[j].x = fmaf(d[j].x, v[j].x, dgacc[j].x); dgacc[j].y = fmaf(d[j].y, v[j].y, dgacc[j].y);
+      dgacc[j].z = fmaf(d[j].z, v[j].z, dgacc[j].z); dgacc[j].w = fmaf(d[j].w, v[j].w, dgacc[j].w);
+      dbacc[j].x += d[j].x; dbacc[j].y += d[j].y; dbacc[j].z += d[j].z; dbacc[j].w += d[j].w;
+      d[j].x *= gm[j].x; d[j].y *= gm[j].y; d[j].z *= gm[j].z; d[j].w *= gm[j].w;   // d = dxhat
+      m1 += d[j].x + d[j].y + d[j].z + d[j].w;
+      m2 += d[j].x * v[j].x + d[j].y * v[j].y + d[j].z * v[j].z + d[j].w * v[j].w;
+    }
+    m1 = warp_sum(m1) / H;
+    m2 = warp_sum(m2) / H;
+    float4* op = reinterpret_cast<float4*>(ds + (int64_t)row * H);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      float4 o;
+      o.x = rstd * (d[j].x - m1 - v[j].x * m2); o.y = rstd * (d[j].y - m1 - v[j].y * m2);
+      o.z = rstd * (d[j].z - m1 - v[j].z * m2); o.w = rstd * (d[j].w - m1 - v[j].w * m2);
+      op[j * 32 + lane] = o;
+      if (dsbf) {
+        const uint32_t h0 = pack_bf16x2(o.x, o.y), h1 = pack_bf16x2(o.z, o.w);
+        *reinterpret_cast<uint2*>(dsbf + (int64_t)row * ldy + (j * 32 + lane) * 4) = make_uint2(h0, h1);
+        if (write_lo) {
+          const float2 f0 = unpack_bf16x2(h0), f1 = unpack_bf16x2(h1);
+          *reinterpret_cast<uint2*>(dsbf + (int64_t)row * ldy + H + (j * 32 + lane) * 4) =
+              make_uint2(pack_bf16x2(o.x - f0.x, o.y - f0.y), pack_bf16x2(o.z - f1.x, o.w - f1.y));
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const int c = (j * 32 + lane) * 4;
+    atomicAdd(dgamma + c, dgacc[j].x); atomicAdd(dgamma + c + 1, dgacc[j].y); atomicAdd(dgamma + c + 2, dgacc[j].z); atomicAdd(dgamma + c + 3, dgacc[j].w);
+    atomicAdd(dbeta + c, dbacc[j].x); atomicAdd(dbeta + c + 1, dbacc[j].y); atomicAdd(dbeta + c + 2, dbacc[j].z); atomicAdd(dbeta + c + 3, dbacc[j].w);
+  }
+}
+
+extern "C" int ddimb_layernorm512_bwd(const float* a, const float* b, const float* dy1, const float* dy2, const float* gamma, float* ds,
+                                      void* dsbf, long long ldy, int write_lo, float* dgamma, float* dbeta, int rows, float eps,
+                                      cudaStream_t stream) {
+  DDIMB_CHECK_ARG(a && dy1 && gamma && ds && dgamma && dbeta && rows >= 1);
+  DDIMB_CHECK_ARG(!dsbf || (ldy % 4 == 0 && ldy >= (write_lo ? 1024 : 512)));
+  DDIMB_PROF(stream, "layernorm512_bwd", write_lo, 0, 512.0 * rows * 4.0 * (2 + (b ? 1 : 0) + (dy2 ? 1 : 0)), 0.0);
+  int blocks = (rows + 7) / 8;
+  if (blocks > 2 * ddimb_num_sms()) blocks = 2 * ddimb_num_sms();
+  layernorm512_bwd_kernel<<<blocks, 256, 0, stream>>>(a, b, dy1, dy2, gamma, ds, reinterpret_cast<__nv_bfloat16*>(dsbf), ldy, write_lo, dgamma,
+                                                      dbeta, rows, eps);
+  DDIMB_LAUNCH_CHECK();
+  return DDIMB_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ gelu_new forward / backward (bf16)
+// training keeps the pre-activation u (hf activations.py:59-66): act = gelu_new(u);  du = dact * gelu_new'(u)
+__global__ void __launch_bounds__(256) gelu_kernel(const uint4* __restrict__ u, const uint4* __restrict__ dact, uint4* __restrict__ out, int64_t n8) {
+  const float k = 0.7978845608028654f;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n8; i += (int64_t)gridDim.x * blockDim.x) {
+    float x[8], o[8];
+    unpack8(u[i], x);
+    if (dact == nullptr) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o[j] = gelu_new_fast(x[j]);
+    } else {
+      float g[8];
+      unpack8(dact[i], g);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float x2 = x[j] * x[j];
+        const float th = tanh_approx(k * fmaf(0.044715f * x[j], x2, x[j]));
+        const float d = 0.5f * (1.0f + th) + 0.5f * x[j] * (1.0f - th * th) * k * fmaf(3.0f * 0.044715f, x2, 1.0f);
+        o[j] = g[j] * d;
+      }
+    }
+    out[i] = pack8(o);
+  }
+}
+
+extern "C" int ddimb_gelu(const void* u, const void* dact, void* out, long long n, cudaStream_t stream) {
+  DDIMB_CHECK_ARG(u && out && n > 0 && n % 8 == 0);
+  DDIMB_PROF(stream, "gelu", dact ? 1 : 0, 0, 2.0 * n * (dact ? 3 : 2), 0.0);
+  int64_t blocks = (n / 8 + 255) / 256;
+  if (blocks > 8LL * ddimb_num_sms()) blocks = 8LL * ddimb_num_sms();
+  gelu_kernel<<<(int)blocks, 256, 0, stream>>>(reinterpret_cast<const uint4*>(u), reinterpret_cast<const uint4*>(dact), reinterpret_cast<uint4*>(out), n / 8);
+  DDIMB_LAUNCH_CHECK();
+  return DDIMB_OK;
+}
+
+// fp32 (a [+ b]) -> bf16 hi (+ lo) operand planes [rows][ldy]; optional in-place-safe fp32 sum output
+__global__ void __launch_bounds__(256) add_split_kernel(const float4* __restrict__ a, const float4* __restrict__ b, float4* __restrict__ sum_out,
+                                                        __nv_bfloat16* __restrict__ ybf, int64_t ldy, int H, int write_lo, int64_t n4) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
+    float4 o = a[i];
+    if (b) { const float4 t = b[i]; o.x += t.x; o.y += t.y; o.z += t.z; o.w += t.w; }
+    if (sum_out) sum_out[i] = o;
+    const int64_t row = (i * 4) / H, col = (i * 4) % H;
+    const uint32_t h0 = pack_bf16x2(o.x, o.y), h1 = pack_bf16x2(o.z, o.w);
+    *reinterpret_cast<uint2*>(ybf + row * ldy + col) = make_uint2(h0, h1);
+    if (write_lo) {
+      const float2 f0 = unpack_bf16x2(h0), f1 = unpack_bf16x2(h1);
+      *reinterpret_cast<uint2*>(ybf + row * ldy + H + col) = make_uint2(pack_bf16x2(o.x - f0.x, o.y - f0.y), pack_bf16x2(o.z - f1.x, o.w - f1.y));
+    }
+  }
+}
+
+extern "C" int ddimb_add_split_bf16(const float* a, const float* b, float* sum_out, void* ybf, long long ldy, int H, int write_lo, long long rows,
+                                    cudaStream_t stream) {
+  DDIMB_CHECK_ARG(a && ybf && rows >= 1 && H % 4 == 0 && ldy % 4 == 0);
+  DDIMB_PROF(stream, "add_split_bf16", H, write_lo, (double)rows * H * (4.0 * (b ? 2 : 1) + (write_lo ? 4.0 : 2.0)), 0.0);
+  const int64_t n4 = rows * H / 4;
+  int64_t blocks = (n4 + 255) / 256;
+  if (blocks > 8LL * ddimb_num_sms()) blocks = 8LL * ddimb_num_sms();
+  add_split_kernel<<<(int)blocks, 256, 0, stream>>>(reinterpret_cast<const float4*>(a), reinterpret_cast<const float4*>(b),
+                                                    reinterpret_cast<float4*>(sum_out), reinterpret_cast<__nv_bfloat16*>(ybf), ldy, H, write_lo, n4);
+  DDIMB_LAUNCH_CHECK();
+  return DDIMB_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ dropout (13 sites of the FNet branch)
+// reference models/diffusion.py:129,144 and hf modeling_fnet.py:226-231 (nn.Dropout(0.1), training only).  Counter-based mask:
+// keep(i) = hash(seed, i) >= p * 2^32; y = x * keep / (1 - p).  Backward applies the same call to the gradient.
+__device__ __forceinline__ uint32_t mix32(uint64_t x) {
+  x ^= x >> 33; x *= 0xff51afd7ed558ccdULL; x ^= x >> 33; x *= 0xc4ceb9fe1a85ec53ULL; x ^= x >> 33;
+  return (uint32_t)x;
+}
+__global__ void __launch_bounds__(256) dropout_kernel(const float* __restrict__ x, float* __restrict__ y, int64_t n, uint32_t thresh, float scale,
+                                                      uint64_t seed) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    y[i] = mix32(seed + (uint64_t)i * 0x9E3779B97F4A7C15ULL) >= thresh ? x[i] * scale : 0.f;
+}
+
+extern "C" int ddimb_dropout(const float* x, float* y, long long n, float p, unsigned long long seed, cudaStream_t stream) {
+  DDIMB_CHECK_ARG(x && y && n > 0 && p >= 0.f && p < 1.f);
+  DDIMB_PROF(stream, "dropout", 0, 0, 8.0 * n, 0.0);
+  int64_t blocks = (n + 255) / 256;
+  if (blocks > 8LL * ddimb_num_sms()) blocks = 8LL * ddimb_num_sms();
+  dropout_kernel<<<(int)blocks, 256, 0, stream>>>(x, y, n, (uint32_t)((double)p * 4294967296.0), 1.0f / (1.0f - p), seed);
+  DDIMB_LAUNCH_CHECK();
+  return DDIMB_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ token path backward
+// forward (models/diffusion.py:273-275,130-142): v = permute(x)[row][c*W+f] + te[s]; tok = LN_D(v) (D = C*W).
+// dtok fp32 [B*S][D] -> dx bf16 NHWC [B][S][W][C] (+ add: the gradient of the additive skip that reads the same tensor,
+// models/diffusion.py:284), dgamma / dbeta accumulated.  One CTA of C threads per token, as the forward kernel.
+template <int W>
+__global__ void __launch_bounds__(256) tokens_ln_bwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ te,
+                                                            const float* __restrict__ gamma, const float* __restrict__ dtok,
+                                                            const __nv_bfloat16* __restrict__ add, __nv_bfloat16* __restrict__ dx,
+                                                            float* __restrict__ dgamma, float* __restrict__ dbeta, int S, int C, float eps) {
+  const int row = blockIdx.x, s = row % S, c = threadIdx.x;
+  const int D = C * W;
+  __shared__ float red[4][8];
+  float v[W], d[W];
+  const __nv_bfloat16* xp = x + (int64_t)row * W * C;
+  const float* tp = te + (int64_t)s * D + c * W;
+  const float* dp = dtok + (int64_t)row * D + c * W;
+  float sum = 0.f;
+#pragma unroll
+  for (int f = 0; f < W; ++f) { v[f] = __bfloat162float(xp[f * C + c]) + tp[f]; sum += v[f]; d[f] = dp[f]; }
+  const int nw = C >> 5;
+  auto block_sum = [&](float val, int slot) {
+    val = warp_sum(val);
+    if ((c & 31) == 0) red[slot][c >> 5] = val;
+    __syncthreads();
+    float t = 0.f;
+    for (int i = 0; i < nw; ++i) t += red[slot][i];
+    return t;
+  };
+  const float mean = block_sum(sum, 0) / D;
+  float sq = 0.f;
+#pragma unroll
+  for (int f = 0; f < W; ++f) { v[f] -= mean; sq = fmaf(v[f], v[f], sq); }
+  const float rstd = rsqrtf(block_sum(sq, 1) / D + eps);
+  float m1 = 0.f, m2 = 0.f;
+#pragma unroll
+  for (int f = 0; f < W; ++f) {
+    v[f] *= rstd;                                   // xhat
+    atomicAdd(dgamma + c * W + f, d[f] * v[f]);
+    atomicAdd(dbeta + c * W + f, d[f]);
+    d[f] *= gamma[c * W + f];                       // dxhat
+    m1 += d[f]; m2 = fmaf(d[f], v[f], m2);
+  }
+  m1 = block_sum(m1, 2) / D;
+  m2 = block_sum(m2, 3) / D;
+  __nv_bfloat16* op = dx + (int64_t)row * W * C;
+  const __nv_bfloat16* ap = add ? add + (int64_t)row * W * C : nullptr;
+#pragma unroll
+  for (int f = 0; f < W; ++f) {
+    float o = rstd * (d[f] - m1 - v[f] * m2);
+    if (ap) o += __bfloat162float(ap[f * C + c]);
+    op[f * C + c] = __float2bfloat16_rn(o);
+  }
+}
+
+extern "C" int ddimb_tokens_ln_bwd(const void* x, const float* te, const float* gamma, const float* dtok, const void* add, void* dx,
+                                   float* dgamma, float* dbeta, int B, int S, int W, int C, float eps, cudaStream_t stream) {
+  DDIMB_CHECK_ARG(x && te && gamma && dtok && dx && dgamma && dbeta && W == 8 && C % 32 == 0 && C <= 256);
+  DDIMB_PROF(stream, "tokens_ln_bwd", C, W, (double)B * S * W * C * (2.0 + 4.0 + 2.0 + (add ? 2.0 : 0.0)), 0.0);
+  tokens_ln_bwd_kernel<8><<<B * S, C, 0, stream>>>(reinterpret_cast<const __nv_bfloat16*>(x), te, gamma, dtok,
+                                                    reinterpret_cast<const __nv_bfloat16*>(add), reinterpret_cast<__nv_bfloat16*>(dx), dgamma, dbeta, S, C, eps);
+  DDIMB_LAUNCH_CHECK();
+  return DDIMB_OK;
+}
+
+// backward of models/diffusion.py:277-279: gradient NHWC bf16 [B][S][W][C] -> token-major bf16 [B*S][C*W] (GEMM operand)
+template <int W>
+__global__ void __launch_bounds__(256) nhwc_to_tokens_kernel(const __nv_bfloat16* __restrict__ g, __nv_bfloat16* __restrict__ tok, int C) {
+  const int row = blockIdx.x, c = threadIdx.x;
+  const __nv_bfloat16* gp = g + (int64_t)row * W * C;
+  float v[W];
+#pragma unroll
+  for (int f = 0; f < W; ++f) v[f] = __bfloat162float(gp[f * C + c]);
+  uint32_t o[W / 2];
+#pragma unroll
+  for (int f = 0; f < W; f += 2) o[f >> 1] = pack_bf16x2(v[f], v[f + 1]);
+  uint4* op = reinterpret_cast<uint4*>(tok + (int64_t)row * C * W + c * W);
+#pragma unroll
+  for (int i = 0; i < W / 8; ++i) stg_v4(op + i, make_uint4(o[4 * i], o[4 * i + 1], o[4 * i + 2], o[4 * i + 3]));
+}
+
+extern "C" int ddimb_nhwc_to_tokens(const void* g, void* tok, int B, int S, int W, int C, cudaStream_t stream) {
+  DDIMB_CHECK_ARG(g && tok && W == 8 && C % 32 == 0 && C <= 256);
+  DDIMB_PROF(stream, "nhwc_to_tokens", C, W, (double)B * S * W * C * 4.0, 0.0);
+  nhwc_to_tokens_kernel<8><<<B * S, C, 0, stream>>>(reinterpret_cast<const __nv_bfloat16*>(g), reinterpret_cast<__nv_bfloat16*>(tok), C);
+  DDIMB_LAUNCH_CHECK();
+  return DDIMB_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ temb MLP backward (fp32, B rows)
+// forward (models/diffusion.py:107-120) as run in training: z1 = L0(te[t]); z2 = L1(silu(z1)); temb = L2(silu(z2)).
+// dw[n][k] += sum_r g[r][n] * f(in[row(r)][k]),  db[n] += sum_r g[r][n];  f = SiLU when in_act.
+__global__ void __launch_bounds__(512) linear_small_wgrad_kernel(const float* __restrict__ g, const float* __restrict__ in,
+                                                                const int64_t* __restrict__ idx, float* __restrict__ dw,
+                                                                float* __restrict__ db, int rows, int K, int N, int in_act) {
+  const int n = blockIdx.x;
+  float bsum = 0.f;
+  for (int k = threadIdx.x; k < K; k += blockDim.x) {
+    float acc = 0.f;
+    for (int r = 0; r < rows; ++r) {
+      float iv = in[(idx ? idx[r] : (int64_t)r) * K + k];
+      if (in_act) iv = silu_exact(iv);
+      acc = fmaf(g[(int64_t)r * N + n], iv, acc);
+    }
+    dw[(int64_t)n * K + k] += acc;
+  }
+  if (threadIdx.x == 0) {
+    for (int r = 0; r < rows; ++r) bsum += g[(int64_t)r * N + n];
+    db[n] += bsum;
+  }
+}
+
+extern "C" int ddimb_linear_small_wgrad(const float* g, const float* in, const long long* idx, float* dw, float* db, int rows, int K, int N,
+                                        int in_act, cudaStream_t stream) {
+  DDIMB_CHECK_ARG(g && in && dw && db && rows >= 1 && K >= 1 && N >= 1);
+  DDIMB_PROF(stream, "linear_small_wgrad", N, K, 4.0 * ((double)N * K + (double)rows * (K + N)), 2.0 * rows * N * K);
+  linear_small_wgrad_kernel<<<N, K < 512 ? K : 512, 0, stream>>>(g, in, reinterpret_cast<const int64_t*>(idx), dw, db, rows, K, N, in_act);
+  DDIMB_LAUNCH_CHECK();
+  return DDIMB_OK;
+}
+
+// out[r][k] = (z ? silu'(z[r][k]) : 1) * sum_n g[r][n] * w[n][k]
+__global__ void __launch_bounds__(512) linear_small_dgrad_kernel(const float* __restrict__ g, const float* __restrict__ w,
+                                                                const float* __restrict__ z, float* __restrict__ out, int K, int N) {
+  extern __shared__ float s_g[];
+  const int r = blockIdx.x;
+  for (int n = threadIdx.x; n < N; n += blockDim.x) s_g[n] = g[(int64_t)r * N + n];
+  __syncthreads();
+  for (int k = threadIdx.x; k < K; k += blockDim.x) {
+    float acc = 0.f;
+    for (int n = 0; n < N; ++n) acc = fmaf(s_g[n], w[(int64_t)n * K + k], acc);
+    if (z) acc *= dsilu_exact(z[(int64_t)r * K + k]);
+    out[(int64_t)r * K + k] = acc;
+  }
+}
+
+extern "C" int ddimb_linear_small_dgrad(const float* g, const float* w, const float* z, float* out, int rows, int K, int N, cudaStream_t stream) {
+  DDIMB_CHECK_ARG(g && w && out && rows >= 1 && K >= 1 && N >= 1 && N <= 8192);
+  DDIMB_PROF(stream, "linear_small_dgrad", N, K, 4.0 * ((double)N * K + (double)rows * (2 * K + N)), 2.0 * rows * N * K);
+  linear_small_dgrad_kernel<<<rows, K < 512 ? K : 512, N * sizeof(float), stream>>>(g, w, z, out, K, N);
+  DDIMB_LAUNCH_CHECK();
+  return DDIMB_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ conv_in / conv_out parameter gradients
+// conv_in (models/diffusion.py:189-198): dw[co][ci][ky][kx] += sum g[b,t,f,co] * x[b,ci,t+ky-1,f+kx-1], db[co] += sum g;
+// g = g1 + g2 (bf16 NHWC: conv_in's output feeds the first residual block AND the last additive skip).  lane = co.
+template <int CIN>
+__global__ void __launch_bounds__(256) conv_in_wgrad_kernel(const float* __restrict__ x, const __nv_bfloat16* __restrict__ g1,
+                                                           const __nv_bfloat16* __restrict__ g2, float* __restrict__ dw, float* __restrict__ db,
+                                                           int T, int F) {
+  constexpr int NA = CIN * 9 + 1;
+  __shared__ float s_acc[8][NA][32];
+  const int b = blockIdx.y, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int t = blockIdx.x * 8 + warp;
+  float acc[NA];
+#pragma unroll
+  for (int i = 0; i < NA; ++i) acc[i] = 0.f;
+  if (t < T) {
+    const __nv_bfloat16* gp1 = g1 + (((int64_t)b * T + t) * F) * 32 + lane;
+    const __nv_bfloat16* gp2 = g2 ? g2 + (((int64_t)b * T + t) * F) * 32 + lane : nullptr;
+    for (int f = 0; f < F; ++f) {
+      float gv = __bfloat162float(gp1[(int64_t)f * 32]);
+      if (gp2) gv += __bfloat162float(gp2[(int64_t)f * 32]);
+      acc[NA - 1] += gv;
+#pragma unroll
+      for (int ci = 0; ci < CIN; ++ci) {
+        const float* xp = x + ((int64_t)(b * CIN + ci) * T) * F;
+#pragma unroll
+        for (int ky = 0; ky < 3; ++ky) {
+          const int tt = t + ky - 1;
+          if (tt < 0 || tt >= T) continue;
+#pragma unroll
+          for (int kx = 0; kx < 3; ++kx) {
+            const int ff = f + kx - 1;
+            if (ff < 0 || ff >= F) continue;
+            acc[ci * 9 + ky * 3 + kx] = fmaf(gv, __ldg(xp + (int64_t)tt * F + ff), acc[ci * 9 + ky * 3 + kx]);
+          }
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < NA; ++i) s_acc[warp][i][lane] = acc[i];
+  __syncthreads();
+  for (int o = threadIdx.x; o < NA * 32; o += blockDim.x) {
+    const int i = o >> 5, co = o & 31;
+    float s = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) s += s_acc[w][i][co];
+    if (i == NA - 1) atomicAdd(db + co, s);
+    else atomicAdd(dw + (int64_t)co * CIN * 9 + i, s);
+  }
+}
+
+extern "C" int ddimb_conv_in_wgrad(const float* x, const void* g1, const void* g2, float* dw, float* db, int B, int Cin, int T, int F,
+                                   int Cout, cudaStream_t stream) {
+  DDIMB_CHECK_ARG(x && g1 && dw && db && B >= 1 && Cin == 2 && Cout == 32);
+  DDIMB_PROF(stream, "conv_in_wgrad", Cin, Cout, (double)B * T * F * (4.0 * Cin + 2.0 * Cout * (g2 ? 2 : 1)), 18.0 * Cin * Cout * B * T * F);
+  conv_in_wgrad_kernel<2><<<dim3((T + 7) / 8, B), 256, 0, stream>>>(x, reinterpret_cast<const __nv_bfloat16*>(g1),
+                                                                    reinterpret_cast<const __nv_bfloat16*>(g2), dw, db, T, F);
+  DDIMB_LAUNCH_CHECK();
+  return DDIMB_OK;
+}
+
+// conv_out (models/diffusion.py:199-208,284): out[b,co,t,f] = bias + sum w[co][ci][ky][kx] * (h + skip)[b,t+ky-1,f+kx-1,ci].
+// dw[co][ci][ky][kx] += sum dout[b,co,t,f] * hs[b,t+ky-1,f+kx-1,ci], db[co] += sum dout.  lane = ci; a warp walks one row of hs.
+template <int CO>
+__global__ void __launch_bounds__(256) conv_out_wgrad_kernel(const __nv_bfloat16* __restrict__ h, const __nv_bfloat16* __restrict__ skip,
+                                                            const float* __restrict__ dout, float* __restrict__ dw, float* __restrict__ db,
+                                                            int T, int F) {
+  constexpr int NA = CO * 9;
+  __shared__ float s_acc[8][NA][32];
+  __shared__ float s_b[8][CO];
+  const int b = blockIdx.y, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int tq = blockIdx.x * 8 + warp;   // row of hs
+  float acc[NA];
+#pragma unroll
+  for (int i = 0; i < NA; ++i) acc[i] = 0.f;
+  float bacc = 0.f;
+  if (tq < T) {
+    const int64_t rowoff = (((int64_t)b * T + tq) * F) * 32 + lane;
+    for (int fq = 0; fq < F; ++fq) {
+      float v = __bfloat162float(h[rowoff + (int64_t)fq * 32]);
+      if (skip) v += __bfloat162float(skip[rowoff + (int64_t)fq * 32]);
+#pragma unroll
+      for (int co = 0; co < CO; ++co) {
+        const float* dp = dout + ((int64_t)(b * CO + co) * T) * F;
+#pragma unroll
+        for (int ky = 0; ky < 3; ++ky) {
+          const int t = tq - ky + 1;
+          if (t < 0 || t >= T) continue;
+#pragma unroll
+          for (int kx = 0; kx < 3; ++kx) {
+            const int f = fq - kx + 1;
+            if (f < 0 || f >= F) continue;
+            acc[co * 9 + ky * 3 + kx] = fmaf(v, __ldg(dp + (int64_t)t * F + f), acc[co * 9 + ky * 3 + kx]);
+          }
+        }
+      }
+    }
+    if (lane < CO) {
+      const float* dp = dout + ((int64_t)(b * CO + lane) * T + tq) * F;
+      for (int f = 0; f < F; ++f) bacc += dp[f];
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < NA; ++i) s_acc[warp][i][lane] = acc[i];
+  if (lane < CO) s_b[warp][lane] = bacc;
+  __syncthreads();
+  for (int o = threadIdx.x; o < NA * 32; o += blockDim.x) {
+    const int i = o >> 5, ci = o & 31;
+    const int co = i / 9, tap = i - co * 9;
+    float s = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) s += s_acc[w][i][ci];
+    atomicAdd(dw + ((int64_t)co * 32 + ci) * 9 + tap, s);
+  }
+  if (threadIdx.x < CO) {
+    float s = 0.f;
+    for (int w = 0; w < 8; ++w) s += s_b[w][threadIdx.x];
+    atomicAdd(db + threadIdx.x, s);
+  }
+}
+
+extern "C" int ddimb_conv_out_wgrad(const void* h, const void* skip, const float* dout, float* dw, float* db, int B, int T, int F, int Cin,
+                                    int Cout, cudaStream_t stream) {
+  DDIMB_CHECK_ARG(h && dout && dw && db && B >= 1 && Cin == 32 && Cout == 2);
+  DDIMB_PROF(stream, "conv_out_wgrad", Cin, Cout, (double)B * T * F * (2.0 * Cin * (skip ? 2 : 1) + 4.0 * Cout), 18.0 * Cin * Cout * B * T * F);
+  conv_out_wgrad_kernel<2><<<dim3((T + 7) / 8, B), 256, 0, stream>>>(reinterpret_cast<const __nv_bfloat16*>(h), reinterpret_cast<const __nv_bfloat16*>(skip),
+                                                                     dout, dw, db, T, F);
+  DDIMB_LAUNCH_CHECK();
+  return DDIMB_OK;
+}

@@ -175,9 +175,14 @@ __device__ __forceinline__ void conv_epilogue_tile(uint32_t trow, const float* w
         stg_v4(op + 8 * q, make_uint4(pack_bf16x2(f[8 * q], f[8 * q + 1]), pack_bf16x2(f[8 * q + 2], f[8 * q + 3]),
                                       pack_bf16x2(f[8 * q + 4], f[8 * q + 5]), pack_bf16x2(f[8 * q + 6], f[8 * q + 7])));
       if (want_stats) {
+        if (act == 3) {
+          // training: the PRE-activation was stored (its SiLU derivative is needed in backward); the following GroupNorm
+          // normalises silu(value), so the statistics are those of silu(value)
+#pragma unroll
+          for (int j = 0; j < 32; ++j) f[j] = silu_fast(__bfloat162float(__float2bfloat16_rn(f[j])));
+        }
 #pragma unroll
         for (int j = 0; j < 32; j += 4) {
-          constexpr int dummy = 0; (void)dummy;
           const int g = ((c0 + j) % CMOD) / CG;   // compile-time after unrolling
           float s1 = (f[j] + f[j + 1]) + (f[j + 2] + f[j + 3]);
           float s2 = fmaf(f[j], f[j], fmaf(f[j + 1], f[j + 1], fmaf(f[j + 2], f[j + 2], f[j + 3] * f[j + 3])));

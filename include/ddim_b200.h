@@ -68,7 +68,7 @@ int ddimb_conv_out(const void* x, const void* skip, const float* w, const float*
 
 /* models/diffusion.py:28-40,49,52 -- Conv2d 3x3 s1 p1 on NHWC bf16.  w: bf16 [Cout][9*Cin], k = (ky*3+kx)*Cin + ci.
  * Epilogue: + bias[Cout] (nullable) + bias_b[b*bias_b_stride + co] (nullable; the temb slice of :49), act (0 none,
- * 1 SiLU of :50,53), + add (nullable bf16, same shape as out), GroupNorm partial sums into stats (nullable). */
+ * 1 SiLU of :50,53, 3 training: store the pre-activation but take the statistics of its SiLU), + add (nullable bf16, same shape as out), GroupNorm partial sums into stats (nullable). */
 int ddimb_conv3x3(const void* x, const void* w, const float* bias, const float* bias_b, int bias_b_stride, int act,
                   const void* add, void* out, double* stats, int B, int T, int W, int Cin, int Cout, cudaStream_t stream);
 
@@ -107,12 +107,14 @@ int ddimb_fourier_mix(const void* x, long long ldx, const void* wh, const void* 
 /* ---- GroupNorm / LayerNorm / token repacks -------------------------------------------------------------------- */
 
 /* models/diffusion.py:17-26,47-56 -- GroupNorm(8, C, eps) applied from precomputed statistics.
- * mode 0: y = gn(x); mode 1: y = silu(gn(x)); mode 2: y = res + gn(x) and accumulate stats_out of y.
+ * mode 0: y = gn(x); mode 1: y = silu(gn(x)); mode 2: y = res + gn(x) and accumulate stats_out of y;
+ * modes 3 / 4 (training, x is a stored pre-activation): as 0 / 2 on silu(x).
  * beta nullable (norm[2] has no bias, :26). */
 int ddimb_gn_apply(const void* x, const void* res, void* y, const double* stats_in, double* stats_out, const float* gamma,
                    const float* beta, int mode, int B, long long positions, int C, float eps, cudaStream_t stream);
 
-/* models/diffusion.py:107-120 -- BetaEmbedding layers in fp32: out[r][n] = act(in[idx?idx[r]:r] . w[n] + bias[n]). */
+/* models/diffusion.py:107-120 -- BetaEmbedding layers in fp32: out[r][n] = act(in[idx?idx[r]:r] . w[n] + bias[n]);
+ * act bit 0: SiLU on the output; bit 1: SiLU on the input (training keeps the pre-activations). */
 int ddimb_linear_small(const float* in, const long long* idx, const float* w, const float* bias, float* out, int rows,
                        int K, int N, int act, cudaStream_t stream);
 
@@ -128,6 +130,66 @@ int ddimb_layernorm512(const float* a, const float* b, const float* gamma, const
                        long long ldy, int write_lo, int rows, float eps, cudaStream_t stream);
 /* fp32 [rows][H] -> bf16 hi (+ lo) planes of a [rows][ldy] operand buffer. */
 int ddimb_split_bf16(const float* a, void* ybf, long long ldy, int H, int write_lo, long long rows, cudaStream_t stream);
+
+
+/* ---- training: weight gradients (tcgen05, both operands MN-major; csrc/gemm_tn.cuh) ------------------------------ */
+/* Every *_wgrad ACCUMULATES into a caller-zeroed fp32 gradient laid out exactly like the torch parameter. */
+
+/* autograd of Conv2d 3x3 (models/diffusion.py:28-40): dw[Cout][Cin][3][3] += sum dy[b,t,w,co] x[b,t+ky-1,w+kx-1,ci]. */
+int ddimb_conv3x3_wgrad(const void* x, const void* dy, float* dw, int B, int T, int W, int Cin, int Cout, cudaStream_t stream);
+/* autograd of Downsample (models/diffusion.py:70-78): x [B][T][W][Cin], dy [B][T/2][W/2][Cout], dw[Cout][Cin][4][4]. */
+int ddimb_conv_down4x4_wgrad(const void* x, const void* dy, float* dw, int B, int T, int W, int Cin, int Cout, cudaStream_t stream);
+/* autograd of Upsample (models/diffusion.py:59-67): x [B][T][W][Cin], dy [B][2T][2W][Cout], dw[Cin][Cout][4][4]. */
+int ddimb_conv_up4x4_wgrad(const void* x, const void* dy, float* dw, int B, int T, int W, int Cin, int Cout, cudaStream_t stream);
+/* autograd of nn.Linear: dw[N][K] += g[rows][N]^T a[rows][K]; a, g bf16 with leading dimensions lda, ldg. */
+int ddimb_linear_wgrad(const void* a, long long lda, const void* g, long long ldg, float* dw, int rows, int N, int K, cudaStream_t stream);
+
+/* ---- training: GroupNorm / SiLU backward (models/diffusion.py:42-56) ------------------------------------------------ */
+/* type 0: y = silu(gn(x)) (norm[0]); type 1: y = gn(silu(u)) (norm[1], norm[2]; u is the stored pre-activation).
+ * g = dL/dy (bf16), z = x or u (bf16), stats = forward (sum, sumsq) of the GroupNorm input.
+ * reduce: R[B][C][2] (double, caller-zeroed) = per-(sample, channel) sums the apply pass and the parameter gradients need.
+ * apply:  out = dL/dx (+ add) for type 0, dL/du for type 1; sums_out (nullable, double [B][C], caller-zeroed) += sum over
+ *         positions of out (the conv bias / temb-slice gradient).
+ * param:  dgamma[C] (+= ) and dbeta[C] (+=, nullable). */
+int ddimb_gn_bwd_reduce(const void* g, const void* z, const double* stats, const float* gamma, const float* beta, double* R, int type, int B,
+                        long long positions, int C, float eps, cudaStream_t stream);
+int ddimb_gn_bwd_apply(const void* g, const void* z, const void* add, void* out, const double* stats, const double* R, const float* gamma,
+                       const float* beta, double* sums_out, int type, int B, long long positions, int C, float eps, cudaStream_t stream);
+int ddimb_gn_bwd_param(const double* R, const double* stats, float* dgamma, float* dbeta, int B, long long positions, int C, float eps,
+                       cudaStream_t stream);
+/* out[c] += sum_r x[r][c] (bias gradients); x bf16 or fp32 [rows][ld]. */
+int ddimb_colsum(const void* x, int is_bf16, long long ld, long long rows, int C, float* out, cudaStream_t stream);
+/* double [B][C] sums -> out_b[b*ldb + c] += s (temb slice gradient, nullable) and out_c[c] += sum_b s (bias gradient, nullable). */
+int ddimb_sums_scatter(const double* sums, float* out_b, long long ldb, float* out_c, int B, int C, cudaStream_t stream);
+
+/* ---- training: FNet branch / token path / temb MLP / network boundary ------------------------------------------- */
+/* backward of ddimb_layernorm512: dy = dy1 + dy2 (nullable); ds = dL/d(a+b) as fp32 and (dsbf nullable) bf16 hi | lo planes;
+ * dgamma / dbeta accumulated. */
+int ddimb_layernorm512_bwd(const float* a, const float* b, const float* dy1, const float* dy2, const float* gamma, float* ds, void* dsbf,
+                           long long ldy, int write_lo, float* dgamma, float* dbeta, int rows, float eps, cudaStream_t stream);
+/* hf activations.py:59-66 on a stored bf16 pre-activation: dact == NULL: out = gelu_new(u); else out = dact * gelu_new'(u). */
+int ddimb_gelu(const void* u, const void* dact, void* out, long long n, cudaStream_t stream);
+/* fp32 (a [+ b]) -> optional fp32 sum and bf16 hi (+ lo) operand planes [rows][ldy]. */
+int ddimb_add_split_bf16(const float* a, const float* b, float* sum_out, void* ybf, long long ldy, int H, int write_lo, long long rows,
+                         cudaStream_t stream);
+/* nn.Dropout (models/diffusion.py:129,144; hf modeling_fnet.py:226-231): counter-based mask from (seed, index); the backward
+ * is the same call on the gradient. */
+int ddimb_dropout(const float* x, float* y, long long n, float p, unsigned long long seed, cudaStream_t stream);
+/* backward of ddimb_tokens_ln (+ add: gradient of the additive skip reading the same tensor); dgamma / dbeta accumulated. */
+int ddimb_tokens_ln_bwd(const void* x, const float* te, const float* gamma, const float* dtok, const void* add, void* dx, float* dgamma,
+                        float* dbeta, int B, int S, int W, int C, float eps, cudaStream_t stream);
+/* backward of ddimb_tokens_to_nhwc w.r.t. the tokens: NHWC bf16 [B][S][W][C] -> bf16 [B*S][C*W]. */
+int ddimb_nhwc_to_tokens(const void* g, void* tok, int B, int S, int W, int C, cudaStream_t stream);
+/* backward of ddimb_linear_small (act bit 0 = SiLU on the output, bit 1 = SiLU on the input):
+ * wgrad: dw[N][K] += g^T f(in), db[N] += colsum(g); dgrad: out[r][k] = (z ? silu'(z[r][k]) : 1) sum_n g[r][n] w[n][k]. */
+int ddimb_linear_small_wgrad(const float* g, const float* in, const long long* idx, float* dw, float* db, int rows, int K, int N, int in_act,
+                             cudaStream_t stream);
+int ddimb_linear_small_dgrad(const float* g, const float* w, const float* z, float* out, int rows, int K, int N, cudaStream_t stream);
+/* parameter gradients of conv_in (g = g1 + g2, bf16 NHWC; g2 nullable) and conv_out (hs = h + skip). */
+int ddimb_conv_in_wgrad(const float* x, const void* g1, const void* g2, float* dw, float* db, int B, int Cin, int T, int F, int Cout,
+                        cudaStream_t stream);
+int ddimb_conv_out_wgrad(const void* h, const void* skip, const float* dout, float* dw, float* db, int B, int T, int F, int Cin, int Cout,
+                         cudaStream_t stream);
 
 #ifdef __cplusplus
 }
