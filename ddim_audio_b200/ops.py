@@ -174,3 +174,131 @@ def split_bf16(a, ybf, write_lo):
     rows, H = a.shape
     call("ddimb_split_bf16", ptr(a, f32), ptr(ybf, bf16), ybf.stride(0), H, 1 if write_lo else 0, rows)
     return ybf
+
+
+# ---------------------------------------------------------------------------------------- training: weight gradients
+def conv3x3_wgrad(x, dy, dw):
+    """dw fp32 [Cout, Cin, 3, 3] += autograd of Conv2d 3x3 (x, dy bf16 NHWC)."""
+    B, T, W, Cin = x.shape
+    call("ddimb_conv3x3_wgrad", ptr(x, bf16), ptr(dy, bf16), ptr(dw, f32), B, T, W, Cin, dy.shape[-1])
+
+
+def conv_down4x4_wgrad(x, dy, dw):
+    B, T, W, Cin = x.shape
+    call("ddimb_conv_down4x4_wgrad", ptr(x, bf16), ptr(dy, bf16), ptr(dw, f32), B, T, W, Cin, dy.shape[-1])
+
+
+def conv_up4x4_wgrad(x, dy, dw):
+    B, T, W, Cin = x.shape
+    call("ddimb_conv_up4x4_wgrad", ptr(x, bf16), ptr(dy, bf16), ptr(dw, f32), B, T, W, Cin, dy.shape[-1])
+
+
+def linear_wgrad(a, g, dw, rows=None, K=None):
+    """dw fp32 [N, K] += g[rows, N]^T a[rows, K] (bf16 operands, row stride = leading dimension)."""
+    rows = a.shape[0] if rows is None else rows
+    N, Kw = dw.shape
+    K = Kw if K is None else K
+    assert a.stride(-1) == 1 and g.stride(-1) == 1
+    call("ddimb_linear_wgrad", a.data_ptr(), a.stride(0), g.data_ptr(), g.stride(0), ptr(dw, f32), rows, N, K)
+
+
+# ---------------------------------------------------------------------------------------- training: GroupNorm backward
+def gn_bwd_reduce(g, z, stats, gamma, beta, gtype, eps):
+    B, C = z.shape[0], z.shape[-1]
+    R = torch.zeros((B, C, 2), dtype=f64, device=z.device)
+    call("ddimb_gn_bwd_reduce", ptr(g, bf16), ptr(z, bf16), ptr(stats, f64), ptr(gamma, f32), ptr(beta, f32), ptr(R, f64), int(gtype), B,
+         z.numel() // (B * C), C, float(eps))
+    return R
+
+
+def gn_bwd_apply(g, z, stats, R, gamma, beta, gtype, eps, add=None, sums=False, out=None):
+    B, C = z.shape[0], z.shape[-1]
+    if out is None:
+        out = torch.empty_like(z)
+    s = torch.zeros((B, C), dtype=f64, device=z.device) if sums else None
+    call("ddimb_gn_bwd_apply", ptr(g, bf16), ptr(z, bf16), ptr(add, bf16), ptr(out, bf16), ptr(stats, f64), ptr(R, f64), ptr(gamma, f32),
+         ptr(beta, f32), ptr(s, f64), int(gtype), B, z.numel() // (B * C), C, float(eps))
+    return out, s
+
+
+def gn_bwd_param(R, stats, dgamma, dbeta, positions, eps):
+    B, C = R.shape[0], R.shape[1]
+    call("ddimb_gn_bwd_param", ptr(R, f64), ptr(stats, f64), ptr(dgamma, f32), ptr(dbeta, f32), B, int(positions), C, float(eps))
+
+
+def colsum(x, out):
+    """out fp32 [C] += column sums of x viewed as [rows, C] (bf16 or fp32; last dim contiguous)."""
+    x2 = x.reshape(-1, x.shape[-1])
+    call("ddimb_colsum", x2.data_ptr(), 1 if x.dtype == bf16 else 0, x2.stride(0), x2.shape[0], x2.shape[1], ptr(out, f32))
+
+
+def sums_scatter(sums, out_b=None, ldb=0, out_c=None):
+    B, C = sums.shape
+    call("ddimb_sums_scatter", ptr(sums, f64), out_b.data_ptr() if out_b is not None else None, int(ldb), ptr(out_c, f32), B, C)
+
+
+# ---------------------------------------------------------------------------------------- training: FNet / tokens / temb / boundary
+def layernorm512_bwd(a, b, dy1, dy2, gamma, dgamma, dbeta, eps, dsbf=None, write_lo=False):
+    rows = a.shape[0]
+    ds = torch.empty_like(a)
+    call("ddimb_layernorm512_bwd", ptr(a, f32), ptr(b, f32), ptr(dy1, f32), ptr(dy2, f32), ptr(gamma, f32), ptr(ds), ptr(dsbf, bf16),
+         dsbf.stride(0) if dsbf is not None else 0, 1 if write_lo else 0, ptr(dgamma, f32), ptr(dbeta, f32), rows, float(eps))
+    return ds
+
+
+def gelu(u, dact=None):
+    out = torch.empty_like(u)
+    call("ddimb_gelu", ptr(u, bf16), ptr(dact, bf16), ptr(out, bf16), u.numel())
+    return out
+
+
+def add_split_bf16(a, b, ybf, write_lo, sum_out=None):
+    rows, H = a.shape
+    call("ddimb_add_split_bf16", ptr(a, f32), ptr(b, f32), ptr(sum_out, f32), ptr(ybf, bf16), ybf.stride(0), H, 1 if write_lo else 0, rows)
+    return ybf
+
+
+def dropout(x, p, seed, out=None):
+    if out is None:
+        out = torch.empty_like(x)
+    call("ddimb_dropout", ptr(x, f32), ptr(out, f32), x.numel(), float(p), int(seed) & 0xFFFFFFFFFFFFFFFF)
+    return out
+
+
+def tokens_ln_bwd(x, te, gamma, dtok, add, dgamma, dbeta, eps):
+    B, S, W, Cc = x.shape
+    dx = torch.empty_like(x)
+    call("ddimb_tokens_ln_bwd", ptr(x, bf16), ptr(te, f32), ptr(gamma, f32), ptr(dtok, f32), ptr(add, bf16), ptr(dx, bf16), ptr(dgamma, f32),
+         ptr(dbeta, f32), B, S, W, Cc, float(eps))
+    return dx
+
+
+def nhwc_to_tokens(g):
+    B, S, W, Cc = g.shape
+    tok = torch.empty((B * S, Cc * W), dtype=bf16, device=g.device)
+    call("ddimb_nhwc_to_tokens", ptr(g, bf16), ptr(tok, bf16), B, S, W, Cc)
+    return tok
+
+
+def linear_small_wgrad(g, inp, dw, db, in_act, idx=None):
+    rows, N = g.shape
+    K = dw.shape[1]
+    call("ddimb_linear_small_wgrad", ptr(g, f32), ptr(inp, f32), ptr(idx, i64), ptr(dw, f32), ptr(db, f32), rows, K, N, 1 if in_act else 0)
+
+
+def linear_small_dgrad(g, w, z):
+    rows, N = g.shape
+    K = w.shape[1]
+    out = torch.empty((rows, K), dtype=f32, device=g.device)
+    call("ddimb_linear_small_dgrad", ptr(g, f32), ptr(w, f32), ptr(z, f32), ptr(out), rows, K, N)
+    return out
+
+
+def conv_in_wgrad(x, g1, g2, dw, db):
+    B, Cin, T, F = x.shape
+    call("ddimb_conv_in_wgrad", ptr(x, f32), ptr(g1, bf16), ptr(g2, bf16), ptr(dw, f32), ptr(db, f32), B, Cin, T, F, dw.shape[0])
+
+
+def conv_out_wgrad(h, skip, dout, dw, db):
+    B, T, F, Cin = h.shape
+    call("ddimb_conv_out_wgrad", ptr(h, bf16), ptr(skip, bf16), ptr(dout, f32), ptr(dw, f32), ptr(db, f32), B, T, F, Cin, dw.shape[0])
