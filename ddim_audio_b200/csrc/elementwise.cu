@@ -269,7 +269,7 @@ template <int CO>
 __global__ void __launch_bounds__(128) conv_in_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
                                                      __nv_bfloat16* __restrict__ out, double* __restrict__ stats, int Cin, int T, int F) {
   extern __shared__ float sw[];   // [tap][ci][CO] + bias[CO]
-  __shared__ float s_red[16];
+  __shared__ float s_red[4][16];   // per-warp partial sums, combined in warp order (run-to-run reproducible)
   const int b = blockIdx.z, t = blockIdx.y;
   const int nw = 9 * Cin * CO;
   for (int i = threadIdx.x; i < nw; i += blockDim.x) {
@@ -278,7 +278,6 @@ __global__ void __launch_bounds__(128) conv_in_kernel(const float* __restrict__ 
     sw[i] = w[(co * Cin + ci) * 9 + tap];
   }
   for (int i = threadIdx.x; i < CO; i += blockDim.x) sw[nw + i] = bias[i];
-  if (threadIdx.x < 16) s_red[threadIdx.x] = 0.f;
   __syncthreads();
   const int f = blockIdx.x * blockDim.x + threadIdx.x;
   float acc[CO];
@@ -323,10 +322,12 @@ __global__ void __launch_bounds__(128) conv_in_kernel(const float* __restrict__ 
         for (int j = 0; j < CG; ++j) { const float v = acc[g * CG + j]; s1 += v; s2 = fmaf(v, v, s2); }
       }
       s1 = warp_sum(s1); s2 = warp_sum(s2);
-      if ((threadIdx.x & 31) == 0) { atomicAdd(&s_red[2 * g], s1); atomicAdd(&s_red[2 * g + 1], s2); }
+      if ((threadIdx.x & 31) == 0) { s_red[threadIdx.x >> 5][2 * g] = s1; s_red[threadIdx.x >> 5][2 * g + 1] = s2; }
     }
     __syncthreads();
-    if (threadIdx.x < 16) atomicAdd(stats + b * 16 + threadIdx.x, (double)s_red[threadIdx.x]);
+    if (threadIdx.x < 16)
+      atomicAdd(stats + b * 16 + threadIdx.x,
+                (double)((s_red[0][threadIdx.x] + s_red[1][threadIdx.x]) + (s_red[2][threadIdx.x] + s_red[3][threadIdx.x])));
   }
 }
 

@@ -186,6 +186,7 @@ class Model(nn.Module):
         self._packed = None
         self._packed_key = None
         self._consts = {}
+        self.flat_grad = None       # flat fp32 buffer the last backward wrote every parameter gradient into
 
     # ------------------------------------------------------------------ dtype strings (audio.yml:26,42)
     def _apply_type_string(self, s: str):
@@ -198,37 +199,55 @@ class Model(nn.Module):
         return tuple((p.data_ptr(), p._version) for p in self.parameters())
 
     @torch.no_grad()
-    def _pack(self):
-        """bf16 K-major operand copies of every GEMM weight (layouts: include/ddim_b200.h)."""
+    def _pack(self, train=False):
+        """bf16 K-major operand copies of every GEMM weight (layouts: include/ddim_b200.h).  ``train`` adds the operands of
+        the data-gradient GEMMs: 3x3 kernels flipped + transposed, Linear weights transposed; a Downsample's data gradient
+        runs the ConvTranspose kernel on the SAME weight tensor and vice versa."""
         bf = torch.bfloat16
-        pk = {}
+        pk = {"train": train}
 
         def c3(w):      # [Co, Ci, 3, 3] -> [Co, (ky*3+kx)*Ci + ci]
             return w.detach().permute(0, 2, 3, 1).reshape(w.shape[0], -1).to(bf).contiguous()
 
-        def rb(m):
-            return dict(g0=m.norm[0].weight, b0=m.norm[0].bias, g1=m.norm[1].weight, b1=m.norm[1].bias, g2=m.norm[2].weight,
-                        w0=c3(m.conv[0].weight), w1=c3(m.conv[1].weight), cb1=m.conv[1].bias, C=m.channels)
+        def c3d(w):     # data-gradient operand: [Ci, (ky*3+kx)*Co + co] of the flipped kernel
+            return w.detach().flip(2, 3).permute(1, 2, 3, 0).reshape(w.shape[1], -1).to(bf).contiguous()
+
+        def as_conv(w):   # [O, I, 4, 4] -> [O, (ky*4+kx)*I + i]   (ddimb_conv_down4x4 operand)
+            return w.detach().permute(0, 2, 3, 1).reshape(w.shape[0], -1).to(bf).contiguous()
+
+        def as_convT(w):  # [I, O, 4, 4] -> [(ky*4+kx)*O + o, i]    (ddimb_conv_up4x4 operand)
+            return w.detach().permute(2, 3, 1, 0).reshape(-1, w.shape[0]).to(bf).contiguous()
+
+        def rb(m, prefix):
+            d = dict(g0=m.norm[0].weight, b0=m.norm[0].bias, g1=m.norm[1].weight, b1=m.norm[1].bias, g2=m.norm[2].weight,
+                     w0=c3(m.conv[0].weight), w1=c3(m.conv[1].weight), cb1=m.conv[1].bias, C=m.channels, prefix=prefix)
+            if train:
+                d["w0d"], d["w1d"] = c3d(m.conv[0].weight), c3d(m.conv[1].weight)
+            return d
 
         down = []
-        for stage in list(self.down_modules)[1:]:
+        for si, stage in enumerate(list(self.down_modules)[1:], start=1):
             ent = dict(down=None, blocks=[])
-            for m in stage:
+            for mj, m in enumerate(stage):
+                prefix = f"down_modules.{si}.{mj}"
                 if isinstance(m, Downsample):
-                    w = m.conv.weight.detach()                                       # [Co, Ci, 4, 4]
-                    ent["down"] = dict(w=w.permute(0, 2, 3, 1).reshape(w.shape[0], -1).to(bf).contiguous(), b=m.conv.bias)
+                    ent["down"] = dict(w=as_conv(m.conv.weight), b=m.conv.bias, prefix=prefix)
+                    if train:
+                        ent["down"]["wd"] = as_convT(m.conv.weight)
                 else:
-                    ent["blocks"].append(rb(m))
+                    ent["blocks"].append(rb(m, prefix))
             down.append(ent)
         up = []
-        for stage in list(self.up_modules)[:-1]:
+        for si, stage in enumerate(list(self.up_modules)[:-1]):
             ent = dict(up=None, blocks=[])
-            for m in stage:
+            for mj, m in enumerate(stage):
+                prefix = f"up_modules.{si}.{mj}"
                 if isinstance(m, Upsample):
-                    w = m.conv.weight.detach()                                       # [Ci, Co, 4, 4] -> [(ky*4+kx)*Co + co, ci]
-                    ent["up"] = dict(w=w.permute(2, 3, 1, 0).reshape(-1, w.shape[0]).to(bf).contiguous(), b=m.conv.bias)
+                    ent["up"] = dict(w=as_convT(m.conv.weight), b=m.conv.bias, prefix=prefix)
+                    if train:
+                        ent["up"]["wd"] = as_conv(m.conv.weight)
                 else:
-                    ent["blocks"].append(rb(m))
+                    ent["blocks"].append(rb(m, prefix))
             up.append(ent)
         pk["down"], pk["up"] = down, up
         tr = self.transformer
@@ -236,7 +255,21 @@ class Model(nn.Module):
         pk["out_w"] = tr.compute_out.weight.detach().to(bf).contiguous()
         pk["fnet"] = [dict(w1=l.intermediate.dense.weight.detach().to(bf).contiguous(),
                            w2=l.output.dense.weight.detach().to(bf).contiguous()) for l in tr.encoder.layer]
+        if train:
+            pk["proj_wt"] = tr.embedding.projection.weight.detach().t().to(bf).contiguous()
+            pk["out_wt"] = tr.compute_out.weight.detach().t().to(bf).contiguous()
+            for d, l in zip(pk["fnet"], tr.encoder.layer):
+                d["w1t"] = l.intermediate.dense.weight.detach().t().to(bf).contiguous()
+                d["w2t"] = l.output.dense.weight.detach().t().to(bf).contiguous()
+            w = self.up_modules[-1].weight.detach()                                  # conv_out [2, 32, 3, 3]
+            pk["conv_out_wd"] = w.flip(2, 3).permute(1, 0, 2, 3).float().contiguous()  # conv_in-shaped data-gradient kernel
         return pk
+
+    def _packed_for(self, train):
+        key = self._pack_key()
+        if self._packed is None or key != self._packed_key or (train and not self._packed["train"]):
+            self._packed, self._packed_key = self._pack(train), key
+        return self._packed
 
     def _const(self, key, build):
         if key not in self._consts:
@@ -270,10 +303,7 @@ class Model(nn.Module):
         nl = self.levels
         if Cin != cfg.channels or F != cfg.f_size or T % (2 ** (nl - 1)) != 0:
             raise RuntimeError(f"ddim_audio_b200: unsupported input shape {tuple(x.shape)} (need C={cfg.channels}, F={cfg.f_size}, T % {2 ** (nl - 1)} == 0)")
-        key = self._pack_key()
-        if self._packed is None or key != self._packed_key:
-            self._packed, self._packed_key = self._pack(), key
-        pk = self._packed
+        pk = self._packed_for(False)
         dev = x.device
         x = x.contiguous().float()
         t = t.to(device=dev, dtype=torch.int64).contiguous()
@@ -348,4 +378,16 @@ class Model(nn.Module):
         return ops.conv_out(h, hidden.pop(), conv_last.weight, conv_last.bias)
 
     def forward(self, input, t):
+        if torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters()):
+            # training: one autograd node over the whole network (models/training.py); backward runs in library kernels
+            from .training import DenoiserFn
+            if not input.is_cuda:
+                raise RuntimeError("ddim_audio_b200.Model.forward needs CUDA tensors: there is no CPU path")
+            cfg = self.config
+            B, Cin, T, F = input.shape
+            if Cin != cfg.channels or F != cfg.f_size or T % (2 ** (self.levels - 1)) != 0:
+                raise RuntimeError(f"ddim_audio_b200: unsupported input shape {tuple(input.shape)}")
+            x = input.detach().contiguous().float()
+            tt = t.to(device=x.device, dtype=torch.int64).contiguous()
+            return DenoiserFn.apply(self, x, tt, *self.parameters())
         return self._forward_impl(input, t)

@@ -376,6 +376,26 @@ def noise_estimation_loss(model, x0, t, e, a, keepdim=False):
     return per if keepdim else per.mean(dim=0)
 
 
+def loss_and_grads(sd, x0, t, e, a, cfg=AUDIO_CFG, dtype=torch.float32):
+    """functions/losses.py:4-18 followed by ``loss.backward()`` (runners/diffusion.py:154) in eval mode (dropout off):
+    returns (loss, {parameter name: gradient}) from torch autograd over the restated forward."""
+    params = {k: v.detach().to(dtype).clone().requires_grad_(k != "temb.te") for k, v in sd.items()}
+    x = q_sample(x0.to(dtype), t, e.to(dtype), a.to(dtype))
+    out = model_forward(params, x, t.long(), cfg)
+    loss = (e.to(dtype) - out).square().sum(dim=(1, 2, 3)).mean(dim=0)
+    loss.backward()
+    return loss.detach(), {k: p.grad for k, p in params.items() if p.grad is not None}
+
+
+def grad_fingerprint(name: str, g: torch.Tensor):
+    """(L2 norm, sum, projection on a seeded N(0,1) direction) of one gradient tensor, float64: what tests/golden/grad_*.npz
+    stores per parameter (full gradients are 47 M floats)."""
+    seed = sum((i + 1) * ord(c) for i, c in enumerate(name)) % (2 ** 31)
+    d = torch.randn(g.numel(), generator=torch.Generator().manual_seed(seed), dtype=torch.float64)
+    gd = g.detach().double().flatten().cpu()
+    return float(gd.norm()), float(gd.sum()), float(gd @ d)
+
+
 def antithetic_t(n: int, num_timesteps: int, generator: Optional[torch.Generator] = None) -> torch.Tensor:
     """runners/diffusion.py:141-142."""
     t = torch.randint(low=0, high=num_timesteps, size=((n + 1) // 2,), generator=generator)

@@ -28,6 +28,7 @@ OUT = os.path.join(os.path.dirname(HERE), "tests", "golden")
 MODEL_CASES = [("model_b2_t64", 2, 64, 11), ("model_b1_t32", 1, 32, 12), ("model_b3_t96", 3, 96, 13)]
 SAMPLER_CASES = [("ddim_b2_t32_eta0", 2, 32, 21, 0.0, 5, None), ("ddim_b1_t64_eta1", 1, 64, 22, 1.0, 4, {0, 2, -1})]
 LOSS_CASES = [("loss_b4_t32", 4, 32, 31)]
+GRAD_CASES = [("grad_b2_t32", 2, 32, 41)]
 
 
 def main():
@@ -93,6 +94,25 @@ def main():
         print(f"{name}: oracle {float(got):.6f} reference {float(ref):.6f}")
         np.savez_compressed(os.path.join(OUT, name + ".npz"), loss=ref.numpy(), per_sample=refk.numpy(), t=t.numpy(),
                             meta=np.array([b, T, seed]))
+
+    # gradients of the training loss through the UNMODIFIED reference (eval mode: dropout off),
+    # stored as per-parameter fingerprints (norm, sum, seeded projection) + the oracle's agreement with them
+    for name, b, T, seed in GRAD_CASES:
+        x0, e, t = O.synthetic_inputs(b, T, seed)
+        fresh()
+        model.zero_grad(set_to_none=True)
+        loss = ref_loss(model, x0, t, e, alphas)
+        loss.backward()
+        oloss, ograds = O.loss_and_grads(sd, x0, t, e, alphas)
+        keys, fps, worst = [], [], 0.0
+        for k, p in model.named_parameters():
+            keys.append(k)
+            fps.append(O.grad_fingerprint(k, p.grad))
+            worst = max(worst, O.rel_l2(ograds[k], p.grad))
+        print(f"{name}: loss oracle {float(oloss):.6f} reference {float(loss):.6f}; worst per-parameter grad rel-l2 oracle vs reference {worst:.3e}")
+        np.savez_compressed(os.path.join(OUT, name + ".npz"), loss=loss.detach().numpy(), keys=np.array(keys), fp=np.array(fps, dtype=np.float64),
+                            t=t.numpy(), meta=np.array([b, T, seed]))
+        model.zero_grad(set_to_none=True)
 
     # the reference's own default init under torch.manual_seed(0): the drop-in Model must consume the RNG identically
     torch.manual_seed(0)

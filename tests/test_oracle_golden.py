@@ -80,3 +80,18 @@ def test_ddim_coefficients_edge_cases():
     co1 = O.ddim_coefficients(a, range(0, 1000, 250), eta=1.0)
     assert all(c["c1"] > 0 for c in co1[:-1]) and co1[-1]["c1"] == 0.0
     assert O.select_index_for(1000, 10) == {999, 888, 777, 666, 555, 444, 333, 222, 111, 0}
+
+
+def test_loss_gradients_match_reference_fingerprint(oracle_sd, golden_dir):
+    """autograd through the oracle vs gradients of the UNMODIFIED reference (per-parameter norm / sum / seeded projection)."""
+    g = _load(golden_dir, "grad_b2_t32")
+    b, T, seed = (int(v) for v in g["meta"])
+    x0, e, t = O.synthetic_inputs(b, T, seed)
+    loss, grads = O.loss_and_grads(oracle_sd, x0, t, e, O.alphas_cumprod())
+    assert float(loss) == pytest.approx(float(g["loss"]), rel=1e-5)
+    keys = [str(k) for k in g["keys"]]
+    assert keys == [k for k in oracle_sd.keys() if k != "temb.te"] and len(keys) == 388
+    for k, fp in zip(keys, g["fp"]):
+        norm, s, proj = O.grad_fingerprint(k, grads[k])
+        assert norm == pytest.approx(fp[0], rel=2e-3, abs=1e-6), k
+        assert abs(proj - fp[2]) <= 2e-3 * max(fp[0], 1e-6) + 1e-6, k      # projection on a unit-variance direction ~ norm
