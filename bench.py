@@ -50,6 +50,8 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--cpu-sample-steps", type=int, default=2)
+    ap.add_argument("--mode", default="sample", choices=["sample", "train"],
+                    help="sample: DDIM sample-steps/s (the headline, BASELINE configs[2]); train: noise_estimation_loss fwd+bwd samples/s (configs[1]/[4])")
     return ap.parse_args()
 
 
@@ -187,6 +189,39 @@ def run_reference(args):
     print(json.dumps(line), flush=True)
 
 
+def roofline_from_profile(prof, K):
+    """Per-kernel-class table + the dominant class's roofline object from the library profiler's records."""
+    pk = peaks()
+    tot_ms = sum(p["ms"] for p in prof) or 1.0
+    kern = []
+    t_roof = 0.0
+    for p in sorted(prof, key=lambda q: -q["ms"]):
+        tb = p["bytes"] / (pk["hbm"] * 1e9) * 1e3
+        tf = p["flops"] / (pk["tensor"] * 1e12) * 1e3
+        bound = "hbm" if tb >= tf else "tensor"
+        t_roof += max(tb, tf)
+        kern.append({"name": p["name"], "share": round(p["ms"] / tot_ms, 4), "ms_per_call": round(p["ms"] / p["calls"], 5), "calls_per_step": p["calls"] / K,
+                     "bound": bound, "frac": round(max(tb, tf) / p["ms"], 4) if p["ms"] > 0 else None,
+                     "gbs": round(p["bytes"] / p["ms"] * 1e-6, 1), "tflops": round(p["flops"] / p["ms"] * 1e-9, 1)})
+    top = sorted(prof, key=lambda q: -q["ms"])[0]
+    tb = top["bytes"] / (pk["hbm"] * 1e9)
+    tf = top["flops"] / (pk["tensor"] * 1e12)
+    traffic = None
+    tr_path = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tr_path):
+        traffic = json.load(open(tr_path)).get(top["name"])
+    if tb >= tf:
+        ach = top["bytes"] / (top["ms"] * 1e-3) * 1e-9
+        roof = {"bound": "hbm", "achieved": ach, "peak": pk["hbm"], "unit": "GB/s", "frac": ach / pk["hbm"]}
+    else:
+        ach = top["flops"] / (top["ms"] * 1e-3) * 1e-12
+        roof = {"bound": "tensor", "achieved": ach, "peak": pk["tensor"], "unit": "TFLOP/s", "frac": ach / pk["tensor"]}
+    roof.update({"traffic": traffic, "kernel": top["name"], "share_of_step": top["ms"] / tot_ms, "launch_ms": top["ms"] / max(top["launches"], 1),
+                 "algorithmic_bytes_per_launch": top["bytes"] / max(top["launches"], 1), "algorithmic_flops_per_launch": top["flops"] / max(top["launches"], 1),
+                 "peak_source": pk["source"], "timed": "CUDA events on the launching stream around every launch of the timed region"})
+    return roof, kern, t_roof
+
+
 # ------------------------------------------------------------------------------------------------ the B200 arm
 def run_b200(args):
     import torch
@@ -256,35 +291,7 @@ def run_b200(args):
     finite = bool(torch.isfinite(xt).all().item())
     del xt
 
-    # ---------------- roofline: dominant kernel class of the timed region
-    pk = peaks()
-    tot_ms = sum(p["ms"] for p in prof) or 1.0
-    kern = []
-    t_roof = 0.0
-    for p in sorted(prof, key=lambda q: -q["ms"]):
-        tb = p["bytes"] / (pk["hbm"] * 1e9) * 1e3
-        tf = p["flops"] / (pk["tensor"] * 1e12) * 1e3
-        bound = "hbm" if tb >= tf else "tensor"
-        t_roof += max(tb, tf)
-        kern.append({"name": p["name"], "share": round(p["ms"] / tot_ms, 4), "ms_per_call": round(p["ms"] / p["calls"], 5), "calls_per_step": p["calls"] / K,
-                     "bound": bound, "frac": round(max(tb, tf) / p["ms"], 4) if p["ms"] > 0 else None,
-                     "gbs": round(p["bytes"] / p["ms"] * 1e-6, 1), "tflops": round(p["flops"] / p["ms"] * 1e-9, 1)})
-    top = sorted(prof, key=lambda q: -q["ms"])[0]
-    tb = top["bytes"] / (pk["hbm"] * 1e9)
-    tf = top["flops"] / (pk["tensor"] * 1e12)
-    traffic = None
-    tr_path = os.path.join(ROOT, "profiles", "traffic.json")
-    if os.path.exists(tr_path):
-        traffic = json.load(open(tr_path)).get(top["name"])
-    if tb >= tf:
-        ach = top["bytes"] / (top["ms"] * 1e-3) * 1e-9
-        roof = {"bound": "hbm", "achieved": ach, "peak": pk["hbm"], "unit": "GB/s", "frac": ach / pk["hbm"]}
-    else:
-        ach = top["flops"] / (top["ms"] * 1e-3) * 1e-12
-        roof = {"bound": "tensor", "achieved": ach, "peak": pk["tensor"], "unit": "TFLOP/s", "frac": ach / pk["tensor"]}
-    roof.update({"traffic": traffic, "kernel": top["name"], "share_of_step": top["ms"] / tot_ms, "launch_ms": top["ms"] / max(top["launches"], 1),
-                 "algorithmic_bytes_per_launch": top["bytes"] / max(top["launches"], 1), "algorithmic_flops_per_launch": top["flops"] / max(top["launches"], 1),
-                 "peak_source": pk["source"], "timed": "CUDA events on the launching stream around every launch of the timed region"})
+    roof, kern, t_roof = roofline_from_profile(prof, K)
 
     # ---------------- e2e: public API, pinned host x in, both snapshot lists out, every step
     e2e = None
@@ -324,7 +331,130 @@ def run_b200(args):
                        "snapshots": "none inside the device-timed steps (config 3 selects 10 of 1000 steps); every step in e2e"},
             "clocks": clk, "e2e": e2e, "gpu_launches": int(launches), "roofline": roof, "cpu_baseline": cpu,
             "step_roofline": {"t_roof_ms_per_step": t_roof / K, "frac": (t_roof / K) / (ms / K), "note": "sum over kernels of max(bytes/HBM peak, flops/tensor peak) / measured step"},
-            "kernels": kern[:12], "finite": finite,
+            "kernels": kern, "finite": finite,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+# ------------------------------------------------------------------------------------------------ training arm (--mode train)
+def run_train(args):
+    """BASELINE configs[1] / [4]: audio.yml noise_estimation_loss forward + backward (+ NCCL gradient all-reduce when N > 1),
+    per-GPU batch ``--batch`` (default 32) at T = ``--t-size`` (default 1024), dropout 0.1 active.  A step = one loss +
+    backward over one batch; value = samples/s.  The optimizer step is not part of the metric."""
+    import torch
+    import torch.distributed as dist
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the B200 arm has no CPU fallback")
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    from ddim_audio_b200 import _C
+    from ddim_audio_b200.config import audio_config
+    from ddim_audio_b200.functions.losses import noise_estimation_loss
+    from ddim_audio_b200.models.diffusion import Model
+    from ddim_audio_b200.runners import dist as rdist
+    from ddim_audio_b200.runners.diffusion import antithetic_timesteps
+
+    sd = synthetic_state_dict()
+    model = Model(audio_config("torch.FloatTensor")).to(dev)
+    model.load_state_dict(sd, strict=True)
+    model.train()
+    al = alphas_cumprod().to(dev)
+    B = args.batch if args.batch != 64 else 32
+    T = args.t_size if args.t_size != 8192 else 1024
+    K, W = args.steps, max(args.warmup, 0)
+    g = torch.Generator().manual_seed(4321 + rank)
+    x_host = torch.randn(B, 2, T, F_SIZE, generator=g).pin_memory()
+    e_host = torch.randn(B, 2, T, F_SIZE, generator=g).pin_memory()
+    t_host = antithetic_timesteps(B, 1000, g)
+    params = list(model.parameters())
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(v):
+        if world > 1:
+            tns = torch.tensor([v], dtype=torch.float64, device=dev)
+            dist.all_reduce(tns, op=dist.ReduceOp.MAX)
+            return float(tns.item())
+        return v
+
+    def step(x0, e, t):
+        model.zero_grad(set_to_none=True)
+        loss = noise_estimation_loss(model, x0, t, e, al)
+        (loss / world if world > 1 else loss).backward()
+        rdist.allreduce_gradients(params, model.flat_grad)
+        return loss
+
+    x0, e, t = x_host.to(dev), e_host.to(dev), t_host.to(dev)
+    for _ in range(W):
+        step(x0, e, t)
+    clocks = ClockSampler(local)
+    barrier()
+    clocks.start()
+    _C.prof_enable(True)
+    _C.prof_report()
+    l0 = _C.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(K):
+        loss = step(x0, e, t)
+    e1.record()
+    barrier()
+    launches = _C.launch_count() - l0
+    ms = max_over_ranks(e0.elapsed_time(e1))
+    prof = _C.prof_report()
+    _C.prof_enable(False)
+    clk = clocks.stop()
+    value = world * B * K / (ms * 1e-3)
+    finite = bool(torch.isfinite(loss).item()) and all(bool(torch.isfinite(p.grad).all().item()) for p in params[:8])
+    roof, kern, t_roof = roofline_from_profile(prof, K)
+
+    # e2e: pinned host batch in, loss scalar out, every step
+    e2e = None
+    if not args.no_e2e:
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(K):
+            l = step(x_host.to(dev, non_blocking=True), e_host.to(dev, non_blocking=True), t_host.to(dev, non_blocking=True))
+            lv = float(l.item())
+        barrier()
+        dt = max_over_ranks(time.perf_counter() - t0)
+        e2e = {"value": world * B * K / dt, "unit": "samples/s", "h2d_bytes_per_step": 2 * x_host.numel() * 4 + 8 * B, "d2h_bytes_per_step": 4,
+               "ms_per_step": 1e3 * dt / K, "api": "noise_estimation_loss(model, x0, t, e, alphas).backward() on a pinned host batch + loss.item()", "last_loss": lv}
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        from oracle import ddim_oracle as O
+        cores = os.cpu_count() or 1
+        torch.set_num_threads(cores)
+        xs, es, ts = x_host[:1].clone(), e_host[:1].clone(), t_host[:1].clone()
+        O.loss_and_grads(sd, xs[:, :, :32], ts, es[:, :, :32], alphas_cumprod())
+        t0 = time.perf_counter()
+        O.loss_and_grads(sd, xs, ts, es, alphas_cumprod())
+        dt = time.perf_counter() - t0
+        cpu = {"value": 1.0 / dt, "unit": "samples/s", "cores": cores, "kind": "port",
+               "sample": f"1 of the {B} samples, x[1,2,{T},{F_SIZE}], one loss + backward (torch CPU autograd over the oracle), {dt:.1f} s"}
+
+    if rank == 0:
+        line = {
+            "metric": "train_samples_per_sec", "value": value, "unit": "samples/s", "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms / K,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": f"audio.yml noise_estimation_loss fwd+bwd, x[{B},2,{T},{F_SIZE}] per GPU, dropout 0.1 (BASELINE configs[1]/[4] shape)",
+                       "batch_per_gpu": B, "t_size": T, "f_size": F_SIZE, "storage": "bf16 NHWC activations and activation gradients, fp32 accumulate, fp32 weight gradients",
+                       "parallelism": f"data-parallel x{world}" + (", one NCCL all-reduce of the flat fp32 gradient buffer per step" if world > 1 else ""),
+                       "l2": "inputs larger than L2 (level-0 activations are 537 MB each)" if B * T >= 16384 else "small debug shape"},
+            "clocks": clk, "e2e": e2e, "gpu_launches": int(launches), "roofline": roof, "cpu_baseline": cpu,
+            "step_roofline": {"t_roof_ms_per_step": t_roof / K, "frac": (t_roof / K) / (ms / K)}, "kernels": kern, "finite": finite,
         }
         print(json.dumps(line), flush=True)
     if world > 1:
@@ -335,6 +465,8 @@ def main():
     args = parse_args()
     if args.impl == "reference":
         run_reference(args)
+    elif args.mode == "train":
+        run_train(args)
     else:
         run_b200(args)
 
