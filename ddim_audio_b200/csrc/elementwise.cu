@@ -262,151 +262,6 @@ extern "C" int ddimb_gn_apply(const void* x, const void* res, void* y, const dou
   return DDIMB_OK;
 }
 
-// ------------------------------------------------------------------------------------------------ conv_in
-// reference models/diffusion.py:189-198: Conv2d(2 -> 32, k3 p1) on the fp32 NCHW network input; writes NHWC bf16 and
-// the GroupNorm statistics of the first residual block.  One thread per output position, all 32 channels.
-template <int CO>
-__global__ void __launch_bounds__(128) conv_in_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
-                                                     __nv_bfloat16* __restrict__ out, double* __restrict__ stats, int Cin, int T, int F) {
-  extern __shared__ float sw[];   // [tap][ci][CO] + bias[CO]
-  __shared__ float s_red[4][16];   // per-warp partial sums, combined in warp order (run-to-run reproducible)
-  const int b = blockIdx.z, t = blockIdx.y;
-  const int nw = 9 * Cin * CO;
-  for (int i = threadIdx.x; i < nw; i += blockDim.x) {
-    // w is [CO][Cin][3][3]
-    const int co = i % CO, r = i / CO, ci = r % Cin, tap = r / Cin;
-    sw[i] = w[(co * Cin + ci) * 9 + tap];
-  }
-  for (int i = threadIdx.x; i < CO; i += blockDim.x) sw[nw + i] = bias[i];
-  __syncthreads();
-  const int f = blockIdx.x * blockDim.x + threadIdx.x;
-  float acc[CO];
-#pragma unroll
-  for (int c = 0; c < CO; ++c) acc[c] = sw[nw + c];
-  const bool active = f < F;
-  if (active) {
-    for (int ci = 0; ci < Cin; ++ci) {
-      const float* xp = x + ((int64_t)(b * Cin + ci) * T) * F;
-#pragma unroll
-      for (int ky = 0; ky < 3; ++ky) {
-        const int tt = t + ky - 1;
-        if (tt < 0 || tt >= T) continue;
-#pragma unroll
-        for (int kx = 0; kx < 3; ++kx) {
-          const int ff = f + kx - 1;
-          if (ff < 0 || ff >= F) continue;
-          const float v = __ldg(xp + (int64_t)tt * F + ff);
-          const float4* wp = reinterpret_cast<const float4*>(sw + ((ky * 3 + kx) * Cin + ci) * CO);
-#pragma unroll
-          for (int c = 0; c < CO; c += 4) {
-            const float4 w4 = wp[c >> 2];
-            acc[c] = fmaf(v, w4.x, acc[c]); acc[c + 1] = fmaf(v, w4.y, acc[c + 1]);
-            acc[c + 2] = fmaf(v, w4.z, acc[c + 2]); acc[c + 3] = fmaf(v, w4.w, acc[c + 3]);
-          }
-        }
-      }
-    }
-    uint4* op = reinterpret_cast<uint4*>(out + (((int64_t)b * T + t) * F + f) * CO);
-#pragma unroll
-    for (int c = 0; c < CO; c += 8)
-      stg_v4(op + (c >> 3), make_uint4(pack_bf16x2(acc[c], acc[c + 1]), pack_bf16x2(acc[c + 2], acc[c + 3]),
-                                       pack_bf16x2(acc[c + 4], acc[c + 5]), pack_bf16x2(acc[c + 6], acc[c + 7])));
-  }
-  if (stats) {
-    constexpr int CG = CO / 8;
-#pragma unroll
-    for (int g = 0; g < 8; ++g) {
-      float s1 = 0.f, s2 = 0.f;
-      if (active) {
-#pragma unroll
-        for (int j = 0; j < CG; ++j) { const float v = acc[g * CG + j]; s1 += v; s2 = fmaf(v, v, s2); }
-      }
-      s1 = warp_sum(s1); s2 = warp_sum(s2);
-      if ((threadIdx.x & 31) == 0) { s_red[threadIdx.x >> 5][2 * g] = s1; s_red[threadIdx.x >> 5][2 * g + 1] = s2; }
-    }
-    __syncthreads();
-    if (threadIdx.x < 16)
-      atomicAdd(stats + b * 16 + threadIdx.x,
-                (double)((s_red[0][threadIdx.x] + s_red[1][threadIdx.x]) + (s_red[2][threadIdx.x] + s_red[3][threadIdx.x])));
-  }
-}
-
-extern "C" int ddimb_conv_in(const float* x, const float* w, const float* bias, void* out, double* stats, int B, int Cin, int T, int F,
-                             int Cout, cudaStream_t stream) {
-  DDIMB_CHECK_ARG(x && w && bias && out && B >= 1 && Cin >= 1 && Cin <= 8 && Cout == 32);
-  DDIMB_PROF(stream, "conv_in", Cin, Cout, (double)B * T * F * (4.0 * Cin + 2.0 * Cout), 18.0 * Cin * Cout * B * T * F);
-  const int smem = (9 * Cin * Cout + Cout) * 4;
-  conv_in_kernel<32><<<dim3((F + 127) / 128, T, B), 128, smem, stream>>>(x, w, bias, reinterpret_cast<__nv_bfloat16*>(out), stats, Cin, T, F);
-  DDIMB_LAUNCH_CHECK();
-  return DDIMB_OK;
-}
-
-// ------------------------------------------------------------------------------------------------ conv_out
-// reference models/diffusion.py:199-208: Conv2d(32 -> 2, k3 p1); reads NHWC bf16, writes the fp32 NCHW epsilon.
-template <int CI, int CO>
-__global__ void __launch_bounds__(128) conv_out_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ x2,
-                                                      const float* __restrict__ w, const float* __restrict__ bias,
-                                                      float* __restrict__ out, int T, int F) {
-  __shared__ float sw[9 * CI * CO];   // [tap][ci][co]
-  const int b = blockIdx.z, t = blockIdx.y;
-  for (int i = threadIdx.x; i < 9 * CI * CO; i += blockDim.x) {
-    const int co = i % CO, r = i / CO, ci = r % CI, tap = r / CI;
-    sw[i] = w[(co * CI + ci) * 9 + tap];   // w is [CO][CI][3][3]
-  }
-  __syncthreads();
-  const int f = blockIdx.x * blockDim.x + threadIdx.x;
-  if (f >= F) return;
-  float acc[CO];
-#pragma unroll
-  for (int c = 0; c < CO; ++c) acc[c] = bias[c];
-#pragma unroll
-  for (int ky = 0; ky < 3; ++ky) {
-    const int tt = t + ky - 1;
-    if (tt < 0 || tt >= T) continue;
-#pragma unroll
-    for (int kx = 0; kx < 3; ++kx) {
-      const int ff = f + kx - 1;
-      if (ff < 0 || ff >= F) continue;
-      const int64_t off = (((int64_t)b * T + tt) * F + ff) * CI;
-      const uint4* xp = reinterpret_cast<const uint4*>(x + off);
-      const uint4* xp2 = x2 ? reinterpret_cast<const uint4*>(x2 + off) : nullptr;
-      const float* wp = sw + (ky * 3 + kx) * CI * CO;
-#pragma unroll
-      for (int c8 = 0; c8 < CI / 8; ++c8) {
-        const uint4 v = __ldg(xp + c8);
-        const uint32_t vw[4] = {v.x, v.y, v.z, v.w};
-        uint4 v2 = make_uint4(0u, 0u, 0u, 0u);
-        if (xp2) v2 = __ldg(xp2 + c8);
-        const uint32_t vw2[4] = {v2.x, v2.y, v2.z, v2.w};
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          float2 p2 = unpack_bf16x2(vw[j]);
-          const float2 q2 = unpack_bf16x2(vw2[j]);   // the additive skip of models/diffusion.py:284 (bf16 zero when absent)
-          p2.x += q2.x; p2.y += q2.y;
-          const int ci = c8 * 8 + 2 * j;
-#pragma unroll
-          for (int c = 0; c < CO; ++c) {
-            acc[c] = fmaf(p2.x, wp[ci * CO + c], acc[c]);
-            acc[c] = fmaf(p2.y, wp[(ci + 1) * CO + c], acc[c]);
-          }
-        }
-      }
-    }
-  }
-#pragma unroll
-  for (int c = 0; c < CO; ++c) out[(((int64_t)b * CO + c) * T + t) * F + f] = acc[c];
-}
-
-extern "C" int ddimb_conv_out(const void* x, const void* skip, const float* w, const float* bias, float* out, int B, int T, int F,
-                              int Cin, int Cout, cudaStream_t stream) {
-  DDIMB_CHECK_ARG(x && w && bias && out && B >= 1 && Cin == 32 && Cout == 2);
-  DDIMB_PROF(stream, "conv_out", Cin, Cout, (double)B * T * F * (2.0 * Cin * (skip ? 2 : 1) + 4.0 * Cout), 18.0 * Cin * Cout * B * T * F);
-  conv_out_kernel<32, 2><<<dim3((F + 127) / 128, T, B), 128, 0, stream>>>(reinterpret_cast<const __nv_bfloat16*>(x),
-                                                                          reinterpret_cast<const __nv_bfloat16*>(skip), w, bias, out, T, F);
-  DDIMB_LAUNCH_CHECK();
-  return DDIMB_OK;
-}
-
 // ------------------------------------------------------------------------------------------------ small fp32 Linear (temb MLP)
 // reference models/diffusion.py:107-120 (BetaEmbedding): out[r][n] = act(sum_k in[idx ? idx[r] : r][k] * w[n][k] + bias[n]).
 // One warp per output feature; rows <= 64.  5 MFLOP per row -- launch-bound, kept in fp32 for parity.

@@ -52,6 +52,16 @@ elif a.op == "gn":
     bet = torch.randn(C, device=dev, generator=g)
     sti = torch.stack([x.double().reshape(B, -1, 8, C // 8).sum(dim=(1, 3)), (x.double() ** 2).reshape(B, -1, 8, C // 8).sum(dim=(1, 3))], -1).contiguous()
     fn = lambda: ops.gn_apply(x, sti, gam, bet, 1, 1e-6)
+elif a.op == "conv_out":
+    w = torch.randn(2, 32, 3, 3, device=dev, generator=g) / 17
+    b = torch.randn(2, device=dev, generator=g)
+    sk = torch.randn(B, T, W, 32, device=dev, generator=g).to(bf)
+    fn = lambda: ops.conv_out(x, sk, w, b)
+elif a.op == "conv_in":
+    xi = torch.randn(B, 2, T, W, device=dev, generator=g)
+    w = torch.randn(32, 2, 3, 3, device=dev, generator=g) / 4
+    b = torch.randn(32, device=dev, generator=g)
+    fn = lambda: ops.conv_in(xi, w, b, st)
 else:
     raise SystemExit("unknown op")
 fn()
