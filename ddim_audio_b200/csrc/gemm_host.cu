@@ -30,9 +30,21 @@ static int launch_gemm(GemmParams& p, const CUtensorMap& tmA, const CUtensorMap&
     if (tp.nseg * p.n_seg > brows) brows = tp.nseg * p.n_seg;
   }
   p.b_rows_per_stage = brows;
-  const int stage_bytes = (ck == 64 ? GemmSmem<64>::stage_bytes(brows) : GemmSmem<32>::stage_bytes(brows));
-  DDIMB_CHECK_ARG(stage_bytes % 1024 == 0);
   const int max_smem = 232448;   // 227 KB opt-in limit per CTA on sm_100
+  // K chunks per stage: a barrier round should cover >= 128 of K (the MMA issue thread pays a fixed cost per round), as long
+  // as at least three stages still fit
+  int max_chunk = 1;
+  for (int t = 0; t < p.ntaps; ++t)
+    if (p.taps[t].nchunk > max_chunk) max_chunk = p.taps[t].nchunk;
+  int kps = 1;
+  for (int k = 2; k <= max_chunk && k * ck <= 128; ++k) {
+    const int sbk = (ck == 64 ? GemmSmem<64>::stage_bytes(brows, k) : GemmSmem<32>::stage_bytes(brows, k));
+    if ((max_smem - 1024 - kGemmAuxBytes) / sbk >= 3) kps = k;
+  }
+  { const char* e = getenv("DDIMB_KPS"); if (e && atoi(e) >= 1) kps = atoi(e) < max_chunk ? atoi(e) : max_chunk; }
+  p.kps = kps;
+  const int stage_bytes = (ck == 64 ? GemmSmem<64>::stage_bytes(brows, kps) : GemmSmem<32>::stage_bytes(brows, kps));
+  DDIMB_CHECK_ARG(stage_bytes % 1024 == 0);
   int stages = (max_smem - 1024 - kGemmAuxBytes) / stage_bytes;
   if (stages > 8) stages = 8;
   DDIMB_CHECK_ARG(stages >= 2);

@@ -40,6 +40,7 @@ struct GemmParams {
   int32_t b_batched;    // B dim-2 coordinate = batch index (else 0)
   int32_t b_rows_per_stage;  // max nseg * n_seg
   int32_t num_stages;
+  int32_t kps;          // K chunks per pipeline stage (a stage holds up to kps chunks of ONE tap: fewer, larger barrier rounds)
   int32_t tmem_cols;    // power of two >= 32
   int32_t num_acc_bufs; // 1 or 2
   int32_t ntaps;
@@ -66,7 +67,7 @@ struct GemmSmem {
   static constexpr int kABytes = kTileM * CK * 2;
   static constexpr int kSwizzle = (CK == 64) ? 2 : 4;  // descriptor code: 2 = 128B, 4 = 64B
   static constexpr int kSBO = 8 * CK * 2;              // 8-row group pitch
-  __host__ __device__ static int stage_bytes(int b_rows) { return kABytes + b_rows * CK * 2; }
+  __host__ __device__ static int stage_bytes(int b_rows, int kps) { return kps * (kABytes + b_rows * CK * 2); }
 };
 
 constexpr int kGemmAuxBytes = 1024 + 4096;  // barriers, tmem pointer, per-warp bias copies
@@ -202,7 +203,8 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;   // swizzle atoms need 1024-B alignment
   uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
-  const int stage_bytes = GemmSmem<CK>::stage_bytes(p.b_rows_per_stage);
+  const int stage_bytes = GemmSmem<CK>::stage_bytes(p.b_rows_per_stage, p.kps);
+  const int b_chunk_bytes = p.b_rows_per_stage * CK * 2;   // B region of one chunk
   const uint32_t aux = smem_base + p.num_stages * stage_bytes;
   // aux layout: full[8] @0, empty[8] @64, tmem_full[2] @128, tmem_empty[2] @144, tmem_ptr @160, per-warp bias float[4][256] @1024
   const uint32_t bar_full = aux, bar_empty = aux + 64, bar_tfull = aux + 128, bar_tempty = aux + 144;
@@ -246,16 +248,21 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         const int nt = it.i[4];
         for (int t = 0; t < p.ntaps; ++t) {
           const TapDesc& tp = p.taps[t];
-          const uint32_t tx = (uint32_t)(GemmSmem<CK>::kABytes + tp.nseg * p.n_seg * CK * 2);
-          for (int ch = 0; ch < tp.nchunk; ++ch) {
+          const uint32_t tx1 = (uint32_t)(GemmSmem<CK>::kABytes + tp.nseg * p.n_seg * CK * 2);
+          for (int ch0 = 0; ch0 < tp.nchunk; ch0 += p.kps) {
+            const int nch = min(p.kps, tp.nchunk - ch0);
             mbar_wait(bar_empty + 8 * stage, phase ^ 1, 1);
             const uint32_t sa = smem_base + stage * stage_bytes;
-            const uint32_t sb = sa + GemmSmem<CK>::kABytes;
-            mbar_arrive_expect_tx(bar_full + 8 * stage, tx);
-            tma_load_5d(sa, &tmA, bar_full + 8 * stage, tp.a_c0 + ch * CK, c1 + tp.da[0], c2 + tp.da[1], c3 + tp.da[2], c4 + tp.da[3]);
-            for (int sg = 0; sg < tp.nseg; ++sg)
-              tma_load_3d(sb + sg * p.n_seg * CK * 2, &tmB, bar_full + 8 * stage, tp.b_k0 + ch * CK,
-                          nt * p.n_tile_stride + tp.b_n0 + sg * p.n_seg, bb);
+            const uint32_t sb = sa + p.kps * GemmSmem<CK>::kABytes;
+            mbar_arrive_expect_tx(bar_full + 8 * stage, tx1 * (uint32_t)nch);
+            for (int i = 0; i < nch; ++i) {
+              const int ch = ch0 + i;
+              tma_load_5d(sa + i * GemmSmem<CK>::kABytes, &tmA, bar_full + 8 * stage, tp.a_c0 + ch * CK, c1 + tp.da[0], c2 + tp.da[1], c3 + tp.da[2],
+                          c4 + tp.da[3]);
+              for (int sg = 0; sg < tp.nseg; ++sg)
+                tma_load_3d(sb + i * b_chunk_bytes + sg * p.n_seg * CK * 2, &tmB, bar_full + 8 * stage, tp.b_k0 + ch * CK,
+                            nt * p.n_tile_stride + tp.b_n0 + sg * p.n_seg, bb);
+            }
             if (++stage == p.num_stages) { stage = 0; phase ^= 1; }
           }
         }
@@ -277,22 +284,25 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         uint32_t written = 0;
         for (int t = 0; t < p.ntaps; ++t) {
           const TapDesc& tp = p.taps[t];
-          for (int ch = 0; ch < tp.nchunk; ++ch) {
+          for (int ch0 = 0; ch0 < tp.nchunk; ch0 += p.kps) {
+            const int nch = min(p.kps, tp.nchunk - ch0);
             mbar_wait(bar_full + 8 * stage, phase, 3);
             tc_fence_after();
             const uint32_t sa = smem_base + stage * stage_bytes;
-            const uint32_t sb = sa + GemmSmem<CK>::kABytes;
-            const uint64_t adesc = make_kmajor_desc(sa, GemmSmem<CK>::kSBO, GemmSmem<CK>::kSwizzle);
-            for (int sg = 0; sg < tp.nseg; ++sg) {
-              const int col = tp.tmem_col0 + sg * p.n_seg;
-              const uint32_t bit = 1u << (col / p.n_seg);
-              const uint64_t bdesc = make_kmajor_desc(sb + sg * p.n_seg * CK * 2, GemmSmem<CK>::kSBO, GemmSmem<CK>::kSwizzle);
+            const uint32_t sb = sa + p.kps * GemmSmem<CK>::kABytes;
+            for (int i = 0; i < nch; ++i) {
+              const uint64_t adesc = make_kmajor_desc(sa + i * GemmSmem<CK>::kABytes, GemmSmem<CK>::kSBO, GemmSmem<CK>::kSwizzle);
+              for (int sg = 0; sg < tp.nseg; ++sg) {
+                const int col = tp.tmem_col0 + sg * p.n_seg;
+                const uint32_t bit = 1u << (col / p.n_seg);
+                const uint64_t bdesc = make_kmajor_desc(sb + i * b_chunk_bytes + sg * p.n_seg * CK * 2, GemmSmem<CK>::kSBO, GemmSmem<CK>::kSwizzle);
 #pragma unroll
-              for (int k = 0; k < CK / 16; ++k) {
-                // +32 bytes along K inside the swizzle atom == +2 in the (addr >> 4) start-address field
-                umma_bf16(acc0 + (uint32_t)col, adesc + 2 * k, bdesc + 2 * k, idesc, ((written & bit) != 0u) | (k > 0));
+                for (int k = 0; k < CK / 16; ++k) {
+                  // +32 bytes along K inside the swizzle atom == +2 in the (addr >> 4) start-address field
+                  umma_bf16(acc0 + (uint32_t)col, adesc + 2 * k, bdesc + 2 * k, idesc, ((written & bit) != 0u) | (k > 0));
+                }
+                written |= bit;
               }
-              written |= bit;
             }
             umma_commit(bar_empty + 8 * stage);   // smem slot is free once these MMAs have read it
             if (++stage == p.num_stages) { stage = 0; phase ^= 1; }
