@@ -191,32 +191,47 @@ __global__ void __launch_bounds__(256) gn_apply_kernel(const GnArgs a) {
   const uint4* rp = a.res ? reinterpret_cast<const uint4*>(a.res + (int64_t)b * a.per_sample) : nullptr;
   uint4* yp = reinterpret_cast<uint4*>(a.y + (int64_t)b * a.per_sample);
   float sa1 = 0.f, sa2 = 0.f, sb1 = 0.f, sb2 = 0.f;   // channels c0..c0+3 and c0+4..c0+7 (group width is a multiple of 4)
-  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < items; i += (int64_t)gridDim.x * blockDim.x) {
-    const uint4 xv = ldg_nc_v4(xp + i);
-    const uint32_t xw[4] = {xv.x, xv.y, xv.z, xv.w};
-    float f[8];
+  // UNR items per iteration with every load issued before the first use: ~8 x 16 B in flight per thread keeps HBM busy
+  constexpr int UNR = 4;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i0 = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i0 < items; i0 += UNR * stride) {
+    uint4 xv[UNR], rv[UNR];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      float2 t = unpack_bf16x2(xw[j]);
-      if (a.pre_silu) { t.x = silu_fast(t.x); t.y = silu_fast(t.y); }
-      f[2 * j] = fmaf(t.x, sc[2 * j], sh[2 * j]);
-      f[2 * j + 1] = fmaf(t.y, sc[2 * j + 1], sh[2 * j + 1]);
+    for (int u = 0; u < UNR; ++u) {
+      const int64_t i = i0 + u * stride;
+      if (i < items) {
+        xv[u] = ldg_nc_v4(xp + i);
+        if (a.mode == 2) rv[u] = ldg_nc_v4(rp + i);
+      }
     }
-    if (a.mode == 1) {
 #pragma unroll
-      for (int j = 0; j < 8; ++j) f[j] = silu_fast(f[j]);
-    } else if (a.mode == 2) {
-      const uint4 rv = ldg_nc_v4(rp + i);
-      const uint32_t rw[4] = {rv.x, rv.y, rv.z, rv.w};
+    for (int u = 0; u < UNR; ++u) {
+      const int64_t i = i0 + u * stride;
+      if (i >= items) break;
+      const uint32_t xw[4] = {xv[u].x, xv[u].y, xv[u].z, xv[u].w};
+      float f[8];
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        const float2 t = unpack_bf16x2(rw[j]);
-        f[2 * j] += t.x; f[2 * j + 1] += t.y;
+        float2 t = unpack_bf16x2(xw[j]);
+        if (a.pre_silu) { t.x = silu_fast(t.x); t.y = silu_fast(t.y); }
+        f[2 * j] = fmaf(t.x, sc[2 * j], sh[2 * j]);
+        f[2 * j + 1] = fmaf(t.y, sc[2 * j + 1], sh[2 * j + 1]);
       }
+      if (a.mode == 1) {
 #pragma unroll
-      for (int j = 0; j < 4; ++j) { sa1 += f[j]; sa2 = fmaf(f[j], f[j], sa2); sb1 += f[4 + j]; sb2 = fmaf(f[4 + j], f[4 + j], sb2); }
+        for (int j = 0; j < 8; ++j) f[j] = silu_fast(f[j]);
+      } else if (a.mode == 2) {
+        const uint32_t rw[4] = {rv[u].x, rv[u].y, rv[u].z, rv[u].w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const float2 t = unpack_bf16x2(rw[j]);
+          f[2 * j] += t.x; f[2 * j + 1] += t.y;
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) { sa1 += f[j]; sa2 = fmaf(f[j], f[j], sa2); sb1 += f[4 + j]; sb2 = fmaf(f[4 + j], f[4 + j], sb2); }
+      }
+      stg_v4(yp + i, make_uint4(pack_bf16x2(f[0], f[1]), pack_bf16x2(f[2], f[3]), pack_bf16x2(f[4], f[5]), pack_bf16x2(f[6], f[7])));
     }
-    stg_v4(yp + i, make_uint4(pack_bf16x2(f[0], f[1]), pack_bf16x2(f[2], f[3]), pack_bf16x2(f[4], f[5]), pack_bf16x2(f[6], f[7])));
   }
   if (a.mode == 2 && a.stats_out) {
     // fixed-order block reduction (run-to-run reproducible): per-thread partials -> shared -> 16 threads sum them in thread order

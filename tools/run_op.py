@@ -52,6 +52,12 @@ elif a.op == "gn":
     bet = torch.randn(C, device=dev, generator=g)
     sti = torch.stack([x.double().reshape(B, -1, 8, C // 8).sum(dim=(1, 3)), (x.double() ** 2).reshape(B, -1, 8, C // 8).sum(dim=(1, 3))], -1).contiguous()
     fn = lambda: ops.gn_apply(x, sti, gam, bet, 1, 1e-6)
+elif a.op == "gn2":
+    gam = torch.randn(C, device=dev, generator=g)
+    sti = torch.stack([x.double().reshape(B, -1, 8, C // 8).sum(dim=(1, 3)), (x.double() ** 2).reshape(B, -1, 8, C // 8).sum(dim=(1, 3))], -1).contiguous()
+    res = torch.randn(B, T, W, C, device=dev, generator=g).to(bf)
+    yb = torch.empty_like(x)
+    fn = lambda: ops.gn_apply(x, sti, gam, None, 2, 1e-6, res=res, stats_out=st, out=yb)
 elif a.op == "conv_out":
     w = torch.randn(2, 32, 3, 3, device=dev, generator=g) / 17
     b = torch.randn(2, device=dev, generator=g)
