@@ -12,7 +12,7 @@ import os
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libddim_b200.so")
+LIB_PATH = os.environ.get("DDIMB_LIB_PATH") or os.path.join(_HERE, "lib", "libddim_b200.so")   # override: kernel-variant A/B runs (tools/)
 
 if not os.path.exists(LIB_PATH):
     raise ImportError(

@@ -7,13 +7,22 @@
 // is what the reference's zero padding of the ACTIVATED tensor means); then all 9 taps are tcgen05.mma's whose A descriptors
 // simply start kx rows further into slot (t + ky - 1) -- the swizzle is a function of the absolute shared-memory address,
 // so a row-shifted start needs no re-layout (tools/umma_probe.cu).  The 9 weight tiles stay resident in shared memory.
-// Warp roles (320 threads): 0 = TMA producer, 1 = MMA issuer, 2-5 = epilogue, 6-9 = transform.
+// Warp roles (576 threads): 0 = TMA producer, 1 = MMA issuer, 2-9 = epilogue (two warps per TMEM lane quarter, alternating
+// output rows), 10-17 = transform (every eighth row strip each).  The epilogue and transform warps are latency-bound
+// dependent chains (ncu: one warp of each per scheduler issued every ~6 cycles), so each scheduler gets two of each.
 #pragma once
 #include "umma_gemm.cuh"
 
 namespace ddimb {
 
-constexpr int kWideThreads = 320;
+#ifndef DDIMB_WIDE_EPI
+#define DDIMB_WIDE_EPI 8
+#endif
+#ifndef DDIMB_WIDE_XF
+#define DDIMB_WIDE_XF 8
+#endif
+constexpr int kWideEpiWarps = DDIMB_WIDE_EPI, kWideXfWarps = DDIMB_WIDE_XF;   // 4 or 8 epilogue warps
+constexpr int kWideThreads = 32 * (2 + kWideEpiWarps + kWideXfWarps);
 constexpr int kWidePos = 130;   // positions per row strip: 128 + 2 halo columns
 
 struct WideParams {
@@ -47,7 +56,7 @@ struct WideCfg {
   static constexpr int kWBytes = 9 * C * C * 2;
   static constexpr int kSwizzle = (C == 64) ? 2 : 4;
   static constexpr int kSBO = 8 * kRowBytes;
-  static constexpr int kAuxBytes = 1024 + 4096 + 4 * C * 8;   // barriers | epilogue bias copies | transform scale/shift copies
+  static constexpr int kAuxBytes = 1024 + 4096 + kWideXfWarps * C * 8;   // barriers | epilogue bias copies | transform scale/shift copies
   static constexpr int kSmemBytes = 1024 + kWBytes + kSlots * kSlotBytes + kAuxBytes;
 };
 
@@ -121,7 +130,7 @@ conv3x3_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 
   if (warp == 0) {
     // ================================================================ TMA producer
-    if (lane == 0) {
+    if (elect_one()) {
       mbar_arrive_expect_tx(bar_w, (uint32_t)Cfg::kWBytes);
       // per kx one B tile of 3C rows: row block j holds ky = 2 - j, i.e. the output rows (rr-2, rr-1, rr) an input row rr feeds
       for (int ky = 0; ky < 3; ++ky)
@@ -134,73 +143,88 @@ conv3x3_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           const uint32_t slot = cnt % NS, use = cnt / NS;
           mbar_wait(bar_empty + 8 * slot, (use & 1) ^ 1, 11);
           mbar_arrive_expect_tx(bar_raw + 8 * slot, (uint32_t)(kWidePos * Cfg::kRowBytes));
-          tma_load_4d(a_base + slot * Cfg::kSlotBytes, &tmA, bar_raw + 8 * slot, 0, u.w0 - 1, u.t0 - 1 + rr, u.b);
+          if (p.dbg & 8) tma_load_4d(a_base + slot * Cfg::kSlotBytes, &tmA, bar_raw + 8 * slot, 0, 127, (int)(blockIdx.x & 63), 0);
+          else tma_load_4d(a_base + slot * Cfg::kSlotBytes, &tmA, bar_raw + 8 * slot, 0, u.w0 - 1, u.t0 - 1 + rr, u.b);
         }
       }
     }
   } else if (warp == 1) {
     // ================================================================ MMA issuer (single thread)
-    if (lane == 0) {
+    // Input-row-major issue order: input row rr of a unit feeds output rows rr-2 (ky=2), rr-1 (ky=1) and rr (ky=0), whose
+    // accumulators are adjacent TMEM column blocks, so one MMA of N = 3C serves all three and the A tile is read from shared
+    // memory once per (kx, k) instead of three times.  Output row rr receives its FIRST contribution here (overwrite).
+    // The issuing thread is the critical resource (ncu + tools/umma_tput.cu: the tensor pipe needs 56 cycles per N=96 MMA, a
+    // branchy issue path spent ~150): per row the (<= 3) accumulator segments are worked out ONCE, the 3 x C/16 steps are then
+    // straight-line code over precomputed descriptor words.
+    if (elect_one()) {
       const uint32_t bar_in = fused ? bar_ready : bar_raw;
       mbar_wait(bar_w, 0, 12);
       tc_fence_after();
-      // Input-row-major issue order: input row rr of a unit feeds output rows rr-2 (ky=2), rr-1 (ky=1) and rr (ky=0), whose
-      // accumulators are adjacent TMEM column blocks, so one MMA of N = 3C serves all three and the A tile is read from shared
-      // memory once per (kx, k) instead of three times.  Output row rr receives its FIRST contribution here (overwrite).
-      const uint32_t idesc1 = make_idesc_bf16(kTileM, (uint32_t)C), idesc2 = make_idesc_bf16(kTileM, (uint32_t)(2 * C)),
-                     idesc3 = make_idesc_bf16(kTileM, (uint32_t)(3 * C));
+      constexpr uint32_t kTile16 = (uint32_t)(C * C * 2) >> 4;          // one C x C weight tile, in descriptor units
+      const uint64_t desc_hi = make_kmajor_desc(0, Cfg::kSBO, Cfg::kSwizzle);
+      const uint32_t w_lo = (w_base & 0x3FFFFu) >> 4;
       uint32_t cnt = 0, otile = 0;
       WideUnit u;
       for (int unit = blockIdx.x; unit < p.num_units; unit += gridDim.x) {
         u.set(p, unit);
         for (int rr = 0; rr < u.rows + 2; ++rr) {
           const uint32_t slot = (cnt + rr) % NS;
-          mbar_wait(bar_in + 8 * slot, ((cnt + rr) / NS) & 1, 13);
-          if (rr < u.rows) {
-            const uint32_t nbuf = (otile + rr) % NB, use = (otile + rr) / NB;
-            mbar_wait(bar_aempty + 8 * nbuf, (use & 1) ^ 1, 14);
-          }
-          tc_fence_after();
           // output blocks j = 0, 1, 2 <-> output rows rr-2, rr-1, rr (ky = 2, 1, 0); block 2 is a first contribution
           const bool v0 = rr >= 2, v1 = rr >= 1 && rr - 1 < u.rows, v2 = rr < u.rows;
-          const uint32_t b0 = (otile + rr - 2) % NB, b1 = (otile + rr - 1) % NB, b2 = (otile + rr) % NB;
-          const bool m01 = v0 && v1 && b1 != 0 && !(p.dbg & 1);          // blocks 0,1 adjacent in TMEM
-          const bool m012 = m01 && v2 && b2 != 0;                        // all three adjacent
-          const uint32_t sa = a_base + slot * Cfg::kSlotBytes;
+          const uint32_t b0 = (otile + rr + NB - 2) % NB, b1 = (b0 + 1) % NB, b2 = (b0 + 2) % NB;
+          // The valid blocks fb..lb are a contiguous range; the TMEM ring wraps at most once inside it (where a block's ring
+          // index is 0), so the accumulating steps need at most two MMAs: segment A = fb..split-1, segment B = split..lb at column 0.
+          const int fb = v0 ? 0 : (v1 ? 1 : 2), lb = v2 ? 2 : (v1 ? 1 : 0);
+          int split = lb + 1;
+          if (fb < 1 && 1 <= lb && b1 == 0) split = 1;
+          else if (fb < 2 && 2 <= lb && b2 == 0) split = 2;
+          const bool has_b = split <= lb;
+          const uint32_t ta = tmem_base + ((b0 + (uint32_t)fb) % NB) * C;
+          const uint32_t wa = (uint32_t)fb * kTile16, wb2 = (uint32_t)split * kTile16;
+          const uint32_t ia = make_idesc_bf16(kTileM, (uint32_t)(split - fb) * C), ib = make_idesc_bf16(kTileM, (uint32_t)(lb - split + 1) * C);
+          // first step (kx = 0, k = 0): block 2 is overwritten on its own, blocks fb..lbi accumulate
+          const int lbi = v2 ? 1 : lb;
+          const int spl_i = split < lbi + 1 ? split : lbi + 1;
+          const bool has_ai = fb <= lbi, has_bi = split <= lbi;
+          const uint32_t iai = make_idesc_bf16(kTileM, (uint32_t)(has_ai ? spl_i - fb : 1) * C);
+          const uint32_t ibi = make_idesc_bf16(kTileM, (uint32_t)(has_bi ? lbi - split + 1 : 1) * C);
+          mbar_wait(bar_in + 8 * slot, ((cnt + rr) / NS) & 1, 13);
+          if (v2) mbar_wait(bar_aempty + 8 * b2, (((otile + rr) / NB) & 1) ^ 1, 14);
+          tc_fence_after();
+          const uint32_t a_lo = ((a_base + slot * Cfg::kSlotBytes) & 0x3FFFFu) >> 4;
+          if (!(p.dbg & 4)) {
+            {
+              const uint64_t ad = desc_hi | (uint64_t)a_lo;
+              if (has_ai) umma_bf16(ta, ad, desc_hi | (uint64_t)(w_lo + wa), iai, 1u);
+              if (has_bi) umma_bf16(tmem_base, ad, desc_hi | (uint64_t)(w_lo + wb2), ibi, 1u);
+              if (v2) umma_bf16(tmem_base + b2 * C, ad, desc_hi | (uint64_t)(w_lo + 2 * kTile16), make_idesc_bf16(kTileM, (uint32_t)C), 0u);
+            }
 #pragma unroll
-          for (int kx = 0; kx < 3; ++kx) {
-            const uint64_t adesc = make_kmajor_desc(sa + kx * Cfg::kRowBytes, Cfg::kSBO, Cfg::kSwizzle);
-            const uint64_t bd0 = make_kmajor_desc(w_base + (kx * 3 + 0) * C * C * 2, Cfg::kSBO, Cfg::kSwizzle);
-            const uint64_t bd1 = make_kmajor_desc(w_base + (kx * 3 + 1) * C * C * 2, Cfg::kSBO, Cfg::kSwizzle);
-            const uint64_t bd2 = make_kmajor_desc(w_base + (kx * 3 + 2) * C * C * 2, Cfg::kSBO, Cfg::kSwizzle);
+            for (int kx = 0; kx < 3; ++kx) {
 #pragma unroll
-            for (int k = 0; k < C / 16; ++k) {
-              const bool init = (kx == 0 && k == 0);
-              if (m012 && !init) {
-                umma_bf16(tmem_base + b0 * C, adesc + 2 * k, bd0 + 2 * k, idesc3, 1u);
-              } else {
-                if (m01) {
-                  umma_bf16(tmem_base + b0 * C, adesc + 2 * k, bd0 + 2 * k, idesc2, 1u);
-                } else {
-                  if (v0) umma_bf16(tmem_base + b0 * C, adesc + 2 * k, bd0 + 2 * k, idesc1, 1u);
-                  if (v1) umma_bf16(tmem_base + b1 * C, adesc + 2 * k, bd1 + 2 * k, idesc1, 1u);
-                }
-                if (v2) umma_bf16(tmem_base + b2 * C, adesc + 2 * k, bd2 + 2 * k, idesc1, init ? 0u : 1u);
+              for (int k = 0; k < C / 16; ++k) {
+                if (kx == 0 && k == 0) continue;
+                const uint64_t ad = desc_hi | (uint64_t)(a_lo + (uint32_t)(kx * (Cfg::kRowBytes >> 4) + 2 * k));
+                const uint32_t wl = w_lo + (uint32_t)(kx * 3) * kTile16 + 2 * k;
+                umma_bf16(ta, ad, desc_hi | (uint64_t)(wl + wa), ia, 1u);
+                if (has_b) umma_bf16(tmem_base, ad, desc_hi | (uint64_t)(wl + wb2), ib, 1u);
               }
             }
           }
-          umma_commit(bar_empty + 8 * slot);                                   // this input row is consumed
-          if (rr >= 2) umma_commit(bar_afull + 8 * ((otile + rr - 2) % NB));   // output row rr-2 is complete
+          umma_commit(bar_empty + 8 * slot);                  // this input row is consumed
+          if (v0) umma_commit(bar_afull + 8 * b0);            // output row rr-2 is complete
         }
         cnt += u.rows + 2;
         otile += u.rows;
       }
     }
-  } else if (warp < 6) {
-    // ================================================================ epilogue (TMEM lane quarter = warp % 4)
+  } else if (warp < 2 + kWideEpiWarps) {
+    // ================================================================ epilogue (TMEM lane quarter = warp % 4; group = output row parity)
     const int q = warp & 3;
+    const uint32_t grp = (uint32_t)(warp - 2) >> 2;
+    constexpr uint32_t kGrpMask = kWideEpiWarps / 4 - 1;
     const int row = q * 32 + lane;
-    float* wb = bias_smem + q * 256;
+    float* wb = bias_smem + (warp - 2) * 128;
     ConvEpiState<C> st;
     st.reset();
     st.cur_batch = -1;
@@ -217,12 +241,13 @@ conv3x3_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         __syncwarp();
       }
       for (int ot = 0; ot < u.rows; ++ot, ++tile) {
+        if ((tile & kGrpMask) != grp) continue;
         const uint32_t buf = tile % NB, use = tile / NB;
         const int64_t addr0 = ((((int64_t)u.b * p.T + (u.t0 + ot)) * p.W) + u.w0 + row) * C;
         mbar_wait(bar_afull + 8 * buf, use & 1, 15);
         tc_fence_after();
         const uint32_t trow = tmem_base + ((uint32_t)(q * 32) << 16) + buf * C;
-        conv_epilogue_tile<C, C>(trow, wb, p.act, p.add, p.out, addr0, true, p.stats != nullptr, st);
+        if (!(p.dbg & 2)) conv_epilogue_tile<C, C>(trow, wb, p.act, p.add, p.out, addr0, !(p.dbg & 16), p.stats != nullptr, st);
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(bar_aempty + 8 * buf);
@@ -231,9 +256,9 @@ conv3x3_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     st.flush(p.stats, lane);
   } else if (fused) {
     // ================================================================ transform: GroupNorm affine (+SiLU) in place
-    // Each of the four warps owns every fourth row strip, so four rows are in flight and one warp's load->math->store
+    // Each of the eight warps owns every eighth row strip, so eight rows are in flight and one warp's load->math->store
     // latency chain overlaps with the others'.  Lane -> (position, 16-byte chunk) with a fixed logical chunk per lane.
-    const int tw = warp - 6;
+    const int tw = warp - (2 + kWideEpiWarps);
     constexpr int CH = C / 8;                           // 16-byte chunks per position
     const int j = lane % CH;                            // logical chunk (channels 8j .. 8j+7), fixed per lane
     const int p0 = lane / CH;
@@ -267,7 +292,7 @@ conv3x3_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       }
       const bool left_edge = (u.w0 == 0), right_edge = (u.w0 + 128 == p.W);
       for (int rr = 0; rr < u.rows + 2; ++rr, ++cnt) {
-        if ((int)(cnt & 3) != tw) continue;
+        if ((int)(cnt % kWideXfWarps) != tw) continue;
         const uint32_t slot = cnt % NS, use = cnt / NS;
         const int t = u.t0 - 1 + rr;
         const bool row_ok = (t >= 0) && (t < p.T);

@@ -96,7 +96,7 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
   if (nmine > 0) {
     if (warp == 0) {
       // ================================================================ TMA producer
-      if (lane == 0) {
+      if (elect_one()) {
         const uint32_t x_atom_bytes = (uint32_t)(kTnChunk * p.x_at * 2), y_atom_bytes = (uint32_t)(kTnChunk * p.y_at * 2);
         const uint32_t tx = (uint32_t)m_atoms * x_atom_bytes + (uint32_t)n_atoms * y_atom_bytes;
         int stage = 0;
@@ -125,8 +125,8 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
         }
       }
     } else if (warp == 1) {
-      // ================================================================ MMA issuer (single thread)
-      if (lane == 0) {
+      // ================================================================ MMA issuer (one elected thread: common.cuh elect_one)
+      if (elect_one()) {
         const uint32_t n_cols = (uint32_t)(n_atoms * p.y_at);
         // kind::f16, D = f32, A = B = bf16, both operands MN-major (bits 15, 16)
         const uint32_t idesc = make_idesc_bf16(128, n_cols) | (1u << 15) | (1u << 16);

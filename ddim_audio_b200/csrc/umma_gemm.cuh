@@ -237,7 +237,7 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 
   if (warp == 0) {
     // ================================================================ TMA producer
-    if (lane == 0) {
+    if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
       TileIter it;
@@ -269,8 +269,8 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       }
     }
   } else if (warp == 1) {
-    // ================================================================ MMA issuer (single thread)
-    if (lane == 0) {
+    // ================================================================ MMA issuer (one elected thread: common.cuh elect_one)
+    if (elect_one()) {
       const uint32_t idesc = make_idesc_bf16(kTileM, (uint32_t)p.n_seg);
       int stage = 0;
       uint32_t phase = 0;
