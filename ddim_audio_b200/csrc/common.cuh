@@ -96,6 +96,45 @@ __device__ __forceinline__ float2 unpack_bf16x2(uint32_t u) {
   return __bfloat1622float2(v);
 }
 
+// ---------------------------------------------------------------- packed fp32x2 math (sm_100: FFMA2 / FADD2, one issue slot for two lanes of work)
+__device__ __forceinline__ uint64_t pack2(float lo, float hi) {
+  uint64_t d;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "f"(lo), "f"(hi));
+  return d;
+}
+__device__ __forceinline__ uint64_t pack2u(uint32_t lo, uint32_t hi) {
+  uint64_t d;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "r"(lo), "r"(hi));
+  return d;
+}
+__device__ __forceinline__ float2 unpack2(uint64_t v) {
+  float2 r;
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(r.x), "=f"(r.y) : "l"(v));
+  return r;
+}
+__device__ __forceinline__ uint64_t ffma2(uint64_t a, uint64_t b, uint64_t c) {
+  uint64_t d;
+  asm("fma.rn.ftz.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+__device__ __forceinline__ uint64_t fadd2(uint64_t a, uint64_t b) {
+  uint64_t d;
+  asm("add.rn.ftz.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+// two bf16 (one 32-bit word) -> fp32x2
+__device__ __forceinline__ uint64_t bf16x2_to_f32x2(uint32_t w) { return pack2u(w << 16, w & 0xffff0000u); }
+// fp32x2 -> two bf16 (round to nearest even)
+__device__ __forceinline__ uint32_t f32x2_to_bf16x2(uint64_t v) {
+  const float2 f = unpack2(v);
+  return pack_bf16x2(f.x, f.y);
+}
+// SiLU of 2u given u = x/2:  x * sigmoid(x) = u * tanh(u) + u   (one MUFU per value, one FFMA2 per pair)
+__device__ __forceinline__ uint64_t silu2_from_half(uint64_t u) {
+  const float2 f = unpack2(u);
+  return ffma2(u, pack2(tanh_approx(f.x), tanh_approx(f.y)), u);
+}
+
 // 128-bit streaming load / store
 __device__ __forceinline__ uint4 ldg_nc_v4(const void* p) {
   uint4 r;

@@ -7,8 +7,8 @@
 // is what the reference's zero padding of the ACTIVATED tensor means); then all 9 taps are tcgen05.mma's whose A descriptors
 // simply start kx rows further into slot (t + ky - 1) -- the swizzle is a function of the absolute shared-memory address,
 // so a row-shifted start needs no re-layout (tools/umma_probe.cu).  The 9 weight tiles stay resident in shared memory.
-// Warp roles (576 threads): 0 = TMA producer, 1 = MMA issuer, 2-9 = epilogue (two warps per TMEM lane quarter, alternating
-// output rows), 10-17 = transform (every eighth row strip each).  The epilogue and transform warps are latency-bound
+// Warp roles (512 threads, 128 registers each): 0 = TMA producer, 1 = MMA issuer, 2-9 = epilogue (two warps per TMEM lane quarter, alternating
+// output rows), 10-15 = transform (every sixth row strip each).  The epilogue and transform warps are latency-bound
 // dependent chains (ncu: one warp of each per scheduler issued every ~6 cycles), so each scheduler gets two of each.
 #pragma once
 #include "umma_gemm.cuh"
@@ -19,7 +19,7 @@ namespace ddimb {
 #define DDIMB_WIDE_EPI 8
 #endif
 #ifndef DDIMB_WIDE_XF
-#define DDIMB_WIDE_XF 8
+#define DDIMB_WIDE_XF 6
 #endif
 constexpr int kWideEpiWarps = DDIMB_WIDE_EPI, kWideXfWarps = DDIMB_WIDE_XF;   // 4 or 8 epilogue warps
 constexpr int kWideThreads = 32 * (2 + kWideEpiWarps + kWideXfWarps);
@@ -235,14 +235,10 @@ conv3x3_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       if (u.b != st.cur_batch) {
         st.flush(p.stats, lane);
         st.cur_batch = u.b;
-        __syncwarp();
-        for (int c = lane; c < C; c += 32)
-          wb[c] = (p.bias ? p.bias[c] : 0.f) + (p.bias_b ? p.bias_b[(int64_t)u.b * p.bias_b_stride + c] : 0.f);
-        __syncwarp();
+        conv_epilogue_bias<C>(wb, p.bias, p.bias_b, u.b, p.bias_b_stride, p.act, lane);
       }
-      for (int ot = 0; ot < u.rows; ++ot, ++tile) {
-        if ((tile & kGrpMask) != grp) continue;
-        const uint32_t buf = tile % NB, use = tile / NB;
+      for (int ot = (int)((grp - tile) & kGrpMask); ot < u.rows; ot += (int)kGrpMask + 1) {   // this group's output rows only
+        const uint32_t buf = (tile + ot) % NB, use = (tile + ot) / NB;
         const int64_t addr0 = ((((int64_t)u.b * p.T + (u.t0 + ot)) * p.W) + u.w0 + row) * C;
         mbar_wait(bar_afull + 8 * buf, use & 1, 15);
         tc_fence_after();
@@ -252,6 +248,7 @@ conv3x3_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         __syncwarp();
         if (lane == 0) mbar_arrive(bar_aempty + 8 * buf);
       }
+      tile += (uint32_t)u.rows;
     }
     st.flush(p.stats, lane);
   } else if (fused) {
@@ -266,7 +263,8 @@ conv3x3_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     constexpr int NIT = (kWidePos + PSTEP - 1) / PSTEP;
     constexpr int BATCH = 6;                            // 16-byte loads in flight per lane
     float* tab = gn_smem + tw * 2 * C;                  // this warp's [scale C | shift C]
-    float sc[8], sh[8];
+    uint64_t sc2[4], sh2[4];                            // (scale, shift) pairs of this lane's 8 channels; pre-halved when SiLU follows
+    const float pre = (p.prologue == 2) ? 0.5f : 1.0f;  // silu(a) = u*tanh(u)+u with u = a/2
     int cur_b = -1;
     uint32_t cnt = 0;
     WideUnit u;
@@ -283,12 +281,12 @@ conv3x3_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           if (var < 0) var = 0;
           const float rstd = (float)(1.0 / sqrt(var + (double)p.eps));
           const float s = p.gn_gamma[c] * rstd;
-          tab[c] = s;
-          tab[C + c] = (p.gn_beta ? p.gn_beta[c] : 0.f) - (float)mean * s;
+          tab[c] = pre * s;
+          tab[C + c] = pre * ((p.gn_beta ? p.gn_beta[c] : 0.f) - (float)mean * s);
         }
         __syncwarp();
 #pragma unroll
-        for (int e = 0; e < 8; ++e) { sc[e] = tab[8 * j + e]; sh[e] = tab[C + 8 * j + e]; }
+        for (int e = 0; e < 4; ++e) { sc2[e] = pack2(tab[8 * j + 2 * e], tab[8 * j + 2 * e + 1]); sh2[e] = pack2(tab[C + 8 * j + 2 * e], tab[C + 8 * j + 2 * e + 1]); }
       }
       const bool left_edge = (u.w0 == 0), right_edge = (u.w0 + 128 == p.W);
       for (int rr = 0; rr < u.rows + 2; ++rr, ++cnt) {
@@ -320,10 +318,9 @@ conv3x3_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                 uint32_t w4[4] = {v[i].x, v[i].y, v[i].z, v[i].w};
 #pragma unroll
                 for (int e = 0; e < 4; ++e) {
-                  const float2 x2 = unpack_bf16x2(w4[e]);
-                  float a = fmaf(x2.x, sc[2 * e], sh[2 * e]), b2 = fmaf(x2.y, sc[2 * e + 1], sh[2 * e + 1]);
-                  if (p.prologue == 2) { a = silu_fast(a); b2 = silu_fast(b2); }
-                  w4[e] = zero ? 0u : pack_bf16x2(a, b2);
+                  uint64_t a2 = ffma2(bf16x2_to_f32x2(w4[e]), sc2[e], sh2[e]);
+                  if (p.prologue == 2) a2 = silu2_from_half(a2);
+                  w4[e] = zero ? 0u : f32x2_to_bf16x2(a2);
                 }
                 *reinterpret_cast<uint4*>(sb + off[i]) = make_uint4(w4[0], w4[1], w4[2], w4[3]);
               }

@@ -110,33 +110,51 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
 }
 
 // Epilogue state of one thread (= one accumulator row) of a convolution: GroupNorm partial sums stay in registers across
-// tiles and are reduced (warp shuffle, then one double atomicAdd per value per warp) only when the sample changes.
+// tiles (as fp32x2 pairs, so they are fed by FADD2 / FFMA2) and are reduced (warp shuffle, then one double atomicAdd per value
+// per warp) only when the sample changes.
 template <int CMOD>
 struct ConvEpiState {
-  float sacc[16];
+  uint64_t s1[8], s2[8];   // per group: (sum, sum) and (sum of squares, sum of squares) over even / odd channels
   int cur_batch;
   __device__ __forceinline__ void reset() {
 #pragma unroll
-    for (int k = 0; k < 16; ++k) sacc[k] = 0.f;
+    for (int k = 0; k < 8; ++k) { s1[k] = 0ull; s2[k] = 0ull; }
   }
   __device__ __forceinline__ void flush(double* stats, int lane) {
     if (cur_batch < 0 || stats == nullptr) return;
 #pragma unroll
-    for (int k = 0; k < 16; ++k) {
-      const float v = warp_sum(sacc[k]);
-      if (lane == 0) atomicAdd(stats + (int64_t)cur_batch * 16 + k, (double)v);
+    for (int k = 0; k < 8; ++k) {
+      const float2 a = unpack2(s1[k]), b = unpack2(s2[k]);
+      const float v1 = warp_sum(a.x + a.y), v2 = warp_sum(b.x + b.y);
+      if (lane == 0) {
+        atomicAdd(stats + (int64_t)cur_batch * 16 + 2 * k, (double)v1);
+        atomicAdd(stats + (int64_t)cur_batch * 16 + 2 * k + 1, (double)v2);
+      }
     }
     reset();
   }
 };
 
+// This warp's shared-memory copy of the per-channel epilogue bias of sample `batch`: (bias + temb slice) * s, where s = 0.5
+// when the epilogue applies SiLU (conv_epilogue_tile evaluates it as u*tanh(u)+u on u = (x+b)/2) and 1 otherwise.
+template <int CMOD>
+__device__ __forceinline__ void conv_epilogue_bias(float* wb, const float* bias, const float* bias_b, int64_t batch, int bias_b_stride, int act, int lane) {
+  const float s = (act == 1) ? 0.5f : 1.0f;
+  __syncwarp();
+  for (int c = lane; c < CMOD; c += 32) wb[c] = s * ((bias ? bias[c] : 0.f) + (bias_b ? bias_b[batch * bias_b_stride + c] : 0.f));
+  __syncwarp();
+}
+
 // One tile of the convolution epilogue: TMEM -> registers -> + (bias + temb) -> activation -> + skip -> bf16 NHWC store,
 // GroupNorm partial sums of the stored values.  NACC accumulator columns, column c is channel c % CMOD; wb = this warp's
-// shared-memory copy of the combined per-channel bias of the current sample.
+// shared-memory bias copy (conv_epilogue_bias).  All arithmetic is packed fp32x2: per element 1/2 FFMA2 (bias), 1 MUFU +
+// 1/2 FFMA2 (SiLU), 1/2 F2FP (pack), 1/2 FADD2 + 1/2 FFMA2 (statistics).
 template <int NACC, int CMOD>
 __device__ __forceinline__ void conv_epilogue_tile(uint32_t trow, const float* wb, int act, const __nv_bfloat16* add, __nv_bfloat16* out,
                                                    int64_t addr0, bool valid, bool want_stats, ConvEpiState<CMOD>& st) {
   constexpr int CG = CMOD / 8;   // channels per GroupNorm group (multiple of 4)
+  const float sf = (act == 1) ? 0.5f : 1.0f;
+  const uint64_t s2x = pack2(sf, sf);
 #pragma unroll
   for (int c0 = 0; c0 < NACC; c0 += 32) {
     uint32_t v[32];
@@ -147,47 +165,46 @@ __device__ __forceinline__ void conv_epilogue_tile(uint32_t trow, const float* w
       for (int q = 0; q < 4; ++q) av[q] = ldg_nc_v4(add + addr0 + c0 + 8 * q);
     }
     tmem_ld_wait();
-    float f[32];
+    uint64_t f[16];
 #pragma unroll
-    for (int j = 0; j < 32; j += 4) {
-      const float4 b4 = *reinterpret_cast<const float4*>(wb + ((c0 + j) % CMOD));
-      f[j] = __uint_as_float(v[j]) + b4.x; f[j + 1] = __uint_as_float(v[j + 1]) + b4.y;
-      f[j + 2] = __uint_as_float(v[j + 2]) + b4.z; f[j + 3] = __uint_as_float(v[j + 3]) + b4.w;
+    for (int j = 0; j < 16; j += 2) {
+      const ulonglong2 b4 = *reinterpret_cast<const ulonglong2*>(wb + ((c0 + 2 * j) % CMOD));
+      f[j] = ffma2(pack2u(v[2 * j], v[2 * j + 1]), s2x, b4.x);
+      f[j + 1] = ffma2(pack2u(v[2 * j + 2], v[2 * j + 3]), s2x, b4.y);
     }
     if (act == 1) {
 #pragma unroll
-      for (int j = 0; j < 32; ++j) f[j] = silu_fast(f[j]);
+      for (int j = 0; j < 16; ++j) f[j] = silu2_from_half(f[j]);
     }
     if (add != nullptr && valid) {
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
         const uint32_t aw[4] = {av[q].x, av[q].y, av[q].z, av[q].w};
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const float2 t2 = unpack_bf16x2(aw[j]);
-          f[8 * q + 2 * j] += t2.x; f[8 * q + 2 * j + 1] += t2.y;
-        }
+        for (int j = 0; j < 4; ++j) f[4 * q + j] = fadd2(f[4 * q + j], bf16x2_to_f32x2(aw[j]));
       }
     }
     if (valid) {
       __nv_bfloat16* op = out + addr0 + c0;
 #pragma unroll
       for (int q = 0; q < 4; ++q)
-        stg_v4(op + 8 * q, make_uint4(pack_bf16x2(f[8 * q], f[8 * q + 1]), pack_bf16x2(f[8 * q + 2], f[8 * q + 3]),
-                                      pack_bf16x2(f[8 * q + 4], f[8 * q + 5]), pack_bf16x2(f[8 * q + 6], f[8 * q + 7])));
+        stg_v4(op + 8 * q, make_uint4(f32x2_to_bf16x2(f[4 * q]), f32x2_to_bf16x2(f[4 * q + 1]), f32x2_to_bf16x2(f[4 * q + 2]),
+                                      f32x2_to_bf16x2(f[4 * q + 3])));
       if (want_stats) {
         if (act == 3) {
           // training: the PRE-activation was stored (its SiLU derivative is needed in backward); the following GroupNorm
           // normalises silu(value), so the statistics are those of silu(value)
 #pragma unroll
-          for (int j = 0; j < 32; ++j) f[j] = silu_fast(__bfloat162float(__float2bfloat16_rn(f[j])));
+          for (int j = 0; j < 16; ++j) {
+            const float2 t = unpack2(f[j]);
+            f[j] = pack2(silu_fast(__bfloat162float(__float2bfloat16_rn(t.x))), silu_fast(__bfloat162float(__float2bfloat16_rn(t.y))));
+          }
         }
 #pragma unroll
-        for (int j = 0; j < 32; j += 4) {
-          const int g = ((c0 + j) % CMOD) / CG;   // compile-time after unrolling
-          float s1 = (f[j] + f[j + 1]) + (f[j + 2] + f[j + 3]);
-          float s2 = fmaf(f[j], f[j], fmaf(f[j + 1], f[j + 1], fmaf(f[j + 2], f[j + 2], f[j + 3] * f[j + 3])));
-          st.sacc[2 * g] += s1; st.sacc[2 * g + 1] += s2;
+        for (int j = 0; j < 16; ++j) {
+          const int g = ((c0 + 2 * j) % CMOD) / CG;   // compile-time after unrolling
+          st.s1[g] = fadd2(st.s1[g], f[j]);
+          st.s2[g] = ffma2(f[j], f[j], st.s2[g]);
         }
       }
     }
@@ -337,10 +354,7 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         if (batch != st.cur_batch) {
           st.flush(p.stats, lane);
           st.cur_batch = batch;
-          __syncwarp();
-          for (int c = lane; c < CMOD; c += 32)
-            wb[c] = (p.bias ? p.bias[c] : 0.f) + (p.bias_b ? p.bias_b[(int64_t)batch * p.bias_b_stride + c] : 0.f);
-          __syncwarp();
+          conv_epilogue_bias<CMOD>(wb, p.bias, p.bias_b, batch, p.bias_b_stride, p.act, lane);
         }
         const int buf = local % p.num_acc_bufs;
         const uint32_t use = (uint32_t)(local / p.num_acc_bufs);
