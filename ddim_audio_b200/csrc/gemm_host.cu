@@ -6,6 +6,7 @@
 #include "../../include/ddim_b200.h"
 #include "umma_gemm.cuh"
 #include "conv_wide.cuh"
+#include "conv_window.cuh"
 
 using namespace ddimb;
 
@@ -160,6 +161,57 @@ extern "C" int ddimb_conv3x3_gn(const void* x, const double* gn_stats, const flo
   return launch_conv_wide(x, gn_stats, gn_gamma, gn_beta, gn_eps, gn_mode, w, bias, bias_b, bias_b_stride, act, add, out, stats, B, T, W, C, stream);
 }
 
+// ------------------------------------------------------------------------------------------------ window 3x3 conv (C = 96)
+// csrc/conv_window.cuh.  The weight operand keeps the ABI layout ([Cout][9 * Cin], K-major); its pre-swizzled tile image is
+// rebuilt into a per-device scratch buffer by a 27-block kernel ahead of every launch (166 KB: noise next to the conv, and
+// never stale when the weights are updated in place).  Launches are assumed to be stream-ordered per device.
+static int win_smem_bytes(int W, int* nr, int* plane) {
+  const int WP = W + 2;
+  *nr = 3 + ceil_div(257, WP);
+  *plane = ceil_div(*nr * WP * 64, 1024) * 1024;
+  return 1024 + 2 * kWinChunks * *plane + kWinBStages * kWinBStage + kWinAux;
+}
+
+static bool conv_window_supported(int Cin, int Cout, int W) {
+  static const bool off = getenv("DDIMB_NO_WINDOW") != nullptr;
+  int nr, plane;
+  return !off && Cin == kWinC && Cout == kWinC && W + 2 <= 256 && win_smem_bytes(W, &nr, &plane) <= 232448 && nr <= 256;
+}
+
+static int launch_conv_window(const void* x, const void* w, const float* bias, const float* bias_b, int bias_b_stride, int act, const void* add,
+                              void* out, double* stats, int B, int T, int W, cudaStream_t stream) {
+  static uint8_t* scratch[64] = {nullptr};
+  int dev = 0;
+  DDIMB_CUDA(cudaGetDevice(&dev));
+  DDIMB_CHECK_ARG(dev >= 0 && dev < 64);
+  if (!scratch[dev]) DDIMB_CUDA(cudaMalloc(&scratch[dev], 9 * kWinChunks * kWinBStage));
+  win_swizzle_weights_kernel<<<9 * kWinChunks, 256, 0, stream>>>(reinterpret_cast<const __nv_bfloat16*>(w), scratch[dev]);
+  DDIMB_LAUNCH_CHECK();
+  WinParams p;
+  memset(&p, 0, sizeof(p));
+  p.B = B; p.T = T; p.W = W; p.WP = W + 2;
+  const int smem = win_smem_bytes(W, &p.NR, &p.plane_bytes);
+  p.units_per_b = ceil_div(T * p.WP, kWinUnit);
+  p.num_units = B * p.units_per_b;
+  p.wswz = scratch[dev];
+  p.out = reinterpret_cast<__nv_bfloat16*>(out); p.add = reinterpret_cast<const __nv_bfloat16*>(add);
+  p.bias = bias; p.bias_b = bias_b; p.stats = stats; p.bias_b_stride = bias_b_stride; p.act = act;
+  CUtensorMap tmA;
+  {
+    uint64_t dims[4] = {(uint64_t)kWinC, (uint64_t)W, (uint64_t)T, (uint64_t)B};
+    uint64_t str[3] = {(uint64_t)kWinC, (uint64_t)W * kWinC, (uint64_t)T * W * kWinC};
+    uint32_t box[4] = {32, (uint32_t)p.WP, (uint32_t)p.NR, 1};
+    int r = make_tmap_bf16(&tmA, x, 4, dims, str, box, 32);
+    if (r) return r;
+  }
+  static bool attr = false;
+  if (!attr) { DDIMB_CUDA(cudaFuncSetAttribute(conv3x3_window_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448)); attr = true; }
+  const int grid = p.num_units < ddimb_num_sms() ? p.num_units : ddimb_num_sms();
+  conv3x3_window_kernel<<<grid, kWinThreads, smem, stream>>>(tmA, p);
+  DDIMB_LAUNCH_CHECK();
+  return DDIMB_OK;
+}
+
 // ------------------------------------------------------------------------------------------------ Conv2d 3x3 s1 p1
 // reference: models/diffusion.py:28-40 (Residual_Block.conv), evaluated on NHWC bf16.
 extern "C" int ddimb_conv3x3(const void* x, const void* w, const float* bias, const float* bias_b, int bias_b_stride, int act,
@@ -172,6 +224,8 @@ extern "C" int ddimb_conv3x3(const void* x, const void* w, const float* bias, co
   DDIMB_CHECK_ARG(Cin % 32 == 0 && Cout % 32 == 0 && Cout <= 256 && Cin <= 256);
   if (ddimb_conv3x3_wide_supported(Cin, Cout, W))
     return launch_conv_wide(x, nullptr, nullptr, nullptr, 0.f, 0, w, bias, bias_b, bias_b_stride, act, add, out, stats, B, T, W, Cin, stream);
+  if (conv_window_supported(Cin, Cout, W))
+    return launch_conv_window(x, w, bias, bias_b, bias_b_stride, act, add, out, stats, B, T, W, stream);
   const int ck = pick_ck(Cin);
   int bw, bt;
   spatial_tile(T, W, &bw, &bt);

@@ -149,12 +149,28 @@ __device__ __forceinline__ void conv_epilogue_bias(float* wb, const float* bias,
 // GroupNorm partial sums of the stored values.  NACC accumulator columns, column c is channel c % CMOD; wb = this warp's
 // shared-memory bias copy (conv_epilogue_bias).  All arithmetic is packed fp32x2: per element 1/2 FFMA2 (bias), 1 MUFU +
 // 1/2 FFMA2 (SiLU), 1/2 F2FP (pack), 1/2 FADD2 + 1/2 FFMA2 (statistics).
+// `stage` (optional): 2 KB of shared memory private to the calling warp.  A thread owns one position, so a direct 16-byte
+// store instruction touches 32 different cache lines (one per lane); staged, each 32-channel chunk goes through shared memory
+// and is written so that four consecutive lanes cover the 64 contiguous bytes of one position: 8 line segments per
+// instruction instead of 32 (the LSU wavefront count, not HBM, bounded the epilogue warps: ncu lg/mio throttle).
 template <int NACC, int CMOD>
 __device__ __forceinline__ void conv_epilogue_tile(uint32_t trow, const float* wb, int act, const __nv_bfloat16* add, __nv_bfloat16* out,
-                                                   int64_t addr0, bool valid, bool want_stats, ConvEpiState<CMOD>& st) {
+                                                   int64_t addr0, bool valid, bool want_stats, ConvEpiState<CMOD>& st,
+                                                   uint8_t* stage = nullptr) {
   constexpr int CG = CMOD / 8;   // channels per GroupNorm group (multiple of 4)
   const float sf = (act == 1) ? 0.5f : 1.0f;
   const uint64_t s2x = pack2(sf, sf);
+  const int lane_ = threadIdx.x & 31;
+  int64_t saddr[4];
+  bool svalid[4];
+  if (stage != nullptr) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {                 // store iteration i: this lane writes granule (lane & 3) of position 8 i + lane / 4
+      const int src = 8 * i + (lane_ >> 2);
+      saddr[i] = __shfl_sync(0xffffffffu, addr0, src) + (lane_ & 3) * 8;
+      svalid[i] = __shfl_sync(0xffffffffu, (int)valid, src) != 0;
+    }
+  }
 #pragma unroll
   for (int c0 = 0; c0 < NACC; c0 += 32) {
     uint32_t v[32];
@@ -184,12 +200,29 @@ __device__ __forceinline__ void conv_epilogue_tile(uint32_t trow, const float* w
         for (int j = 0; j < 4; ++j) f[4 * q + j] = fadd2(f[4 * q + j], bf16x2_to_f32x2(aw[j]));
       }
     }
-    if (valid) {
-      __nv_bfloat16* op = out + addr0 + c0;
+    if (stage != nullptr) {
+      // position-major 64-byte rows, 16-byte granule index XOR (position >> 1) & 3: conflict-free for both access patterns
+      __syncwarp();
 #pragma unroll
       for (int q = 0; q < 4; ++q)
-        stg_v4(op + 8 * q, make_uint4(f32x2_to_bf16x2(f[4 * q]), f32x2_to_bf16x2(f[4 * q + 1]), f32x2_to_bf16x2(f[4 * q + 2]),
-                                      f32x2_to_bf16x2(f[4 * q + 3])));
+        *reinterpret_cast<uint4*>(stage + lane_ * 64 + ((q ^ ((lane_ >> 1) & 3)) << 4)) =
+            make_uint4(f32x2_to_bf16x2(f[4 * q]), f32x2_to_bf16x2(f[4 * q + 1]), f32x2_to_bf16x2(f[4 * q + 2]), f32x2_to_bf16x2(f[4 * q + 3]));
+      __syncwarp();
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int pos = 8 * i + (lane_ >> 2);
+        const uint4 v4 = *reinterpret_cast<const uint4*>(stage + pos * 64 + (((lane_ & 3) ^ ((pos >> 1) & 3)) << 4));
+        if (svalid[i]) stg_v4(out + saddr[i] + c0, v4);
+      }
+    }
+    if (valid) {
+      if (stage == nullptr) {
+        __nv_bfloat16* op = out + addr0 + c0;
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+          stg_v4(op + 8 * q, make_uint4(f32x2_to_bf16x2(f[4 * q]), f32x2_to_bf16x2(f[4 * q + 1]), f32x2_to_bf16x2(f[4 * q + 2]),
+                                        f32x2_to_bf16x2(f[4 * q + 3])));
+      }
       if (want_stats) {
         if (act == 3) {
           // training: the PRE-activation was stored (its SiLU derivative is needed in backward); the following GroupNorm

@@ -61,6 +61,8 @@ def test_linear_strided_operand_and_lo_plane(ops):
 CONV_CASES = [  # (C, W, T, B)
     (32, 256, 8, 1), (32, 256, 5, 2), (64, 128, 16, 3), (96, 64, 8, 1), (128, 32, 12, 2), (192, 16, 10, 1), (256, 8, 4, 3),
     (256, 8, 1, 1), (128, 32, 1, 1),
+    # C = 96 runs the flattened-window kernel (csrc/conv_window.cuh): unit boundaries inside a row, ragged last unit, tiny images
+    (96, 64, 33, 3), (96, 64, 1, 2), (96, 64, 130, 2), (96, 32, 7, 2), (96, 16, 5, 1),
 ]
 
 
