@@ -56,7 +56,9 @@ struct WideCfg {
   static constexpr int kWBytes = 9 * C * C * 2;
   static constexpr int kSwizzle = (C == 64) ? 2 : 4;
   static constexpr int kSBO = 8 * kRowBytes;
-  static constexpr int kAuxBytes = 1024 + 4096 + kWideXfWarps * C * 8;   // barriers | epilogue bias copies | transform scale/shift copies
+  static constexpr int kXfTabBytes = ((kWideXfWarps * C * 8 + 1023) / 1024) * 1024;
+  static constexpr bool kStage = (C == 32);           // smem-staged epilogue stores (C = 64 has no room beside an 8-row ring; measured neutral here)
+  static constexpr int kAuxBytes = 1024 + 4096 + kXfTabBytes + (kStage ? kWideEpiWarps * 2048 : 0);   // barriers | epilogue bias copies | transform scale/shift copies | store staging
   static constexpr int kSmemBytes = 1024 + kWBytes + kSlots * kSlotBytes + kAuxBytes;
 };
 
@@ -225,6 +227,7 @@ conv3x3_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     constexpr uint32_t kGrpMask = kWideEpiWarps / 4 - 1;
     const int row = q * 32 + lane;
     float* wb = bias_smem + (warp - 2) * 128;
+    uint8_t* stage = aux_gen + 1024 + 4096 + Cfg::kXfTabBytes + (warp - 2) * 2048;
     ConvEpiState<C> st;
     st.reset();
     st.cur_batch = -1;
@@ -243,7 +246,7 @@ conv3x3_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         mbar_wait(bar_afull + 8 * buf, use & 1, 15);
         tc_fence_after();
         const uint32_t trow = tmem_base + ((uint32_t)(q * 32) << 16) + buf * C;
-        if (!(p.dbg & 2)) conv_epilogue_tile<C, C>(trow, wb, p.act, p.add, p.out, addr0, !(p.dbg & 16), p.stats != nullptr, st);
+        if (!(p.dbg & 2)) conv_epilogue_tile<C, C>(trow, wb, p.act, p.add, p.out, addr0, !(p.dbg & 16), p.stats != nullptr, st, (!Cfg::kStage || (p.dbg & 32)) ? nullptr : stage);
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(bar_aempty + 8 * buf);

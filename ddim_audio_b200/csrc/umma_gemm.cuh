@@ -70,7 +70,7 @@ struct GemmSmem {
   __host__ __device__ static int stage_bytes(int b_rows, int kps) { return kps * (kABytes + b_rows * CK * 2); }
 };
 
-constexpr int kGemmAuxBytes = 1024 + 4096;  // barriers, tmem pointer, per-warp bias copies
+constexpr int kGemmAuxBytes = 1024 + 4096 + 4 * 2048;  // barriers, tmem pointer | per-warp bias copies | per-warp store staging
 
 // Mixed-radix tile counter (W tiles, T tiles, dim-3 tiles, batch, N tiles) advanced by gridDim.x per step without any
 // division: the step is decomposed once, every digit then carries at most 1.
@@ -375,6 +375,7 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     if constexpr (NACC > 0) {
       // ---------------- convolution epilogue
       float* wb = bias_smem + q * 256;
+      uint8_t* stage = reinterpret_cast<uint8_t*>(bias_smem) + 4096 + q * 2048;
       ConvEpiState<CMOD> st;
       st.reset();
       st.cur_batch = -1;
@@ -394,7 +395,7 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         mbar_wait(bar_tfull + 8 * buf, use & 1, 4);
         tc_fence_after();
         const uint32_t trow = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * NACC);
-        conv_epilogue_tile<NACC, CMOD>(trow, wb, p.act, p.add, out, addr0, valid, p.stats != nullptr, st);
+        conv_epilogue_tile<NACC, CMOD>(trow, wb, p.act, p.add, out, valid ? addr0 : 0, valid, p.stats != nullptr, st, stage);
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(bar_tempty + 8 * buf);
