@@ -7,6 +7,7 @@
 //     3-row fp32 ring of (x + skip) in shared memory (each input row read from HBM once, halo columns included);
 //   * conv_in's GroupNorm partial sums stay in registers for the whole strip (one set of fp64 atomics per CTA).
 // The constant bank is process-global: calls on DIFFERENT streams with different weights must not overlap.
+#include <stdlib.h>
 #include "../../include/ddim_b200.h"
 #include "common.cuh"
 
@@ -215,11 +216,15 @@ extern "C" int ddimb_conv_in(const float* x, const float* w, const float* bias, 
   return DDIMB_OK;
 }
 
+int ddimb_conv_out_tc(const void* x, const void* skip, const float* w, const float* bias, float* out, int B, int T, int F, cudaStream_t stream);
+
 // models/diffusion.py:284,199-208 -- Conv2d(32 -> 2, k3 p1) of (x + skip): x, skip (nullable) bf16 NHWC, w fp32 [2][32][3][3], out fp32 NCHW.
 extern "C" int ddimb_conv_out(const void* x, const void* skip, const float* w, const float* bias, float* out, int B, int T, int F,
                               int Cin, int Cout, cudaStream_t stream) {
   DDIMB_CHECK_ARG(x && w && bias && out && B >= 1 && Cin == 32 && Cout == 2 && B <= 65535);
   DDIMB_PROF(stream, "conv_out", Cin, Cout, (double)B * T * F * (2.0 * Cin * (skip ? 2 : 1) + 4.0 * Cout), 18.0 * Cin * Cout * B * T * F);
+  if (F % 128 == 0 && getenv("DDIMB_NO_CONVOUT_TC") == nullptr)   // tensor-core path (csrc/conv_out_tc.cuh); the strip kernel below covers ragged F
+    return ddimb_conv_out_tc(x, skip, w, bias, out, B, T, F, stream);
   DDIMB_CUDA(cudaMemcpyToSymbolAsync(c_w_out, w, sizeof(float) * 2 * 32 * 9, 0, cudaMemcpyDeviceToDevice, stream));
   DDIMB_CUDA(cudaMemcpyToSymbolAsync(c_w_out, bias, sizeof(float) * 2, sizeof(float) * 2 * 32 * 9, cudaMemcpyDeviceToDevice, stream));
   const int strips = (F + 127) / 128;

@@ -55,12 +55,6 @@ __global__ void __launch_bounds__(256) win_swizzle_weights_kernel(const __nv_bfl
   }
 }
 
-__device__ __forceinline__ void bulk_load(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
-  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst), "l"(src), "r"(bytes),
-               "r"(bar)
-               : "memory");
-}
-
 struct WinUnit {
   int b, p0, t_lo, off0;
   __device__ __forceinline__ void set(const WinParams& p, int u) {
@@ -136,7 +130,7 @@ conv3x3_window_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
           const uint32_t s = cnt % kWinBStages, use = cnt / kWinBStages;
           mbar_wait(bar_bempty + 8 * s, (use & 1) ^ 1, 32);
           mbar_arrive_expect_tx(bar_bfull + 8 * s, (uint32_t)kWinBStage);
-          bulk_load(b_base + s * kWinBStage, p.wswz + (int64_t)tile * kWinBStage, (uint32_t)kWinBStage, bar_bfull + 8 * s);
+          bulk_load_g2s(b_base + s * kWinBStage, p.wswz + (int64_t)tile * kWinBStage, (uint32_t)kWinBStage, bar_bfull + 8 * s);
         }
       }
     }

@@ -7,6 +7,7 @@
 #include "umma_gemm.cuh"
 #include "conv_wide.cuh"
 #include "conv_window.cuh"
+#include "conv_out_tc.cuh"
 
 using namespace ddimb;
 
@@ -208,6 +209,41 @@ static int launch_conv_window(const void* x, const void* w, const float* bias, c
   if (!attr) { DDIMB_CUDA(cudaFuncSetAttribute(conv3x3_window_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448)); attr = true; }
   const int grid = p.num_units < ddimb_num_sms() ? p.num_units : ddimb_num_sms();
   conv3x3_window_kernel<<<grid, kWinThreads, smem, stream>>>(tmA, p);
+  DDIMB_LAUNCH_CHECK();
+  return DDIMB_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ conv_out on the tensor cores
+// csrc/conv_out_tc.cuh; called by ddimb_conv_out (conv_boundary.cu) when F is a multiple of 128.  w is the fp32 parameter
+// [2][32][3][3]; its bf16 hi/lo tile image is rebuilt into a per-device scratch buffer ahead of every launch.
+int ddimb_conv_out_tc(const void* x, const void* skip, const float* w, const float* bias, float* out, int B, int T, int F, cudaStream_t stream) {
+  static uint8_t* scratch[64] = {nullptr};
+  int dev = 0;
+  DDIMB_CUDA(cudaGetDevice(&dev));
+  DDIMB_CHECK_ARG(dev >= 0 && dev < 64 && F % 128 == 0);
+  if (!scratch[dev]) DDIMB_CUDA(cudaMalloc(&scratch[dev], kCoWBytes));
+  co_weight_image_kernel<<<1, 256, 0, stream>>>(w, scratch[dev]);
+  DDIMB_LAUNCH_CHECK();
+  CoParams p;
+  memset(&p, 0, sizeof(p));
+  p.B = B; p.T = T; p.W = F;
+  int rt = 64;
+  while (rt > 8 && (long long)B * (F / 128) * ceil_div(T, rt) < 4LL * ddimb_num_sms()) rt /= 2;
+  p.RT = rt; p.units_t = ceil_div(T, rt); p.num_units = B * (F / 128) * p.units_t;
+  p.planes = skip ? 2 : 1;
+  p.wimg = scratch[dev]; p.bias = bias; p.out = out;
+  CUtensorMap tmX, tmS;
+  uint64_t dims[4] = {32, (uint64_t)F, (uint64_t)T, (uint64_t)B};
+  uint64_t str[3] = {32, (uint64_t)F * 32, (uint64_t)T * F * 32};
+  uint32_t box[4] = {32, (uint32_t)kWidePos, 1, 1};
+  int r = make_tmap_bf16(&tmX, x, 4, dims, str, box, 32);
+  if (r) return r;
+  r = make_tmap_bf16(&tmS, skip ? skip : x, 4, dims, str, box, 32);
+  if (r) return r;
+  static bool attr = false;
+  if (!attr) { DDIMB_CUDA(cudaFuncSetAttribute(conv_out_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kCoSmem)); attr = true; }
+  const int grid = p.num_units < ddimb_num_sms() ? p.num_units : ddimb_num_sms();
+  conv_out_tc_kernel<<<grid, kCoThreads, kCoSmem, stream>>>(tmX, tmS, p);
   DDIMB_LAUNCH_CHECK();
   return DDIMB_OK;
 }

@@ -85,7 +85,7 @@ def test_gn_apply(ops, C, P, mode):
         assert_stats(so, ref, f"gn stats C={C}")
 
 
-@pytest.mark.parametrize("B,T", [(1, 32), (3, 64)])
+@pytest.mark.parametrize("B,T", [(1, 32), (3, 64), (2, 1), (1, 77), (2, 300)])
 def test_conv_in_out(ops, B, T):
     g = torch.Generator(device=DEV).manual_seed(7)
     F = 256
