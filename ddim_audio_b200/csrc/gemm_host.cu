@@ -8,6 +8,7 @@
 #include "conv_wide.cuh"
 #include "conv_window.cuh"
 #include "conv_out_tc.cuh"
+#include "conv_down_wide.cuh"
 
 using namespace ddimb;
 
@@ -300,6 +301,45 @@ extern "C" int ddimb_conv3x3(const void* x, const void* w, const float* bias, co
   return launch_gemm(p, tmA, tmB, ck, stream, true);
 }
 
+// ------------------------------------------------------------------------------------------------ wide Downsample (32 -> 64)
+// csrc/conv_down_wide.cuh; w keeps the ABI layout, its swizzled tile image is rebuilt per call into a per-device scratch buffer.
+static bool conv_down_wide_supported(int Cin, int Cout, int T, int W) {
+  static const bool off = getenv("DDIMB_NO_DOWN_WIDE") != nullptr;
+  return !off && Cin == kDwCin && Cout == kDwCout && T % 2 == 0 && W % 256 == 0;
+}
+
+static int launch_conv_down_wide(const void* x, const void* w, const float* bias, void* out, double* stats, int B, int T, int W, cudaStream_t stream) {
+  static uint8_t* scratch[64] = {nullptr};
+  int dev = 0;
+  DDIMB_CUDA(cudaGetDevice(&dev));
+  DDIMB_CHECK_ARG(dev >= 0 && dev < 64);
+  if (!scratch[dev]) DDIMB_CUDA(cudaMalloc(&scratch[dev], kDwWBytes));
+  dw_weight_image_kernel<<<4, 256, 0, stream>>>(reinterpret_cast<const __nv_bfloat16*>(w), scratch[dev]);
+  DDIMB_LAUNCH_CHECK();
+  DwParams p;
+  memset(&p, 0, sizeof(p));
+  p.B = B; p.T = T; p.W = W;
+  const int To = T / 2, strips = (W / 2) / 128;
+  int rt = 64;
+  while (rt > 8 && (long long)B * strips * ceil_div(To, rt) < 4LL * ddimb_num_sms()) rt /= 2;
+  p.RT = rt; p.units_t = ceil_div(To, rt); p.num_units = B * strips * p.units_t;
+  p.wimg = scratch[dev]; p.bias = bias; p.out = reinterpret_cast<__nv_bfloat16*>(out); p.stats = stats;
+  CUtensorMap tmA;
+  {
+    uint64_t dims[4] = {64, (uint64_t)W / 2, (uint64_t)T, (uint64_t)B};
+    uint64_t str[3] = {64, (uint64_t)W * 32, (uint64_t)T * W * 32};
+    uint32_t box[4] = {64, (uint32_t)kWidePos, 1, 1};
+    int r = make_tmap_bf16(&tmA, x, 4, dims, str, box, 64);
+    if (r) return r;
+  }
+  static bool attr = false;
+  if (!attr) { DDIMB_CUDA(cudaFuncSetAttribute(conv_down_wide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kDwSmem)); attr = true; }
+  const int grid = p.num_units < ddimb_num_sms() ? p.num_units : ddimb_num_sms();
+  conv_down_wide_kernel<<<grid, kDwThreads, kDwSmem, stream>>>(tmA, p);
+  DDIMB_LAUNCH_CHECK();
+  return DDIMB_OK;
+}
+
 // ------------------------------------------------------------------------------------------------ Conv2d 4x4 s2 p1
 // reference: models/diffusion.py:70-78 (Downsample).  The NHWC input is viewed space-to-depth as
 // (2*Cin, W/2, 2, T/2, B): kernel column kx in {1,2} is one contiguous 2*Cin slab of column pair f', kx=0 / kx=3 are
@@ -311,6 +351,7 @@ extern "C" int ddimb_conv_down4x4(const void* x, const void* w, const float* bia
   DDIMB_PROF(stream, "conv_down4x4", Cin, W, npos * (4.0 * Cin + Cout) * 2 + 32.0 * Cin * Cout, 32.0 * Cin * Cout * npos);
   DDIMB_CHECK_ARG(W >= 16 && W <= 256 && (W & (W - 1)) == 0);
   DDIMB_CHECK_ARG(Cin % 32 == 0 && Cout % 32 == 0 && Cout <= 256 && Cin <= 256);
+  if (conv_down_wide_supported(Cin, Cout, T, W)) return launch_conv_down_wide(x, w, bias, out, stats, B, T, W, stream);
   const int ck = pick_ck(Cin);
   const int To = T / 2, Wo = W / 2;
   int bw, bt;

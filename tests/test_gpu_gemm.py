@@ -91,7 +91,9 @@ def test_conv3x3(ops, C, W, T, B, variant):
 
 
 @pytest.mark.parametrize("Cin,Cout,W,T,B", [(32, 64, 256, 8, 1), (64, 96, 128, 4, 2), (96, 128, 64, 8, 3), (128, 192, 32, 6, 1),
-                                            (192, 256, 16, 2, 2), (192, 256, 16, 64, 1)])
+                                            (192, 256, 16, 2, 2), (192, 256, 16, 64, 1),
+                                            # 32 -> 64 at W = 256 runs csrc/conv_down_wide.cuh: one output row, ragged units, several samples
+                                            (32, 64, 256, 2, 2), (32, 64, 256, 70, 3)])
 def test_conv_down4x4(ops, Cin, Cout, W, T, B):
     g = torch.Generator(device=DEV).manual_seed(Cin + W)
     x = _bf(torch.randn(B, T, W, Cin, device=DEV, generator=g))
