@@ -9,6 +9,7 @@
 #include "conv_window.cuh"
 #include "conv_out_tc.cuh"
 #include "conv_down_wide.cuh"
+#include "conv_up_wide.cuh"
 
 using namespace ddimb;
 
@@ -396,6 +397,47 @@ extern "C" int ddimb_conv_down4x4(const void* x, const void* w, const float* bia
   return launch_gemm(p, tmA, tmB, ck, stream, true);
 }
 
+// ------------------------------------------------------------------------------------------------ wide Upsample (64 -> 32)
+// csrc/conv_up_wide.cuh; w keeps the ABI layout, its swizzled tile image is rebuilt per call into a per-device scratch buffer.
+static bool conv_up_wide_supported(int Cin, int Cout, int W) {
+  static const bool off = getenv("DDIMB_NO_UP_WIDE") != nullptr;
+  return !off && Cin == kUwCin && Cout == kUwCout && W % 128 == 0;
+}
+
+static int launch_conv_up_wide(const void* x, const void* w, const float* bias, const void* skip, void* out, double* stats, int B, int T, int W,
+                               cudaStream_t stream) {
+  static uint8_t* scratch[64] = {nullptr};
+  int dev = 0;
+  DDIMB_CUDA(cudaGetDevice(&dev));
+  DDIMB_CHECK_ARG(dev >= 0 && dev < 64);
+  if (!scratch[dev]) DDIMB_CUDA(cudaMalloc(&scratch[dev], kUwWBytes));
+  uw_weight_image_kernel<<<3, 256, 0, stream>>>(reinterpret_cast<const __nv_bfloat16*>(w), scratch[dev]);
+  DDIMB_LAUNCH_CHECK();
+  UwParams p;
+  memset(&p, 0, sizeof(p));
+  p.B = B; p.T = T; p.W = W;
+  const int strips = W / 128;
+  int rt = 32;
+  while (rt > 4 && (long long)B * strips * ceil_div(T, rt) < 4LL * ddimb_num_sms()) rt /= 2;
+  p.RT = rt; p.units_t = ceil_div(T, rt); p.num_units = B * strips * p.units_t;
+  p.wimg = scratch[dev]; p.bias = bias; p.skip = reinterpret_cast<const __nv_bfloat16*>(skip);
+  p.out = reinterpret_cast<__nv_bfloat16*>(out); p.stats = stats;
+  CUtensorMap tmA;
+  {
+    uint64_t dims[4] = {64, (uint64_t)W, (uint64_t)T, (uint64_t)B};
+    uint64_t str[3] = {64, (uint64_t)W * 64, (uint64_t)T * W * 64};
+    uint32_t box[4] = {64, (uint32_t)kWidePos, 1, 1};
+    int r = make_tmap_bf16(&tmA, x, 4, dims, str, box, 64);
+    if (r) return r;
+  }
+  static bool attr = false;
+  if (!attr) { DDIMB_CUDA(cudaFuncSetAttribute(conv_up_wide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kUwSmem)); attr = true; }
+  const int grid = p.num_units < ddimb_num_sms() ? p.num_units : ddimb_num_sms();
+  conv_up_wide_kernel<<<grid, kUwThreads, kUwSmem, stream>>>(tmA, p);
+  DDIMB_LAUNCH_CHECK();
+  return DDIMB_OK;
+}
+
 // ------------------------------------------------------------------------------------------------ ConvTranspose2d 4x4 s2 p1
 // reference: models/diffusion.py:59-67 (Upsample) followed by the additive skip of :284.
 // Output row parity r is one launch: out[2t'+r, 2f'+s, co] = sum over (dy, dx) of in[t'+dy, f'+dx, :] . Wt[:, co, ky, kx],
@@ -408,6 +450,7 @@ extern "C" int ddimb_conv_up4x4(const void* x, const void* w, const float* bias,
   DDIMB_PROF(stream, "conv_up4x4", Cin, W, npos * (Cin + 4.0 * Cout * (skip ? 2 : 1)) * 2 + 32.0 * Cin * Cout, 32.0 * Cin * Cout * npos);
   DDIMB_CHECK_ARG(W >= 8 && W <= 128 && (W & (W - 1)) == 0);
   DDIMB_CHECK_ARG(Cin % 32 == 0 && Cout % 32 == 0 && Cout <= 256 && Cin <= 256);
+  if (conv_up_wide_supported(Cin, Cout, W)) return launch_conv_up_wide(x, w, bias, skip, out, stats, B, T, W, stream);
   const int ck = pick_ck(Cin);
   int bw, bt;
   spatial_tile(T, W, &bw, &bt);

@@ -145,10 +145,30 @@ __device__ __forceinline__ void conv_epilogue_bias(float* wb, const float* bias,
   __syncwarp();
 }
 
+// Coalesced request of this warp's `add` (skip) words for one tile: word pre[4 c + i] is granule (lane & 3) of position
+// 8 i + lane / 4 in 32-channel chunk c, so four consecutive lanes read the 64 contiguous bytes of one position (every 32-byte
+// sector is requested once; a thread reading its own position's 64 B in four 16-byte loads requests each sector twice and
+// touches 32 cache lines per instruction).  conv_epilogue_tile redistributes the words through its staging buffer.
+template <int NACC>
+__device__ __forceinline__ void conv_epilogue_prefetch_add(const __nv_bfloat16* add, int64_t addr0, bool valid, uint4 (&pre)[NACC / 8]) {
+  const int lane_ = threadIdx.x & 31;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int src = 8 * i + (lane_ >> 2);
+    const int64_t a = __shfl_sync(0xffffffffu, addr0, src) + (lane_ & 3) * 8;
+    const bool ok = __shfl_sync(0xffffffffu, (int)valid, src) != 0;
+#pragma unroll
+    for (int c = 0; c < NACC / 32; ++c) pre[4 * c + i] = (add != nullptr && ok) ? ldg_nc_v4(add + a + 32 * c) : make_uint4(0u, 0u, 0u, 0u);
+  }
+}
+
 // One tile of the convolution epilogue: TMEM -> registers -> + (bias + temb) -> activation -> + skip -> bf16 NHWC store,
 // GroupNorm partial sums of the stored values.  NACC accumulator columns, column c is channel c % CMOD; wb = this warp's
 // shared-memory bias copy (conv_epilogue_bias).  All arithmetic is packed fp32x2: per element 1/2 FFMA2 (bias), 1 MUFU +
 // 1/2 FFMA2 (SiLU), 1/2 F2FP (pack), 1/2 FADD2 + 1/2 FFMA2 (statistics).
+// `addpre` (optional): the NACC/8 16-byte words of `add` for this thread, loaded by the caller BEFORE it waited for the
+// accumulator (conv_epilogue_prefetch_add): the skip tensor does not depend on the MMAs, so its HBM latency is taken off the
+// epilogue's critical path (one batch of loads in flight per warp bounded the up-convolutions at ~2 TB/s).
 // `stage` (optional): 2 KB of shared memory private to the calling warp.  A thread owns one position, so a direct 16-byte
 // store instruction touches 32 different cache lines (one per lane); staged, each 32-channel chunk goes through shared memory
 // and is written so that four consecutive lanes cover the 64 contiguous bytes of one position: 8 line segments per
@@ -156,7 +176,7 @@ __device__ __forceinline__ void conv_epilogue_bias(float* wb, const float* bias,
 template <int NACC, int CMOD>
 __device__ __forceinline__ void conv_epilogue_tile(uint32_t trow, const float* wb, int act, const __nv_bfloat16* add, __nv_bfloat16* out,
                                                    int64_t addr0, bool valid, bool want_stats, ConvEpiState<CMOD>& st,
-                                                   uint8_t* stage = nullptr) {
+                                                   uint8_t* stage = nullptr, const uint4* addpre = nullptr) {
   constexpr int CG = CMOD / 8;   // channels per GroupNorm group (multiple of 4)
   const float sf = (act == 1) ? 0.5f : 1.0f;
   const uint64_t s2x = pack2(sf, sf);
@@ -176,11 +196,30 @@ __device__ __forceinline__ void conv_epilogue_tile(uint32_t trow, const float* w
     uint32_t v[32];
     tmem_ld32(trow + (uint32_t)c0, v);
     uint4 av[4];
-    if (add != nullptr && valid) {
+    const bool staged_add = stage != nullptr && (add != nullptr || addpre != nullptr);
+    if (staged_add) {
+      // coalesced words (prefetched by the caller, or requested here) -> staging -> this thread's own 64 bytes
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        if (addpre != nullptr) av[i] = addpre[(c0 >> 3) + i];
+        else av[i] = svalid[i] ? ldg_nc_v4(add + saddr[i] + c0) : make_uint4(0u, 0u, 0u, 0u);
+      }
+    } else if (add != nullptr && valid) {
 #pragma unroll
       for (int q = 0; q < 4; ++q) av[q] = ldg_nc_v4(add + addr0 + c0 + 8 * q);
     }
     tmem_ld_wait();
+    if (staged_add) {
+      __syncwarp();
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int pos = 8 * i + (lane_ >> 2);
+        *reinterpret_cast<uint4*>(stage + pos * 64 + (((lane_ & 3) ^ ((pos >> 1) & 3)) << 4)) = av[i];
+      }
+      __syncwarp();
+#pragma unroll
+      for (int q = 0; q < 4; ++q) av[q] = *reinterpret_cast<const uint4*>(stage + lane_ * 64 + ((q ^ ((lane_ >> 1) & 3)) << 4));
+    }
     uint64_t f[16];
 #pragma unroll
     for (int j = 0; j < 16; j += 2) {
@@ -192,7 +231,7 @@ __device__ __forceinline__ void conv_epilogue_tile(uint32_t trow, const float* w
 #pragma unroll
       for (int j = 0; j < 16; ++j) f[j] = silu2_from_half(f[j]);
     }
-    if (add != nullptr && valid) {
+    if ((add != nullptr || addpre != nullptr) && valid) {
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
         const uint32_t aw[4] = {av[q].x, av[q].y, av[q].z, av[q].w};
@@ -392,10 +431,13 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         }
         const int buf = local % p.num_acc_bufs;
         const uint32_t use = (uint32_t)(local / p.num_acc_bufs);
+        uint4 pre[NACC / 8];
+        if (p.add != nullptr) conv_epilogue_prefetch_add<NACC>(p.add, valid ? addr0 : 0, valid, pre);   // in flight while the MMAs finish
         mbar_wait(bar_tfull + 8 * buf, use & 1, 4);
         tc_fence_after();
         const uint32_t trow = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * NACC);
-        conv_epilogue_tile<NACC, CMOD>(trow, wb, p.act, p.add, out, valid ? addr0 : 0, valid, p.stats != nullptr, st, stage);
+        conv_epilogue_tile<NACC, CMOD>(trow, wb, p.act, p.add, out, valid ? addr0 : 0, valid, p.stats != nullptr, st, stage,
+                                       p.add != nullptr ? pre : nullptr);
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(bar_tempty + 8 * buf);

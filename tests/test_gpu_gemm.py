@@ -108,7 +108,9 @@ def test_conv_down4x4(ops, Cin, Cout, W, T, B):
 
 
 @pytest.mark.parametrize("Cin,Cout,W,T,B", [(256, 192, 8, 1, 1), (256, 192, 8, 4, 2), (192, 128, 16, 6, 1), (128, 96, 32, 4, 3),
-                                            (96, 64, 64, 8, 1), (64, 32, 128, 4, 2)])
+                                            (96, 64, 64, 8, 1), (64, 32, 128, 4, 2),
+                                            # 64 -> 32 at W = 128 runs csrc/conv_up_wide.cuh: single row, ragged units, ring wrap over many rows
+                                            (64, 32, 128, 1, 1), (64, 32, 128, 37, 3), (64, 32, 128, 300, 1)])
 @pytest.mark.parametrize("with_skip", [False, True])
 def test_conv_up4x4(ops, Cin, Cout, W, T, B, with_skip):
     g = torch.Generator(device=DEV).manual_seed(Cin + W + 1)
