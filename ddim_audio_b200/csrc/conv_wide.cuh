@@ -50,7 +50,12 @@ template <int C>
 struct WideCfg {
   static constexpr int kRowBytes = C * 2;
   static constexpr int kSlotBytes = ((kWidePos * kRowBytes + 1023) / 1024) * 1024;
-  static constexpr int kSlots = (C == 32) ? 16 : 8;   // rows in flight: HBM latency x bandwidth needs > 60 KB per SM
+  // rows in flight (HBM latency x bandwidth needs > 60 KB per SM).  MUST be a multiple of the transform warp count: a transform
+  // warp owns rows r = tw (mod kWideXfWarps), so with kSlots % kWideXfWarps == 0 it is also the only warp that ever waits on the
+  // "raw" barrier of a given slot, and it cannot run a whole phase ahead of it.  With 8 slots and 6 warps a fast warp (affine-only
+  // prologue) could reach a slot before the PREVIOUS row of that slot had landed, its parity wait aliased to the phase before, and
+  // the CTA deadlocked (seen at T = 4096).
+  static constexpr int kSlots = (C == 32) ? 3 * kWideXfWarps : kWideXfWarps;
   static constexpr int kAccBufs = 8;                // output rows in flight in TMEM
   static constexpr int kTmemCols = 8 * C;           // 256 / 512 columns
   static constexpr int kWBytes = 9 * C * C * 2;
@@ -84,6 +89,94 @@ struct WideUnit {
   }
 };
 
+// Transform warp of conv3x3_wide_kernel: GroupNorm affine (MODE 1) or affine + SiLU (MODE 2) applied in place to the row
+// strips this warp owns (every kWideXfWarps-th).  Lane -> (position p0 + 32/CH * k, 16-byte chunk j): consecutive k are 512 B
+// apart for both channel counts.  The loop body is branch-free (mode is a template parameter, only the 2-position tail and the
+// two image-edge halo positions are special) so the independent pair chains of a batch interleave: the branchy version spent
+// ~1040 warp instructions per row at 6 cycles each, most of them control flow around 16-byte granules.
+template <int C, int MODE>
+__device__ __forceinline__ void wide_transform_warp(const WideParams& p, uint8_t* a_gen, uint32_t bar_raw, uint32_t bar_ready, float* tab, int tw,
+                                                    int lane) {
+  using Cfg = WideCfg<C>;
+  constexpr int NS = Cfg::kSlots;
+  constexpr int CH = C / 8;                           // 16-byte chunks per position
+  constexpr int PSTEP = 32 / CH;                      // positions per warp iteration (x row bytes = 512 B)
+  constexpr int NFULL = 128 / PSTEP;                  // iterations in which every lane has a position (positions 0..127)
+  constexpr int BATCH = (C == 64) ? 4 : 8;
+  const int j = lane % CH, p0 = lane / CH;
+  // byte offset of this lane's granule in iteration k: p0 row + k * 512, chunk j XOR the row's swizzle phase
+  const uint32_t off_e = (uint32_t)(p0 * Cfg::kRowBytes) + (uint32_t)(((C == 64) ? (j ^ (p0 & 7)) : (j ^ ((p0 >> 1) & 3))) << 4);
+  const uint32_t off_o = (C == 64) ? (off_e ^ 64u) : off_e;     // C = 64: the phase of rows p0 + 4 (odd k) differs in bit 2 of the chunk index
+  const float pre = (MODE == 2) ? 0.5f : 1.0f;                  // silu(a) = u * tanh(u) + u with u = a / 2
+  uint64_t sc2[4], sh2[4];
+  auto granule = [&](uint4 v, bool zero) -> uint4 {
+    uint32_t w4[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      uint64_t a2 = ffma2(bf16x2_to_f32x2(w4[e]), sc2[e], sh2[e]);
+      if (MODE == 2) a2 = silu2_from_half(a2);
+      w4[e] = zero ? 0u : f32x2_to_bf16x2(a2);
+    }
+    return make_uint4(w4[0], w4[1], w4[2], w4[3]);
+  };
+  int cur_b = -1;
+  uint32_t cnt = 0;
+  WideUnit u;
+  for (int unit = blockIdx.x; unit < p.num_units; unit += gridDim.x) {
+    u.set(p, unit);
+    if (u.b != cur_b) {
+      cur_b = u.b;
+      __syncwarp();
+      for (int c = lane; c < C; c += 32) {
+        const int g = c / (C / 8);
+        const double n = (double)p.T * p.W * (C / 8);
+        const double mean = p.gn_stats[(u.b * 8 + g) * 2] / n;
+        double var = p.gn_stats[(u.b * 8 + g) * 2 + 1] / n - mean * mean;
+        if (var < 0) var = 0;
+        const float rstd = (float)(1.0 / sqrt(var + (double)p.eps));
+        const float sc = p.gn_gamma[c] * rstd;
+        tab[c] = pre * sc;
+        tab[C + c] = pre * ((p.gn_beta ? p.gn_beta[c] : 0.f) - (float)mean * sc);
+      }
+      __syncwarp();
+#pragma unroll
+      for (int e = 0; e < 4; ++e) { sc2[e] = pack2(tab[8 * j + 2 * e], tab[8 * j + 2 * e + 1]); sh2[e] = pack2(tab[C + 8 * j + 2 * e], tab[C + 8 * j + 2 * e + 1]); }
+    }
+    const bool left_edge = (u.w0 == 0), right_edge = (u.w0 + 128 == p.W);
+    // first row of this unit owned by this warp, then every kWideXfWarps-th
+    int rr = (int)((uint32_t)(tw + kWideXfWarps - (int)(cnt % kWideXfWarps)) % kWideXfWarps);
+    for (; rr < u.rows + 2; rr += kWideXfWarps) {
+      const uint32_t c2 = cnt + (uint32_t)rr;
+      const uint32_t slot = c2 % NS, use = c2 / NS;
+      const int t = u.t0 - 1 + rr;
+      uint8_t* sb = a_gen + slot * Cfg::kSlotBytes;
+      mbar_wait(bar_raw + 8 * slot, use & 1, 16);
+      if (t >= 0 && t < p.T) {   // a row outside the image is all padding: TMA wrote zeros and affine(0) != 0 must not be applied
+        // C = 64 keeps a rolled loop of small batches: there the tensor pipe and the epilogue's MUFU budget bound the kernel and the
+        // fully unrolled transform measured 11% SLOWER end to end (it finishes rows in bursts that delay the epilogue warps).
+#pragma unroll(C == 64 ? 1 : NFULL / BATCH)
+        for (int k0 = 0; k0 < NFULL; k0 += BATCH) {
+          uint4 v[BATCH];
+#pragma unroll
+          for (int i = 0; i < BATCH; ++i) v[i] = *reinterpret_cast<const uint4*>(sb + (((k0 + i) & 1) ? off_o : off_e) + (k0 + i) * 512);
+#pragma unroll
+          for (int i = 0; i < BATCH; ++i)
+            *reinterpret_cast<uint4*>(sb + (((k0 + i) & 1) ? off_o : off_e) + (k0 + i) * 512) =
+                granule(v[i], (k0 + i == 0) && left_edge && p0 == 0);
+        }
+        if (p0 < 2) {   // positions 128, 129 (iteration NFULL; NFULL is even)
+          uint4* q = reinterpret_cast<uint4*>(sb + off_e + NFULL * 512);
+          *q = granule(*q, right_edge && p0 == 1);
+        }
+      }
+      fence_proxy_async_smem();     // generic-proxy writes -> visible to the tensor core's async-proxy reads
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_ready + 8 * slot);
+    }
+    cnt += (uint32_t)(u.rows + 2);
+  }
+}
+
 template <int C>
 __global__ void __launch_bounds__(kWideThreads, 1)
 conv3x3_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const __grid_constant__ WideParams p) {
@@ -97,9 +190,10 @@ conv3x3_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   uint8_t* a_gen = smem_gen + Cfg::kWBytes;
   const uint32_t aux = a_base + NS * Cfg::kSlotBytes;
   uint8_t* aux_gen = a_gen + NS * Cfg::kSlotBytes;
-  // aux: raw_full[16] @0, ready[16] @128, empty[16] @256, acc_full[8] @384, acc_empty[8] @448, wfull @512, tmem ptr @520
-  const uint32_t bar_raw = aux, bar_ready = aux + 128, bar_empty = aux + 256, bar_afull = aux + 384, bar_aempty = aux + 448, bar_w = aux + 512;
-  volatile uint32_t* tmem_ptr_gen = reinterpret_cast<volatile uint32_t*>(aux_gen + 520);
+  // aux: raw_full[24] @0, ready[24] @192, empty[24] @384, acc_full[8] @576, acc_empty[8] @640, wfull @704, tmem ptr @712
+  static_assert(NS <= 24 && NS % kWideXfWarps == 0, "ring slots: a multiple of the transform warp count");
+  const uint32_t bar_raw = aux, bar_ready = aux + 192, bar_empty = aux + 384, bar_afull = aux + 576, bar_aempty = aux + 640, bar_w = aux + 704;
+  volatile uint32_t* tmem_ptr_gen = reinterpret_cast<volatile uint32_t*>(aux_gen + 712);
   float* bias_smem = reinterpret_cast<float*>(aux_gen + 1024);
   float* gn_smem = reinterpret_cast<float*>(aux_gen + 1024 + 4096);
 
@@ -122,7 +216,7 @@ conv3x3_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     mbar_fence_init();
   }
   if (warp == 1) {
-    tmem_alloc(aux + 520, (uint32_t)Cfg::kTmemCols);
+    tmem_alloc(aux + 712, (uint32_t)Cfg::kTmemCols);
     tmem_relinquish();
   }
   tc_fence_before();
@@ -256,85 +350,9 @@ conv3x3_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     st.flush(p.stats, lane);
   } else if (fused) {
     // ================================================================ transform: GroupNorm affine (+SiLU) in place
-    // Each of the eight warps owns every eighth row strip, so eight rows are in flight and one warp's load->math->store
-    // latency chain overlaps with the others'.  Lane -> (position, 16-byte chunk) with a fixed logical chunk per lane.
-    const int tw = warp - (2 + kWideEpiWarps);
-    constexpr int CH = C / 8;                           // 16-byte chunks per position
-    const int j = lane % CH;                            // logical chunk (channels 8j .. 8j+7), fixed per lane
-    const int p0 = lane / CH;
-    constexpr int PSTEP = 32 / CH;                      // positions per warp iteration
-    constexpr int NIT = (kWidePos + PSTEP - 1) / PSTEP;
-    constexpr int BATCH = 6;                            // 16-byte loads in flight per lane
-    float* tab = gn_smem + tw * 2 * C;                  // this warp's [scale C | shift C]
-    uint64_t sc2[4], sh2[4];                            // (scale, shift) pairs of this lane's 8 channels; pre-halved when SiLU follows
-    const float pre = (p.prologue == 2) ? 0.5f : 1.0f;  // silu(a) = u*tanh(u)+u with u = a/2
-    int cur_b = -1;
-    uint32_t cnt = 0;
-    WideUnit u;
-    for (int unit = blockIdx.x; unit < p.num_units; unit += gridDim.x) {
-      u.set(p, unit);
-      if (u.b != cur_b) {
-        cur_b = u.b;
-        __syncwarp();
-        for (int c = lane; c < C; c += 32) {
-          const int g = c / (C / 8);
-          const double n = (double)p.T * p.W * (C / 8);
-          const double mean = p.gn_stats[(u.b * 8 + g) * 2] / n;
-          double var = p.gn_stats[(u.b * 8 + g) * 2 + 1] / n - mean * mean;
-          if (var < 0) var = 0;
-          const float rstd = (float)(1.0 / sqrt(var + (double)p.eps));
-          const float s = p.gn_gamma[c] * rstd;
-          tab[c] = pre * s;
-          tab[C + c] = pre * ((p.gn_beta ? p.gn_beta[c] : 0.f) - (float)mean * s);
-        }
-        __syncwarp();
-#pragma unroll
-        for (int e = 0; e < 4; ++e) { sc2[e] = pack2(tab[8 * j + 2 * e], tab[8 * j + 2 * e + 1]); sh2[e] = pack2(tab[C + 8 * j + 2 * e], tab[C + 8 * j + 2 * e + 1]); }
-      }
-      const bool left_edge = (u.w0 == 0), right_edge = (u.w0 + 128 == p.W);
-      for (int rr = 0; rr < u.rows + 2; ++rr, ++cnt) {
-        if ((int)(cnt % kWideXfWarps) != tw) continue;
-        const uint32_t slot = cnt % NS, use = cnt / NS;
-        const int t = u.t0 - 1 + rr;
-        const bool row_ok = (t >= 0) && (t < p.T);
-        uint8_t* sb = a_gen + slot * Cfg::kSlotBytes;
-        mbar_wait(bar_raw + 8 * slot, use & 1, 16);
-        if (!row_ok) {
-          // a row outside the image is all padding: zeros (TMA already filled zeros, but affine(0) != 0 must not be applied)
-        } else {
-#pragma unroll 1
-          for (int i0 = 0; i0 < NIT; i0 += BATCH) {
-            uint4 v[BATCH];
-            uint32_t off[BATCH];
-#pragma unroll
-            for (int i = 0; i < BATCH; ++i) {
-              const int pos = p0 + (i0 + i) * PSTEP;
-              const int sw = (C == 64) ? (pos & 7) : ((pos >> 1) & 3);
-              off[i] = (uint32_t)(pos * Cfg::kRowBytes + ((j ^ sw) << 4));
-              if (pos < kWidePos) v[i] = *reinterpret_cast<const uint4*>(sb + off[i]);
-            }
-#pragma unroll
-            for (int i = 0; i < BATCH; ++i) {
-              const int pos = p0 + (i0 + i) * PSTEP;
-              if (pos < kWidePos) {
-                const bool zero = (pos == 0 && left_edge) || (pos == kWidePos - 1 && right_edge);
-                uint32_t w4[4] = {v[i].x, v[i].y, v[i].z, v[i].w};
-#pragma unroll
-                for (int e = 0; e < 4; ++e) {
-                  uint64_t a2 = ffma2(bf16x2_to_f32x2(w4[e]), sc2[e], sh2[e]);
-                  if (p.prologue == 2) a2 = silu2_from_half(a2);
-                  w4[e] = zero ? 0u : f32x2_to_bf16x2(a2);
-                }
-                *reinterpret_cast<uint4*>(sb + off[i]) = make_uint4(w4[0], w4[1], w4[2], w4[3]);
-              }
-            }
-          }
-        }
-        fence_proxy_async_smem();     // generic-proxy writes -> visible to the tensor core's async-proxy reads
-        __syncwarp();
-        if (lane == 0) mbar_arrive(bar_ready + 8 * slot);
-      }
-    }
+    float* tab = gn_smem + (warp - (2 + kWideEpiWarps)) * 2 * C;
+    if (p.prologue == 2) wide_transform_warp<C, 2>(p, a_gen, bar_raw, bar_ready, tab, warp - (2 + kWideEpiWarps), lane);
+    else wide_transform_warp<C, 1>(p, a_gen, bar_raw, bar_ready, tab, warp - (2 + kWideEpiWarps), lane);
   }
 
   tc_fence_before();
