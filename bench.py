@@ -235,6 +235,7 @@ def run_b200(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")   # keep stdout to the one JSON line
         dist.init_process_group("nccl", device_id=dev)
 
     from ddim_audio_b200 import _C, ops
@@ -311,7 +312,7 @@ def run_b200(args):
             dt = max_over_ranks(time.perf_counter() - t0)
         nbytes = x_host.numel() * 4
         e2e = {"value": world * B * K / dt, "unit": UNIT, "h2d_bytes_per_step": nbytes + 8 * B, "d2h_bytes_per_step": 2 * nbytes, "ms_per_step": 1e3 * dt / K,
-               "api": "generalized_steps(x_pinned_host, [t], model, alphas, None, eta=0) once per step"}
+               "api": "generalized_steps(x_pinned_host, [t], model, alphas, None, eta=0) once per step (4 sample groups pipelined over PCIe)"}
 
     # ---------------- CPU baseline (oracle; rank 0 at N=1 only)
     cpu = None

@@ -45,6 +45,15 @@ class _SnapshotPipe:
             dev_tensor.record_stream(self.stream)
         return host
 
+    def push_into(self, dev_tensor, host_view):
+        """Same, into a caller-owned (pinned) host tensor or a dim-0 slice of one."""
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream(self.device))
+        with torch.cuda.stream(self.stream):
+            self.stream.wait_event(ev)
+            host_view.copy_(dev_tensor, non_blocking=True)
+            dev_tensor.record_stream(self.stream)
+
     def drain(self):
         self.stream.synchronize()
 
@@ -79,7 +88,24 @@ def ddim_loop_device(xt, seq, model, alpha_list, eta=0.0, select_index=None, noi
     return xt
 
 
+def _chunk_bounds(B, n):
+    n = max(1, min(int(n), B))
+    base, rem = divmod(B, n)
+    out, c0 = [], 0
+    for k in range(n):
+        c1 = c0 + base + (1 if k < rem else 0)
+        out.append((c0, c1))
+        c0 = c1
+    return out
+
+
 def generalized_steps(x, seq, model, alpha, select_index, **kwargs):
+    """functions/denoising.py:10-52.  Returns ``(xs, x0_preds)``: lists of CPU fp32 tensors, ``xs[0]`` being the input.
+
+    A HOST ``x`` is processed as ``chunks`` independent sample groups (keyword, default 4 when eta == 0 and no explicit
+    noise stream is given; samples never interact -- SURVEY.md section 8e): every group's host->device copy is queued up front
+    on a copy stream and its snapshots return on another, so the PCIe traffic of one group hides behind the denoiser of the
+    next instead of bracketing the whole batch.  A CUDA ``x`` runs as one group."""
     if not torch.cuda.is_available():
         raise RuntimeError("ddim_audio_b200.generalized_steps needs a CUDA device: there is no CPU path")
     eta = kwargs.get("eta", 0)
@@ -87,14 +113,41 @@ def generalized_steps(x, seq, model, alpha, select_index, **kwargs):
     with torch.no_grad():
         alpha_list = [1.0] + alpha.to("cpu", torch.float32).numpy().tolist()          # :12
         device = x.device if x.is_cuda else torch.device("cuda", torch.cuda.current_device())
-        xs, x0_preds = [x], []
-        xt = x.to(device=device, dtype=torch.float32, copy=True, non_blocking=True).contiguous()
+        B = x.size(0)
+        nchunk = 1
+        if not x.is_cuda and noise is None and eta == 0:
+            nchunk = kwargs.get("chunks", 4 if B >= 8 else 1)
+        bounds = _chunk_bounds(B, nchunk)
+        cur = torch.cuda.current_stream(device)
         pipe = _SnapshotPipe(device)
+        # ---- inputs: all host->device copies are queued now, on their own stream
+        staged = []
+        if x.is_cuda:
+            staged.append((x.to(dtype=torch.float32, copy=True).contiguous(), None))
+        else:
+            h2d = torch.cuda.Stream(device=device)
+            for c0, c1 in bounds:
+                with torch.cuda.stream(h2d):
+                    xc = x[c0:c1].to(device=device, dtype=torch.float32, non_blocking=True).contiguous()
+                    ev = torch.cuda.Event()
+                    ev.record(h2d)
+                staged.append((xc, ev))
+        # ---- snapshots of step k land in slices [c0:c1] of one full-batch pinned tensor per list entry
+        out_x0, out_xs = [], []
+        for (c0, c1), (xt, ev) in zip(bounds, staged):
+            if ev is not None:
+                cur.wait_event(ev)
+                xt.record_stream(cur)
+            k = [0]
 
-        def snap(x0_buf, xs_buf):
-            x0_preds.append(pipe.push(x0_buf))                                         # :29-34
-            xs.append(pipe.push(xs_buf))                                               # :45-50
+            def snap(x0_buf, xs_buf, c0=c0, c1=c1, k=k):
+                if k[0] == len(out_x0):
+                    out_x0.append(torch.empty((B,) + tuple(x0_buf.shape[1:]), dtype=torch.float32, pin_memory=True))
+                    out_xs.append(torch.empty((B,) + tuple(xs_buf.shape[1:]), dtype=torch.float32, pin_memory=True))
+                pipe.push_into(x0_buf, out_x0[k[0]][c0:c1])                             # :29-34
+                pipe.push_into(xs_buf, out_xs[k[0]][c0:c1])                             # :45-50
+                k[0] += 1
 
-        ddim_loop_device(xt, seq, model, alpha_list, eta, select_index, noise, snap)
+            ddim_loop_device(xt, seq, model, alpha_list, eta, select_index, noise, snap)
         pipe.drain()
-    return xs, x0_preds
+    return [x] + out_xs, out_x0

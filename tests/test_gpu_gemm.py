@@ -145,7 +145,9 @@ def test_fourier_mix(ops, B, S):
 
 
 # ---------------------------------------------------------------------------------------------- wide 3x3 conv (+ fused GroupNorm)
-WIDE_CASES = [(32, 256, 8, 1), (32, 256, 70, 2), (32, 128, 33, 3), (64, 128, 16, 2), (64, 256, 9, 1), (64, 128, 130, 2), (32, 256, 1, 1)]
+WIDE_CASES = [(32, 256, 8, 1), (32, 256, 70, 2), (32, 128, 33, 3), (64, 128, 16, 2), (64, 256, 9, 1), (64, 128, 130, 2), (32, 256, 1, 1),
+              # long strips (many ring revolutions per CTA): the shape at which a ring / transform-warp phase aliasing once deadlocked
+              (64, 128, 4096, 6), (32, 256, 2048, 5)]
 
 
 @pytest.mark.parametrize("C,W,T,B", WIDE_CASES)

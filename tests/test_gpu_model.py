@@ -102,3 +102,21 @@ def test_loss_vs_reference_golden(model, golden_dir):
         loss = loss_registry["simple"](model, x0.to(DEV), t.to(DEV), e.to(DEV), a)
     np.testing.assert_allclose(per.cpu().numpy(), g["per_sample"], rtol=3e-2)
     assert float(loss) == pytest.approx(float(g["loss"]), rel=3e-2)
+
+
+@pytest.mark.parametrize("B,chunks", [(9, 4), (8, 3), (2, None)])
+def test_generalized_steps_host_input_is_pipelined_by_sample_groups(model, B, chunks):
+    """A pinned HOST x runs as independent sample groups (H2D / snapshots overlapped with the denoiser): the lists must equal
+    the single-group run on a device tensor sample for sample (samples never interact: SURVEY.md section 8e)."""
+    from ddim_audio_b200.functions.denoising import generalized_steps
+    x, _, _ = O.synthetic_inputs(B, 32, 321)
+    seq = O.uniform_seq(1000, 3)
+    al = O.alphas_cumprod().to(DEV)
+    kw = {} if chunks is None else {"chunks": chunks}
+    xs_h, x0_h = generalized_steps(x.pin_memory(), seq, model, al, {0, 2}, eta=0.0, **kw)
+    xs_d, x0_d = generalized_steps(x.to(DEV), seq, model, al, {0, 2}, eta=0.0)
+    assert len(xs_h) == len(xs_d) == 3 and len(x0_h) == len(x0_d) == 2
+    assert not xs_h[0].is_cuda and torch.equal(xs_h[0], x)
+    for a, b in zip(xs_h[1:] + x0_h, xs_d[1:] + x0_d):
+        assert a.shape == b.shape == x.shape and not a.is_cuda
+        assert rel_l2(a, b) < 1e-3    # identical arithmetic per sample; only the fp64 statistics atomics may reorder
