@@ -8,6 +8,7 @@
 #include "conv_wide.cuh"
 #include "conv_window.cuh"
 #include "conv_out_tc.cuh"
+#include "conv_in_tc.cuh"
 #include "conv_down_wide.cuh"
 #include "conv_up_wide.cuh"
 
@@ -246,6 +247,33 @@ int ddimb_conv_out_tc(const void* x, const void* skip, const float* w, const flo
   if (!attr) { DDIMB_CUDA(cudaFuncSetAttribute(conv_out_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kCoSmem)); attr = true; }
   const int grid = p.num_units < ddimb_num_sms() ? p.num_units : ddimb_num_sms();
   conv_out_tc_kernel<<<grid, kCoThreads, kCoSmem, stream>>>(tmX, tmS, p);
+  DDIMB_LAUNCH_CHECK();
+  return DDIMB_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ conv_in on the tensor cores
+// csrc/conv_in_tc.cuh; called by ddimb_conv_in (conv_boundary.cu) when F is a multiple of 128.  w is the fp32 parameter
+// [32][2][3][3]; its bf16 [hi | hi | lo] tile image is rebuilt into a per-device scratch buffer ahead of every launch.
+int ddimb_conv_in_tc(const float* x, const float* w, const float* bias, void* out, double* stats, int B, int T, int F, cudaStream_t stream) {
+  static uint8_t* scratch[64] = {nullptr};
+  int dev = 0;
+  DDIMB_CUDA(cudaGetDevice(&dev));
+  DDIMB_CHECK_ARG(dev >= 0 && dev < 64 && F % 128 == 0);
+  if (!scratch[dev]) DDIMB_CUDA(cudaMalloc(&scratch[dev], kCiWBytes));
+  ci_weight_image_kernel<<<1, 256, 0, stream>>>(w, scratch[dev]);
+  DDIMB_LAUNCH_CHECK();
+  CiParams p;
+  memset(&p, 0, sizeof(p));
+  p.B = B; p.T = T; p.W = F;
+  int rt = kCiStripRows;
+  while (rt > 8 && (long long)B * (F / 128) * ceil_div(T, rt) < 4LL * ddimb_num_sms()) rt /= 2;
+  p.RT = rt; p.units_t = ceil_div(T, rt); p.num_units = B * (F / 128) * p.units_t;
+  if (const char* e = getenv("DDIMB_CI_DBG")) p.dbg = atoi(e);
+  p.x = x; p.wimg = scratch[dev]; p.bias = bias; p.out = reinterpret_cast<__nv_bfloat16*>(out); p.stats = stats;
+  static bool attr = false;
+  if (!attr) { DDIMB_CUDA(cudaFuncSetAttribute(conv_in_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kCiSmem)); attr = true; }
+  const int grid = p.num_units < ddimb_num_sms() ? p.num_units : ddimb_num_sms();
+  conv_in_tc_kernel<<<grid, kCiThreads, kCiSmem, stream>>>(p);
   DDIMB_LAUNCH_CHECK();
   return DDIMB_OK;
 }
