@@ -29,6 +29,8 @@ SIGNATURES = {
     "ddimb_qsample": [_vp, _vp, _vp, _vp, _vp, _i, _ll],
     "ddimb_sqerr_loss": [_vp, _vp, _vp, _i, _ll],
     "ddimb_sqerr_loss_bwd": [_vp, _vp, _vp, _vp, _i, _ll],
+    "ddimb_denoise2d": [_vp, _vp, _vp, _ll, _i, _i, _i, _i, _i],
+    "ddimb_ema_update": [_vp, _i, _ll, _d],
     "ddimb_conv_in": [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i],
     "ddimb_conv_out": [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i],
     "ddimb_conv3x3": [_vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _i, _i, _i, _i, _i],
@@ -64,13 +66,15 @@ SIGNATURES = {
     "ddimb_conv_in_wgrad": [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i],
     "ddimb_conv_out_wgrad": [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i],
 }
-EXPORTS = ["ddimb_version", "ddimb_last_error", "ddimb_launch_count", "ddimb_prof_enable", "ddimb_prof_report", "ddimb_conv3x3_wide_supported"] + list(SIGNATURES)
+EXPORTS = ["ddimb_version", "ddimb_last_error", "ddimb_launch_count", "ddimb_prof_enable", "ddimb_prof_report", "ddimb_conv3x3_wide_supported", "ddimb_denoise2d_workspace"] + list(SIGNATURES)
 
 lib.ddimb_version.restype = _i
 lib.ddimb_last_error.restype = C.c_char_p
 lib.ddimb_launch_count.restype = _ll
 lib.ddimb_conv3x3_wide_supported.argtypes = [_i, _i, _i]
 lib.ddimb_conv3x3_wide_supported.restype = _i
+lib.ddimb_denoise2d_workspace.argtypes = [_i, _i, _i, _i, _i]
+lib.ddimb_denoise2d_workspace.restype = _ll
 lib.ddimb_prof_enable.argtypes = [_i]
 lib.ddimb_prof_enable.restype = _i
 lib.ddimb_prof_report.argtypes = [C.c_char_p, _i]

@@ -47,6 +47,23 @@ def sqerr_loss_bwd(e, output, g):
     return go
 
 
+def denoise_2d(x, iters=5):
+    """External/UPU/signal/denoise.py:45-70 on fp32 ``x[*, 2, T, F]`` -> new tensor."""
+    if x.dim() < 3:
+        raise RuntimeError("denoise_2d: expected x[*, D, H, W]")
+    C, T, F = x.shape[-3:]
+    B = x.numel() // max(1, C * T * F)
+    if B == 0:
+        return torch.empty_like(x)
+    nbytes = int(_C.lib.ddimb_denoise2d_workspace(B, C, T, F, int(iters)))
+    if nbytes < 0:
+        raise RuntimeError(f"denoise_2d: unsupported shape {tuple(x.shape)} (D must be 2, W one of 128/256/512, iters <= 8); there is no CPU path")
+    ws = torch.empty(nbytes, dtype=torch.uint8, device=x.device)
+    out = torch.empty_like(x)
+    call("ddimb_denoise2d", ptr(x, f32), ptr(out, f32), ptr(ws), nbytes, B, C, T, F, int(iters))
+    return out
+
+
 # ---------------------------------------------------------------------------------------- convolutions
 def conv_in(x, w, bias, stats=None):
     B, Cin, T, F = x.shape

@@ -1,8 +1,9 @@
 """``Diffusion`` runner behind the reference's ``Diffusion(args, config).train() / .sample()`` (runners/diffusion.py:90-523),
 reduced to the hot path: schedules (:32-62, :91-128), ``sample_image`` (:475-520), ``sample_sequence`` (:377-398),
-``train_step`` (:130-183) and ``train`` (:201-287).  Dataset loading, the STFT/PNG/WAV codec and ``denoise_2d`` are out of
-scope: ``train`` takes any iterable of ``(x, y)`` batches and ``sample_sequence`` RETURNS the
-``(xs, x0_preds)`` host tensors, optionally handing them to ``self.writer`` (what the reference does at :400-422).
+``train_step`` (:130-183) and ``train`` (:201-287).  Dataset loading and the STFT/PNG/WAV codec are out of scope
+(SURVEY.md section 2): ``train`` takes any iterable of ``(x, y)`` batches and ``sample_sequence`` RETURNS the
+``(xs, x0_preds)`` host tensors -- the x0 list post-filtered by ``denoise_2d`` when ``config.sampling.denoise`` (:400-401) --
+optionally handing them to ``self.writer`` (what the reference does at :402-422).
 
 Rank-aware: under torchrun ``sample_sequence`` shards ``num_samples`` by batch with no collective and
 ``train_step`` all-reduces one flat gradient buffer.  There is no CPU path.
@@ -18,6 +19,8 @@ import torch
 from ..functions.denoising import generalized_steps
 from ..functions.losses import loss_registry
 from ..models.diffusion import Model
+from ..models.ema import EMAHelper
+from ..signal.denoise import denoise_2d
 from . import dist as rdist
 
 
@@ -165,6 +168,8 @@ class Diffusion(object):
                 xs, x0 = self.sample_image(x, model, select_index=self.select_index())
         else:
             xs, x0 = [], []
+        if getattr(cfg.sampling, "denoise", False):
+            x0 = [denoise_2d(y.to(self.device)).cpu() for y in x0]                    # :400-401, per sample -> shards like the loop
         if world > 1:
             xs = rdist.gather_host_lists([t.cpu() for t in xs])
             x0 = rdist.gather_host_lists(x0)
@@ -257,6 +262,10 @@ class Diffusion(object):
             raise NotImplementedError("ddim_audio_b200: dataset loading is out of scope -- pass an iterable of (x, y) batches")
         model = Model(self.config).to(self.device) if model is None else model
         optimizers, schedulers, grad_group = self.build_training(model)
+        if ema_helper is None and getattr(self.config.model, "ema", False):          # :232-236
+            ema_helper = EMAHelper(mu=self.config.model.ema_rate)
+            ema_helper.register(model)
+        self.ema_helper = ema_helper
         n_iters = self.config.training.n_iters if max_steps is None else max_steps
         step, epoch, log = 0, 0, None
         while step < n_iters:

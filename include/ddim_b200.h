@@ -54,6 +54,26 @@ int ddimb_sqerr_loss(const float* e, const float* output, double* per_sample, in
 int ddimb_sqerr_loss_bwd(const float* e, const float* output, const float* g, float* grad_output, int B,
                          long long per_sample_elems, cudaStream_t stream);
 
+/* ---- post-filter on the returned x0 snapshots --------------------------------------- */
+
+/* External/UPU/signal/denoise.py:45-70 (denoise_2d, torch branch; called at runners/diffusion.py:400-401) on
+ * x[B][C][T][F] fp32 (leading dims flattened into B): r = x - median_F(x); r -= median_T(r) (torch's LOWER median, exact);
+ * then `iters` (the reference uses 5) times: denom = 1/(1e-9 + ||r||_2 over C), num = r denom,
+ * r -= mean_F(num)/mean_F(denom), r -= mean_T(num)/mean_T(denom).  out may alias x.  C must be 2 (audio.yml) and
+ * F one of 128 / 256 / 512, iters <= 8.  workspace: DEVICE scratch of at least ddimb_denoise2d_workspace(B, C, T, F, iters)
+ * bytes (256-byte aligned; -1 = unsupported shape). */
+long long ddimb_denoise2d_workspace(int B, int C, int T, int F, int iters);
+int ddimb_denoise2d(const float* x, float* out, void* workspace, long long workspace_bytes, int B, int C, int T, int F, int iters,
+                    cudaStream_t stream);
+
+/* ---- EMA of the parameters ------------------------------------------------------------- */
+
+/* models/ema.py:16-23 -- shadow = (1 - mu) param + mu shadow for EVERY registered parameter in one launch (bit-exact: the
+ * reference's operation order and fp32 roundings).  chunk_table: DEVICE array of nchunks records
+ * {const float* param; float* shadow; long long count; long long pad} (32 bytes each, 16-byte aligned pointers, count <= 2^31),
+ * one CTA per record; total_elems = sum of the counts (profiler bookkeeping only). */
+int ddimb_ema_update(const void* chunk_table, int nchunks, long long total_elems, double mu, cudaStream_t stream);
+
 /* ---- network boundary convolutions (CUDA cores; K = 18 / N = 2 are not tensor-core shapes) -------------------- */
 
 /* models/diffusion.py:189-198 -- Conv2d(Cin=2 -> 32, k3 p1): x fp32 NCHW, w fp32 [32][Cin][3][3], out bf16 NHWC. */

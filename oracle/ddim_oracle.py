@@ -417,3 +417,57 @@ def synthetic_inputs(batch: int, t_size: int, seed: int = 1234, cfg=AUDIO_CFG):
 def rel_l2(a: torch.Tensor, b: torch.Tensor) -> float:
     a, b = a.double().flatten(), b.double().flatten()
     return float((a - b).norm() / b.norm().clamp_min(1e-30))
+
+
+# --------------------------------------------------------------------------------------
+# denoise_2d post-filter on every returned x0
+# External/UPU/signal/denoise.py:45-70 (torch branch); call site runners/diffusion.py:400-401
+# --------------------------------------------------------------------------------------
+def lower_median(x: torch.Tensor, dim: int) -> torch.Tensor:
+    """``Tensor.median(dim, keepdim=True)[0]``: for an even count torch returns the LOWER of the two middle values,
+    i.e. element ``(n - 1) // 2`` of the sorted slice (denoise.py:54-55 relies on it)."""
+    n = x.shape[dim]
+    return torch.sort(x, dim=dim)[0].narrow(dim, (n - 1) // 2, 1)
+
+
+def denoise_2d(x: torch.Tensor, iters: int = 5) -> torch.Tensor:
+    """denoise.py:45-70 for ``x[*, D, H, W]``: subtract the median over W, then the median over H of the result (:54-55);
+    then 5 times (:63-69): ``denom = 1 / (1e-9 + ||r||_2 over D)``, ``num = r * denom`` (formed ONCE per iteration),
+    and for axis W then H: ``r -= mean_axis(num) / mean_axis(denom)``."""
+    r = x - lower_median(x, -1)
+    r = r - lower_median(r, -2)
+    for _ in range(iters):
+        denom = 1 / (1e-9 + torch.linalg.norm(r, ord=2, dim=-3, keepdim=True))
+        num = r * denom
+        for axis in (-1, -2):
+            a = num.mean(dim=axis, keepdim=True) / denom.mean(dim=axis, keepdim=True)
+            r = r - a
+    return r
+
+
+def denoise_inputs(batch: int, t_size: int, seed: int, cfg=AUDIO_CFG, f_size: Optional[int] = None) -> torch.Tensor:
+    """Seeded x0-like input for the post-filter: unit noise plus the per-row / per-column offsets and the outliers the
+    filter exists to remove (so the medians and the five mean iterations all do real work)."""
+    g = torch.Generator().manual_seed(seed)
+    F_ = cfg["f_size"] if f_size is None else f_size
+    C = cfg["channels"]
+    x = torch.randn(batch, C, t_size, F_, generator=g)
+    x = x + 0.7 * torch.randn(batch, C, t_size, 1, generator=g) + 1.3 * torch.randn(batch, C, 1, F_, generator=g)
+    spikes = (torch.rand(batch, C, t_size, F_, generator=g) < 0.01).float() * 25.0 * torch.randn(batch, C, t_size, F_, generator=g)
+    return x + spikes + 0.25
+
+
+# --------------------------------------------------------------------------------------
+# EMA of the parameters (SURVEY.md §8 row f3) -- models/ema.py:16-23, runners/diffusion.py:182-183
+# --------------------------------------------------------------------------------------
+def ema_update(shadow: Dict[str, torch.Tensor], params: Dict[str, torch.Tensor], mu: float) -> Dict[str, torch.Tensor]:
+    """models/ema.py:19-23: ``shadow = (1 - mu) * param + mu * shadow`` (two rounded products, then the sum), per tensor."""
+    return {k: (1.0 - mu) * params[k] + mu * shadow[k] for k in shadow}
+
+
+def ema_case(seed: int, steps: int = 3):
+    """Seeded parameter trajectories for the EMA fixtures: ragged sizes (scalar, odd, > one 16 K chunk)."""
+    g = torch.Generator().manual_seed(seed)
+    shapes = {"a.weight": (7, 5, 3, 3), "a.bias": (7,), "b.weight": (130, 257), "c.scale": (1,), "d.weight": (3, 16384 + 5)}
+    traj = [{k: torch.randn(s, generator=g) for k, s in shapes.items()} for _ in range(steps + 1)]
+    return shapes, traj

@@ -140,3 +140,6 @@ def test_runner_train_step_updates_parameters(oracle_sd):
     _, log = r.train(loader=[(x0, None)], model=m, max_steps=2)
     assert log["step"] == 2 and np.isfinite(log["loss"])
     assert not torch.equal(before, m.transformer.compute_out.weight.detach())
+    # config.model.ema: the runner registered the fused EMAHelper (runners/diffusion.py:232-236) and updated it every step
+    sh = r.ema_helper.shadow["transformer.compute_out.weight"]
+    assert torch.isfinite(sh).all() and not torch.equal(sh, before) and not torch.equal(sh, m.transformer.compute_out.weight.detach())

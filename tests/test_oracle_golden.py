@@ -95,3 +95,34 @@ def test_loss_gradients_match_reference_fingerprint(oracle_sd, golden_dir):
         norm, s, proj = O.grad_fingerprint(k, grads[k])
         assert norm == pytest.approx(fp[0], rel=2e-3, abs=1e-6), k
         assert abs(proj - fp[2]) <= 2e-3 * max(fp[0], 1e-6) + 1e-6, k      # projection on a unit-variance direction ~ norm
+
+
+@pytest.mark.parametrize("name", ["denoise_b2_t48", "denoise_b1_t33_f128"])
+def test_denoise_2d(golden_dir, name):
+    """the post-filter restatement against outputs of the reference's own denoise_2d
+    (External/UPU/signal/denoise.py:45-70), minted by oracle/make_golden_denoise.py."""
+    g = _load(golden_dir, name)
+    b, T, F_, seed = (int(v) for v in g["meta"])
+    x = O.denoise_inputs(b, T, seed, f_size=F_)
+    got = O.denoise_2d(x)
+    np.testing.assert_allclose(got.numpy(), g["out"], rtol=0, atol=1e-5)
+
+
+def test_lower_median_is_torch_median():
+    g = torch.Generator().manual_seed(3)
+    for n in (1, 2, 7, 8, 33):
+        x = torch.randn(3, n, 5, generator=g)
+        assert torch.equal(O.lower_median(x, 1), x.median(dim=1, keepdim=True)[0])
+
+
+def test_ema_update(golden_dir):
+    """the EMA restatement against the final shadow of the reference's own EMAHelper (models/ema.py:16-23)
+    after three updates, minted by oracle/make_golden_ema.py."""
+    g = _load(golden_dir, "ema_steps")
+    mu = float(g["mu"])
+    _, traj = O.ema_case(int(g["seed"]))
+    shadow = {k: v.clone() for k, v in traj[0].items()}
+    for step in traj[1:]:
+        shadow = O.ema_update(shadow, step, mu)
+    for k, v in shadow.items():
+        assert np.array_equal(v.numpy(), g[k.replace(".", "__")]), k
