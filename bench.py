@@ -50,8 +50,13 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--cpu-sample-steps", type=int, default=2)
-    ap.add_argument("--mode", default="sample", choices=["sample", "train"],
-                    help="sample: DDIM sample-steps/s (the headline, BASELINE configs[2]); train: noise_estimation_loss fwd+bwd samples/s (configs[1]/[4])")
+    ap.add_argument("--mode", default="sample", choices=["sample", "train", "parity"],
+                    help="sample: DDIM sample-steps/s (the headline, BASELINE configs[2]); train: noise_estimation_loss fwd+bwd samples/s "
+                         "(configs[1]/[4]); parity: configs[0] -- 50 DDIM steps, batch 4, T=1024 on the GPU and on the CPU oracle, "
+                         "per-step eps and final-sample error")
+    ap.add_argument("--parity-steps", type=int, default=50)
+    ap.add_argument("--parity-batch", type=int, default=4)
+    ap.add_argument("--parity-t-size", type=int, default=1024)
     return ap.parse_args()
 
 
@@ -462,10 +467,89 @@ def run_train(args):
         dist.destroy_process_group()
 
 
+def run_parity(args):
+    """BASELINE configs[0]: x[4,2,1024,256], seq = range(0,1000,20) (50 steps), eta = 0, select_index
+    None.  The CPU oracle (checker) walks its own trajectory; at every step the CUDA denoiser is ALSO evaluated on the oracle's
+    xt (teacher-forced per-step eps error), and the free-running CUDA trajectory through the public ``generalized_steps`` is
+    compared snapshot by snapshot (final-sample max-abs / rel-L2).  One JSON line; not a throughput bench."""
+    import torch
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py --mode parity: no CUDA device")
+    torch.cuda.set_device(0)
+    dev = torch.device("cuda", 0)
+    from ddim_audio_b200.config import audio_config
+    from ddim_audio_b200.functions.denoising import generalized_steps
+    from ddim_audio_b200.models.diffusion import Model
+    from oracle import ddim_oracle as O
+
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    sd = synthetic_state_dict()
+    model = Model(audio_config("torch.FloatTensor")).to(dev)
+    model.load_state_dict(sd, strict=True)
+    model.eval()
+    omodel = O.OracleModel(sd)
+    al = alphas_cumprod()
+    B, T, n = args.parity_batch, args.parity_t_size, args.parity_steps
+    seq = list(range(0, 1000, 1000 // 50))[:n] if n <= 50 else list(range(0, 1000, max(1, 1000 // n)))
+    x = torch.randn(B, 2, T, F_SIZE, generator=torch.Generator().manual_seed(1234))
+
+    with torch.no_grad():
+        generalized_steps(x.to(dev), seq[:2], model, al.to(dev), None, eta=0.0)       # warm-up (weight packing, descriptors)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        xs_g, x0_g = generalized_steps(x.to(dev), seq, model, al.to(dev), None, eta=0.0)
+        torch.cuda.synchronize()
+        gpu_s = time.perf_counter() - t0
+
+    rel = lambda a, b: float((a.double() - b.double()).norm() / b.double().norm().clamp_min(1e-30))
+    xt = x.clone()
+    t = torch.zeros(B, dtype=torch.long)
+    eps_rel, eps_max_over_std, traj_rel, x0_rel = [], [], [], []
+    cpu_s = 0.0
+    for k, c in enumerate(O.ddim_coefficients(al, seq, 0.0)):
+        t[...] = c["i"]
+        t0 = time.perf_counter()
+        et = omodel(xt, t)
+        cpu_s += time.perf_counter() - t0
+        with torch.no_grad():
+            et_g = model(xt.to(dev), t.to(dev)).float().cpu()
+        eps_rel.append(rel(et_g, et))
+        eps_max_over_std.append(float((et_g - et).abs().max() / et.std().clamp_min(1e-30)))
+        t0 = time.perf_counter()
+        xt.add_(et, alpha=-((1 - c["at"]) ** 0.5)).div_(c["at"] ** 0.5)                # functions/denoising.py:27
+        x0_rel.append(rel(x0_g[k].cpu(), xt))
+        xt.mul_(c["at_next"] ** 0.5).add_(et, alpha=c["c2"])                           # :41-43, eta = 0
+        cpu_s += time.perf_counter() - t0
+        traj_rel.append(rel(xs_g[k + 1].cpu(), xt))
+    final_g = xs_g[-1].cpu()
+    line = {
+        "mode": "parity", "impl": "b200-vs-oracle",
+        "config": {"workload": f"audio.yml DDIM generalized_steps, x[{B},2,{T},{F_SIZE}], {len(seq)} steps of the uniform 50-step schedule, "
+                               f"eta=0, select_index=None (BASELINE configs[0])", "weights": "seeded random init, norm.2.weight <- 0.5 randn"},
+        "tolerance": {"per_step_eps_rel_l2": 2e-2, "per_step_eps_max_abs_over_std": 0.114,
+                      "note": "bf16 activation storage, fp32 accumulate (DESIGN.md section 2)"},
+        "per_step_eps": {"teacher_forced": True, "rel_l2_max": max(eps_rel), "rel_l2_mean": sum(eps_rel) / len(eps_rel),
+                         "max_abs_over_std_max": max(eps_max_over_std), "rel_l2_first_last": [eps_rel[0], eps_rel[-1]]},
+        "free_running": {"xs_rel_l2_by_step": [round(v, 6) for v in traj_rel[:: max(1, len(traj_rel) // 10)]] + [round(traj_rel[-1], 6)],
+                         "x0_pred_rel_l2_last": x0_rel[-1]},
+        "final_sample": {"max_abs": float((final_g - xt).abs().max()), "rel_l2": traj_rel[-1], "ref_std": float(xt.std()),
+                         "ref_abs_max": float(xt.abs().max())},
+        "cpu": {"kind": "port", "cores": cores, "seconds": cpu_s, "sample_steps_per_s": B * len(seq) / cpu_s},
+        "gpu": {"seconds": gpu_s, "sample_steps_per_s": B * len(seq) / gpu_s,
+                "api": "generalized_steps(x_cuda, seq, model, alphas, None, eta=0): every snapshot copied to the host, wall clock"},
+        "pass": bool(max(eps_rel) <= 2e-2 and max(eps_max_over_std) <= 0.114),
+    }
+    print(json.dumps(line), flush=True)
+
+
 def main():
     args = parse_args()
     if args.impl == "reference":
         run_reference(args)
+    elif args.mode == "parity":
+        run_parity(args)
     elif args.mode == "train":
         run_train(args)
     else:
