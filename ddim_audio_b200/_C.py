@@ -31,6 +31,8 @@ SIGNATURES = {
     "ddimb_sqerr_loss_bwd": [_vp, _vp, _vp, _vp, _i, _ll],
     "ddimb_denoise2d": [_vp, _vp, _vp, _ll, _i, _i, _i, _i, _i],
     "ddimb_ema_update": [_vp, _i, _ll, _d],
+    "ddimb_grad_clip": [_vp, _i, _ll, _d, _vp, _vp],
+    "ddimb_optim_step": [_vp, _i, _ll, _i, _d, _d, _d, _d, _d, _ll],
     "ddimb_conv_in": [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i],
     "ddimb_conv_out": [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i],
     "ddimb_conv3x3": [_vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _i, _i, _i, _i, _i],

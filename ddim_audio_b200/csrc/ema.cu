@@ -17,7 +17,7 @@ struct EmaChunk {
 
 __global__ void __launch_bounds__(256) ema_update_kernel(const EmaChunk* __restrict__ table, float one_minus_mu, float mu) {
   const EmaChunk c = table[blockIdx.x];
-  const int n4 = (int)(c.n >> 2);
+  const int n4 = ((reinterpret_cast<uintptr_t>(c.p) | reinterpret_cast<uintptr_t>(c.s)) & 15) ? 0 : (int)(c.n >> 2);
   const float4* p4 = reinterpret_cast<const float4*>(c.p);
   float4* s4 = reinterpret_cast<float4*>(c.s);
   for (int i = threadIdx.x; i < n4; i += 256) {

@@ -40,8 +40,6 @@ class EMAHelper(object):
                 raise RuntimeError("ddim_audio_b200.EMAHelper: parameters and shadow must be CUDA tensors (there is no CPU path)")
             if p.dtype != torch.float32 or s.dtype != torch.float32 or not p.is_contiguous() or not s.is_contiguous() or s.shape != p.shape:
                 raise RuntimeError("ddim_audio_b200.EMAHelper: expected contiguous float32 parameter / shadow pairs of equal shape")
-            if (p.data_ptr() | s.data_ptr()) & 15:
-                raise RuntimeError("ddim_audio_b200.EMAHelper: parameter storage must be 16-byte aligned")
             n = p.numel()
             total += n
             for off in range(0, n, CHUNK):

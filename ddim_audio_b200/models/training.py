@@ -23,12 +23,14 @@ class _Saved:
 
 
 def _flat_views(model, device):
-    total = sum(p.numel() for p in model.parameters())
+    # every view starts on a 16-byte boundary (128-bit accesses in the optimizer / clip kernels); the <= 3 zero floats of
+    # padding per parameter ride along in the data-parallel all-reduce
+    total = sum((p.numel() + 3) // 4 * 4 for p in model.parameters())
     flat = torch.zeros(total, dtype=torch.float32, device=device)
     views, off = {}, 0
     for name, p in model.named_parameters():
         views[name] = flat[off:off + p.numel()].view(p.shape)
-        off += p.numel()
+        off += (p.numel() + 3) // 4 * 4
     return flat, views
 
 

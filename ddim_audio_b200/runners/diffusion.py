@@ -17,6 +17,7 @@ import numpy as np
 import torch
 
 from ..functions.denoising import generalized_steps
+from ..functions import optim as fused_optim
 from ..functions.losses import loss_registry
 from ..models.diffusion import Model
 from ..models.ema import EMAHelper
@@ -65,22 +66,24 @@ def classify_group(config, model):
 
 
 def get_optimizer(config, parameters):
-    """functions/__init__.py:5-50.  Optimizer arithmetic is out of scope (stock torch objects on the fp32 masters); AdaBelief
-    lives in the reference's GPL submodule External/step-clip-optimizer and is imported from there when present."""
+    """functions/__init__.py:5-50.  AdamW and AdaBelief (the two the reference's audio.yml configures) are the fused library
+    optimizers of ``functions/optim.py`` on CUDA parameters; the other names stay stock torch objects on the fp32 masters."""
     import torch.optim as optim
 
+    from ..functions import optim as fused
+
+    parameters = list(parameters)
+    on_cuda = bool(parameters) and all(p.is_cuda for p in parameters)
     kw = dict(lr=config.lr, weight_decay=config.weight_decay, betas=tuple(config.beta), amsgrad=config.amsgrad, eps=config.eps)
     if config.optimizer == "Adam":
         return optim.Adam(parameters, **kw)
     if config.optimizer == "AdamW":
-        return optim.AdamW(parameters, **kw)
+        return fused.AdamW(parameters, **kw) if on_cuda and not config.amsgrad else optim.AdamW(parameters, **kw)
     if config.optimizer == "AdaBelief":
-        try:
-            from clip_opt import AdaBelief
-        except ImportError as e:
-            raise NotImplementedError("AdaBelief needs the reference's External/step-clip-optimizer on sys.path (out of scope here)") from e
-        return AdaBelief(parameters, weight_decouple=True, fixed_decay=False, rectify=False, clip_step=config.clip_step,
-                         norm_ord=config.norm_ord, **kw)
+        if not on_cuda:
+            raise RuntimeError("ddim_audio_b200: AdaBelief needs CUDA parameters (there is no CPU path)")
+        return fused.AdaBelief(parameters, weight_decouple=True, fixed_decay=False, rectify=False, clip_step=config.clip_step,
+                               norm_ord=config.norm_ord, **kw)
     if config.optimizer == "RMSProp":
         return optim.RMSprop(parameters, lr=config.lr, weight_decay=config.weight_decay)
     if config.optimizer == "SGD":
@@ -236,7 +239,7 @@ class Diffusion(object):
         loggings = {"step": step, "loss": float(loss.item())}
         for g in grad_group.values():
             if g.config.grad_clip is not None:
-                torch.nn.utils.clip_grad_norm_(g.params, g.config.grad_clip)
+                fused_optim.clip_grad_norm_(g.params, g.config.grad_clip)               # :155-160, two launches per group
         for name, opt in optimizers.items():
             out = opt.step()
             if type(out) is dict:

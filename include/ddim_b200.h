@@ -70,9 +70,29 @@ int ddimb_denoise2d(const float* x, float* out, void* workspace, long long works
 
 /* models/ema.py:16-23 -- shadow = (1 - mu) param + mu shadow for EVERY registered parameter in one launch (bit-exact: the
  * reference's operation order and fp32 roundings).  chunk_table: DEVICE array of nchunks records
- * {const float* param; float* shadow; long long count; long long pad} (32 bytes each, 16-byte aligned pointers, count <= 2^31),
+ * {const float* param; float* shadow; long long count; long long pad} (32 bytes each, count <= 2^31; 128-bit path when both
+ * pointers are 16-byte aligned),
  * one CTA per record; total_elems = sum of the counts (profiler bookkeeping only). */
 int ddimb_ema_update(const void* chunk_table, int nchunks, long long total_elems, double mu, cudaStream_t stream);
+
+/* ---- optimizer tail of the train step ------------------------------------------------ */
+
+/* chunk_table for both calls: DEVICE array of nchunks 64-byte records
+ *   {float* param; float* grad; float* exp_avg; float* exp_avg_var_or_sq; long long count; long long pad[3]}
+ * (count <= 2^31; records whose pointers are all 16-byte aligned take the 128-bit path), one CTA per record; total_elems = sum
+ * of counts (profiler bookkeeping).
+ *
+ * ddimb_grad_clip -- torch.nn.utils.clip_grad_norm_ as called at runners/diffusion.py:155-160: total_norm = ||all grads||_2
+ * (fp64 accumulation), grads *= min(1, max_norm / (total_norm + 1e-6)) in place; total_norm_out (nullable, device float)
+ * receives the norm.  sqnorm_scratch: one device double.
+ *
+ * ddimb_optim_step -- one optimizer step of every tensor in the table.  kind 0: torch.optim.AdamW (functions/__init__.py:15-23);
+ * kind 1: AdaBelief as configured at functions/__init__.py:24-42 (AdaBelief.py:112-142: weight_decouple, no fixed_decay, no
+ * amsgrad, no rectify, clip_step None).  step = the 1-based step count used for the bias corrections. */
+int ddimb_grad_clip(const void* chunk_table, int nchunks, long long total_elems, double max_norm, double* sqnorm_scratch,
+                    float* total_norm_out, cudaStream_t stream);
+int ddimb_optim_step(const void* chunk_table, int nchunks, long long total_elems, int kind, double lr, double beta1, double beta2,
+                     double eps, double weight_decay, long long step, cudaStream_t stream);
 
 /* ---- network boundary convolutions (CUDA cores; K = 18 / N = 2 are not tensor-core shapes) -------------------- */
 

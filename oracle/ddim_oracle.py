@@ -471,3 +471,54 @@ def ema_case(seed: int, steps: int = 3):
     shapes = {"a.weight": (7, 5, 3, 3), "a.bias": (7,), "b.weight": (130, 257), "c.scale": (1,), "d.weight": (3, 16384 + 5)}
     traj = [{k: torch.randn(s, generator=g) for k, s in shapes.items()} for _ in range(steps + 1)]
     return shapes, traj
+
+
+# --------------------------------------------------------------------------------------
+# optimizer tail of the train step -- runners/diffusion.py:155-173
+# --------------------------------------------------------------------------------------
+def clip_grad_norm(grads: Dict[str, torch.Tensor], max_norm: float):
+    """torch.nn.utils.clip_grad_norm_ (L2) as called at runners/diffusion.py:155-160: returns (total_norm, clipped grads)."""
+    total = torch.linalg.vector_norm(torch.stack([torch.linalg.vector_norm(g) for g in grads.values()]))
+    coef = torch.clamp(max_norm / (total + 1e-6), max=1.0)
+    return total, {k: g * coef for k, g in grads.items()}
+
+
+def adamw_step(p, g, m, v, step: int, lr: float, betas, eps: float, weight_decay: float):
+    """torch.optim.AdamW single-tensor arithmetic (functions/__init__.py:15-23 constructs it): decoupled decay, lerp first
+    moment, bias corrections as Python floats.  Returns new (p, m, v)."""
+    b1, b2 = betas
+    p = p * (1 - lr * weight_decay)
+    m = m + (g - m) * (1 - b1)
+    v = v * b2 + (1 - b2) * g * g
+    bc1, bc2 = 1 - b1 ** step, 1 - b2 ** step
+    denom = v.sqrt() / (bc2 ** 0.5) + eps
+    return p + (-(lr / bc1)) * (m / denom), m, v
+
+
+def adabelief_step(p, g, m, v, step: int, lr: float, betas, eps: float, weight_decay: float):
+    """External/step-clip-optimizer/clip_opt/adabelief/AdaBelief.py:112-142 with the reference's configuration
+    (functions/__init__.py:36-41: weight_decouple, not fixed_decay, no amsgrad / rectify; audio.yml clip_step null)."""
+    b1, b2 = betas
+    m = m * b1 + (1 - b1) * g                                   # :113
+    r = g - m                                                   # :114
+    v = v * b2 + (1 - b2) * r * r                               # :115-117
+    bc1, bc2 = 1 - b1 ** step, 1 - b2 ** step                   # :119-120
+    denom = v.sqrt() / (bc2 ** 0.5) + eps                       # :130
+    if weight_decay != 0:
+        p = p * (1.0 - weight_decay)                            # :134-137 (rate = [1, lr][fixed_decay] * weight_decay)
+    return p + (-lr / bc1) * (m / denom), m, v                  # :138
+
+
+def optim_case(seed: int, steps: int = 3):
+    """Seeded parameters and per-step gradients for the optimizer fixtures (ragged sizes, one tensor > one 64 K chunk)."""
+    g = torch.Generator().manual_seed(seed)
+    shapes = {"a.weight": (7, 5, 3, 3), "a.bias": (7,), "b.weight": (130, 257), "c.scale": (1,), "d.weight": (2, 65536 + 3)}
+    params = {k: torch.randn(s, generator=g) for k, s in shapes.items()}
+    grads = [{k: 0.3 * torch.randn(s, generator=g) * (1.0 + 4.0 * (i == 1)) for k, s in shapes.items()} for i in range(steps)]
+    return params, grads
+
+
+def optim_probe(t: torch.Tensor) -> torch.Tensor:
+    """What the optimizer fixtures store of a tensor: all of it, or every 7th element above 20 K elements."""
+    t = t.detach().reshape(-1)
+    return t[::7] if t.numel() > 20000 else t

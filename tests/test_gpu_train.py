@@ -124,13 +124,13 @@ def test_train_mode_dropout_runs_and_is_seeded(model):
 
 
 def test_runner_train_step_updates_parameters(oracle_sd):
-    """Diffusion.train over an injected loader: loss/backward in library kernels, stock torch optimizer on the fp32 masters."""
+    """Diffusion.train over an injected loader with audio.yml's own optimizers: loss/backward, gradient clipping, AdaBelief
+    (default group) + AdamW (transformer group) and the EMA all in library kernels on the fp32 masters."""
     import argparse
     from ddim_audio_b200.config import audio_config
     from ddim_audio_b200.models.diffusion import Model
     from ddim_audio_b200.runners.diffusion import Diffusion
     cfg = audio_config()
-    cfg.optimization.optimizer.default.optimizer = "AdamW"        # AdaBelief lives in the reference's GPL submodule
     cfg.training.snapshot_freq = 10 ** 9
     m = Model(cfg)
     m.load_state_dict(oracle_sd, strict=True)

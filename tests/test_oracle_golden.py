@@ -126,3 +126,27 @@ def test_ema_update(golden_dir):
         shadow = O.ema_update(shadow, step, mu)
     for k, v in shadow.items():
         assert np.array_equal(v.numpy(), g[k.replace(".", "__")]), k
+
+
+@pytest.mark.parametrize("name", ["adabelief", "adamw"])
+def test_optimizer_tail(golden_dir, name):
+    """clip_grad_norm_ + AdaBelief / AdamW restatements against three steps of the reference's own
+    optimizers (oracle/make_golden_optim.py).  fp32 rounding only (torch's kernels fuse some multiply-adds)."""
+    g = _load(golden_dir, "optim_steps")
+    cfg = {"adabelief": dict(lr=0.0003, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.00001, warmup=1000),
+           "adamw": dict(lr=0.0005, betas=(0.9, 0.998), eps=1e-6, weight_decay=0.0001, warmup=10000)}[name]
+    params, grads = O.optim_case(int(g["seed"]))
+    m = {k: torch.zeros_like(v) for k, v in params.items()}
+    v = {k: torch.zeros_like(v_) for k, v_ in params.items()}
+    fn = O.adabelief_step if name == "adabelief" else O.adamw_step
+    for i, gr in enumerate(grads):
+        total, cg = O.clip_grad_norm(gr, 1.0)
+        assert float(total) == pytest.approx(float(g[f"{name}__norms"][i]), rel=1e-6)
+        lr = cfg["lr"] * min(((1 + i) / cfg["warmup"]) ** -0.5, (1 + i) / cfg["warmup"])
+        for k in params:
+            params[k], m[k], v[k] = fn(params[k], cg[k], m[k], v[k], i + 1, lr, cfg["betas"], cfg["eps"], cfg["weight_decay"])
+    for k in params:
+        kk = k.replace(".", "__")
+        np.testing.assert_allclose(O.optim_probe(params[k]).numpy(), g[f"{name}__p__{kk}"], rtol=0, atol=1e-7)
+        np.testing.assert_allclose(O.optim_probe(m[k]).numpy(), g[f"{name}__m__{kk}"], rtol=1e-5, atol=1e-9)
+        np.testing.assert_allclose(O.optim_probe(v[k]).numpy(), g[f"{name}__v__{kk}"], rtol=1e-5, atol=1e-12)
