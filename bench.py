@@ -338,6 +338,7 @@ def run_b200(args):
             "clocks": clk, "e2e": e2e, "gpu_launches": int(launches), "roofline": roof, "cpu_baseline": cpu,
             "step_roofline": {"t_roof_ms_per_step": t_roof / K, "frac": (t_roof / K) / (ms / K), "note": "sum over kernels of max(bytes/HBM peak, flops/tensor peak) / measured step"},
             "kernels": kern, "finite": finite,
+            "optimizer_tail": tail,
         }
         print(json.dumps(line), flush=True)
     if world > 1:
@@ -438,6 +439,66 @@ def run_train(args):
         e2e = {"value": world * B * K / dt, "unit": "samples/s", "h2d_bytes_per_step": 2 * x_host.numel() * 4 + 8 * B, "d2h_bytes_per_step": 4,
                "ms_per_step": 1e3 * dt / K, "api": "noise_estimation_loss(model, x0, t, e, alphas).backward() on a pinned host batch + loss.item()", "last_loss": lv}
 
+    # optimizer tail of train_step (runners/diffusion.py:155-183): per-group clip, AdaBelief (default group) + AdamW (transformer
+    # group), EMA -- fused library launches, next to the same arithmetic as stock torch objects (torch AdamW for both groups:
+    # the reference's AdaBelief is a Python loop of ~12 ops per tensor and does not travel to this box)
+    tail = None
+    if rank == 0 and world == 1:
+        from ddim_audio_b200.functions import optim as fused
+        from ddim_audio_b200.models.ema import EMAHelper
+        tr = [p for n, p in model.named_parameters() if n.startswith("transformer.") and p.grad is not None]
+        de = [p for n, p in model.named_parameters() if not n.startswith("transformer.") and p.grad is not None]
+        saved = [p.data.clone() for p in params]
+        gsaved = [p.grad.clone() for p in tr + de]
+
+        def wall_ms(fn, reps=5):
+            fn()
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            for _ in range(reps):
+                fn()
+            torch.cuda.synchronize()
+            return 1e3 * (time.perf_counter() - t0) / reps
+
+        f_opt = [fused.AdamW(tr, lr=5e-4, betas=(0.9, 0.998), eps=1e-6, weight_decay=1e-4),
+                 fused.AdaBelief(de, lr=3e-4, betas=(0.9, 0.999), eps=1e-8, weight_decay=1e-5)]
+        f_ema = EMAHelper(mu=0.9999)
+        f_ema.register(model)
+
+        def fused_tail():
+            fused.clip_grad_norm_(tr, 1.0)
+            fused.clip_grad_norm_(de, 1.0)
+            for o in f_opt:
+                o.step()
+            f_ema.update(model)
+
+        l0 = _C.launch_count()
+        fused_ms = wall_ms(fused_tail)
+        fused_launches = (_C.launch_count() - l0) // 6
+        for p, g_ in zip(tr + de, gsaved):
+            p.grad.copy_(g_)
+        t_opt = [torch.optim.AdamW(tr, lr=5e-4, betas=(0.9, 0.998), eps=1e-6, weight_decay=1e-4),
+                 torch.optim.AdamW(de, lr=3e-4, betas=(0.9, 0.999), eps=1e-8, weight_decay=1e-5)]
+        shadow = {n: p.data.clone() for n, p in model.named_parameters()}
+
+        def torch_tail():
+            torch.nn.utils.clip_grad_norm_(tr, 1.0)
+            torch.nn.utils.clip_grad_norm_(de, 1.0)
+            for o in t_opt:
+                o.step()
+            for n, p in model.named_parameters():                                   # models/ema.py:16-23 as written
+                shadow[n].data = (1.0 - 0.9999) * p.data + 0.9999 * shadow[n].data
+
+        torch_ms = wall_ms(torch_tail)
+        with torch.no_grad():
+            for p, v in zip(params, saved):
+                p.data.copy_(v)
+        n_el = sum(p.numel() for p in tr + de)
+        tail = {"fused_ms": fused_ms, "fused_launches": int(fused_launches), "torch_ms": torch_ms,
+                "fused_GBps": (12.0 + 28.0 + 12.0) * n_el / fused_ms / 1e6, "tensors": len(tr) + len(de), "elements": n_el,
+                "timing": "wall clock incl. host launch cost, synchronize both sides, 5 repetitions",
+                "note": "torch leg = clip_grad_norm_ + torch.optim.AdamW (foreach) for both groups + the reference's per-tensor EMA loop"}
+
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         from oracle import ddim_oracle as O
@@ -461,6 +522,7 @@ def run_train(args):
                        "l2": "inputs larger than L2 (level-0 activations are 537 MB each)" if B * T >= 16384 else "small debug shape"},
             "clocks": clk, "e2e": e2e, "gpu_launches": int(launches), "roofline": roof, "cpu_baseline": cpu,
             "step_roofline": {"t_roof_ms_per_step": t_roof / K, "frac": (t_roof / K) / (ms / K)}, "kernels": kern, "finite": finite,
+            "optimizer_tail": tail,
         }
         print(json.dumps(line), flush=True)
     if world > 1:

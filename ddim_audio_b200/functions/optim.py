@@ -27,8 +27,9 @@ class ChunkTable:
         self.table = None
         self.total = 0
 
-    def get(self, columns, device):
-        """columns: list of 4 lists of equally-shaped tensors (None entries allowed as whole columns)."""
+    def get(self, columns, device, check=None):
+        """columns: list of 4 lists of equally-shaped tensors (None entries allowed as whole columns).  ``check`` (dtype /
+        device / contiguity validation) runs only when a pointer moved and the table is rebuilt."""
         ref = next(c for c in columns if c is not None)
         n_t = len(ref)
         ptrs = np.zeros((n_t, 4), dtype=np.int64)
@@ -39,6 +40,8 @@ class ChunkTable:
         key = (ptrs.tobytes(), numel.tobytes())
         if key == self.key:
             return self.table, self.total
+        if check is not None:
+            check()
         nch = (numel + CHUNK - 1) // CHUNK
         owner = np.repeat(np.arange(n_t), nch)
         first = np.repeat(np.cumsum(nch) - nch, nch)
@@ -74,10 +77,11 @@ def clip_grad_norm_(parameters, max_norm, norm_type=2.0):
     grads = [p.grad for p in parameters if p.grad is not None]
     if not grads:
         return torch.tensor(0.0)
-    _check(grads, "gradients")
+    if not grads[0].is_cuda:
+        raise RuntimeError("ddim_audio_b200.optim: gradients must be CUDA tensors (there is no CPU path)")
     dev = grads[0].device
     slot = _clip_tables.setdefault((dev, len(grads)), (ChunkTable(), torch.zeros(1, dtype=torch.float64, device=dev)))
-    table, total = slot[0].get([None, grads, None, None], dev)
+    table, total = slot[0].get([None, grads, None, None], dev, check=lambda: _check(grads, "gradients"))
     norm = torch.empty((), dtype=torch.float32, device=dev)
     _C.call("ddimb_grad_clip", _C.ptr(table), table.shape[0], total, float(max_norm), _C.ptr(slot[1]), _C.ptr(norm))
     return norm
@@ -94,9 +98,6 @@ class _Fused(Optimizer):
     def _init_state(self, p, state):
         raise NotImplementedError
 
-    def _step_of(self, state):
-        raise NotImplementedError
-
     @torch.no_grad()
     def step(self, closure=None):
         loss = None
@@ -110,21 +111,23 @@ class _Fused(Optimizer):
             if group.get("amsgrad", False):
                 raise NotImplementedError("ddim_audio_b200.optim: amsgrad is not on the reference's configured path (audio.yml:90,101)")
             grads = [p.grad for p in ps]
-            _check(ps, "parameters")
-            _check(grads, "gradients")
-            steps = set()
-            for p in ps:
-                st = self.state[p]
+            if not ps[0].is_cuda:
+                raise RuntimeError("ddim_audio_b200.optim: parameters must be CUDA tensors (there is no CPU path)")
+            states = [self.state[p] for p in ps]
+            for p, st in zip(ps, states):
                 if len(st) == 0:
                     self._init_state(p, st)
-                steps.add(self._bump(st))
-            if len(steps) != 1:
-                raise RuntimeError("ddim_audio_b200.optim: parameters of one group must share a step count")
+            step = self._bump(states)
             beta1, beta2 = group["betas"]
+
+            def check():
+                _check(ps, "parameters")
+                _check(grads, "gradients")
+
             table, total = self._tables.setdefault(gi, ChunkTable()).get(
-                [[p.data for p in ps], grads, [self.state[p]["exp_avg"] for p in ps], [self.state[p][self.SECOND] for p in ps]], ps[0].device)
+                [[p.data for p in ps], grads, [st["exp_avg"] for st in states], [st[self.SECOND] for st in states]], ps[0].device, check)
             _C.call("ddimb_optim_step", _C.ptr(table), table.shape[0], total, self.KIND, float(group["lr"]), float(beta1), float(beta2),
-                    float(group["eps"]), float(group["weight_decay"]), int(steps.pop()))
+                    float(group["eps"]), float(group["weight_decay"]), step)
         return self._result(loss)
 
 
@@ -140,9 +143,13 @@ class AdamW(_Fused):
         st["exp_avg"] = torch.zeros_like(p.data, memory_format=torch.preserve_format)
         st["exp_avg_sq"] = torch.zeros_like(p.data, memory_format=torch.preserve_format)
 
-    def _bump(self, st):
-        st["step"] += 1
-        return int(st["step"])
+    def _bump(self, states):
+        steps = [st["step"] for st in states]
+        torch._foreach_add_(steps, 1)
+        lo, hi = int(steps[0]), int(steps[-1])
+        if lo != hi:
+            raise RuntimeError("ddim_audio_b200.optim: parameters of one group must share a step count")
+        return lo
 
     def _result(self, loss):
         return loss
@@ -169,9 +176,12 @@ class AdaBelief(_Fused):
         st["exp_avg"] = torch.zeros_like(p.data, memory_format=torch.preserve_format)
         st["exp_avg_var"] = torch.zeros_like(p.data, memory_format=torch.preserve_format)
 
-    def _bump(self, st):
-        st["step"] += 1
-        return int(st["step"])
+    def _bump(self, states):
+        for st in states:
+            st["step"] += 1
+        if states[0]["step"] != states[-1]["step"]:
+            raise RuntimeError("ddim_audio_b200.optim: parameters of one group must share a step count")
+        return int(states[0]["step"])
 
     def _result(self, loss):
         return {"loss": loss, "norm": None}

@@ -20,6 +20,7 @@ class EMAHelper(object):
     def __init__(self, mu=0.999):
         self.mu = mu
         self.shadow = {}
+        self._named = None      # (module, [(name, parameter)]) of the last update
         self._table = None      # (device int64 [nchunks, 4], total elements, key of the (param, shadow) pointers it was built for)
 
     def register(self, module):
@@ -30,7 +31,10 @@ class EMAHelper(object):
         self._table = None
 
     def _chunks(self, module):
-        pairs = [(p.data, self.shadow[n]) for n, p in _unwrap(module).named_parameters() if p.requires_grad]
+        inner = _unwrap(module)
+        if self._named is None or self._named[0] is not inner:                      # the module walk is the slow part: once per model
+            self._named = (inner, [(n, p) for n, p in inner.named_parameters()])
+        pairs = [(p.data, self.shadow[n]) for n, p in self._named[1] if p.requires_grad]
         key = tuple((p.data_ptr(), s.data_ptr(), p.numel()) for p, s in pairs)
         if self._table is not None and self._table[2] == key:
             return self._table
