@@ -45,8 +45,8 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--batch", type=int, default=64, help="samples per GPU (config 3: 64)")
-    ap.add_argument("--t-size", type=int, default=8192, help="time frames (audio.yml sampling.t_size: 8192)")
+    ap.add_argument("--batch", type=int, default=None, help="samples per GPU (default: 64, BASELINE configs[2]; --mode train: 32, configs[1])")
+    ap.add_argument("--t-size", type=int, default=None, help="time frames (default: audio.yml sampling.t_size 8192; --mode train: model.t_size 1024)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--cpu-sample-steps", type=int, default=2)
@@ -57,7 +57,13 @@ def parse_args():
     ap.add_argument("--parity-steps", type=int, default=50)
     ap.add_argument("--parity-batch", type=int, default=4)
     ap.add_argument("--parity-t-size", type=int, default=1024)
-    return ap.parse_args()
+    args = ap.parse_args()
+    train = args.mode == "train" and args.impl != "reference"
+    if args.t_size is None:
+        args.t_size = 1024 if train else 8192
+    if args.batch is None:
+        args.batch = 32 if train else 64
+    return args
 
 
 def peaks():
@@ -374,8 +380,8 @@ def run_train(args):
     model.load_state_dict(sd, strict=True)
     model.train()
     al = alphas_cumprod().to(dev)
-    B = args.batch if args.batch != 64 else 32
-    T = args.t_size if args.t_size != 8192 else 1024
+    B = args.batch
+    T = args.t_size
     K, W = args.steps, max(args.warmup, 0)
     g = torch.Generator().manual_seed(4321 + rank)
     x_host = torch.randn(B, 2, T, F_SIZE, generator=g).pin_memory()
