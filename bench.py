@@ -344,7 +344,6 @@ def run_b200(args):
             "clocks": clk, "e2e": e2e, "gpu_launches": int(launches), "roofline": roof, "cpu_baseline": cpu,
             "step_roofline": {"t_roof_ms_per_step": t_roof / K, "frac": (t_roof / K) / (ms / K), "note": "sum over kernels of max(bytes/HBM peak, flops/tensor peak) / measured step"},
             "kernels": kern, "finite": finite,
-            "optimizer_tail": tail,
         }
         print(json.dumps(line), flush=True)
     if world > 1:

@@ -4,6 +4,7 @@
 // just to normalise it.
 #include "../../include/ddim_b200.h"
 #include "common.cuh"
+#include <stdlib.h>
 
 using namespace ddimb;
 
@@ -166,6 +167,7 @@ struct GnArgs {
   float eps;
 };
 
+template <int UNR>
 __global__ void __launch_bounds__(256) gn_apply_kernel(const GnArgs a) {
   __shared__ float s_scale[256], s_shift[256];
   const int b = blockIdx.y, C = a.C, cg = C >> 3;
@@ -192,7 +194,7 @@ __global__ void __launch_bounds__(256) gn_apply_kernel(const GnArgs a) {
   uint4* yp = reinterpret_cast<uint4*>(a.y + (int64_t)b * a.per_sample);
   float sa1 = 0.f, sa2 = 0.f, sb1 = 0.f, sb2 = 0.f;   // channels c0..c0+3 and c0+4..c0+7 (group width is a multiple of 4)
   // UNR items per iteration with every load issued before the first use: ~8 x 16 B in flight per thread keeps HBM busy
-  constexpr int UNR = 4;
+  // (UNR = 8 for the one-operand modes, 4 for mode 2 which also loads the residual)
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t i0 = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i0 < items; i0 += UNR * stride) {
     uint4 xv[UNR], rv[UNR];
@@ -251,6 +253,117 @@ __global__ void __launch_bounds__(256) gn_apply_kernel(const GnArgs a) {
   }
 }
 
+// Balanced variant: the (sample, tile) space is cut into gridDim.x CONTIGUOUS ranges of tiles (tile = blockDim * UNR items of
+// one sample), one CTA per range and exactly as many CTAs as are resident at once -- no partial second wave (the 2-D grid above
+// ran 2.7 waves at 3 CTAs / SM and lost 10-30 % to the tail at C >= 96).  A CTA crosses at most a few sample boundaries; there
+// it flushes its statistics and reloads the per-channel scale / shift.
+template <int UNR>
+__global__ void __launch_bounds__(256) gn_apply_ranges_kernel(const GnArgs a, int64_t tiles_per_sample, int64_t tiles_total) {
+  __shared__ float s_scale[256], s_shift[256];
+  __shared__ float s_part[256][4];
+  const int C = a.C, cg = C >> 3;
+  const int c0 = (threadIdx.x * 8) % C;   // blockDim * 8 is a multiple of C and tiles start on multiples of blockDim
+  const int64_t t_begin = tiles_total * blockIdx.x / gridDim.x, t_end = tiles_total * (blockIdx.x + 1) / gridDim.x;
+  const int64_t items = a.per_sample / 8;
+  float sc[8], sh[8];
+  float sa1 = 0.f, sa2 = 0.f, sb1 = 0.f, sb2 = 0.f;
+  int cur_b = -1;
+  const uint4 *xp = nullptr, *rp = nullptr;
+  uint4* yp = nullptr;
+
+  auto flush = [&](int b) {
+    // fixed-order block reduction, as in gn_apply_kernel
+    s_part[threadIdx.x][0] = sa1; s_part[threadIdx.x][1] = sa2; s_part[threadIdx.x][2] = sb1; s_part[threadIdx.x][3] = sb2;
+    __syncthreads();
+    if (threadIdx.x < 16) {
+      const int g = threadIdx.x >> 1, which = threadIdx.x & 1;
+      float acc = 0.f;
+      for (int t = 0; t < (int)blockDim.x; ++t) {
+        const int tc = (t * 8) % C;
+        if (tc / cg == g) acc += s_part[t][which];
+        if ((tc + 4) / cg == g) acc += s_part[t][2 + which];
+      }
+      atomicAdd(a.stats_out + b * 16 + threadIdx.x, (double)acc);
+    }
+    sa1 = sa2 = sb1 = sb2 = 0.f;
+  };
+
+  for (int64_t tile = t_begin; tile < t_end; ++tile) {
+    const int b = (int)(tile / tiles_per_sample);
+    if (b != cur_b) {   // uniform across the CTA
+      if (cur_b >= 0 && a.mode == 2 && a.stats_out) flush(cur_b);
+      __syncthreads();
+      if (threadIdx.x < C) {
+        const int c = threadIdx.x, g = c / cg;
+        const double n = (double)(a.per_sample / 8);
+        const double mean = a.stats_in[(b * 8 + g) * 2] / n;
+        double var = a.stats_in[(b * 8 + g) * 2 + 1] / n - mean * mean;
+        if (var < 0) var = 0;
+        const float rstd = (float)(1.0 / sqrt(var + (double)a.eps));
+        const float scv = a.gamma[c] * rstd;
+        s_scale[c] = scv;
+        s_shift[c] = (a.beta ? a.beta[c] : 0.f) - (float)mean * scv;
+      }
+      __syncthreads();
+#pragma unroll
+      for (int j = 0; j < 8; ++j) { sc[j] = s_scale[c0 + j]; sh[j] = s_shift[c0 + j]; }
+      xp = reinterpret_cast<const uint4*>(a.x + (int64_t)b * a.per_sample);
+      rp = a.res ? reinterpret_cast<const uint4*>(a.res + (int64_t)b * a.per_sample) : nullptr;
+      yp = reinterpret_cast<uint4*>(a.y + (int64_t)b * a.per_sample);
+      cur_b = b;
+    }
+    const int64_t base = (tile - (int64_t)b * tiles_per_sample) * ((int64_t)blockDim.x * UNR) + threadIdx.x;
+    uint4 xv[UNR], rv[UNR];
+#pragma unroll
+    for (int u = 0; u < UNR; ++u) {
+      xv[u] = ldg_nc_v4(xp + base + u * (int64_t)blockDim.x);
+      if (a.mode == 2) rv[u] = ldg_nc_v4(rp + base + u * (int64_t)blockDim.x);
+    }
+#pragma unroll
+    for (int u = 0; u < UNR; ++u) {
+      const uint32_t xw[4] = {xv[u].x, xv[u].y, xv[u].z, xv[u].w};
+      float f[8];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        float2 t = unpack_bf16x2(xw[j]);
+        if (a.pre_silu) { t.x = silu_fast(t.x); t.y = silu_fast(t.y); }
+        f[2 * j] = fmaf(t.x, sc[2 * j], sh[2 * j]);
+        f[2 * j + 1] = fmaf(t.y, sc[2 * j + 1], sh[2 * j + 1]);
+      }
+      if (a.mode == 1) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) f[j] = silu_fast(f[j]);
+      } else if (a.mode == 2) {
+        const uint32_t rw[4] = {rv[u].x, rv[u].y, rv[u].z, rv[u].w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const float2 t = unpack_bf16x2(rw[j]);
+          f[2 * j] += t.x; f[2 * j + 1] += t.y;
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) { sa1 += f[j]; sa2 = fmaf(f[j], f[j], sa2); sb1 += f[4 + j]; sb2 = fmaf(f[4 + j], f[4 + j], sb2); }
+      }
+      stg_v4(yp + base + u * (int64_t)blockDim.x,
+             make_uint4(pack_bf16x2(f[0], f[1]), pack_bf16x2(f[2], f[3]), pack_bf16x2(f[4], f[5]), pack_bf16x2(f[6], f[7])));
+    }
+  }
+  (void)items;
+  if (cur_b >= 0 && a.mode == 2 && a.stats_out) flush(cur_b);
+}
+
+template <int UNR>
+static int gn_ranges_launch(const GnArgs& a, int B, int threads, int64_t items, int waves_pct, cudaStream_t stream) {
+  const int64_t tile = (int64_t)threads * UNR;
+  const int64_t tps = items / tile, total = tps * B;
+  int occ = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, gn_apply_ranges_kernel<UNR>, threads, 0) != cudaSuccess || occ < 1) occ = 1;
+  int64_t grid = (int64_t)ddimb_num_sms() * occ * waves_pct / 100;
+  if (grid > total) grid = total;
+  if (grid < 1) grid = 1;
+  gn_apply_ranges_kernel<UNR><<<(unsigned)grid, threads, 0, stream>>>(a, tps, total);
+  return 0;
+}
+
 extern "C" int ddimb_gn_apply(const void* x, const void* res, void* y, const double* stats_in, double* stats_out, const float* gamma,
                               const float* beta, int mode, int B, long long positions, int C, float eps, cudaStream_t stream) {
   DDIMB_CHECK_ARG(x && y && stats_in && gamma && B >= 1 && positions >= 1);
@@ -269,10 +382,25 @@ extern "C" int ddimb_gn_apply(const void* x, const void* res, void* y, const dou
   const int threads = (C % 96 == 0) ? 192 : 256;   // threads * 8 must be a multiple of C
   const int64_t items = a.per_sample / 8;
   int64_t bx = (items + threads * 4 - 1) / (threads * 4);
-  const int64_t cap = (int64_t)ddimb_num_sms() * 8 / B + 1;
-  if (bx > cap) bx = cap;
-  if (bx < 1) bx = 1;
-  gn_apply_kernel<<<dim3((unsigned)bx, B), threads, 0, stream>>>(a);
+  static const int env_cps = getenv("DDIMB_GN_CPS") ? atoi(getenv("DDIMB_GN_CPS")) : 0;
+  static const int env_unr = getenv("DDIMB_GN_UNR") ? atoi(getenv("DDIMB_GN_UNR")) : 0;
+  static const int env_old = getenv("DDIMB_GN_OLD") ? atoi(getenv("DDIMB_GN_OLD")) : 0;      // A/B: 1 = the 2-D grid kernel
+  static const int env_waves = getenv("DDIMB_GN_WAVES") ? atoi(getenv("DDIMB_GN_WAVES")) : 100;   // % of one resident wave
+  const int unr = env_unr > 0 ? env_unr : 4;
+  if (!env_old && items % ((int64_t)threads * unr) == 0 && items / ((int64_t)threads * unr) >= 1) {
+    // balanced contiguous ranges, one resident wave
+    if (unr == 8) gn_ranges_launch<8>(a, B, threads, items, env_waves, stream);
+    else gn_ranges_launch<4>(a, B, threads, items, env_waves, stream);
+  } else {
+    const int cps = env_cps > 0 ? env_cps : 8;
+    int64_t cap = (int64_t)ddimb_num_sms() * cps / B + 1;
+    if (bx > cap) bx = cap;
+    if (bx < 1) bx = 1;
+    if (unr == 8)
+      gn_apply_kernel<8><<<dim3((unsigned)bx, B), threads, 0, stream>>>(a);
+    else
+      gn_apply_kernel<4><<<dim3((unsigned)bx, B), threads, 0, stream>>>(a);
+  }
   DDIMB_LAUNCH_CHECK();
   return DDIMB_OK;
 }
