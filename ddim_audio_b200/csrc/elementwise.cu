@@ -387,7 +387,11 @@ extern "C" int ddimb_gn_apply(const void* x, const void* res, void* y, const dou
   static const int env_old = getenv("DDIMB_GN_OLD") ? atoi(getenv("DDIMB_GN_OLD")) : 0;      // A/B: 1 = the 2-D grid kernel
   static const int env_waves = getenv("DDIMB_GN_WAVES") ? atoi(getenv("DDIMB_GN_WAVES")) : 100;   // % of one resident wave
   const int unr = env_unr > 0 ? env_unr : 4;
-  if (!env_old && items % ((int64_t)threads * unr) == 0 && items / ((int64_t)threads * unr) >= 1) {
+  // measured (tools/ab_gn.sh, B = 64, bench shapes): mode 2 -- ranges kernel +13 % at C = 96, +3 % at 128, +31 % at 192, but the
+  // 2-D grid stays 4 % ahead at C = 32 / 64 (tensors large enough to hide its tail); modes 0 / 1 -- ranges +12 % (C = 64) to
+  // +31 % (C = 96, 192); UNR = 8 is no better than 4 anywhere
+  const bool ranges = env_old == 2 ? true : (env_old == 1 ? false : (mode != 2 || C >= 96));
+  if (ranges && items % ((int64_t)threads * unr) == 0 && items / ((int64_t)threads * unr) >= 1) {
     // balanced contiguous ranges, one resident wave
     if (unr == 8) gn_ranges_launch<8>(a, B, threads, items, env_waves, stream);
     else gn_ranges_launch<4>(a, B, threads, items, env_waves, stream);
