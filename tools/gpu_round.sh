@@ -14,7 +14,7 @@ $SMALL > gpurun_out/plain.log 2>&1 && \
 ncu --metrics gpu__time_duration.sum --clock-control none -c 1200 --csv --log-file gpurun_out/launches.csv $SMALL > gpurun_out/ncu_list.log 2>&1
 echo "ncu list rc=$?"
 $SMALL > gpurun_out/plain2.log 2>&1 && \
-ncu --set full --clock-control none -k regex:'gn_apply_kernel|conv3x3_wide_kernel|conv3x3_window_kernel|umma_gemm_kernel|conv_up_wide|conv_down_wide|conv_out_tc|conv_in_strip' -s 150 -c 48 -f -o gpurun_out/prof_${R} $SMALL > gpurun_out/ncu_full.log 2>&1
+ncu --set full --clock-control none -k regex:'gn_apply|conv3x3_wide_kernel|conv3x3_window_kernel|umma_gemm_kernel|conv_up_wide|conv_down_wide|conv_out_tc|conv_in_strip' -s 150 -c 48 -f -o gpurun_out/prof_${R} $SMALL > gpurun_out/ncu_full.log 2>&1
 echo "ncu full rc=$?"
 FULL="python bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-e2e"
 ncu --set full --clock-control none -k regex:conv3x3_wide_kernel -s 4 -c 2 -f -o gpurun_out/prof_${R}_fullshape $FULL > gpurun_out/ncu_fullshape.log 2>&1
