@@ -69,6 +69,39 @@ def test_no_cpu_fallback(built):
             generalized_steps(x, range(0, 1000, 500), m, torch.ones(1000), None)
 
 
+def test_no_cpu_fallback_widened_rows(built):
+    """the post-filter, the fused optimizers / clip and the EMA refuse CPU tensors instead of falling
+    back to torch; the chunk-table builder (host logic) cuts tensors into <= CHUNK records with the right offsets."""
+    import numpy as np
+    import torch.nn as nn
+    from ddim_audio_b200.functions import optim as fused
+    from ddim_audio_b200.models.ema import EMAHelper
+    from ddim_audio_b200.signal.denoise import denoise_2d
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        denoise_2d(torch.zeros(1, 2, 8, 256))
+    with pytest.raises(RuntimeError, match="no CPU"):
+        denoise_2d(np.zeros((1, 2, 8, 256), np.float32))
+    p = nn.Parameter(torch.zeros(8))
+    p.grad = torch.ones(8)
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        fused.clip_grad_norm_([p], 1.0)
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        fused.AdamW([p]).step()
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        fused.AdaBelief([p]).step()
+    lin = nn.Linear(4, 4)
+    h = EMAHelper(mu=0.9)
+    h.register(lin)
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        h.update(lin)
+    a, b = torch.zeros(fused.CHUNK * 2 + 5), torch.zeros(7)
+    table, total = fused.ChunkTable().get([None, [a, b], None, None], "cpu")
+    assert total == a.numel() + b.numel() and table.shape == (4, 8)
+    assert table[:, 4].tolist() == [fused.CHUNK, fused.CHUNK, 5, 7]
+    assert table[:3, 1].tolist() == [a.data_ptr() + 4 * fused.CHUNK * i for i in range(3)] and int(table[3, 1]) == b.data_ptr()
+    assert int(table[:, [0, 2, 3]].abs().sum()) == 0
+
+
 def test_sampler_scalars_match_oracle():
     from ddim_audio_b200.functions.denoising import _ddim_scalars
     a = O.alphas_cumprod()
