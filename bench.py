@@ -39,6 +39,26 @@ UNIT = "sample-steps/s"
 F_SIZE = 256
 
 
+_JSON_OUT = None
+
+
+def claim_stdout():
+    """The contract is ONE JSON line on stdout.  Libraries print there too (NCCL's version banner, written with the C runtime
+    before NCCL_DEBUG_FILE is honoured), so file descriptor 1 is re-pointed at stderr for the whole process and the real stdout
+    is kept aside for ``emit``."""
+    global _JSON_OUT
+    if _JSON_OUT is None:
+        sys.stdout.flush()
+        _JSON_OUT = os.fdopen(os.dup(1), "w")
+        os.dup2(2, 1)
+
+
+def emit(line):
+    out = _JSON_OUT or sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
+
+
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -197,7 +217,7 @@ def run_reference(args):
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def roofline_from_profile(prof, K):
@@ -345,7 +365,7 @@ def run_b200(args):
             "step_roofline": {"t_roof_ms_per_step": t_roof / K, "frac": (t_roof / K) / (ms / K), "note": "sum over kernels of max(bytes/HBM peak, flops/tensor peak) / measured step"},
             "kernels": kern, "finite": finite,
         }
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 
@@ -529,7 +549,7 @@ def run_train(args):
             "step_roofline": {"t_roof_ms_per_step": t_roof / K, "frac": (t_roof / K) / (ms / K)}, "kernels": kern, "finite": finite,
             "optimizer_tail": tail,
         }
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 
@@ -608,11 +628,12 @@ def run_parity(args):
                 "api": "generalized_steps(x_cuda, seq, model, alphas, None, eta=0): every snapshot copied to the host, wall clock"},
         "pass": bool(max(eps_rel) <= 2e-2 and max(eps_max_over_std) <= 0.114),
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def main():
     args = parse_args()
+    claim_stdout()
     if args.impl == "reference":
         run_reference(args)
     elif args.mode == "parity":
