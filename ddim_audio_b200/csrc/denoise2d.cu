@@ -11,7 +11,7 @@
 // The passes, all READ-ONLY over x:
 //   1. row_median_kernel     warp per row, bitonic sort of the register-resident keys (shuffles)   -> rowoff
 //   2. col_hist_kernel x4    column median of (x - rowoff) by 8-bit radix select: shared-memory histograms
-//      col_scan_kernel x4    [256 bins][32 columns] (lane = column = bank: conflict-free atomics), warp per column scan
+//      col_scan_kernel x4    (16-bit counters, two columns per word, 128-bit row loads), warp per column scan
 //   3. denoise_iter_kernel x5  warp per row: column offsets of all earlier steps staged in shared memory, norm over the 2
 //      col_finalize_kernel x5  channels, num / denom, row means by shuffle, column sums registers -> shared -> fp64 atomics
 //   4. denoise_final_kernel  out = r_iters  (the only write)
@@ -88,43 +88,57 @@ __global__ void __launch_bounds__(256) row_median_kernel(const float* __restrict
 }
 
 // ---------------------------------------------------------------------------------------------- 2. column medians
-// grid (F/32, T chunks, B*C).  lane = column, warp = row phase.  One radix digit (8 bits at `shift`) of the keys of
-// (x - rowoff) that still match the column's prefix is histogrammed into hist[col][256] (global, zero on entry).
+// grid (F/128, T chunks, B*C).  A lane owns 4 adjacent columns (one 128-bit load per row), a warp a 512-byte row segment,
+// the 8 warps alternate rows.  One radix digit (8 bits at `shift`) of the keys of (x - rowoff) that still match the column's
+// prefix is histogrammed in shared memory as 16-bit counters (a chunk has <= 1024 rows), two columns per word:
+// sh[bin][64 words], then flushed into hist[col][256] (global, zero on entry).
+constexpr int kHistRows = 1024;
+constexpr int kHistSmem = 256 * 64 * 4;
 __global__ void __launch_bounds__(256) col_hist_kernel(const float* __restrict__ x, const float* __restrict__ rowoff,
                                                        const uint32_t* __restrict__ prefix, uint32_t* __restrict__ hist, int T, int F,
-                                                       int shift, int rpc) {
-  __shared__ uint32_t sh[256 * 32];
-  for (int i = threadIdx.x; i < 256 * 32; i += 256) sh[i] = 0;
+                                                       int shift) {
+  extern __shared__ uint32_t sh[];
+  for (int i = threadIdx.x; i < 256 * 64; i += 256) sh[i] = 0;
   __syncthreads();
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int bc = blockIdx.z;
-  const int col = blockIdx.x * 32 + lane;
+  const int col0 = blockIdx.x * 128 + lane * 4;
   const uint32_t himask = shift == 24 ? 0u : (0xffffffffu << (shift + 8));
-  const uint32_t pfx = prefix[(int64_t)bc * F + col];
-  const int t0 = blockIdx.y * rpc, t1 = min(T, t0 + rpc);
-  const float* xb = x + (int64_t)bc * T * F + col;
+  const uint4 pfx = *reinterpret_cast<const uint4*>(prefix + (int64_t)bc * F + col0);
+  const uint32_t pf[4] = {pfx.x, pfx.y, pfx.z, pfx.w};
+  const int t0 = blockIdx.y * kHistRows, t1 = min(T, t0 + kHistRows);
+  const float* xb = x + (int64_t)bc * T * F + col0;
   const float* rb = rowoff + (int64_t)bc * T;
   for (int t = t0 + warp; t < t1; t += 32) {
-    float v[4], r[4];
+    float4 v[4];
+    float r[4];
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
       const int tt = t + 8 * u;
-      v[u] = tt < t1 ? xb[(int64_t)tt * F] : 0.f;
+      v[u] = tt < t1 ? *reinterpret_cast<const float4*>(xb + (int64_t)tt * F) : make_float4(0.f, 0.f, 0.f, 0.f);
       r[u] = tt < t1 ? rb[tt] : 0.f;
     }
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
       if (t + 8 * u < t1) {
-        const uint32_t key = order_key(__fsub_rn(v[u], r[u]));
-        if ((key & himask) == pfx) atomicAdd(&sh[((key >> shift) & 255u) * 32 + lane], 1u);
+        const float e[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const uint32_t key = order_key(__fsub_rn(e[j], r[u]));
+          if ((key & himask) == pf[j]) atomicAdd(&sh[((key >> shift) & 255u) * 64 + lane * 2 + (j >> 1)], (j & 1) ? 0x10000u : 1u);
+        }
       }
     }
   }
   __syncthreads();
-  uint32_t* hb = hist + ((int64_t)bc * F + blockIdx.x * 32) * 256;
-  for (int i = threadIdx.x; i < 256 * 32; i += 256) {
-    const uint32_t c = sh[i];
-    if (c) atomicAdd(hb + (i & 31) * 256 + (i >> 5), c);
+  uint32_t* hb = hist + ((int64_t)bc * F + blockIdx.x * 128) * 256;
+  for (int i = threadIdx.x; i < 256 * 64; i += 256) {
+    const uint32_t w = sh[i];
+    if (w) {
+      const int c = (i & 63) * 2, bin = i >> 6;
+      if (w & 0xffffu) atomicAdd(hb + c * 256 + bin, w & 0xffffu);
+      if (w >> 16) atomicAdd(hb + (c + 1) * 256 + bin, w >> 16);
+    }
   }
 }
 
@@ -343,9 +357,13 @@ int run(const float* x, float* out, const Workspace& w, int B, int T, int iters,
   DDIMB_CUDA(cudaMemsetAsync(w.colsum, 0, w.colsum_bytes, stream));
   col_select_init_kernel<<<(unsigned)((ncols + 255) / 256), 256, 0, stream>>>(w.prefix, w.krem, ncols, (uint32_t)((T - 1) / 2));
   DDIMB_LAUNCH_CHECK();
-  const int hist_rpc = 1024;
+  static bool hist_attr = false;
+  if (!hist_attr) {
+    DDIMB_CUDA(cudaFuncSetAttribute(col_hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kHistSmem));
+    hist_attr = true;
+  }
   for (int shift = 24; shift >= 0; shift -= 8) {
-    col_hist_kernel<<<dim3(F / 32, (T + hist_rpc - 1) / hist_rpc, B * C), 256, 0, stream>>>(x, w.rowoff, w.prefix, w.hist, T, F, shift, hist_rpc);
+    col_hist_kernel<<<dim3(F / 128, (T + kHistRows - 1) / kHistRows, B * C), 256, kHistSmem, stream>>>(x, w.rowoff, w.prefix, w.hist, T, F, shift);
     DDIMB_LAUNCH_CHECK();
     col_scan_kernel<<<(unsigned)((ncols + 7) / 8), 256, 0, stream>>>(w.hist, w.prefix, w.krem, w.coloff, ncols, shift);
     DDIMB_LAUNCH_CHECK();
