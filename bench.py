@@ -69,6 +69,7 @@ def parse_args():
     ap.add_argument("--t-size", type=int, default=None, help="time frames (default: audio.yml sampling.t_size 8192; --mode train: model.t_size 1024)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--e2e-chunks", type=int, default=0, help="sample groups of the pipelined host path (0 = the API's default)")
     ap.add_argument("--cpu-sample-steps", type=int, default=2)
     ap.add_argument("--mode", default="sample", choices=["sample", "train", "parity"],
                     help="sample: DDIM sample-steps/s (the headline, BASELINE configs[2]); train: noise_estimation_loss fwd+bwd samples/s "
@@ -329,15 +330,16 @@ def run_b200(args):
     e2e = None
     if not args.no_e2e:
         ald = al.to(dev)
+        ckw = {"chunks": args.e2e_chunks} if args.e2e_chunks > 0 else {}
         cur = x_host
         with torch.no_grad():
             for i in range(max(W, 1)):
-                xs, x0 = generalized_steps(cur, [seq_all[-1 - i]], model, ald, None, eta=0.0)
+                xs, x0 = generalized_steps(cur, [seq_all[-1 - i]], model, ald, None, eta=0.0, **ckw)
                 cur = xs[-1]
             barrier()
             t0 = time.perf_counter()
             for i in range(K):
-                xs, x0 = generalized_steps(cur, [seq_all[-1 - W - i]], model, ald, None, eta=0.0)
+                xs, x0 = generalized_steps(cur, [seq_all[-1 - W - i]], model, ald, None, eta=0.0, **ckw)
                 cur = xs[-1]
             barrier()
             dt = max_over_ranks(time.perf_counter() - t0)
