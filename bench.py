@@ -75,6 +75,13 @@ def parse_args():
                     help="sample: DDIM sample-steps/s (the headline, BASELINE configs[2]); train: noise_estimation_loss fwd+bwd samples/s "
                          "(configs[1]/[4]); parity: configs[0] -- 50 DDIM steps, batch 4, T=1024 on the GPU and on the CPU oracle, "
                          "per-step eps and final-sample error")
+    ap.add_argument("--no-parity", action="store_true", help="skip the parity / batch-position objects of the default line")
+    ap.add_argument("--no-small-batch", action="store_true")
+    ap.add_argument("--no-train", action="store_true", help="skip the bounded train leg of the default line")
+    ap.add_argument("--train-batch", type=int, default=32)
+    ap.add_argument("--train-t-size", type=int, default=1024)
+    ap.add_argument("--train-steps", type=int, default=5)
+    ap.add_argument("--train-warmup", type=int, default=3)
     ap.add_argument("--parity-steps", type=int, default=50)
     ap.add_argument("--parity-batch", type=int, default=4)
     ap.add_argument("--parity-t-size", type=int, default=1024)
@@ -177,34 +184,58 @@ def synthetic_state_dict():
 
 
 # ------------------------------------------------------------------------------------------------ CPU legs (oracle = checker / baseline only)
-def cpu_steps(sd, t_size, nsteps, warm=True):
-    """nsteps DDIM steps of the oracle on x[1,2,t_size,256] with every host thread; returns (seconds, cores)."""
+class _Recorder:
+    """Wraps the oracle model: keeps every (xt, t, eps) of the run so the CUDA denoiser can be evaluated teacher-forced."""
+
+    def __init__(self, inner, keep):
+        self.inner, self.keep, self.calls = inner, keep, []
+
+    def __call__(self, x, t):
+        et = self.inner(x, t)
+        if self.keep:
+            self.calls.append((x.clone(), t.clone(), et))
+        return et
+
+
+def cpu_steps(sd, t_size, nsteps, warm=True, record=False):
+    """nsteps DDIM steps of the oracle on x[1,2,t_size,256] with every host thread; returns (seconds, cores, record) where
+    record = None or dict(x, seq, calls=[(xt, t, eps)], xs, x0) of the timed run (the parity object's reference side)."""
     import torch
     from oracle import ddim_oracle as O
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    model = O.OracleModel(sd)
+    model = _Recorder(O.OracleModel(sd), record)
     al = alphas_cumprod()
     g = torch.Generator().manual_seed(1234)
     if warm:
-        O.generalized_steps(torch.randn(1, 2, 32, F_SIZE, generator=g), [999], model, al, set(), eta=0.0)
+        O.generalized_steps(torch.randn(1, 2, 32, F_SIZE, generator=g), [999], O.OracleModel(sd), al, set(), eta=0.0)
     x = torch.randn(1, 2, t_size, F_SIZE, generator=g)
     seq = list(range(0, 1000, 1000 // 50))[-nsteps:] if nsteps <= 50 else list(range(1000))[-nsteps:]
     t0 = time.perf_counter()
-    O.generalized_steps(x, seq, model, al, set(), eta=0.0)
-    return time.perf_counter() - t0, cores
+    xs, x0 = O.generalized_steps(x, seq, model, al, None if record else set(), eta=0.0)
+    dt = time.perf_counter() - t0
+    rec = dict(x=x, seq=seq, calls=model.calls, xs=xs, x0=x0) if record else None
+    return dt, cores, rec
+
+
+def oracle_state_dict():
+    """Weights for the CPU legs that must not load the product library (``--impl reference``): the oracle's own seeded synthetic
+    state_dict (same 389 keys / shapes, live norm.2.weight).  CPU time per step does not depend on the weight values."""
+    from oracle import ddim_oracle as O
+    return O.make_state_dict(seed=0)
 
 
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    sd = synthetic_state_dict()
+    sd = oracle_state_dict()
+    assert "ddim_audio_b200" not in sys.modules, "the reference arm must not load the product package"
     for _ in range(min(args.warmup, 1)):
         cpu_steps(sd, min(args.t_size, 1024), 1)
     per = []
     for _ in range(args.steps):
-        dt, cores = cpu_steps(sd, args.t_size, 1, warm=False)
+        dt, cores, _ = cpu_steps(sd, args.t_size, 1, warm=False)
         per.append(dt)
     total = sum(per)
     value = args.steps / total
@@ -347,13 +378,48 @@ def run_b200(args):
         e2e = {"value": world * B * K / dt, "unit": UNIT, "h2d_bytes_per_step": nbytes + 8 * B, "d2h_bytes_per_step": 2 * nbytes, "ms_per_step": 1e3 * dt / K,
                "api": "generalized_steps(x_pinned_host, [t], model, alphas, None, eta=0) once per step (4 sample groups pipelined over PCIe)"}
 
-    # ---------------- CPU baseline (oracle; rank 0 at N=1 only)
-    cpu = None
+    # ---------------- batch-position independence at the headline shape: samples 0 and B-1 of the full batch vs the same samples
+    # run alone (the only check that exercises element offsets past 2^32; samples never interact)
+    batch_pos = None
+    if not args.no_parity and B >= 2:
+        rel = lambda a, b: float((a.double() - b.double()).norm() / b.double().norm().clamp_min(1e-30))
+        with torch.no_grad():
+            xd = x_host.to(dev)
+            tt = torch.full((B,), 999, dtype=torch.int64, device=dev)
+            full = model(xd, tt)
+            first, last = full[:1].clone(), full[B - 1:].clone()
+            del full
+            alone0 = model(xd[:1].contiguous(), tt[:1])
+            alone1 = model(xd[B - 1:].contiguous(), tt[:1])
+            r0, r1 = rel(first, alone0), rel(last, alone1)
+            del xd, first, last, alone0, alone1
+        batch_pos = {"shape": f"x[{B},2,{T},{F_SIZE}]", "samples": [0, B - 1], "eps_rel_l2_vs_batch_of_1": [r0, r1], "tolerance": 2e-2,
+                     "pass": bool(max(r0, r1) <= 2e-2),
+                     "note": "a different batch size changes the fp32 summation order of the GroupNorm statistics; bf16 storage amplifies that "
+                             "to the path's own rounding noise, so the bound is the model tolerance"}
+
+    # ---------------- CPU baseline (oracle; rank 0 at N=1 only) + parity of the CUDA path against that very run
+    cpu, parity = None, None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         n = args.cpu_sample_steps
-        dt, cores = cpu_steps(sd, T, n)
+        dt, cores, rec = cpu_steps(sd, T, n, record=not args.no_parity)
         cpu = {"value": n / dt, "unit": UNIT, "cores": cores, "kind": "port",
                "sample": f"x[1,2,{T},{F_SIZE}] (1 of the {B} samples), {n} DDIM steps, fp32 torch CPU ops, {dt:.1f} s"}
+        if rec is not None:
+            parity = parity_vs_record(rec, model, al, dev)
+
+    # ---------------- small batches (launch-bound regime): BASELINE configs[0] geometry and the reference's own default (audio.yml:76-77)
+    small = None
+    if rank == 0 and not args.no_small_batch:
+        small = small_batch_leg(model, al, dev)
+
+    # ---------------- training (BASELINE metric "train samples/sec", configs[1]/[4]): bounded leg, every rank, NCCL all-reduce when N > 1
+    train = None
+    if not args.no_train:
+        del x_host
+        torch.cuda.empty_cache()
+        train = train_leg(sd, dev, world, rank, local, args.train_batch, args.train_t_size, args.train_steps, max(args.train_warmup, 3),
+                          prof_kernels=True, tail=False, cpu=False)
 
     if rank == 0:
         line = {
@@ -365,49 +431,95 @@ def run_b200(args):
                        "snapshots": "none inside the device-timed steps (config 3 selects 10 of 1000 steps); every step in e2e"},
             "clocks": clk, "e2e": e2e, "gpu_launches": int(launches), "roofline": roof, "cpu_baseline": cpu,
             "step_roofline": {"t_roof_ms_per_step": t_roof / K, "frac": (t_roof / K) / (ms / K), "note": "sum over kernels of max(bytes/HBM peak, flops/tensor peak) / measured step"},
-            "kernels": kern, "finite": finite,
+            "kernels": kern, "finite": finite, "parity": parity, "batch_position": batch_pos, "small_batch": small, "train": train,
         }
         emit(line)
     if world > 1:
         dist.destroy_process_group()
 
 
+def parity_vs_record(rec, model, al, dev):
+    """The CUDA path against the oracle run that ``cpu_baseline`` just timed (same weights, same sample x[1,2,T,256], same steps):
+    per-step eps teacher-forced on the oracle's own xt, and the free-running public-API trajectory against the oracle's snapshots.
+    Tolerance: DESIGN.md section 2 (bf16 activation storage, fp32 accumulate)."""
+    import torch
+    from ddim_audio_b200.functions.denoising import generalized_steps
+    rel = lambda a, b: float((a.double() - b.double()).norm() / b.double().norm().clamp_min(1e-30))
+    eps_rel, eps_abs = [], []
+    with torch.no_grad():
+        for xt, t, et in rec["calls"]:
+            got = model(xt.to(dev), t.to(dev)).float().cpu()
+            eps_rel.append(rel(got, et))
+            eps_abs.append(float((got - et).abs().max() / et.std().clamp_min(1e-30)))
+        xs, x0 = generalized_steps(rec["x"].to(dev), rec["seq"], model, al.to(dev), None, eta=0.0)
+    final = rel(xs[-1].cpu(), rec["xs"][-1])
+    x0_rel = [rel(a.cpu(), b) for a, b in zip(x0, rec["x0"])]
+    ok = max(eps_rel) <= 2e-2 and max(eps_abs) <= 0.114 and final <= 5e-2
+    return {"shape": f"x{list(rec['x'].shape)}", "steps": len(rec["seq"]), "seq": [int(v) for v in rec["seq"]], "reference": "CPU oracle (the cpu_baseline run itself)",
+            "per_step_eps_rel_l2": eps_rel, "max_abs_over_std": eps_abs, "x0_pred_rel_l2": x0_rel, "final_rel_l2": final,
+            "tolerance": 2e-2, "tolerance_max_abs_over_std": 0.114, "tolerance_final_rel_l2": 5e-2, "pass": bool(ok)}
+
+
+def small_batch_leg(model, al, dev, steps=10, warm=3):
+    """Launch-bound shapes through the public API on a device-resident x (no snapshots: select_index = empty set): BASELINE
+    configs[0] geometry x[4,2,1024,256] and the reference's own default x[2,2,8192,256] (audio.yml:76-77)."""
+    import torch
+    from ddim_audio_b200.functions.denoising import generalized_steps
+    out = {}
+    ald = al.to(dev)
+    for name, (b, t) in {"b4_t1024": (4, 1024), "b2_t8192": (2, 8192)}.items():
+        x = torch.randn(b, 2, t, F_SIZE, generator=torch.Generator().manual_seed(7)).to(dev)
+        seq_w, seq_k = list(range(1000))[-warm:], list(range(1000))[-(warm + steps):-warm]
+        with torch.no_grad():
+            generalized_steps(x, seq_w, model, ald, set(), eta=0.0)
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            t0 = time.perf_counter()
+            e0.record()
+            generalized_steps(x, seq_k, model, ald, set(), eta=0.0)
+            e1.record()
+            torch.cuda.synchronize()
+            wall = time.perf_counter() - t0
+        out[name] = {"shape": f"x[{b},2,{t},{F_SIZE}]", "steps": steps, "sample_steps_per_s": b * steps / wall, "ms_per_step_wall": 1e3 * wall / steps,
+                     "ms_per_step_device": e0.elapsed_time(e1) / steps}
+    out["api"] = "generalized_steps(x_cuda, seq, model, alphas, set(), eta=0), wall clock with synchronize on both sides"
+    return out
+
+
 # ------------------------------------------------------------------------------------------------ training arm (--mode train)
-def run_train(args):
-    """BASELINE configs[1] / [4]: audio.yml noise_estimation_loss forward + backward (+ NCCL gradient all-reduce when N > 1),
-    per-GPU batch ``--batch`` (default 32) at T = ``--t-size`` (default 1024), dropout 0.1 active.  A step = one loss +
-    backward over one batch; value = samples/s.  The optimizer step is not part of the metric."""
+def train_leg(sd, dev, world, rank, local, B, T, K, W, prof_kernels=True, tail=False, cpu=False, e2e=True):
+    """BASELINE configs[1] / [4]: K full train steps of audio.yml at x[B,2,T,256] per GPU, dropout 0.1 active -- per step:
+    zero_grad, noise_estimation_loss forward + backward (functions/losses.py:4-18), NCCL all-reduce of the flat gradient buffer
+    when N > 1, clip_grad_norm_ per group, AdaBelief + AdamW, LambdaLR, EMA (runners/diffusion.py:130-183), and the re-pack of the
+    bf16 GEMM operands the changed weights force on the next forward.  Returns the ``train`` object of the JSON line
+    (``samples_per_s`` = whole-job samples / max-over-ranks device time of the FULL step; ``fwd_bwd`` is the SURVEY.md section 8d
+    metric: loss + backward + all-reduce only)."""
+    import argparse
+
     import torch
     import torch.distributed as dist
-
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py: no CUDA device -- the B200 arm has no CPU fallback")
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
     from ddim_audio_b200 import _C
     from ddim_audio_b200.config import audio_config
+    from ddim_audio_b200.functions import optim as fused
     from ddim_audio_b200.functions.losses import noise_estimation_loss
     from ddim_audio_b200.models.diffusion import Model
+    from ddim_audio_b200.models.ema import EMAHelper
     from ddim_audio_b200.runners import dist as rdist
-    from ddim_audio_b200.runners.diffusion import antithetic_timesteps
+    from ddim_audio_b200.runners.diffusion import Diffusion, antithetic_timesteps
 
-    sd = synthetic_state_dict()
-    model = Model(audio_config("torch.FloatTensor")).to(dev)
+    cfg = audio_config("torch.FloatTensor")
+    model = Model(cfg).to(dev)
     model.load_state_dict(sd, strict=True)
     model.train()
+    runner = Diffusion(argparse.Namespace(log_path=None), cfg, device=dev)
+    optimizers, schedulers, grad_group = runner.build_training(model)
+    ema = EMAHelper(mu=cfg.model.ema_rate)
+    ema.register(model)
     al = alphas_cumprod().to(dev)
-    B = args.batch
-    T = args.t_size
-    K, W = args.steps, max(args.warmup, 0)
     g = torch.Generator().manual_seed(4321 + rank)
     x_host = torch.randn(B, 2, T, F_SIZE, generator=g).pin_memory()
     e_host = torch.randn(B, 2, T, F_SIZE, generator=g).pin_memory()
-    t_host = antithetic_timesteps(B, 1000, g)
+    t_host = antithetic_timesteps(B, 1000, g).pin_memory()
     params = list(model.parameters())
 
     def barrier():
@@ -422,11 +534,28 @@ def run_train(args):
             return float(tns.item())
         return v
 
-    def step(x0, e, t):
-        model.zero_grad(set_to_none=True)
+    def step(x0, e, t, ev=None):
+        if ev:
+            ev[0].record()
+        for o in optimizers.values():
+            o.zero_grad(set_to_none=True)
         loss = noise_estimation_loss(model, x0, t, e, al)
         (loss / world if world > 1 else loss).backward()
+        if ev:
+            ev[1].record()
         rdist.allreduce_gradients(params, model.flat_grad)
+        if ev:
+            ev[2].record()
+        for gg in grad_group.values():
+            if gg.config.grad_clip is not None:
+                fused.clip_grad_norm_(gg.params, gg.config.grad_clip)
+        for o in optimizers.values():
+            o.step()
+        for sc in schedulers.values():
+            sc.step()
+        ema.update(model)
+        if ev:
+            ev[3].record()
         return loss
 
     x0, e, t = x_host.to(dev), e_host.to(dev), t_host.to(dev)
@@ -435,27 +564,45 @@ def run_train(args):
     clocks = ClockSampler(local)
     barrier()
     clocks.start()
-    _C.prof_enable(True)
-    _C.prof_report()
+    if prof_kernels:
+        _C.prof_enable(True)
+        _C.prof_report()
     l0 = _C.launch_count()
+    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(4)] for _ in range(K)]
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    for _ in range(K):
-        loss = step(x0, e, t)
+    for k in range(K):
+        loss = step(x0, e, t, evs[k])
     e1.record()
     barrier()
     launches = _C.launch_count() - l0
     ms = max_over_ranks(e0.elapsed_time(e1))
-    prof = _C.prof_report()
-    _C.prof_enable(False)
+    prof = _C.prof_report() if prof_kernels else []
+    if prof_kernels:
+        _C.prof_enable(False)
     clk = clocks.stop()
-    value = world * B * K / (ms * 1e-3)
-    finite = bool(torch.isfinite(loss).item()) and all(bool(torch.isfinite(p.grad).all().item()) for p in params[:8])
-    roof, kern, t_roof = roofline_from_profile(prof, K)
+    fb_ms = max_over_ranks(sum(v[0].elapsed_time(v[2]) for v in evs) / K)
+    ar_ms = max_over_ranks(sum(v[1].elapsed_time(v[2]) for v in evs) / K)
+    tail_ms = max_over_ranks(sum(v[2].elapsed_time(v[3]) for v in evs) / K)
+    finite = bool(torch.isfinite(loss).item()) and all(bool(torch.isfinite(p).all().item()) for p in params[:8])
+    roof, kern, t_roof = roofline_from_profile(prof, K) if prof else (None, [], 0.0)
+    n_el = sum(p.numel() for p in params)
 
-    # e2e: pinned host batch in, loss scalar out, every step
-    e2e = None
-    if not args.no_e2e:
+    out = {"metric": "train_samples_per_sec", "samples_per_s": world * B * K / (ms * 1e-3), "unit": "samples/s", "ms_per_step": ms / K,
+           "steps": K, "warmup": W, "n_gpus": world, "batch_per_gpu": B, "t_size": T,
+           "workload": f"audio.yml train step, x[{B},2,{T},{F_SIZE}] per GPU, dropout 0.1: loss + backward" + (" + NCCL all-reduce" if world > 1 else "") +
+                       " + clip + AdaBelief/AdamW + EMA + operand re-pack (BASELINE configs[1]/[4] shape)",
+           "fwd_bwd": {"samples_per_s": world * B / (fb_ms * 1e-3), "ms_per_step": fb_ms, "note": "zero_grad + loss + backward + all-reduce only (SURVEY.md section 8d train metric)"},
+           "allreduce_ms": ar_ms, "allreduce_bytes": int(model.flat_grad.numel() * 4) if world > 1 else 0,
+           "optimizer_tail": {"ms": tail_ms, "elements": n_el, "GBps": (12.0 + 28.0 + 12.0) * n_el / max(tail_ms, 1e-9) / 1e6,
+                              "what": "clip x groups + AdaBelief + AdamW + LambdaLR + EMA, device time between events"},
+           "gpu_launches": int(launches), "roofline": roof,
+           "step_roofline": {"t_roof_ms_per_step": t_roof / K, "frac": (t_roof / K) / (ms / K)} if prof else None,
+           "kernels": kern[:12], "clocks": clk, "finite": finite, "last_loss": float(loss.item()), "dtype": "bf16",
+           "timing": "CUDA events around K full steps, barrier + synchronize both sides, max over ranks"}
+
+    # e2e: pinned host batch in, loss scalar out, every step (the runner's own train_step does exactly this)
+    if e2e:
         barrier()
         t0 = time.perf_counter()
         for _ in range(K):
@@ -463,20 +610,15 @@ def run_train(args):
             lv = float(l.item())
         barrier()
         dt = max_over_ranks(time.perf_counter() - t0)
-        e2e = {"value": world * B * K / dt, "unit": "samples/s", "h2d_bytes_per_step": 2 * x_host.numel() * 4 + 8 * B, "d2h_bytes_per_step": 4,
-               "ms_per_step": 1e3 * dt / K, "api": "noise_estimation_loss(model, x0, t, e, alphas).backward() on a pinned host batch + loss.item()", "last_loss": lv}
+        out["e2e"] = {"value": world * B * K / dt, "unit": "samples/s", "h2d_bytes_per_step": 2 * x_host.numel() * 4 + 8 * B, "d2h_bytes_per_step": 4,
+                      "ms_per_step": 1e3 * dt / K, "api": "full train step on a pinned host batch + loss.item()", "last_loss": lv}
 
-    # optimizer tail of train_step (runners/diffusion.py:155-183): per-group clip, AdaBelief (default group) + AdamW (transformer
-    # group), EMA -- fused library launches, next to the same arithmetic as stock torch objects (torch AdamW for both groups:
-    # the reference's AdaBelief is a Python loop of ~12 ops per tensor and does not travel to this box)
-    tail = None
-    if rank == 0 and world == 1:
-        from ddim_audio_b200.functions import optim as fused
-        from ddim_audio_b200.models.ema import EMAHelper
+    # fused tail next to the same arithmetic as stock torch objects (torch AdamW for both groups: the reference's AdaBelief is a
+    # Python loop of ~12 ops per tensor and does not travel to this box)
+    if tail and rank == 0 and world == 1:
         tr = [p for n, p in model.named_parameters() if n.startswith("transformer.") and p.grad is not None]
         de = [p for n, p in model.named_parameters() if not n.startswith("transformer.") and p.grad is not None]
         saved = [p.data.clone() for p in params]
-        gsaved = [p.grad.clone() for p in tr + de]
 
         def wall_ms(fn, reps=5):
             fn()
@@ -487,23 +629,6 @@ def run_train(args):
             torch.cuda.synchronize()
             return 1e3 * (time.perf_counter() - t0) / reps
 
-        f_opt = [fused.AdamW(tr, lr=5e-4, betas=(0.9, 0.998), eps=1e-6, weight_decay=1e-4),
-                 fused.AdaBelief(de, lr=3e-4, betas=(0.9, 0.999), eps=1e-8, weight_decay=1e-5)]
-        f_ema = EMAHelper(mu=0.9999)
-        f_ema.register(model)
-
-        def fused_tail():
-            fused.clip_grad_norm_(tr, 1.0)
-            fused.clip_grad_norm_(de, 1.0)
-            for o in f_opt:
-                o.step()
-            f_ema.update(model)
-
-        l0 = _C.launch_count()
-        fused_ms = wall_ms(fused_tail)
-        fused_launches = (_C.launch_count() - l0) // 6
-        for p, g_ in zip(tr + de, gsaved):
-            p.grad.copy_(g_)
         t_opt = [torch.optim.AdamW(tr, lr=5e-4, betas=(0.9, 0.998), eps=1e-6, weight_decay=1e-4),
                  torch.optim.AdamW(de, lr=3e-4, betas=(0.9, 0.999), eps=1e-8, weight_decay=1e-5)]
         shadow = {n: p.data.clone() for n, p in model.named_parameters()}
@@ -516,18 +641,14 @@ def run_train(args):
             for n, p in model.named_parameters():                                   # models/ema.py:16-23 as written
                 shadow[n].data = (1.0 - 0.9999) * p.data + 0.9999 * shadow[n].data
 
-        torch_ms = wall_ms(torch_tail)
+        out["optimizer_tail"]["torch_ms"] = wall_ms(torch_tail)
+        out["optimizer_tail"]["torch_note"] = "clip_grad_norm_ + torch.optim.AdamW (foreach) for both groups + the reference's per-tensor EMA loop, wall clock"
         with torch.no_grad():
             for p, v in zip(params, saved):
                 p.data.copy_(v)
-        n_el = sum(p.numel() for p in tr + de)
-        tail = {"fused_ms": fused_ms, "fused_launches": int(fused_launches), "torch_ms": torch_ms,
-                "fused_GBps": (12.0 + 28.0 + 12.0) * n_el / fused_ms / 1e6, "tensors": len(tr) + len(de), "elements": n_el,
-                "timing": "wall clock incl. host launch cost, synchronize both sides, 5 repetitions",
-                "note": "torch leg = clip_grad_norm_ + torch.optim.AdamW (foreach) for both groups + the reference's per-tensor EMA loop"}
+        model.mark_params_dirty()
 
-    cpu = None
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+    if cpu and rank == 0 and world == 1:
         from oracle import ddim_oracle as O
         cores = os.cpu_count() or 1
         torch.set_num_threads(cores)
@@ -536,20 +657,42 @@ def run_train(args):
         t0 = time.perf_counter()
         O.loss_and_grads(sd, xs, ts, es, alphas_cumprod())
         dt = time.perf_counter() - t0
-        cpu = {"value": 1.0 / dt, "unit": "samples/s", "cores": cores, "kind": "port",
-               "sample": f"1 of the {B} samples, x[1,2,{T},{F_SIZE}], one loss + backward (torch CPU autograd over the oracle), {dt:.1f} s"}
+        out["cpu_baseline"] = {"value": 1.0 / dt, "unit": "samples/s", "cores": cores, "kind": "port",
+                               "sample": f"1 of the {B} samples, x[1,2,{T},{F_SIZE}], one loss + backward (torch CPU autograd over the oracle), {dt:.1f} s"}
+    del model, optimizers, ema, x0, e, t
+    torch.cuda.empty_cache()
+    return out
 
+
+def run_train(args):
+    """``--mode train``: the train leg alone as the JSON line (value = full-step samples/s)."""
+    import torch
+    import torch.distributed as dist
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the B200 arm has no CPU fallback")
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+        dist.init_process_group("nccl", device_id=dev)
+    sd = synthetic_state_dict()
+    tr = train_leg(sd, dev, world, rank, local, args.batch, args.t_size, args.steps, max(args.warmup, 0), prof_kernels=True, tail=True,
+                   cpu=not args.no_cpu_baseline, e2e=not args.no_e2e)
     if rank == 0:
+        B, T = args.batch, args.t_size
         line = {
-            "metric": "train_samples_per_sec", "value": value, "unit": "samples/s", "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms / K,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-            "config": {"workload": f"audio.yml noise_estimation_loss fwd+bwd, x[{B},2,{T},{F_SIZE}] per GPU, dropout 0.1 (BASELINE configs[1]/[4] shape)",
-                       "batch_per_gpu": B, "t_size": T, "f_size": F_SIZE, "storage": "bf16 NHWC activations and activation gradients, fp32 accumulate, fp32 weight gradients",
+            "metric": "train_samples_per_sec", "value": tr["samples_per_s"], "unit": "samples/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": tr["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": tr["workload"], "batch_per_gpu": B, "t_size": T, "f_size": F_SIZE,
+                       "storage": "bf16 NHWC activations and activation gradients, fp32 accumulate, fp32 weight gradients",
                        "parallelism": f"data-parallel x{world}" + (", one NCCL all-reduce of the flat fp32 gradient buffer per step" if world > 1 else ""),
                        "l2": "inputs larger than L2 (level-0 activations are 537 MB each)" if B * T >= 16384 else "small debug shape"},
-            "clocks": clk, "e2e": e2e, "gpu_launches": int(launches), "roofline": roof, "cpu_baseline": cpu,
-            "step_roofline": {"t_roof_ms_per_step": t_roof / K, "frac": (t_roof / K) / (ms / K)}, "kernels": kern, "finite": finite,
-            "optimizer_tail": tail,
+            "clocks": tr["clocks"], "e2e": tr.get("e2e"), "gpu_launches": tr["gpu_launches"], "roofline": tr["roofline"], "cpu_baseline": tr.get("cpu_baseline"),
+            "step_roofline": tr["step_roofline"], "kernels": tr["kernels"], "finite": tr["finite"], "train": tr,
         }
         emit(line)
     if world > 1:

@@ -87,6 +87,15 @@ for _name, _args in SIGNATURES.items():
     _fn.restype = _i
 
 
+# Generation of "some parameter tensor was rewritten through a raw device pointer" (fused optimizer step, EMA copy-in):
+# such writes bump neither ``Tensor._version`` nor ``data_ptr()``, so Model keys its packed bf16 operand copies on this.
+param_epoch = [0]
+
+
+def bump_param_epoch() -> None:
+    param_epoch[0] += 1
+
+
 def _stream() -> int:
     return torch.cuda.current_stream().cuda_stream
 

@@ -128,6 +128,7 @@ class _Fused(Optimizer):
                 [[p.data for p in ps], grads, [st["exp_avg"] for st in states], [st[self.SECOND] for st in states]], ps[0].device, check)
             _C.call("ddimb_optim_step", _C.ptr(table), table.shape[0], total, self.KIND, float(group["lr"]), float(beta1), float(beta2),
                     float(group["eps"]), float(group["weight_decay"]), step)
+        _C.bump_param_epoch()       # the masters changed behind torch's version counters: Model re-packs its bf16 operands
         return self._result(loss)
 
 

@@ -15,7 +15,7 @@ from typing import List
 import torch
 import torch.nn as nn
 
-from .. import ops
+from .. import _C, ops
 
 GN_GROUPS = 8        # models/diffusion.py:19
 GN_EPS = 1e-6        # models/diffusion.py:20
@@ -185,6 +185,7 @@ class Model(nn.Module):
             self._apply_type_string(cfg.dtype)
         self._packed = None
         self._packed_key = None
+        self._gen = getattr(self, "_gen", 0) + 1
         self._consts = {}
         self.flat_grad = None       # flat fp32 buffer the last backward wrote every parameter gradient into
 
@@ -195,8 +196,31 @@ class Model(nn.Module):
         self.type(s)            # 'torch.cuda.FloatTensor' also moves the module to the GPU, as in the reference
 
     # ------------------------------------------------------------------ kernel-ready weights
-    def _pack_key(self):
-        return tuple((p.data_ptr(), p._version) for p in self.parameters())
+    def mark_params_dirty(self):
+        """Call after writing parameters in a way torch cannot see (``p.data.copy_``, raw-pointer kernels): the packed bf16
+        operand copies are rebuilt on the next forward.  ``load_state_dict``, ``train()`` / ``eval()``, ``.to()`` / ``.type()``,
+        the fused optimizers' ``step()`` and ``EMAHelper.ema()`` do this themselves."""
+        self._gen = getattr(self, "_gen", 0) + 1
+
+    def load_state_dict(self, *args, **kwargs):
+        self.mark_params_dirty()
+        return super().load_state_dict(*args, **kwargs)
+
+    def train(self, mode=True):
+        # the reference's sample() is load_state_dict -> ema_helper.ema(model) -> model.eval() (runners/diffusion.py:303-315):
+        # a mode switch is where a foreign ``param.data.copy_`` (its own EMAHelper) becomes visible at the latest
+        self.mark_params_dirty()
+        return super().train(mode)
+
+    def _apply(self, fn, *args, **kwargs):
+        self.mark_params_dirty()
+        return super()._apply(fn, *args, **kwargs)
+
+    def _pack_key(self, train):
+        """Sampling: two counters (no walk over the 389 parameters per forward).  Training adds the (pointer, version) walk so a
+        stock torch optimizer's in-place update is seen too (100 us next to an 85 ms step)."""
+        base = (_C.param_epoch[0], self._gen)
+        return (base, tuple((p.data_ptr(), p._version) for p in self.parameters()) if train else None)
 
     @torch.no_grad()
     def _pack(self, train=False):
@@ -266,9 +290,11 @@ class Model(nn.Module):
         return pk
 
     def _packed_for(self, train):
-        key = self._pack_key()
-        if self._packed is None or key != self._packed_key or (train and not self._packed["train"]):
-            self._packed, self._packed_key = self._pack(train), key
+        base, walk = self._pack_key(train)
+        pk = self._packed
+        fresh = pk is not None and self._packed_key[0] == base and (not train or (pk["train"] and self._packed_key[1] == walk))
+        if not fresh:
+            self._packed, self._packed_key = self._pack(train), (base, walk)
         return self._packed
 
     def _const(self, key, build):

@@ -65,6 +65,10 @@ class EMAHelper(object):
         for name, param in _unwrap(module).named_parameters():
             if param.requires_grad:
                 param.data.copy_(self.shadow[name].data)
+        _C.bump_param_epoch()       # ``.data.copy_`` leaves ``_version`` alone: tell Model its packed operands are stale
+        mark = getattr(_unwrap(module), "mark_params_dirty", None)
+        if mark is not None:
+            mark()
 
     def ema_copy(self, module):
         """:32-46."""

@@ -231,11 +231,13 @@ class Diffusion(object):
             rdist.allreduce_gradients(list(model.parameters()), getattr(model, "flat_grad", None))
         return loss
 
-    def train_step(self, model, x, optimizers, schedulers, grad_group, ema_helper, step, epoch):
+    def train_step(self, model, x, optimizers, schedulers, grad_group, ema_helper, step, epoch, t=None, e=None):
+        """:130-199.  ``t`` / ``e`` (extension, default None = drawn as the reference draws them, :137-142) inject the timesteps
+        and the noise for reproducible runs."""
         model.train()
         for opt in optimizers.values():
             opt.zero_grad(set_to_none=True)
-        loss = self.loss_and_backward(model, x)
+        loss = self.loss_and_backward(model, x, t=t, e=e)
         loggings = {"step": step, "loss": float(loss.item())}
         for g in grad_group.values():
             if g.config.grad_clip is not None:

@@ -120,3 +120,61 @@ def test_generalized_steps_host_input_is_pipelined_by_sample_groups(model, B, ch
     for a, b in zip(xs_h[1:] + x0_h, xs_d[1:] + x0_d):
         assert a.shape == b.shape == x.shape and not a.is_cuda
         assert rel_l2(a, b) < 1e-3    # identical arithmetic per sample; only the fp64 statistics atomics may reorder
+
+
+PROBE_T, PROBE_F = 61, 7      # oracle/make_golden_fullshape.py
+
+
+def test_forward_t8192_vs_reference_golden_and_oracle(model, oracle_sd, golden_dir):
+    """The sampling geometry x[1,2,8192,256] (audio.yml:77): strided probe + norm of the UNMODIFIED reference's output
+    (tests/golden/model_b1_t8192.npz), and the full tensor against the oracle run on this box's CPU."""
+    g = _load(golden_dir, "model_b1_t8192")
+    b, T, seed = (int(v) for v in g["meta"])
+    x, _, t = O.synthetic_inputs(b, T, seed)
+    assert np.array_equal(t.numpy(), g["t"])
+    out = model(x.to(DEV), t.to(DEV)).cpu()
+    ref_p = torch.from_numpy(g["probe"])
+    norm, _, _, std = (float(v) for v in g["summary"])
+    got_p = out[..., ::PROBE_T, ::PROBE_F]
+    r, m = rel_l2(got_p, ref_p), float((got_p - ref_p).abs().max())
+    print(f"t8192 probe: rel-l2 {r:.3e} max-abs {m:.3e} (ref std {std:.3f}); norm {float(out.double().norm()):.4f} vs {norm:.4f}")
+    assert r <= EPS_REL and m <= EPS_ABS_PER_STD * std
+    assert abs(float(out.double().norm()) - norm) <= EPS_REL * norm
+    ref = O.OracleModel(oracle_sd)(x, t)
+    r, m = rel_l2(out, ref), float((out - ref).abs().max())
+    print(f"t8192 full tensor vs oracle: rel-l2 {r:.3e} max-abs {m:.3e}")
+    assert r <= EPS_REL and m <= EPS_ABS_PER_STD * float(ref.std())
+
+
+def test_generalized_steps_configs0_geometry(model, oracle_sd, golden_dir):
+    """BASELINE configs[0] geometry x[4,2,1024,256], last 3 steps of range(0,1000,20), eta 0: every snapshot against the
+    reference-minted probes, and the per-step eps teacher-forced on the oracle's own trajectory (run on this box's CPU):
+    rel-L2 <= 2e-2, max-abs <= 0.114 std."""
+    from ddim_audio_b200.functions.denoising import generalized_steps
+    g = _load(golden_dir, "ddim_b4_t1024_s3")
+    b, T, seed, nsteps = (int(v) for v in g["meta"])
+    seq = [int(v) for v in g["seq"]]
+    assert seq == list(range(0, 1000, 20))[-nsteps:]
+    x, _, _ = O.synthetic_inputs(b, T, seed)
+    al = O.alphas_cumprod()
+    xs, x0 = generalized_steps(x.to(DEV), seq, model, al.to(DEV), None, eta=0.0)
+    assert len(xs) == nsteps + 1 and len(x0) == nsteps
+    worst = 0.0
+    for got, want, summ in zip(xs[1:] + x0, list(g["xs_probe"]) + list(g["x0_probe"]), list(g["xs_summary"]) + list(g["x0_summary"])):
+        worst = max(worst, rel_l2(got[..., ::PROBE_T, ::PROBE_F], torch.from_numpy(want)))
+        assert abs(float(got.double().norm()) - float(summ[0])) <= 5e-2 * float(summ[0])
+    print(f"configs[0] geometry: worst snapshot probe rel-l2 {worst:.3e}")
+    assert worst <= 5e-2
+    # teacher-forced per-step eps
+    omodel = O.OracleModel(oracle_sd)
+    xt = x.clone()
+    t = torch.zeros(b, dtype=torch.long)
+    for c in O.ddim_coefficients(al, seq, 0.0):
+        t[...] = c["i"]
+        et = omodel(xt, t)
+        et_g = model(xt.to(DEV), t.to(DEV)).cpu()
+        r, m = rel_l2(et_g, et), float((et_g - et).abs().max() / et.std())
+        print(f"  step t={c['i']}: eps rel-l2 {r:.3e} max-abs/std {m:.3e}")
+        assert r <= EPS_REL and m <= EPS_ABS_PER_STD
+        xt.add_(et, alpha=-((1 - c["at"]) ** 0.5)).div_(c["at"] ** 0.5)
+        xt.mul_(c["at_next"] ** 0.5).add_(et, alpha=c["c2"])

@@ -150,3 +150,23 @@ def test_optimizer_tail(golden_dir, name):
         np.testing.assert_allclose(O.optim_probe(params[k]).numpy(), g[f"{name}__p__{kk}"], rtol=0, atol=1e-7)
         np.testing.assert_allclose(O.optim_probe(m[k]).numpy(), g[f"{name}__m__{kk}"], rtol=1e-5, atol=1e-9)
         np.testing.assert_allclose(O.optim_probe(v[k]).numpy(), g[f"{name}__v__{kk}"], rtol=1e-5, atol=1e-12)
+
+
+def test_fullshape_goldens_forward_t8192(oracle_sd, golden_dir):
+    """The oracle at the sampling geometry x[1,2,8192,256] against the reference-minted probe (oracle/make_golden_fullshape.py)."""
+    g = _load(golden_dir, "model_b1_t8192")
+    b, T, seed = (int(v) for v in g["meta"])
+    x, _, t = O.synthetic_inputs(b, T, seed)
+    out = O.OracleModel(oracle_sd)(x, t)
+    np.testing.assert_allclose(out[..., ::61, ::7].numpy(), g["probe"], **TOL)
+    assert float(out.double().norm()) == pytest.approx(float(g["summary"][0]), rel=1e-5)
+
+
+def test_fullshape_goldens_ddim_configs0_geometry(oracle_sd, golden_dir):
+    """The oracle's generalized_steps at BASELINE configs[0] geometry x[4,2,1024,256] (last 3 steps of range(0,1000,20))."""
+    g = _load(golden_dir, "ddim_b4_t1024_s3")
+    b, T, seed, nsteps = (int(v) for v in g["meta"])
+    x, _, _ = O.synthetic_inputs(b, T, seed)
+    xs, x0 = O.generalized_steps(x, [int(v) for v in g["seq"]], O.OracleModel(oracle_sd), O.alphas_cumprod(), None, eta=0.0)
+    for got, want in zip(xs[1:] + x0, list(g["xs_probe"]) + list(g["x0_probe"])):
+        np.testing.assert_allclose(got[..., ::61, ::7].numpy(), want, rtol=0, atol=5e-4)
