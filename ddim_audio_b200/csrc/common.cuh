@@ -204,6 +204,24 @@ __device__ __forceinline__ void bulk_load_g2s(uint32_t dst, const void* src, uin
                : "memory");
 }
 
+// ---- TMA stores (shared -> global).  Bulk async-groups are per THREAD: every lane of the warp executes the store wrapper (one
+// elected lane issues), the commit and the wait, so whichever lane was elected also waits; for the others both are no-ops.
+__device__ __forceinline__ void tma_store_4d_e(const void* tmap, uint32_t src, int c0, int c1, int c2, int c3) {
+  asm volatile(
+      "{\n\t.reg .pred q;\n\t"
+      "elect.sync _|q, 0xffffffff;\n\t"
+      "@q cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];\n\t}" ::"l"(tmap),
+      "r"(src), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+      : "memory");
+}
+__device__ __forceinline__ void bulk_commit_group() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+// the shared-memory SOURCE of all but the newest N committed groups has been read (the buffer may be overwritten)
+template <int N>
+__device__ __forceinline__ void bulk_wait_group_read() { asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory"); }
+// all but the newest N committed groups are complete (writes performed)
+template <int N>
+__device__ __forceinline__ void bulk_wait_group() { asm volatile("cp.async.bulk.wait_group %0;" ::"n"(N) : "memory"); }
+
 // ---------------------------------------------------------------- tcgen05 / TMEM
 __device__ __forceinline__ void tmem_alloc(uint32_t dst_smem, uint32_t ncols) {
   asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(ncols) : "memory");

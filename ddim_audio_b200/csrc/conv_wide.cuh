@@ -43,7 +43,6 @@ struct WideParams {
   double* stats;
   int32_t bias_b_stride;
   int32_t act;
-  int32_t dbg;            // experiment switch (DDIMB_WIDE_DBG)
 };
 
 template <int C>
@@ -62,8 +61,9 @@ struct WideCfg {
   static constexpr int kSwizzle = (C == 64) ? 2 : 4;
   static constexpr int kSBO = 8 * kRowBytes;
   static constexpr int kXfTabBytes = ((kWideXfWarps * C * 8 + 1023) / 1024) * 1024;
-  static constexpr bool kStage = (C == 32);           // smem-staged epilogue stores (C = 64 has no room beside an 8-row ring; measured neutral here)
-  static constexpr int kAuxBytes = 1024 + 4096 + kXfTabBytes + (kStage ? kWideEpiWarps * 2048 : 0);   // barriers | epilogue bias copies | transform scale/shift copies | store staging
+  static constexpr bool kStage = (C == 32);           // the legacy (skip-add) epilogue's smem-staged stores need 2 KB per warp: C = 32 only
+  static constexpr int kStageBytes = 32 * C * 2;      // one epilogue warp's output tile (32 positions x C channels): the TMA store's source
+  static constexpr int kAuxBytes = 1024 + 4096 + kXfTabBytes + kWideEpiWarps * kStageBytes;   // barriers | epilogue bias copies | transform scale/shift copies | store staging
   static constexpr int kSmemBytes = 1024 + kWBytes + kSlots * kSlotBytes + kAuxBytes;
 };
 
@@ -177,9 +177,106 @@ __device__ __forceinline__ void wide_transform_warp(const WideParams& p, uint8_t
   }
 }
 
+// Epilogue warp of conv3x3_wide_kernel (no skip operand): TMEM -> registers -> (+bias/temb) -> SiLU -> bf16 -> this warp's
+// [32 positions][C] staging tile in the TMA swizzle image (16-byte chunk j of position r at slot j ^ phase(r): the 8 lanes of a
+// quarter warp hit 8 different bank groups) -> ONE cp.async.bulk.tensor store per tile.  Everything invariant over the tile loop
+// is a template parameter or hoisted; the accumulator buffer is handed back to the MMA warp as soon as it is in registers.
+// (ncu r02: the generic epilogue spent ~600 instructions per 32 x 32 tile, most of them address / predicate bookkeeping, and its
+// eight warps were the busiest of the CTA.)
+template <int C, int ACT, bool STATS>
+__device__ __forceinline__ void wide_epilogue_lean(const WideParams& p, const CUtensorMap* tmO, uint32_t tmem_base, uint32_t bar_afull,
+                                                   uint32_t bar_aempty, float* wb, uint8_t* stage_gen, int warp, int lane) {
+  using Cfg = WideCfg<C>;
+  constexpr int NB = Cfg::kAccBufs;
+  constexpr uint32_t kGrpMask = kWideEpiWarps / 4 - 1;
+  constexpr int CG = C / 8;
+  const int q = warp & 3;
+  const uint32_t grp = (uint32_t)(warp - 2) >> 2;
+  const uint32_t stage = smem_u32(stage_gen);
+  const uint32_t phase = (C == 64) ? (uint32_t)(lane & 7) : (uint32_t)((lane >> 1) & 3);
+  uint8_t* srow = stage_gen + lane * (C * 2);
+  const uint64_t s2x = (ACT == 1) ? pack2(0.5f, 0.5f) : pack2(1.0f, 1.0f);
+  ConvEpiState<C> st;
+  st.reset();
+  st.cur_batch = -1;
+  uint32_t tile = 0;
+  bool pending = false;
+  WideUnit u;
+  for (int unit = blockIdx.x; unit < p.num_units; unit += gridDim.x) {
+    u.set(p, unit);
+    if (u.b != st.cur_batch) {
+      if (STATS) st.flush(p.stats, lane);
+      st.cur_batch = u.b;
+      conv_epilogue_bias<C>(wb, p.bias, p.bias_b, u.b, p.bias_b_stride, ACT, lane);
+    }
+    const int wq = u.w0 + q * 32;
+    for (int ot = (int)((grp - tile) & kGrpMask); ot < u.rows; ot += (int)kGrpMask + 1) {   // this group's output rows only
+      const uint32_t buf = (tile + ot) % NB, use = (tile + ot) / NB;
+      mbar_wait(bar_afull + 8 * buf, use & 1, 15);
+      tc_fence_after();
+      const uint32_t trow = tmem_base + ((uint32_t)(q * 32) << 16) + buf * C;
+      if (pending) {            // the previous tile's store has read the staging tile
+        bulk_wait_group_read<0>();
+        __syncwarp();
+      }
+#pragma unroll
+      for (int c0 = 0; c0 < C; c0 += 32) {
+        uint32_t v[32];
+        tmem_ld32(trow + (uint32_t)c0, v);
+        tmem_ld_wait();
+        if (c0 + 32 == C) {     // accumulators are in registers: the MMA warp may overwrite the buffer
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(bar_aempty + 8 * buf);
+        }
+        uint64_t f[16];
+#pragma unroll
+        for (int j = 0; j < 16; j += 2) {
+          const ulonglong2 b4 = *reinterpret_cast<const ulonglong2*>(wb + c0 + 2 * j);
+          f[j] = ffma2(pack2u(v[2 * j], v[2 * j + 1]), s2x, b4.x);
+          f[j + 1] = ffma2(pack2u(v[2 * j + 2], v[2 * j + 3]), s2x, b4.y);
+        }
+        if (ACT == 1) {
+#pragma unroll
+          for (int j = 0; j < 16; ++j) f[j] = silu2_from_half(f[j]);
+        }
+#pragma unroll
+        for (int qq = 0; qq < 4; ++qq)
+          *reinterpret_cast<uint4*>(srow + ((((uint32_t)(c0 >> 3) + qq) ^ phase) << 4)) =
+              make_uint4(f32x2_to_bf16x2(f[4 * qq]), f32x2_to_bf16x2(f[4 * qq + 1]), f32x2_to_bf16x2(f[4 * qq + 2]), f32x2_to_bf16x2(f[4 * qq + 3]));
+        if (STATS) {
+          if (ACT == 3) {
+            // training: the PRE-activation is stored; the following GroupNorm normalises silu(stored value)
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              const float2 t = unpack2(f[j]);
+              f[j] = pack2(silu_fast(__bfloat162float(__float2bfloat16_rn(t.x))), silu_fast(__bfloat162float(__float2bfloat16_rn(t.y))));
+            }
+          }
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            const int g = (c0 + 2 * j) / CG;   // compile-time after unrolling
+            st.s1[g] = fadd2(st.s1[g], f[j]);
+            st.s2[g] = ffma2(f[j], f[j], st.s2[g]);
+          }
+        }
+      }
+      fence_proxy_async_smem();   // generic-proxy writes of every lane -> visible to the TMA engine
+      __syncwarp();
+      tma_store_4d_e(tmO, stage, 0, wq, u.t0 + ot, u.b);
+      bulk_commit_group();
+      pending = true;
+    }
+    tile += (uint32_t)u.rows;
+  }
+  if (STATS) st.flush(p.stats, lane);
+  bulk_wait_group<0>();
+}
+
 template <int C>
 __global__ void __launch_bounds__(kWideThreads, 1)
-conv3x3_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const __grid_constant__ WideParams p) {
+conv3x3_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmO,
+                    const __grid_constant__ WideParams p) {
   using Cfg = WideCfg<C>;
   constexpr int NS = Cfg::kSlots, NB = Cfg::kAccBufs;
   extern __shared__ uint8_t smem_raw[];
@@ -203,6 +300,7 @@ conv3x3_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
+    tma_prefetch_desc(&tmO);
     for (int s = 0; s < NS; ++s) {
       mbar_init(bar_raw + 8 * s, 1);
       mbar_init(bar_ready + 8 * s, 1);    // the transform warp that owns the row
@@ -239,8 +337,7 @@ conv3x3_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           const uint32_t slot = cnt % NS, use = cnt / NS;
           mbar_wait(bar_empty + 8 * slot, (use & 1) ^ 1, 11);
           mbar_arrive_expect_tx(bar_raw + 8 * slot, (uint32_t)(kWidePos * Cfg::kRowBytes));
-          if (p.dbg & 8) tma_load_4d(a_base + slot * Cfg::kSlotBytes, &tmA, bar_raw + 8 * slot, 0, 127, (int)(blockIdx.x & 63), 0);
-          else tma_load_4d(a_base + slot * Cfg::kSlotBytes, &tmA, bar_raw + 8 * slot, 0, u.w0 - 1, u.t0 - 1 + rr, u.b);
+          tma_load_4d(a_base + slot * Cfg::kSlotBytes, &tmA, bar_raw + 8 * slot, 0, u.w0 - 1, u.t0 - 1 + rr, u.b);
         }
       }
     }
@@ -288,7 +385,7 @@ conv3x3_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           if (v2) mbar_wait(bar_aempty + 8 * b2, (((otile + rr) / NB) & 1) ^ 1, 14);
           tc_fence_after();
           const uint32_t a_lo = ((a_base + slot * Cfg::kSlotBytes) & 0x3FFFFu) >> 4;
-          if (!(p.dbg & 4)) {
+          {
             {
               const uint64_t ad = desc_hi | (uint64_t)a_lo;
               if (has_ai) umma_bf16(ta, ad, desc_hi | (uint64_t)(w_lo + wa), iai, 1u);
@@ -316,38 +413,50 @@ conv3x3_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     }
   } else if (warp < 2 + kWideEpiWarps) {
     // ================================================================ epilogue (TMEM lane quarter = warp % 4; group = output row parity)
-    const int q = warp & 3;
-    const uint32_t grp = (uint32_t)(warp - 2) >> 2;
-    constexpr uint32_t kGrpMask = kWideEpiWarps / 4 - 1;
-    const int row = q * 32 + lane;
     float* wb = bias_smem + (warp - 2) * 128;
-    uint8_t* stage = aux_gen + 1024 + 4096 + Cfg::kXfTabBytes + (warp - 2) * 2048;
-    ConvEpiState<C> st;
-    st.reset();
-    st.cur_batch = -1;
-    uint32_t tile = 0;
-    WideUnit u;
-    for (int unit = blockIdx.x; unit < p.num_units; unit += gridDim.x) {
-      u.set(p, unit);
-      if (u.b != st.cur_batch) {
-        st.flush(p.stats, lane);
-        st.cur_batch = u.b;
-        conv_epilogue_bias<C>(wb, p.bias, p.bias_b, u.b, p.bias_b_stride, p.act, lane);
+    uint8_t* stage = aux_gen + 1024 + 4096 + Cfg::kXfTabBytes + (warp - 2) * Cfg::kStageBytes;
+    if (p.add == nullptr) {
+      const bool want = p.stats != nullptr;
+#define DDIMB_WIDE_EPI_CASE(A)                                                                                        \
+  if (p.act == A) {                                                                                                   \
+    if (want) wide_epilogue_lean<C, A, true>(p, &tmO, tmem_base, bar_afull, bar_aempty, wb, stage, warp, lane);       \
+    else wide_epilogue_lean<C, A, false>(p, &tmO, tmem_base, bar_afull, bar_aempty, wb, stage, warp, lane);           \
+  }
+      DDIMB_WIDE_EPI_CASE(0) DDIMB_WIDE_EPI_CASE(1) DDIMB_WIDE_EPI_CASE(3)
+#undef DDIMB_WIDE_EPI_CASE
+    } else {
+      // ---- legacy path: skip operand added after the activation (generic tile epilogue, direct / smem-staged stores)
+      const int q = warp & 3;
+      const uint32_t grp = (uint32_t)(warp - 2) >> 2;
+      constexpr uint32_t kGrpMask = kWideEpiWarps / 4 - 1;
+      const int row = q * 32 + lane;
+      ConvEpiState<C> st;
+      st.reset();
+      st.cur_batch = -1;
+      uint32_t tile = 0;
+      WideUnit u;
+      for (int unit = blockIdx.x; unit < p.num_units; unit += gridDim.x) {
+        u.set(p, unit);
+        if (u.b != st.cur_batch) {
+          st.flush(p.stats, lane);
+          st.cur_batch = u.b;
+          conv_epilogue_bias<C>(wb, p.bias, p.bias_b, u.b, p.bias_b_stride, p.act, lane);
+        }
+        for (int ot = (int)((grp - tile) & kGrpMask); ot < u.rows; ot += (int)kGrpMask + 1) {   // this group's output rows only
+          const uint32_t buf = (tile + ot) % NB, use = (tile + ot) / NB;
+          const int64_t addr0 = ((((int64_t)u.b * p.T + (u.t0 + ot)) * p.W) + u.w0 + row) * C;
+          mbar_wait(bar_afull + 8 * buf, use & 1, 15);
+          tc_fence_after();
+          const uint32_t trow = tmem_base + ((uint32_t)(q * 32) << 16) + buf * C;
+          conv_epilogue_tile<C, C>(trow, wb, p.act, p.add, p.out, addr0, true, p.stats != nullptr, st, Cfg::kStage ? stage : nullptr);
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(bar_aempty + 8 * buf);
+        }
+        tile += (uint32_t)u.rows;
       }
-      for (int ot = (int)((grp - tile) & kGrpMask); ot < u.rows; ot += (int)kGrpMask + 1) {   // this group's output rows only
-        const uint32_t buf = (tile + ot) % NB, use = (tile + ot) / NB;
-        const int64_t addr0 = ((((int64_t)u.b * p.T + (u.t0 + ot)) * p.W) + u.w0 + row) * C;
-        mbar_wait(bar_afull + 8 * buf, use & 1, 15);
-        tc_fence_after();
-        const uint32_t trow = tmem_base + ((uint32_t)(q * 32) << 16) + buf * C;
-        if (!(p.dbg & 2)) conv_epilogue_tile<C, C>(trow, wb, p.act, p.add, p.out, addr0, !(p.dbg & 16), p.stats != nullptr, st, (!Cfg::kStage || (p.dbg & 32)) ? nullptr : stage);
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(bar_aempty + 8 * buf);
-      }
-      tile += (uint32_t)u.rows;
+      st.flush(p.stats, lane);
     }
-    st.flush(p.stats, lane);
   } else if (fused) {
     // ================================================================ transform: GroupNorm affine (+SiLU) in place
     float* tab = gn_smem + (warp - (2 + kWideEpiWarps)) * 2 * C;

@@ -128,6 +128,14 @@ static int launch_conv_wide(const void* x, const double* gn_stats, const float* 
     int r = make_tmap_bf16(&tmB, w, 3, dims, str, box, C);
     if (r) return r;
   }
+  CUtensorMap tmO;   // output tiles leave through TMA: one [32 positions][C] box per epilogue warp and output row
+  {
+    uint64_t dims[4] = {(uint64_t)C, (uint64_t)W, (uint64_t)T, (uint64_t)B};
+    uint64_t str[3] = {(uint64_t)C, (uint64_t)W * C, (uint64_t)T * W * C};
+    uint32_t box[4] = {(uint32_t)C, 32, 1, 1};
+    int r = make_tmap_bf16(&tmO, out, 4, dims, str, box, C);
+    if (r) return r;
+  }
   WideParams p;
   memset(&p, 0, sizeof(p));
   p.B = B; p.T = T; p.W = W;
@@ -137,16 +145,15 @@ static int launch_conv_wide(const void* x, const double* gn_stats, const float* 
   p.prologue = gn_mode; p.eps = gn_eps; p.gn_stats = gn_stats; p.gn_gamma = gn_gamma; p.gn_beta = gn_beta;
   p.out = reinterpret_cast<__nv_bfloat16*>(out); p.add = reinterpret_cast<const __nv_bfloat16*>(add);
   p.bias = bias; p.bias_b = bias_b; p.stats = stats; p.bias_b_stride = bias_b_stride; p.act = act;
-  { const char* e = getenv("DDIMB_WIDE_DBG"); p.dbg = e ? atoi(e) : 0; }
   const int grid = p.num_units < ddimb_num_sms() ? p.num_units : ddimb_num_sms();
   if (C == 32) {
     static bool attr = false;
     if (!attr) { DDIMB_CUDA(cudaFuncSetAttribute(conv3x3_wide_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, WideCfg<32>::kSmemBytes)); attr = true; }
-    conv3x3_wide_kernel<32><<<grid, kWideThreads, WideCfg<32>::kSmemBytes, stream>>>(tmA, tmB, p);
+    conv3x3_wide_kernel<32><<<grid, kWideThreads, WideCfg<32>::kSmemBytes, stream>>>(tmA, tmB, tmO, p);
   } else {
     static bool attr = false;
     if (!attr) { DDIMB_CUDA(cudaFuncSetAttribute(conv3x3_wide_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, WideCfg<64>::kSmemBytes)); attr = true; }
-    conv3x3_wide_kernel<64><<<grid, kWideThreads, WideCfg<64>::kSmemBytes, stream>>>(tmA, tmB, p);
+    conv3x3_wide_kernel<64><<<grid, kWideThreads, WideCfg<64>::kSmemBytes, stream>>>(tmA, tmB, tmO, p);
   }
   DDIMB_LAUNCH_CHECK();
   return DDIMB_OK;
