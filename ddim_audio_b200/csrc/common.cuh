@@ -214,6 +214,15 @@ __device__ __forceinline__ void tma_store_4d_e(const void* tmap, uint32_t src, i
       "r"(src), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
       : "memory");
 }
+// 1-D bulk store shared -> global (no tensor map, no per-box-row cost in the TMA engine); bytes a multiple of 16
+__device__ __forceinline__ void bulk_store_s2g_e(void* dst, uint32_t src, uint32_t bytes) {
+  asm volatile(
+      "{\n\t.reg .pred q;\n\t"
+      "elect.sync _|q, 0xffffffff;\n\t"
+      "@q cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;\n\t}" ::"l"(dst),
+      "r"(src), "r"(bytes)
+      : "memory");
+}
 __device__ __forceinline__ void bulk_commit_group() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 // the shared-memory SOURCE of all but the newest N committed groups has been read (the buffer may be overwritten)
 template <int N>

@@ -18,6 +18,9 @@ namespace ddimb {
 #ifndef DDIMB_WIDE_EPI
 #define DDIMB_WIDE_EPI 8
 #endif
+#ifndef DDIMB_WIDE_BULKST
+#define DDIMB_WIDE_BULKST 1
+#endif
 #ifndef DDIMB_WIDE_XF
 #define DDIMB_WIDE_XF 6
 #endif
@@ -190,6 +193,9 @@ __device__ __forceinline__ void wide_epilogue_lean(const WideParams& p, const CU
   constexpr int NB = Cfg::kAccBufs;
   constexpr uint32_t kGrpMask = kWideEpiWarps / 4 - 1;
   constexpr int CG = C / 8;
+  // C = 32: a tensor store costs the TMA engine ~4 cycles per 64-byte box row (as the loads do) and the engine, not HBM, bounded the
+  // kernel; the warp's 32 positions x 64 B are contiguous in global memory, so they leave as ONE 1-D bulk copy instead
+  constexpr bool kBulk = (C == 32) && (DDIMB_WIDE_BULKST != 0);
   const int q = warp & 3;
   const uint32_t grp = (uint32_t)(warp - 2) >> 2;
   const uint32_t stage = smem_u32(stage_gen);
@@ -240,10 +246,28 @@ __device__ __forceinline__ void wide_epilogue_lean(const WideParams& p, const CU
 #pragma unroll
           for (int j = 0; j < 16; ++j) f[j] = silu2_from_half(f[j]);
         }
+        if (kBulk) {
+          // linear [32 positions][64 B] tile for a 1-D bulk store: lane writes its chunks in the rotated order (i + phase) & 3 so the 8
+          // lanes of a quarter warp still hit 8 different bank groups; the rotation of the four 16-byte register groups is two
+          // stages of per-lane selects
+          uint4 ch[4];
 #pragma unroll
-        for (int qq = 0; qq < 4; ++qq)
-          *reinterpret_cast<uint4*>(srow + ((((uint32_t)(c0 >> 3) + qq) ^ phase) << 4)) =
-              make_uint4(f32x2_to_bf16x2(f[4 * qq]), f32x2_to_bf16x2(f[4 * qq + 1]), f32x2_to_bf16x2(f[4 * qq + 2]), f32x2_to_bf16x2(f[4 * qq + 3]));
+          for (int qq = 0; qq < 4; ++qq)
+            ch[qq] = make_uint4(f32x2_to_bf16x2(f[4 * qq]), f32x2_to_bf16x2(f[4 * qq + 1]), f32x2_to_bf16x2(f[4 * qq + 2]), f32x2_to_bf16x2(f[4 * qq + 3]));
+          const bool r2 = (phase & 2u) != 0, r1 = (phase & 1u) != 0;
+          auto sel = [](bool c, const uint4& a, const uint4& b) { return make_uint4(c ? a.x : b.x, c ? a.y : b.y, c ? a.z : b.z, c ? a.w : b.w); };
+          const uint4 a0 = sel(r2, ch[2], ch[0]), a1 = sel(r2, ch[3], ch[1]), a2 = sel(r2, ch[0], ch[2]), a3 = sel(r2, ch[1], ch[3]);
+          const uint4 b0 = sel(r1, a1, a0), b1 = sel(r1, a2, a1), b2 = sel(r1, a3, a2), b3 = sel(r1, a0, a3);
+          *reinterpret_cast<uint4*>(srow + (((0u + phase) & 3u) << 4)) = b0;
+          *reinterpret_cast<uint4*>(srow + (((1u + phase) & 3u) << 4)) = b1;
+          *reinterpret_cast<uint4*>(srow + (((2u + phase) & 3u) << 4)) = b2;
+          *reinterpret_cast<uint4*>(srow + (((3u + phase) & 3u) << 4)) = b3;
+        } else {
+#pragma unroll
+          for (int qq = 0; qq < 4; ++qq)
+            *reinterpret_cast<uint4*>(srow + ((((uint32_t)(c0 >> 3) + qq) ^ phase) << 4)) =
+                make_uint4(f32x2_to_bf16x2(f[4 * qq]), f32x2_to_bf16x2(f[4 * qq + 1]), f32x2_to_bf16x2(f[4 * qq + 2]), f32x2_to_bf16x2(f[4 * qq + 3]));
+        }
         if (STATS) {
           if (ACT == 3) {
             // training: the PRE-activation is stored; the following GroupNorm normalises silu(stored value)
@@ -263,7 +287,10 @@ __device__ __forceinline__ void wide_epilogue_lean(const WideParams& p, const CU
       }
       fence_proxy_async_smem();   // generic-proxy writes of every lane -> visible to the TMA engine
       __syncwarp();
-      tma_store_4d_e(tmO, stage, 0, wq, u.t0 + ot, u.b);
+#ifndef DDIMB_WIDE_NOSTORE
+      if (kBulk) bulk_store_s2g_e(p.out + ((((int64_t)u.b * p.T + (u.t0 + ot)) * p.W) + wq) * C, stage, 32 * C * 2);
+      else tma_store_4d_e(tmO, stage, 0, wq, u.t0 + ot, u.b);
+#endif
       bulk_commit_group();
       pending = true;
     }

@@ -17,7 +17,30 @@ using namespace ddimb;
 #include "tmap.cuh"
 
 // Fill the derived fields of GemmParams and launch.  A map is 5-D, B map is 3-D.
-static int launch_gemm(GemmParams& p, const CUtensorMap& tmA, const CUtensorMap& tmB, int ck, cudaStream_t stream, bool conv = false) {
+// 4-D tensor maps {accumulator column, w, t, batch} of a convolution's output and skip operand for the TMA epilogue: box = the
+// sub-tile one epilogue warp owns (32 positions of the 128-position tile) x CW channels.
+struct EpiMaps {
+  CUtensorMap out, skip;
+};
+static int make_epi_maps(EpiMaps* m, const GemmParams& p, void* out, const void* skip, int ncols, int cmod, int wdim, int tdim_extent,
+                         int batch, int64_t w_stride, int64_t t_stride, int64_t b_stride, int tile_w) {
+  const int cw = (cmod % 64 == 0) ? 64 : 32;
+  const int sw = tile_w < 32 ? tile_w : 32, sth = 32 / sw;
+  uint64_t dims[4] = {(uint64_t)ncols, (uint64_t)wdim, (uint64_t)tdim_extent, (uint64_t)batch};
+  uint64_t str[3] = {(uint64_t)w_stride, (uint64_t)t_stride, (uint64_t)b_stride};
+  uint32_t box[4] = {(uint32_t)cw, (uint32_t)sw, (uint32_t)sth, 1};
+  int r = make_tmap_bf16(&m->out, out, 4, dims, str, box, cw);
+  if (r) return r;
+  r = make_tmap_bf16(&m->skip, skip ? skip : out, 4, dims, str, box, cw);
+  (void)p;
+  return r;
+}
+
+static int launch_gemm(GemmParams& p, const CUtensorMap& tmA, const CUtensorMap& tmB, int ck, cudaStream_t stream, bool conv = false,
+                       const EpiMaps* epi = nullptr) {
+  if (conv) DDIMB_CHECK_ARG(epi != nullptr && (p.epi_tdim == 1 || p.epi_tdim == 2));
+  const CUtensorMap& tmO = epi ? epi->out : tmA;
+  const CUtensorMap& tmS = epi ? epi->skip : tmA;
   const int nacc_t = conv ? p.n_acc : 0, cmod_t = conv ? p.bias_mod : 0;
   DDIMB_CHECK_ARG(ck == 32 || ck == 64);
   DDIMB_CHECK_ARG(p.box[0] * p.box[1] * p.box[2] * p.box[3] == kTileM);
@@ -69,7 +92,7 @@ static int launch_gemm(GemmParams& p, const CUtensorMap& tmA, const CUtensorMap&
       DDIMB_CUDA(cudaFuncSetAttribute(umma_gemm_kernel<CKV, NACCV, CMODV>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem)); \
       attr = true;                                                                                                               \
     }                                                                                                                            \
-    umma_gemm_kernel<CKV, NACCV, CMODV><<<grid, kGemmThreads, smem, stream>>>(tmA, tmB, p);                                      \
+    umma_gemm_kernel<CKV, NACCV, CMODV><<<grid, kGemmThreads, smem, stream>>>(tmA, tmB, tmO, tmS, p);                            \
     launched = true;                                                                                                             \
   }
   bool launched = false;
@@ -334,7 +357,13 @@ extern "C" int ddimb_conv3x3(const void* x, const void* w, const float* bias, co
   p.out_stride[0] = Cout; p.out_stride[1] = (int64_t)W * Cout; p.out_stride[3] = (int64_t)T * W * Cout;
   p.out_dim[0] = W; p.out_dim[1] = T; p.out_dim[3] = B;
   p.n_valid = Cout; p.bias_mod = Cout; p.bias_b_stride = bias_b_stride; p.act = act;
-  return launch_gemm(p, tmA, tmB, ck, stream, true);
+  p.epi_tdim = 1;
+  EpiMaps epi;
+  {
+    int r = make_epi_maps(&epi, p, out, add, Cout, Cout, W, T, B, Cout, (int64_t)W * Cout, (int64_t)T * W * Cout, bw);
+    if (r) return r;
+  }
+  return launch_gemm(p, tmA, tmB, ck, stream, true, &epi);
 }
 
 // ------------------------------------------------------------------------------------------------ wide Downsample (32 -> 64)
@@ -429,7 +458,13 @@ extern "C" int ddimb_conv_down4x4(const void* x, const void* w, const float* bia
   p.out_stride[0] = Cout; p.out_stride[2] = (int64_t)Wo * Cout; p.out_stride[3] = (int64_t)To * Wo * Cout;
   p.out_dim[0] = Wo; p.out_dim[2] = To; p.out_dim[3] = B;
   p.n_valid = Cout; p.bias_mod = Cout; p.act = 0;
-  return launch_gemm(p, tmA, tmB, ck, stream, true);
+  p.epi_tdim = 2;
+  EpiMaps epi;
+  {
+    int r = make_epi_maps(&epi, p, out, nullptr, Cout, Cout, Wo, To, B, Cout, (int64_t)Wo * Cout, (int64_t)To * Wo * Cout, bw);
+    if (r) return r;
+  }
+  return launch_gemm(p, tmA, tmB, ck, stream, true, &epi);
 }
 
 // ------------------------------------------------------------------------------------------------ wide Upsample (64 -> 32)
@@ -532,7 +567,16 @@ extern "C" int ddimb_conv_up4x4(const void* x, const void* w, const float* bias,
     p.out_base = (int64_t)r * Wo * Cout;
     p.out_dim[0] = W; p.out_dim[1] = T; p.out_dim[3] = B;
     p.n_valid = 2 * Cout; p.bias_mod = Cout; p.act = 0;
-    int rc = launch_gemm(p, tmA, tmB, ck, stream, true);
+    p.epi_tdim = 1;
+    // output row parity r as a 4-D view: pixel pair f' of output row 2 t' + r holds the 2 * Cout accumulator columns [s][co]
+    EpiMaps epi;
+    {
+      __nv_bfloat16* ob = reinterpret_cast<__nv_bfloat16*>(out) + (int64_t)r * Wo * Cout;
+      const __nv_bfloat16* sb = skip ? reinterpret_cast<const __nv_bfloat16*>(skip) + (int64_t)r * Wo * Cout : nullptr;
+      int rc0 = make_epi_maps(&epi, p, ob, sb, 2 * Cout, Cout, W, T, B, 2 * Cout, (int64_t)2 * Wo * Cout, (int64_t)To * Wo * Cout, bw);
+      if (rc0) return rc0;
+    }
+    int rc = launch_gemm(p, tmA, tmB, ck, stream, true, &epi);
     if (rc) return rc;
   }
   return DDIMB_OK;

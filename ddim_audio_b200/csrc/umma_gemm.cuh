@@ -6,8 +6,9 @@
 //   A rows are the 128 positions of a 5-D TMA box (c, d1, d2, d3, d4) of the NHWC/row-major activation; a tap
 //   shifts the box (da[]) and picks a channel range -- TMA out-of-bounds zero fill IS the conv zero padding.
 //   B rows are output channels of the K-major packed weight (or a per-sample operand for the DFT GEMMs).
-// Warp roles (192 threads): warp0 = TMA producer, warp1 = MMA issuer (+TMEM alloc), warps2-5 = epilogue
-// (TMEM -> registers -> bias/temb/activation/skip-add/GroupNorm partial sums -> global).
+// Warp roles (320 threads): warp0 = TMA producer, warp1 = MMA issuer (+TMEM alloc), warps2-9 = epilogue: two warps per TMEM
+// lane quarter that split the accumulator columns (TMEM -> registers -> bias/temb/activation/skip-add/GroupNorm partial sums ->
+// swizzled shared-memory tile -> TMA store; the skip operand arrives through a TMA load into the same tile).
 #pragma once
 #include "common.cuh"
 
@@ -15,7 +16,8 @@ namespace ddimb {
 
 constexpr int kMaxTaps = 16;
 constexpr int kTileM = 128;
-constexpr int kGemmThreads = 192;
+constexpr int kGemmThreads = 320;
+constexpr int kGemmEpiWarps = 8;
 
 struct TapDesc {
   int16_t da[4];      // coordinate shift of the A box along dims 1..4
@@ -60,6 +62,8 @@ struct GemmParams {
   int32_t bias_b_stride;
   int32_t act;              // 0 none, 1 silu, 2 gelu_new
   int32_t out_f32;          // 1: out is fp32
+  // ---- convolution epilogue through TMA (tmO / tmS: 4-D maps {accumulator column, w, t, batch} of out / add)
+  int32_t epi_tdim;         // which tile dim (1 or 2) is the row-like one
 };
 
 template <int CK>
@@ -70,7 +74,7 @@ struct GemmSmem {
   __host__ __device__ static int stage_bytes(int b_rows, int kps) { return kps * (kABytes + b_rows * CK * 2); }
 };
 
-constexpr int kGemmAuxBytes = 1024 + 4096 + 4 * 2048;  // barriers, tmem pointer | per-warp bias copies | per-warp store staging
+constexpr int kGemmAuxBytes = 1024 + kGemmEpiWarps * 1024 + kGemmEpiWarps * 4096;  // barriers, tmem pointer | per-warp bias copies | per-warp [32 x 64 ch] store tiles
 
 // Mixed-radix tile counter (W tiles, T tiles, dim-3 tiles, batch, N tiles) advanced by gridDim.x per step without any
 // division: the step is decomposed once, every digit then carries at most 1.
@@ -96,6 +100,8 @@ struct TileIter {
     }
   }
 };
+
+__device__ __forceinline__ void fence_proxy_async_smem_() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
 // 32 lanes x 32 consecutive fp32 columns
 __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
@@ -283,20 +289,179 @@ __device__ __forceinline__ void conv_epilogue_tile(uint32_t trow, const float* w
   }
 }
 
+// GroupNorm partial sums of one 32-channel chunk whose first channel is 32 * G0 (f = 16 packed channel pairs)
+template <int CMOD, int G0>
+__device__ __forceinline__ void epi_stats_acc(ConvEpiState<CMOD>& st, const uint64_t (&f)[16]) {
+  if constexpr (G0 * 32 < CMOD) {
+    constexpr int CG = CMOD / 8;
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      constexpr int dummy = 0;
+      const int g = (G0 * 32 + 2 * j + dummy) / CG;   // compile-time after unrolling
+      st.s1[g] = fadd2(st.s1[g], f[j]);
+      st.s2[g] = ffma2(f[j], f[j], st.s2[g]);
+    }
+  }
+}
+
+// Convolution epilogue of umma_gemm_kernel for one epilogue warp (TMEM lane quarter q, column half `half`): per tile and per
+// CW-channel chunk this warp owns: [TMA load of the skip chunk into the staging tile] -> TMEM -> registers -> (+bias/temb) ->
+// activation -> (+skip) -> bf16 -> staging tile in the TMA swizzle image -> ONE cp.async.bulk.tensor store.  Rows outside the
+// tensor are clipped by the store (and excluded from the statistics); everything invariant over the loops is hoisted or a template
+// parameter.  (ncu r02: the previous per-thread staged-store epilogue cost ~3 K cycles per 32-column chunk -- with four epilogue warps
+// every convolution at C >= 96 was epilogue-bound, not tensor-bound.)
+template <int NACC, int CMOD, int ACT>
+__device__ __forceinline__ void conv_epi_loop_tma(const GemmParams& p, const CUtensorMap* tmO, const CUtensorMap* tmS, uint32_t tmem_base,
+                                                  uint32_t bar_tfull, uint32_t bar_tempty, uint32_t bar_skip, float* wb, uint8_t* stage_gen,
+                                                  int q, int half, int lane) {
+  constexpr int CW = (CMOD % 64 == 0) ? 64 : 32;   // channels per store box: 128-byte (SWIZZLE_128B) or 64-byte (SWIZZLE_64B) rows
+  constexpr int NCH = NACC / CW;
+  static_assert(NACC % CW == 0 && CW * 2 * 32 <= 4096, "staging tile");
+  const bool want_stats = p.stats != nullptr, has_add = p.add != nullptr;
+  const uint32_t stage = smem_u32(stage_gen);
+  const uint32_t phase = (CW == 64) ? (uint32_t)(lane & 7) : (uint32_t)((lane >> 1) & 3);
+  uint8_t* srow = stage_gen + lane * (CW * 2);
+  const uint64_t s2x = (ACT == 1) ? pack2(0.5f, 0.5f) : pack2(1.0f, 1.0f);
+  // this thread's position inside the tile (validity / statistics) and the warp's sub-box origin (store / skip-load coordinates)
+  int r = q * 32 + lane;
+  const int r1 = r % p.box[0]; r /= p.box[0];
+  const int r2 = r % p.box[1]; r /= p.box[1];
+  const int r3 = r % p.box[2]; r /= p.box[2];
+  const int r4 = r;
+  const int w_off = (q * 32) % p.box[0], t_off = (q * 32) / p.box[0];
+  const int tdim = p.epi_tdim;
+  ConvEpiState<CMOD> st;
+  st.reset();
+  st.cur_batch = -1;
+  uint32_t skip_ph = 0;
+  bool pending = false;
+  int local = 0;
+  TileIter it;
+  for (it.init(p, blockIdx.x, gridDim.x); it.valid(); it.next(), ++local) {
+    const int d1 = it.i[0] * p.box[0] + r1, d2 = it.i[1] * p.box[1] + r2, d3 = it.i[2] * p.box[2] + r3, d4 = it.i[3] * p.box[3] + r4;
+    const bool valid = d1 < p.out_dim[0] && d2 < p.out_dim[1] && d3 < p.out_dim[2] && d4 < p.out_dim[3];
+    const int batch = it.i[3];
+    if (batch != st.cur_batch) {
+      st.flush(p.stats, lane);
+      st.cur_batch = batch;
+      conv_epilogue_bias<CMOD>(wb, p.bias, p.bias_b, batch, p.bias_b_stride, ACT, lane);
+    }
+    const int cw = it.i[0] * p.box[0] + w_off, ct = it.i[tdim] * p.box[tdim] + t_off;
+    const int buf = local % p.num_acc_bufs;
+    const uint32_t use = (uint32_t)(local / p.num_acc_bufs);
+    const uint32_t trow = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * NACC);
+    bool waited = false;
+#pragma unroll 1
+    for (int k = half; k < NCH; k += 2) {
+      if (pending) {            // the previous store has read the staging tile
+        bulk_wait_group_read<0>();
+        __syncwarp();
+        pending = false;
+      }
+      if (has_add && elect_one()) {
+        mbar_arrive_expect_tx(bar_skip, (uint32_t)(32 * CW * 2));
+        asm volatile("cp.async.bulk.tensor.4d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];" ::"r"(stage),
+                     "l"(tmS), "r"(bar_skip), "r"(k * CW), "r"(cw), "r"(ct), "r"(batch)
+                     : "memory");
+      }
+      if (!waited) {
+        mbar_wait(bar_tfull + 8 * buf, use & 1, 4);
+        tc_fence_after();
+        waited = true;
+      }
+#pragma unroll
+      for (int c0 = 0; c0 < CW; c0 += 32) {
+        uint32_t v[32];
+        tmem_ld32(trow + (uint32_t)(k * CW + c0), v);
+        tmem_ld_wait();
+        if (k + 2 >= NCH && c0 + 32 == CW) {   // this warp's last accumulator columns are in registers
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(bar_tempty + 8 * buf);
+        }
+        const int col = (k * CW + c0) % CMOD;   // channel of v[0] (bias / GroupNorm group)
+        uint64_t f[16];
+#pragma unroll
+        for (int j = 0; j < 16; j += 2) {
+          const ulonglong2 b4 = *reinterpret_cast<const ulonglong2*>(wb + col + 2 * j);
+          f[j] = ffma2(pack2u(v[2 * j], v[2 * j + 1]), s2x, b4.x);
+          f[j + 1] = ffma2(pack2u(v[2 * j + 2], v[2 * j + 3]), s2x, b4.y);
+        }
+        if (ACT == 1) {
+#pragma unroll
+          for (int j = 0; j < 16; ++j) f[j] = silu2_from_half(f[j]);
+        }
+        if (has_add) {
+          if (c0 == 0) {
+            mbar_wait(bar_skip, skip_ph, 5);
+            skip_ph ^= 1u;
+          }
+#pragma unroll
+          for (int qq = 0; qq < 4; ++qq) {
+            const uint4 a = *reinterpret_cast<const uint4*>(srow + ((((uint32_t)(c0 >> 3) + qq) ^ phase) << 4));
+            f[4 * qq] = fadd2(f[4 * qq], bf16x2_to_f32x2(a.x));
+            f[4 * qq + 1] = fadd2(f[4 * qq + 1], bf16x2_to_f32x2(a.y));
+            f[4 * qq + 2] = fadd2(f[4 * qq + 2], bf16x2_to_f32x2(a.z));
+            f[4 * qq + 3] = fadd2(f[4 * qq + 3], bf16x2_to_f32x2(a.w));
+          }
+        }
+#pragma unroll
+        for (int qq = 0; qq < 4; ++qq)
+          *reinterpret_cast<uint4*>(srow + ((((uint32_t)(c0 >> 3) + qq) ^ phase) << 4)) =
+              make_uint4(f32x2_to_bf16x2(f[4 * qq]), f32x2_to_bf16x2(f[4 * qq + 1]), f32x2_to_bf16x2(f[4 * qq + 2]), f32x2_to_bf16x2(f[4 * qq + 3]));
+        if (want_stats && valid) {
+          if (ACT == 3) {
+            // training: the PRE-activation is stored; the following GroupNorm normalises silu(stored value)
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              const float2 t = unpack2(f[j]);
+              f[j] = pack2(silu_fast(__bfloat162float(__float2bfloat16_rn(t.x))), silu_fast(__bfloat162float(__float2bfloat16_rn(t.y))));
+            }
+          }
+          // st.s1 / st.s2 are register arrays: the group index must be a compile-time constant, so dispatch on the chunk's first
+          // channel (a multiple of 32) and let each case unroll with constant indices
+          switch (col >> 5) {
+            case 0: epi_stats_acc<CMOD, 0>(st, f); break;
+            case 1: epi_stats_acc<CMOD, 1>(st, f); break;
+            case 2: epi_stats_acc<CMOD, 2>(st, f); break;
+            case 3: epi_stats_acc<CMOD, 3>(st, f); break;
+            case 4: epi_stats_acc<CMOD, 4>(st, f); break;
+            case 5: epi_stats_acc<CMOD, 5>(st, f); break;
+            case 6: epi_stats_acc<CMOD, 6>(st, f); break;
+            default: epi_stats_acc<CMOD, 7>(st, f); break;
+          }
+        }
+      }
+      fence_proxy_async_smem_();   // generic-proxy writes of every lane -> visible to the TMA engine
+      __syncwarp();
+      tma_store_4d_e(tmO, stage, k * CW, cw, ct, batch);
+      bulk_commit_group();
+      pending = true;
+    }
+    if (!waited) {              // fewer chunks than column halves: nothing to do, but the MMA warp counts eight arrivals per buffer
+      mbar_wait(bar_tfull + 8 * buf, use & 1, 4);
+      if (lane == 0) mbar_arrive(bar_tempty + 8 * buf);
+    }
+  }
+  st.flush(p.stats, lane);
+  bulk_wait_group<0>();
+}
+
 // NACC / CMOD > 0: convolution instantiation (compile-time accumulator width and channel count, lean epilogue with
 // GroupNorm partial sums); NACC == 0: generic GEMM epilogue (Linear, Fourier mixing; runtime widths, fp32 or bf16 output).
 template <int CK, int NACC, int CMOD>
 __global__ void __launch_bounds__(kGemmThreads, 1)
-umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                 const __grid_constant__ GemmParams p) {
+umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmO,
+                 const __grid_constant__ CUtensorMap tmS, const __grid_constant__ GemmParams p) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;   // swizzle atoms need 1024-B alignment
   uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
   const int stage_bytes = GemmSmem<CK>::stage_bytes(p.b_rows_per_stage, p.kps);
   const int b_chunk_bytes = p.b_rows_per_stage * CK * 2;   // B region of one chunk
   const uint32_t aux = smem_base + p.num_stages * stage_bytes;
-  // aux layout: full[8] @0, empty[8] @64, tmem_full[2] @128, tmem_empty[2] @144, tmem_ptr @160, per-warp bias float[4][256] @1024
-  const uint32_t bar_full = aux, bar_empty = aux + 64, bar_tfull = aux + 128, bar_tempty = aux + 144;
+  // aux layout: full[8] @0, empty[8] @64, tmem_full[2] @128, tmem_empty[2] @144, tmem_ptr @160, skip[8] @192, per-warp bias float[8][256] @1024,
+  // per-warp staging tiles [8][4096] @1024 + 8192
+  const uint32_t bar_full = aux, bar_empty = aux + 64, bar_tfull = aux + 128, bar_tempty = aux + 144, bar_skip = aux + 192;
   volatile uint32_t* tmem_ptr_gen = reinterpret_cast<volatile uint32_t*>(smem_gen + p.num_stages * stage_bytes + 160);
   float* bias_smem = reinterpret_cast<float*>(smem_gen + p.num_stages * stage_bytes + 1024);
 
@@ -311,7 +476,12 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     }
     for (int b = 0; b < 2; ++b) {
       mbar_init(bar_tfull + 8 * b, 1);
-      mbar_init(bar_tempty + 8 * b, 4);   // one arrive per epilogue warp
+      mbar_init(bar_tempty + 8 * b, kGemmEpiWarps);   // one arrive per epilogue warp
+    }
+    for (int w = 0; w < kGemmEpiWarps; ++w) mbar_init(bar_skip + 8 * w, 1);
+    if (NACC > 0) {
+      tma_prefetch_desc(&tmO);
+      if (p.add != nullptr) tma_prefetch_desc(&tmS);
     }
     mbar_fence_init();
   }
@@ -401,8 +571,9 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       }
     }
   } else {
-    // ================================================================ epilogue (warps 2..5, TMEM lane quarter = warp % 4)
+    // ================================================================ epilogue (warps 2..9, TMEM lane quarter = warp % 4, column half = (warp - 2) / 4)
     const int q = warp & 3;
+    const int half = (warp - 2) >> 2;
     const int row = q * 32 + lane;
     int r = row;
     const int r1 = r % p.box[0]; r /= p.box[0];
@@ -413,36 +584,13 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     TileIter it;
     if constexpr (NACC > 0) {
       // ---------------- convolution epilogue
-      float* wb = bias_smem + q * 256;
-      uint8_t* stage = reinterpret_cast<uint8_t*>(bias_smem) + 4096 + q * 2048;
-      ConvEpiState<CMOD> st;
-      st.reset();
-      st.cur_batch = -1;
-      __nv_bfloat16* out = reinterpret_cast<__nv_bfloat16*>(p.out);
-      for (it.init(p, blockIdx.x, gridDim.x); it.valid(); it.next(), ++local) {
-        const int d1 = it.i[0] * p.box[0] + r1, d2 = it.i[1] * p.box[1] + r2, d3 = it.i[2] * p.box[2] + r3, d4 = it.i[3] * p.box[3] + r4;
-        const bool valid = d1 < p.out_dim[0] && d2 < p.out_dim[1] && d3 < p.out_dim[2] && d4 < p.out_dim[3];
-        const int64_t addr0 = p.out_base + d1 * p.out_stride[0] + d2 * p.out_stride[1] + d3 * p.out_stride[2] + d4 * p.out_stride[3];
-        const int batch = it.i[3];
-        if (batch != st.cur_batch) {
-          st.flush(p.stats, lane);
-          st.cur_batch = batch;
-          conv_epilogue_bias<CMOD>(wb, p.bias, p.bias_b, batch, p.bias_b_stride, p.act, lane);
-        }
-        const int buf = local % p.num_acc_bufs;
-        const uint32_t use = (uint32_t)(local / p.num_acc_bufs);
-        uint4 pre[NACC / 8];
-        if (p.add != nullptr) conv_epilogue_prefetch_add<NACC>(p.add, valid ? addr0 : 0, valid, pre);   // in flight while the MMAs finish
-        mbar_wait(bar_tfull + 8 * buf, use & 1, 4);
-        tc_fence_after();
-        const uint32_t trow = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * NACC);
-        conv_epilogue_tile<NACC, CMOD>(trow, wb, p.act, p.add, out, valid ? addr0 : 0, valid, p.stats != nullptr, st, stage,
-                                       p.add != nullptr ? pre : nullptr);
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(bar_tempty + 8 * buf);
-      }
-      st.flush(p.stats, lane);
+      float* wb = bias_smem + (warp - 2) * 256;
+      uint8_t* stage = reinterpret_cast<uint8_t*>(bias_smem) + kGemmEpiWarps * 1024 + (warp - 2) * 4096;
+      const uint32_t bsk = bar_skip + 8 * (warp - 2);
+      if (p.act == 1) conv_epi_loop_tma<NACC, CMOD, 1>(p, &tmO, &tmS, tmem_base, bar_tfull, bar_tempty, bsk, wb, stage, q, half, lane);
+      else if (p.act == 3) conv_epi_loop_tma<NACC, CMOD, 3>(p, &tmO, &tmS, tmem_base, bar_tfull, bar_tempty, bsk, wb, stage, q, half, lane);
+      else conv_epi_loop_tma<NACC, CMOD, 0>(p, &tmO, &tmS, tmem_base, bar_tfull, bar_tempty, bsk, wb, stage, q, half, lane);
+      (void)r1; (void)r2; (void)r3; (void)r4; (void)local;
     } else {
       // ---------------- generic GEMM epilogue (Linear / Fourier mixing)
       for (it.init(p, blockIdx.x, gridDim.x); it.valid(); it.next(), ++local) {
@@ -455,12 +603,12 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         mbar_wait(bar_tfull + 8 * buf, use & 1, 4);
         tc_fence_after();
         const uint32_t trow = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * p.n_acc);
-        for (int c0 = 0; c0 < p.n_acc; c0 += 16) {
+        for (int c0 = 16 * half; c0 < p.n_acc; c0 += 32) {   // the two warps of a lane quarter alternate 16-column steps
           uint32_t v[16];
           tmem_ld16(trow + (uint32_t)c0, v);
           tmem_ld_wait();
           const int gcol = nt * p.n_acc + c0;   // global column of v[0]
-          if (gcol >= p.n_valid) break;         // uniform across the CTA
+          if (gcol >= p.n_valid) break;         // uniform across the warp
           float f[16];
 #pragma unroll
           for (int j = 0; j < 16; ++j) f[j] = __uint_as_float(v[j]);
