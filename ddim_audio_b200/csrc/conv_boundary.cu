@@ -202,15 +202,15 @@ __global__ void __launch_bounds__(128, 3) conv_out_strip_kernel(const __nv_bfloa
 
 }  // namespace
 
-int ddimb_conv_in_tc(const float* x, const float* w, const float* bias, void* out, double* stats, int B, int T, int F, cudaStream_t stream);
+int ddimb_conv_in_tc(const float* x, const uint8_t* wimg, const float* bias, void* out, double* stats, int B, int T, int F, cudaStream_t stream);
 
 // models/diffusion.py:189-198 -- Conv2d(Cin=2 -> 32, k3 p1): x fp32 NCHW, w fp32 [32][Cin][3][3], out bf16 NHWC, GroupNorm partial sums.
-extern "C" int ddimb_conv_in(const float* x, const float* w, const float* bias, void* out, double* stats, int B, int Cin, int T, int F,
-                             int Cout, cudaStream_t stream) {
+extern "C" int ddimb_conv_in(const float* x, const float* w, const void* wimg, const float* bias, void* out, double* stats, int B, int Cin, int T,
+                             int F, int Cout, cudaStream_t stream) {
   DDIMB_CHECK_ARG(x && w && bias && out && B >= 1 && Cin == 2 && Cout == 32 && B <= 65535);
   DDIMB_PROF(stream, "conv_in", Cin, Cout, (double)B * T * F * (4.0 * Cin + 2.0 * Cout), 18.0 * Cin * Cout * B * T * F);
-  if (F % 128 == 0 && getenv("DDIMB_NO_CONVIN_TC") == nullptr)   // tensor-core path (csrc/conv_in_tc.cuh); the strip kernel below covers ragged F
-    return ddimb_conv_in_tc(x, w, bias, out, stats, B, T, F, stream);
+  if (F % 128 == 0)   // tensor-core path (csrc/conv_in_tc.cuh); the strip kernel below covers ragged F
+    return ddimb_conv_in_tc(x, reinterpret_cast<const uint8_t*>(wimg), bias, out, stats, B, T, F, stream);
   DDIMB_CUDA(cudaMemcpyToSymbolAsync(c_w_in, w, sizeof(float) * 32 * 2 * 9, 0, cudaMemcpyDeviceToDevice, stream));
   DDIMB_CUDA(cudaMemcpyToSymbolAsync(c_w_in, bias, sizeof(float) * 32, sizeof(float) * 32 * 2 * 9, cudaMemcpyDeviceToDevice, stream));
   const int strips = (F + 127) / 128;
@@ -220,15 +220,15 @@ extern "C" int ddimb_conv_in(const float* x, const float* w, const float* bias, 
   return DDIMB_OK;
 }
 
-int ddimb_conv_out_tc(const void* x, const void* skip, const float* w, const float* bias, float* out, int B, int T, int F, cudaStream_t stream);
+int ddimb_conv_out_tc(const void* x, const void* skip, const uint8_t* wimg, const float* bias, float* out, int B, int T, int F, cudaStream_t stream);
 
 // models/diffusion.py:284,199-208 -- Conv2d(32 -> 2, k3 p1) of (x + skip): x, skip (nullable) bf16 NHWC, w fp32 [2][32][3][3], out fp32 NCHW.
-extern "C" int ddimb_conv_out(const void* x, const void* skip, const float* w, const float* bias, float* out, int B, int T, int F,
+extern "C" int ddimb_conv_out(const void* x, const void* skip, const float* w, const void* wimg, const float* bias, float* out, int B, int T, int F,
                               int Cin, int Cout, cudaStream_t stream) {
   DDIMB_CHECK_ARG(x && w && bias && out && B >= 1 && Cin == 32 && Cout == 2 && B <= 65535);
   DDIMB_PROF(stream, "conv_out", Cin, Cout, (double)B * T * F * (2.0 * Cin * (skip ? 2 : 1) + 4.0 * Cout), 18.0 * Cin * Cout * B * T * F);
-  if (F % 128 == 0 && getenv("DDIMB_NO_CONVOUT_TC") == nullptr)   // tensor-core path (csrc/conv_out_tc.cuh); the strip kernel below covers ragged F
-    return ddimb_conv_out_tc(x, skip, w, bias, out, B, T, F, stream);
+  if (F % 128 == 0)   // tensor-core path (csrc/conv_out_tc.cuh); the strip kernel below covers ragged F
+    return ddimb_conv_out_tc(x, skip, reinterpret_cast<const uint8_t*>(wimg), bias, out, B, T, F, stream);
   DDIMB_CUDA(cudaMemcpyToSymbolAsync(c_w_out, w, sizeof(float) * 2 * 32 * 9, 0, cudaMemcpyDeviceToDevice, stream));
   DDIMB_CUDA(cudaMemcpyToSymbolAsync(c_w_out, bias, sizeof(float) * 2, sizeof(float) * 2 * 32 * 9, cudaMemcpyDeviceToDevice, stream));
   const int strips = (F + 127) / 128;

@@ -58,6 +58,19 @@ static int launch_gemm(GemmParams& p, const CUtensorMap& tmA, const CUtensorMap&
     if (tp.nseg * p.n_seg > brows) brows = tp.nseg * p.n_seg;
   }
   p.b_rows_per_stage = brows;
+  {
+    // which tap writes each accumulator segment first (that MMA overwrites instead of accumulating)
+    uint32_t seen = 0;
+    for (int t = 0; t < p.ntaps; ++t) {
+      TapDesc& tp = p.taps[t];
+      tp.first_mask = 0;
+      for (int sg = 0; sg < tp.nseg; ++sg) {
+        const uint32_t bit = 1u << (tp.tmem_col0 / p.n_seg + sg);
+        if (!(seen & bit)) tp.first_mask |= 1 << sg;
+        seen |= bit;
+      }
+    }
+  }
   const int max_smem = 232448;   // 227 KB opt-in limit per CTA on sm_100
   // K chunks per stage: a barrier round should cover >= 128 of K (the MMA issue thread pays a fixed cost per round), as long
   // as at least three stages still fit
@@ -124,6 +137,79 @@ static void spatial_tile(int T, int W, int* bw, int* bt) {
   *bw = W >= kTileM ? kTileM : W;
   *bt = kTileM / *bw;
   (void)T;
+}
+
+// ------------------------------------------------------------------------------------------------ tap programs of the generic kernel
+static void conv3x3_taps(GemmParams& p, int Cin, int Cout, int ck) {
+  p.n_seg = Cout; p.n_acc = Cout;
+  p.ntaps = 9;
+  for (int ky = 0; ky < 3; ++ky)
+    for (int kx = 0; kx < 3; ++kx) {
+      TapDesc& tp = p.taps[ky * 3 + kx];
+      tp.da[0] = (int16_t)(kx - 1); tp.da[1] = (int16_t)(ky - 1); tp.da[2] = 0; tp.da[3] = 0;
+      tp.a_c0 = 0; tp.b_k0 = (ky * 3 + kx) * Cin; tp.b_n0 = 0;
+      tp.nchunk = (int16_t)(Cin / ck); tp.nseg = 1; tp.tmem_col0 = 0;
+    }
+}
+
+// Conv2d 4x4 s2 p1 on the space-to-depth view (2*Cin, W/2, 2, T/2, B): kernel column kx in {1,2} is one contiguous 2*Cin slab of
+// column pair f', kx=0 / kx=3 are the upper / lower half of the neighbouring pairs; kernel row ky picks (pair row t'+dy, sub-row r).
+static void down_taps(GemmParams& p, int Cin, int Cout, int ck) {
+  p.n_seg = Cout; p.n_acc = Cout;
+  static const int kDy[4] = {-1, 0, 0, 1}, kR[4] = {1, 0, 1, 0};
+  int nt = 0;
+  for (int ky = 0; ky < 4; ++ky) {
+    // (dx, first channel of the pair slab, kernel column of the first Cin block, number of Cin blocks)
+    const int grp[3][4] = {{0, 0, 1, 2}, {-1, Cin, 0, 1}, {1, 0, 3, 1}};
+    for (int g = 0; g < 3; ++g) {
+      TapDesc& tp = p.taps[nt++];
+      tp.da[0] = (int16_t)grp[g][0]; tp.da[1] = (int16_t)kR[ky]; tp.da[2] = (int16_t)kDy[ky]; tp.da[3] = 0;
+      tp.a_c0 = grp[g][1]; tp.b_k0 = (ky * 4 + grp[g][2]) * Cin; tp.b_n0 = 0;
+      tp.nchunk = (int16_t)(grp[g][3] * Cin / ck); tp.nseg = 1; tp.tmem_col0 = 0;
+    }
+  }
+  p.ntaps = nt;
+}
+
+// ConvTranspose2d 4x4 s2 p1, output row parity r: out[2t'+r, 2f'+s, co] = sum over (dy, dx) of in[t'+dy, f'+dx, :] . Wt[:, co, ky, kx],
+// ky = r + 1 - 2 dy, kx = s + 1 - 2 dx; accumulator columns are [s][co].  Weight operand rows: (ky*4 + kx) * Cout + co.
+static void up_taps(GemmParams& p, int r, int Cin, int Cout, int ck) {
+  p.n_seg = Cout; p.n_acc = 2 * Cout;
+  int nt = 0;
+  const int dys[2] = {0, r == 0 ? -1 : 1};
+  for (int iy = 0; iy < 2; ++iy) {
+    const int dy = dys[iy], ky = r + 1 - 2 * dy;
+    const int dxs[3] = {0, -1, 1};   // dx = 0 first: it writes both column halves
+    for (int ix = 0; ix < 3; ++ix) {
+      const int dx = dxs[ix];
+      TapDesc& tp = p.taps[nt++];
+      tp.da[0] = (int16_t)dx; tp.da[1] = (int16_t)dy; tp.da[2] = 0; tp.da[3] = 0;
+      tp.a_c0 = 0; tp.b_k0 = 0; tp.nchunk = (int16_t)(Cin / ck);
+      if (dx == 0) { tp.nseg = 2; tp.b_n0 = (ky * 4 + 1) * Cout; tp.tmem_col0 = 0; }        // s=0 -> kx=1, s=1 -> kx=2
+      else if (dx < 0) { tp.nseg = 1; tp.b_n0 = (ky * 4 + 3) * Cout; tp.tmem_col0 = 0; }    // s=0, kx=3
+      else { tp.nseg = 1; tp.b_n0 = (ky * 4 + 0) * Cout; tp.tmem_col0 = Cout; }             // s=1, kx=0
+    }
+  }
+  p.ntaps = nt;
+}
+
+// number the (chunk, segment) blocks of p's taps consecutively from `first`; returns the next free block
+static int assign_img_blocks(GemmParams& p, int first) {
+  for (int t = 0; t < p.ntaps; ++t) {
+    p.taps[t].img_blk = first;
+    first += p.taps[t].nchunk * p.taps[t].nseg;
+  }
+  return first;
+}
+
+static int build_generic_wimg(const GemmParams& p, const void* w, uint8_t* img, int ck, int ldw, int first, int next, cudaStream_t stream) {
+  WimgParams q;
+  memset(&q, 0, sizeof(q));
+  q.ntaps = p.ntaps; q.n_seg = p.n_seg; q.ck = ck; q.ldw = ldw; q.nblocks = next - first;
+  for (int t = 0; t < p.ntaps; ++t) { q.taps[t] = p.taps[t]; q.taps[t].img_blk -= first; }
+  wimg_generic_kernel<<<q.nblocks, 256, 0, stream>>>(reinterpret_cast<const __nv_bfloat16*>(w), img + (int64_t)first * p.n_seg * ck * 2, q);
+  DDIMB_LAUNCH_CHECK();
+  return DDIMB_OK;
 }
 
 // ------------------------------------------------------------------------------------------------ wide 3x3 conv (+ fused GroupNorm)
@@ -196,9 +282,7 @@ extern "C" int ddimb_conv3x3_gn(const void* x, const double* gn_stats, const flo
 }
 
 // ------------------------------------------------------------------------------------------------ window 3x3 conv (C = 96)
-// csrc/conv_window.cuh.  The weight operand keeps the ABI layout ([Cout][9 * Cin], K-major); its pre-swizzled tile image is
-// rebuilt into a per-device scratch buffer by a 27-block kernel ahead of every launch (166 KB: noise next to the conv, and
-// never stale when the weights are updated in place).  Launches are assumed to be stream-ordered per device.
+// csrc/conv_window.cuh.  Weights come from the caller's pre-swizzled tile image (ddimb_conv_wimg, kind 0).
 static int win_smem_bytes(int W, int* nr, int* plane) {
   const int WP = W + 2;
   *nr = 3 + ceil_div(257, WP);
@@ -212,22 +296,15 @@ static bool conv_window_supported(int Cin, int Cout, int W) {
   return !off && Cin == kWinC && Cout == kWinC && W + 2 <= 256 && win_smem_bytes(W, &nr, &plane) <= 232448 && nr <= 256;
 }
 
-static int launch_conv_window(const void* x, const void* w, const float* bias, const float* bias_b, int bias_b_stride, int act, const void* add,
+static int launch_conv_window(const void* x, const uint8_t* wimg, const float* bias, const float* bias_b, int bias_b_stride, int act, const void* add,
                               void* out, double* stats, int B, int T, int W, cudaStream_t stream) {
-  static uint8_t* scratch[64] = {nullptr};
-  int dev = 0;
-  DDIMB_CUDA(cudaGetDevice(&dev));
-  DDIMB_CHECK_ARG(dev >= 0 && dev < 64);
-  if (!scratch[dev]) DDIMB_CUDA(cudaMalloc(&scratch[dev], 9 * kWinChunks * kWinBStage));
-  win_swizzle_weights_kernel<<<9 * kWinChunks, 256, 0, stream>>>(reinterpret_cast<const __nv_bfloat16*>(w), scratch[dev]);
-  DDIMB_LAUNCH_CHECK();
   WinParams p;
   memset(&p, 0, sizeof(p));
   p.B = B; p.T = T; p.W = W; p.WP = W + 2;
   const int smem = win_smem_bytes(W, &p.NR, &p.plane_bytes);
   p.units_per_b = ceil_div(T * p.WP, kWinUnit);
   p.num_units = B * p.units_per_b;
-  p.wswz = scratch[dev];
+  p.wswz = wimg;
   p.out = reinterpret_cast<__nv_bfloat16*>(out); p.add = reinterpret_cast<const __nv_bfloat16*>(add);
   p.bias = bias; p.bias_b = bias_b; p.stats = stats; p.bias_b_stride = bias_b_stride; p.act = act;
   CUtensorMap tmA;
@@ -247,16 +324,10 @@ static int launch_conv_window(const void* x, const void* w, const float* bias, c
 }
 
 // ------------------------------------------------------------------------------------------------ conv_out on the tensor cores
-// csrc/conv_out_tc.cuh; called by ddimb_conv_out (conv_boundary.cu) when F is a multiple of 128.  w is the fp32 parameter
-// [2][32][3][3]; its bf16 hi/lo tile image is rebuilt into a per-device scratch buffer ahead of every launch.
-int ddimb_conv_out_tc(const void* x, const void* skip, const float* w, const float* bias, float* out, int B, int T, int F, cudaStream_t stream) {
-  static uint8_t* scratch[64] = {nullptr};
-  int dev = 0;
-  DDIMB_CUDA(cudaGetDevice(&dev));
-  DDIMB_CHECK_ARG(dev >= 0 && dev < 64 && F % 128 == 0);
-  if (!scratch[dev]) DDIMB_CUDA(cudaMalloc(&scratch[dev], kCoWBytes));
-  co_weight_image_kernel<<<1, 256, 0, stream>>>(w, scratch[dev]);
-  DDIMB_LAUNCH_CHECK();
+// csrc/conv_out_tc.cuh; called by ddimb_conv_out (conv_boundary.cu) when F is a multiple of 128.  wimg: the bf16 hi/lo tile image
+// of the fp32 parameter [2][32][3][3] (ddimb_conv_wimg, kind 4).
+int ddimb_conv_out_tc(const void* x, const void* skip, const uint8_t* wimg, const float* bias, float* out, int B, int T, int F, cudaStream_t stream) {
+  DDIMB_CHECK_ARG(F % 128 == 0 && wimg != nullptr);
   CoParams p;
   memset(&p, 0, sizeof(p));
   p.B = B; p.T = T; p.W = F;
@@ -264,7 +335,7 @@ int ddimb_conv_out_tc(const void* x, const void* skip, const float* w, const flo
   while (rt > 8 && (long long)B * (F / 128) * ceil_div(T, rt) < 4LL * ddimb_num_sms()) rt /= 2;
   p.RT = rt; p.units_t = ceil_div(T, rt); p.num_units = B * (F / 128) * p.units_t;
   p.planes = skip ? 2 : 1;
-  p.wimg = scratch[dev]; p.bias = bias; p.out = out;
+  p.wimg = wimg; p.bias = bias; p.out = out;
   CUtensorMap tmX, tmS;
   uint64_t dims[4] = {32, (uint64_t)F, (uint64_t)T, (uint64_t)B};
   uint64_t str[3] = {32, (uint64_t)F * 32, (uint64_t)T * F * 32};
@@ -282,24 +353,17 @@ int ddimb_conv_out_tc(const void* x, const void* skip, const float* w, const flo
 }
 
 // ------------------------------------------------------------------------------------------------ conv_in on the tensor cores
-// csrc/conv_in_tc.cuh; called by ddimb_conv_in (conv_boundary.cu) when F is a multiple of 128.  w is the fp32 parameter
-// [32][2][3][3]; its bf16 [hi | hi | lo] tile image is rebuilt into a per-device scratch buffer ahead of every launch.
-int ddimb_conv_in_tc(const float* x, const float* w, const float* bias, void* out, double* stats, int B, int T, int F, cudaStream_t stream) {
-  static uint8_t* scratch[64] = {nullptr};
-  int dev = 0;
-  DDIMB_CUDA(cudaGetDevice(&dev));
-  DDIMB_CHECK_ARG(dev >= 0 && dev < 64 && F % 128 == 0);
-  if (!scratch[dev]) DDIMB_CUDA(cudaMalloc(&scratch[dev], kCiWBytes));
-  ci_weight_image_kernel<<<1, 256, 0, stream>>>(w, scratch[dev]);
-  DDIMB_LAUNCH_CHECK();
+// csrc/conv_in_tc.cuh; called by ddimb_conv_in (conv_boundary.cu) when F is a multiple of 128.  wimg: the bf16 [hi | hi | lo] tile
+// image of the fp32 parameter [32][2][3][3] (ddimb_conv_wimg, kind 3).
+int ddimb_conv_in_tc(const float* x, const uint8_t* wimg, const float* bias, void* out, double* stats, int B, int T, int F, cudaStream_t stream) {
+  DDIMB_CHECK_ARG(F % 128 == 0 && wimg != nullptr);
   CiParams p;
   memset(&p, 0, sizeof(p));
   p.B = B; p.T = T; p.W = F;
   int rt = kCiStripRows;
   while (rt > 8 && (long long)B * (F / 128) * ceil_div(T, rt) < 4LL * ddimb_num_sms()) rt /= 2;
   p.RT = rt; p.units_t = ceil_div(T, rt); p.num_units = B * (F / 128) * p.units_t;
-  if (const char* e = getenv("DDIMB_CI_DBG")) p.dbg = atoi(e);
-  p.x = x; p.wimg = scratch[dev]; p.bias = bias; p.out = reinterpret_cast<__nv_bfloat16*>(out); p.stats = stats;
+  p.x = x; p.wimg = wimg; p.bias = bias; p.out = reinterpret_cast<__nv_bfloat16*>(out); p.stats = stats;
   static bool attr = false;
   if (!attr) { DDIMB_CUDA(cudaFuncSetAttribute(conv_in_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kCiSmem)); attr = true; }
   const int grid = p.num_units < ddimb_num_sms() ? p.num_units : ddimb_num_sms();
@@ -308,12 +372,79 @@ int ddimb_conv_in_tc(const float* x, const float* w, const float* bias, void* ou
   return DDIMB_OK;
 }
 
+// ------------------------------------------------------------------------------------------------ kernel-ready weight images
+// Every convolution reads its weights from a CALLER-OWNED device buffer holding the weight tiles in the exact shared-memory
+// (swizzled) layout of the kernel that runs for (kind, Cin, Cout, W): the library owns no device memory and re-lays nothing out per
+// call.  kind: 0 Conv2d 3x3 (w bf16 [Cout][9*Cin]), 1 Conv2d 4x4 s2 (w bf16 [Cout][16*Cin]), 2 ConvTranspose2d 4x4 s2 (w bf16
+// [16*Cout][Cin]), 3 conv_in (w fp32 [32][2][3][3]), 4 conv_out (w fp32 [2][32][3][3]).  W = width of the op's INPUT.
+static bool conv_window_supported(int Cin, int Cout, int W);
+static bool conv_down_wide_supported(int Cin, int Cout, int W);
+static bool conv_up_wide_supported(int Cin, int Cout, int W);
+static int win_smem_bytes(int W, int* nr, int* plane);
+
+extern "C" long long ddimb_conv_wimg_bytes(int kind, int Cin, int Cout, int W) {
+  if (Cin < 1 || Cout < 1 || W < 1) return -1;
+  switch (kind) {
+    case 0:
+      if (Cin % 32 || Cout % 32 || Cin > 256 || Cout > 256) return -1;
+      if (ddimb_conv3x3_wide_supported(Cin, Cout, W)) return 0;          // nine tiles, loaded once per CTA straight from w
+      if (conv_window_supported(Cin, Cout, W)) return 9LL * kWinChunks * kWinBStage;
+      return 9LL * Cin * Cout * 2;
+    case 1:
+      if (Cin % 32 || Cout % 32 || Cin > 256 || Cout > 256) return -1;
+      return conv_down_wide_supported(Cin, Cout, W) ? (long long)kDwWBytes : 16LL * Cin * Cout * 2;
+    case 2:
+      if (Cin % 32 || Cout % 32 || Cin > 256 || Cout > 256) return -1;
+      return conv_up_wide_supported(Cin, Cout, W) ? (long long)kUwWBytes : 16LL * Cin * Cout * 2;
+    case 3: return (Cin == 2 && Cout == 32) ? (W % 128 == 0 ? (long long)kCiWBytes : 0) : -1;
+    case 4: return (Cin == 32 && Cout == 2) ? (W % 128 == 0 ? (long long)kCoWBytes : 0) : -1;
+    default: return -1;
+  }
+}
+
+extern "C" int ddimb_conv_wimg(int kind, const void* w, void* wimg, int Cin, int Cout, int W, cudaStream_t stream) {
+  const long long nbytes = ddimb_conv_wimg_bytes(kind, Cin, Cout, W);
+  DDIMB_CHECK_ARG(nbytes >= 0 && w != nullptr);
+  if (nbytes == 0) return DDIMB_OK;
+  DDIMB_CHECK_ARG(wimg != nullptr && (reinterpret_cast<uintptr_t>(wimg) & 15) == 0);
+  uint8_t* img = reinterpret_cast<uint8_t*>(wimg);
+  const __nv_bfloat16* wb = reinterpret_cast<const __nv_bfloat16*>(w);
+  if (kind == 3) { ci_weight_image_kernel<<<1, 256, 0, stream>>>(reinterpret_cast<const float*>(w), img); DDIMB_LAUNCH_CHECK(); return DDIMB_OK; }
+  if (kind == 4) { co_weight_image_kernel<<<1, 256, 0, stream>>>(reinterpret_cast<const float*>(w), img); DDIMB_LAUNCH_CHECK(); return DDIMB_OK; }
+  GemmParams p;
+  init_params(p);
+  if (kind == 0) {
+    if (conv_window_supported(Cin, Cout, W)) { win_swizzle_weights_kernel<<<9 * kWinChunks, 256, 0, stream>>>(wb, img); DDIMB_LAUNCH_CHECK(); return DDIMB_OK; }
+    const int ck = pick_ck(Cin);
+    conv3x3_taps(p, Cin, Cout, ck);
+    return build_generic_wimg(p, w, img, ck, 9 * Cin, 0, assign_img_blocks(p, 0), stream);
+  }
+  if (kind == 1) {
+    if (conv_down_wide_supported(Cin, Cout, W)) { dw_weight_image_kernel<<<4, 256, 0, stream>>>(wb, img); DDIMB_LAUNCH_CHECK(); return DDIMB_OK; }
+    const int ck = pick_ck(Cin);
+    down_taps(p, Cin, Cout, ck);
+    return build_generic_wimg(p, w, img, ck, 16 * Cin, 0, assign_img_blocks(p, 0), stream);
+  }
+  if (conv_up_wide_supported(Cin, Cout, W)) { uw_weight_image_kernel<<<3, 256, 0, stream>>>(wb, img); DDIMB_LAUNCH_CHECK(); return DDIMB_OK; }
+  const int ck = pick_ck(Cin);
+  int first = 0;
+  for (int r = 0; r < 2; ++r) {
+    up_taps(p, r, Cin, Cout, ck);
+    const int next = assign_img_blocks(p, first);
+    int rc = build_generic_wimg(p, w, img, ck, Cin, first, next, stream);
+    if (rc) return rc;
+    first = next;
+  }
+  return DDIMB_OK;
+}
+
 // ------------------------------------------------------------------------------------------------ Conv2d 3x3 s1 p1
 // reference: models/diffusion.py:28-40 (Residual_Block.conv), evaluated on NHWC bf16.
-extern "C" int ddimb_conv3x3(const void* x, const void* w, const float* bias, const float* bias_b, int bias_b_stride, int act,
+extern "C" int ddimb_conv3x3(const void* x, const void* w, const void* wimg, const float* bias, const float* bias_b, int bias_b_stride, int act,
                              const void* add, void* out, double* stats, int B, int T, int W, int Cin, int Cout,
                              cudaStream_t stream) {
   DDIMB_CHECK_ARG(x && w && out && B >= 1 && T >= 1);
+  DDIMB_CHECK_ARG(wimg != nullptr || ddimb_conv_wimg_bytes(0, Cin, Cout, W) == 0);
   const double npos = (double)B * T * W;
   DDIMB_PROF(stream, "conv3x3", Cin, W, npos * (Cin + Cout + (add ? Cout : 0)) * 2 + 18.0 * Cin * Cout, 18.0 * Cin * Cout * npos);
   DDIMB_CHECK_ARG(W >= 8 && W <= 256 && (W & (W - 1)) == 0);
@@ -321,7 +452,7 @@ extern "C" int ddimb_conv3x3(const void* x, const void* w, const float* bias, co
   if (ddimb_conv3x3_wide_supported(Cin, Cout, W))
     return launch_conv_wide(x, nullptr, nullptr, nullptr, 0.f, 0, w, bias, bias_b, bias_b_stride, act, add, out, stats, B, T, W, Cin, stream);
   if (conv_window_supported(Cin, Cout, W))
-    return launch_conv_window(x, w, bias, bias_b, bias_b_stride, act, add, out, stats, B, T, W, stream);
+    return launch_conv_window(x, reinterpret_cast<const uint8_t*>(wimg), bias, bias_b, bias_b_stride, act, add, out, stats, B, T, W, stream);
   const int ck = pick_ck(Cin);
   int bw, bt;
   spatial_tile(T, W, &bw, &bt);
@@ -344,15 +475,10 @@ extern "C" int ddimb_conv3x3(const void* x, const void* w, const float* bias, co
   init_params(p);
   p.box[0] = bw; p.box[1] = bt;
   p.ntile[0] = ceil_div(W, bw); p.ntile[1] = ceil_div(T, bt); p.ntile[3] = B;
-  p.n_seg = Cout; p.n_acc = Cout; p.a_batched = 1;
-  p.ntaps = 9;
-  for (int ky = 0; ky < 3; ++ky)
-    for (int kx = 0; kx < 3; ++kx) {
-      TapDesc& tp = p.taps[ky * 3 + kx];
-      tp.da[0] = (int16_t)(kx - 1); tp.da[1] = (int16_t)(ky - 1); tp.da[2] = 0; tp.da[3] = 0;
-      tp.a_c0 = 0; tp.b_k0 = (ky * 3 + kx) * Cin; tp.b_n0 = 0;
-      tp.nchunk = (int16_t)(Cin / ck); tp.nseg = 1; tp.tmem_col0 = 0;
-    }
+  p.a_batched = 1;
+  conv3x3_taps(p, Cin, Cout, ck);
+  assign_img_blocks(p, 0);
+  p.b_img = reinterpret_cast<const uint8_t*>(wimg);
   p.out = out; p.add = reinterpret_cast<const __nv_bfloat16*>(add); p.bias = bias; p.bias_b = bias_b; p.stats = stats;
   p.out_stride[0] = Cout; p.out_stride[1] = (int64_t)W * Cout; p.out_stride[3] = (int64_t)T * W * Cout;
   p.out_dim[0] = W; p.out_dim[1] = T; p.out_dim[3] = B;
@@ -367,20 +493,13 @@ extern "C" int ddimb_conv3x3(const void* x, const void* w, const float* bias, co
 }
 
 // ------------------------------------------------------------------------------------------------ wide Downsample (32 -> 64)
-// csrc/conv_down_wide.cuh; w keeps the ABI layout, its swizzled tile image is rebuilt per call into a per-device scratch buffer.
-static bool conv_down_wide_supported(int Cin, int Cout, int T, int W) {
+// csrc/conv_down_wide.cuh; weights come from the caller's swizzled tile image (ddimb_conv_wimg, kind 1).
+static bool conv_down_wide_supported(int Cin, int Cout, int W) {
   static const bool off = getenv("DDIMB_NO_DOWN_WIDE") != nullptr;
-  return !off && Cin == kDwCin && Cout == kDwCout && T % 2 == 0 && W % 256 == 0;
+  return !off && Cin == kDwCin && Cout == kDwCout && W % 256 == 0;
 }
 
-static int launch_conv_down_wide(const void* x, const void* w, const float* bias, void* out, double* stats, int B, int T, int W, cudaStream_t stream) {
-  static uint8_t* scratch[64] = {nullptr};
-  int dev = 0;
-  DDIMB_CUDA(cudaGetDevice(&dev));
-  DDIMB_CHECK_ARG(dev >= 0 && dev < 64);
-  if (!scratch[dev]) DDIMB_CUDA(cudaMalloc(&scratch[dev], kDwWBytes));
-  dw_weight_image_kernel<<<4, 256, 0, stream>>>(reinterpret_cast<const __nv_bfloat16*>(w), scratch[dev]);
-  DDIMB_LAUNCH_CHECK();
+static int launch_conv_down_wide(const void* x, const uint8_t* wimg, const float* bias, void* out, double* stats, int B, int T, int W, cudaStream_t stream) {
   DwParams p;
   memset(&p, 0, sizeof(p));
   p.B = B; p.T = T; p.W = W;
@@ -388,7 +507,7 @@ static int launch_conv_down_wide(const void* x, const void* w, const float* bias
   int rt = 64;
   while (rt > 8 && (long long)B * strips * ceil_div(To, rt) < 4LL * ddimb_num_sms()) rt /= 2;
   p.RT = rt; p.units_t = ceil_div(To, rt); p.num_units = B * strips * p.units_t;
-  p.wimg = scratch[dev]; p.bias = bias; p.out = reinterpret_cast<__nv_bfloat16*>(out); p.stats = stats;
+  p.wimg = wimg; p.bias = bias; p.out = reinterpret_cast<__nv_bfloat16*>(out); p.stats = stats;
   CUtensorMap tmA;
   {
     uint64_t dims[4] = {64, (uint64_t)W / 2, (uint64_t)T, (uint64_t)B};
@@ -409,14 +528,14 @@ static int launch_conv_down_wide(const void* x, const void* w, const float* bias
 // reference: models/diffusion.py:70-78 (Downsample).  The NHWC input is viewed space-to-depth as
 // (2*Cin, W/2, 2, T/2, B): kernel column kx in {1,2} is one contiguous 2*Cin slab of column pair f', kx=0 / kx=3 are
 // the upper / lower half of the neighbouring pairs; kernel row ky picks (pair row t'+dy, sub-row r).
-extern "C" int ddimb_conv_down4x4(const void* x, const void* w, const float* bias, void* out, double* stats, int B, int T, int W,
+extern "C" int ddimb_conv_down4x4(const void* x, const void* w, const void* wimg, const float* bias, void* out, double* stats, int B, int T, int W,
                                   int Cin, int Cout, cudaStream_t stream) {
-  DDIMB_CHECK_ARG(x && w && out && B >= 1 && T >= 2 && T % 2 == 0);
+  DDIMB_CHECK_ARG(x && w && wimg && out && B >= 1 && T >= 2 && T % 2 == 0);
   const double npos = (double)B * (T / 2) * (W / 2);
   DDIMB_PROF(stream, "conv_down4x4", Cin, W, npos * (4.0 * Cin + Cout) * 2 + 32.0 * Cin * Cout, 32.0 * Cin * Cout * npos);
   DDIMB_CHECK_ARG(W >= 16 && W <= 256 && (W & (W - 1)) == 0);
   DDIMB_CHECK_ARG(Cin % 32 == 0 && Cout % 32 == 0 && Cout <= 256 && Cin <= 256);
-  if (conv_down_wide_supported(Cin, Cout, T, W)) return launch_conv_down_wide(x, w, bias, out, stats, B, T, W, stream);
+  if (conv_down_wide_supported(Cin, Cout, W)) return launch_conv_down_wide(x, reinterpret_cast<const uint8_t*>(wimg), bias, out, stats, B, T, W, stream);
   const int ck = pick_ck(Cin);
   const int To = T / 2, Wo = W / 2;
   int bw, bt;
@@ -440,20 +559,10 @@ extern "C" int ddimb_conv_down4x4(const void* x, const void* w, const float* bia
   init_params(p);
   p.box[0] = bw; p.box[2] = bt;
   p.ntile[0] = ceil_div(Wo, bw); p.ntile[2] = ceil_div(To, bt); p.ntile[3] = B;
-  p.n_seg = Cout; p.n_acc = Cout; p.a_batched = 1;
-  static const int kDy[4] = {-1, 0, 0, 1}, kR[4] = {1, 0, 1, 0};
-  int nt = 0;
-  for (int ky = 0; ky < 4; ++ky) {
-    // (dx, first channel of the pair slab, kernel column of the first Cin block, number of Cin blocks)
-    const int grp[3][4] = {{0, 0, 1, 2}, {-1, Cin, 0, 1}, {1, 0, 3, 1}};
-    for (int g = 0; g < 3; ++g) {
-      TapDesc& tp = p.taps[nt++];
-      tp.da[0] = (int16_t)grp[g][0]; tp.da[1] = (int16_t)kR[ky]; tp.da[2] = (int16_t)kDy[ky]; tp.da[3] = 0;
-      tp.a_c0 = grp[g][1]; tp.b_k0 = (ky * 4 + grp[g][2]) * Cin; tp.b_n0 = 0;
-      tp.nchunk = (int16_t)(grp[g][3] * Cin / ck); tp.nseg = 1; tp.tmem_col0 = 0;
-    }
-  }
-  p.ntaps = nt;
+  p.a_batched = 1;
+  down_taps(p, Cin, Cout, ck);
+  assign_img_blocks(p, 0);
+  p.b_img = reinterpret_cast<const uint8_t*>(wimg);
   p.out = out; p.bias = bias; p.stats = stats;
   p.out_stride[0] = Cout; p.out_stride[2] = (int64_t)Wo * Cout; p.out_stride[3] = (int64_t)To * Wo * Cout;
   p.out_dim[0] = Wo; p.out_dim[2] = To; p.out_dim[3] = B;
@@ -468,21 +577,14 @@ extern "C" int ddimb_conv_down4x4(const void* x, const void* w, const float* bia
 }
 
 // ------------------------------------------------------------------------------------------------ wide Upsample (64 -> 32)
-// csrc/conv_up_wide.cuh; w keeps the ABI layout, its swizzled tile image is rebuilt per call into a per-device scratch buffer.
+// csrc/conv_up_wide.cuh; weights come from the caller's swizzled tile image (ddimb_conv_wimg, kind 2).
 static bool conv_up_wide_supported(int Cin, int Cout, int W) {
   static const bool off = getenv("DDIMB_NO_UP_WIDE") != nullptr;
   return !off && Cin == kUwCin && Cout == kUwCout && W % 128 == 0;
 }
 
-static int launch_conv_up_wide(const void* x, const void* w, const float* bias, const void* skip, void* out, double* stats, int B, int T, int W,
+static int launch_conv_up_wide(const void* x, const uint8_t* wimg, const float* bias, const void* skip, void* out, double* stats, int B, int T, int W,
                                cudaStream_t stream) {
-  static uint8_t* scratch[64] = {nullptr};
-  int dev = 0;
-  DDIMB_CUDA(cudaGetDevice(&dev));
-  DDIMB_CHECK_ARG(dev >= 0 && dev < 64);
-  if (!scratch[dev]) DDIMB_CUDA(cudaMalloc(&scratch[dev], kUwWBytes));
-  uw_weight_image_kernel<<<3, 256, 0, stream>>>(reinterpret_cast<const __nv_bfloat16*>(w), scratch[dev]);
-  DDIMB_LAUNCH_CHECK();
   UwParams p;
   memset(&p, 0, sizeof(p));
   p.B = B; p.T = T; p.W = W;
@@ -490,7 +592,7 @@ static int launch_conv_up_wide(const void* x, const void* w, const float* bias, 
   int rt = 32;
   while (rt > 4 && (long long)B * strips * ceil_div(T, rt) < 4LL * ddimb_num_sms()) rt /= 2;
   p.RT = rt; p.units_t = ceil_div(T, rt); p.num_units = B * strips * p.units_t;
-  p.wimg = scratch[dev]; p.bias = bias; p.skip = reinterpret_cast<const __nv_bfloat16*>(skip);
+  p.wimg = wimg; p.bias = bias; p.skip = reinterpret_cast<const __nv_bfloat16*>(skip);
   p.out = reinterpret_cast<__nv_bfloat16*>(out); p.stats = stats;
   CUtensorMap tmA;
   {
@@ -513,14 +615,14 @@ static int launch_conv_up_wide(const void* x, const void* w, const float* bias, 
 // Output row parity r is one launch: out[2t'+r, 2f'+s, co] = sum over (dy, dx) of in[t'+dy, f'+dx, :] . Wt[:, co, ky, kx],
 // ky = r + 1 - 2 dy, kx = s + 1 - 2 dx; accumulator columns are [s][co], i.e. the 2*Cout contiguous outputs of pixel pair f'.
 // Weight operand: w[(ky*4 + kx) * Cout + co][ci] (K-major rows).
-extern "C" int ddimb_conv_up4x4(const void* x, const void* w, const float* bias, const void* skip, void* out, double* stats, int B,
+extern "C" int ddimb_conv_up4x4(const void* x, const void* w, const void* wimg, const float* bias, const void* skip, void* out, double* stats, int B,
                                 int T, int W, int Cin, int Cout, cudaStream_t stream) {
-  DDIMB_CHECK_ARG(x && w && out && B >= 1 && T >= 1);
+  DDIMB_CHECK_ARG(x && w && wimg && out && B >= 1 && T >= 1);
   const double npos = (double)B * T * W;
   DDIMB_PROF(stream, "conv_up4x4", Cin, W, npos * (Cin + 4.0 * Cout * (skip ? 2 : 1)) * 2 + 32.0 * Cin * Cout, 32.0 * Cin * Cout * npos);
   DDIMB_CHECK_ARG(W >= 8 && W <= 128 && (W & (W - 1)) == 0);
   DDIMB_CHECK_ARG(Cin % 32 == 0 && Cout % 32 == 0 && Cout <= 256 && Cin <= 256);
-  if (conv_up_wide_supported(Cin, Cout, W)) return launch_conv_up_wide(x, w, bias, skip, out, stats, B, T, W, stream);
+  if (conv_up_wide_supported(Cin, Cout, W)) return launch_conv_up_wide(x, reinterpret_cast<const uint8_t*>(wimg), bias, skip, out, stats, B, T, W, stream);
   const int ck = pick_ck(Cin);
   int bw, bt;
   spatial_tile(T, W, &bw, &bt);
@@ -540,28 +642,16 @@ extern "C" int ddimb_conv_up4x4(const void* x, const void* w, const float* bias,
     if (r) return r;
   }
   const int To = 2 * T, Wo = 2 * W;
+  int img_next = 0;
   for (int r = 0; r < 2; ++r) {
     GemmParams p;
     init_params(p);
     p.box[0] = bw; p.box[1] = bt;
     p.ntile[0] = ceil_div(W, bw); p.ntile[1] = ceil_div(T, bt); p.ntile[3] = B;
-    p.n_seg = Cout; p.n_acc = 2 * Cout; p.a_batched = 1;
-    int nt = 0;
-    const int dys[2] = {0, r == 0 ? -1 : 1};
-    for (int iy = 0; iy < 2; ++iy) {
-      const int dy = dys[iy], ky = r + 1 - 2 * dy;
-      const int dxs[3] = {0, -1, 1};   // dx = 0 first: it writes both column halves
-      for (int ix = 0; ix < 3; ++ix) {
-        const int dx = dxs[ix];
-        TapDesc& tp = p.taps[nt++];
-        tp.da[0] = (int16_t)dx; tp.da[1] = (int16_t)dy; tp.da[2] = 0; tp.da[3] = 0;
-        tp.a_c0 = 0; tp.b_k0 = 0; tp.nchunk = (int16_t)(Cin / ck);
-        if (dx == 0) { tp.nseg = 2; tp.b_n0 = (ky * 4 + 1) * Cout; tp.tmem_col0 = 0; }        // s=0 -> kx=1, s=1 -> kx=2
-        else if (dx < 0) { tp.nseg = 1; tp.b_n0 = (ky * 4 + 3) * Cout; tp.tmem_col0 = 0; }    // s=0, kx=3
-        else { tp.nseg = 1; tp.b_n0 = (ky * 4 + 0) * Cout; tp.tmem_col0 = Cout; }             // s=1, kx=0
-      }
-    }
-    p.ntaps = nt;
+    p.a_batched = 1;
+    up_taps(p, r, Cin, Cout, ck);
+    img_next = assign_img_blocks(p, img_next);
+    p.b_img = reinterpret_cast<const uint8_t*>(wimg);
     p.out = out; p.add = reinterpret_cast<const __nv_bfloat16*>(skip); p.bias = bias; p.stats = stats;
     p.out_stride[0] = 2 * Cout; p.out_stride[1] = (int64_t)2 * Wo * Cout; p.out_stride[3] = (int64_t)To * Wo * Cout;
     p.out_base = (int64_t)r * Wo * Cout;

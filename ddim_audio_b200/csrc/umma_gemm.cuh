@@ -27,6 +27,8 @@ struct TapDesc {
   int16_t nchunk;     // K chunks of CK elements
   int16_t nseg;       // N segments (each n_seg wide: one UMMA + one B box per segment)
   int32_t tmem_col0;  // accumulator column of segment 0
+  int32_t img_blk;    // first block of this tap in the pre-swizzled weight image (block = one (chunk, segment) B tile)
+  int32_t first_mask; // bit sg: this tap is the first writer of accumulator segment sg's columns in a tile (launch_gemm fills it)
 };
 
 struct GemmParams {
@@ -64,6 +66,8 @@ struct GemmParams {
   int32_t out_f32;          // 1: out is fp32
   // ---- convolution epilogue through TMA (tmO / tmS: 4-D maps {accumulator column, w, t, batch} of out / add)
   int32_t epi_tdim;         // which tile dim (1 or 2) is the row-like one
+  // ---- B operand from a pre-swizzled weight image (1-D bulk copies: no per-box-row TMA cost) instead of tmB
+  const uint8_t* b_img;     // blocks of n_seg rows x CK k in the shared-memory (swizzled) layout, in consumption order
 };
 
 template <int CK>
@@ -518,9 +522,18 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
               const int ch = ch0 + i;
               tma_load_5d(sa + i * GemmSmem<CK>::kABytes, &tmA, bar_full + 8 * stage, tp.a_c0 + ch * CK, c1 + tp.da[0], c2 + tp.da[1], c3 + tp.da[2],
                           c4 + tp.da[3]);
-              for (int sg = 0; sg < tp.nseg; ++sg)
-                tma_load_3d(sb + i * b_chunk_bytes + sg * p.n_seg * CK * 2, &tmB, bar_full + 8 * stage, tp.b_k0 + ch * CK,
-                            nt * p.n_tile_stride + tp.b_n0 + sg * p.n_seg, bb);
+              if (p.b_img != nullptr) {
+                // ncu r02: a TMA box costs ~3.5 cycles per ROW whatever its width; with 18-36 weight boxes of Cout rows per tile the
+                // TMA engine, not the tensor pipe, bounded every convolution at C >= 128.  The image is contiguous per block.
+                const uint32_t seg_bytes = (uint32_t)(p.n_seg * CK * 2);
+                for (int sg = 0; sg < tp.nseg; ++sg)
+                  bulk_load_g2s(sb + i * b_chunk_bytes + sg * seg_bytes, p.b_img + (int64_t)(tp.img_blk + ch * tp.nseg + sg) * seg_bytes, seg_bytes,
+                                bar_full + 8 * stage);
+              } else {
+                for (int sg = 0; sg < tp.nseg; ++sg)
+                  tma_load_3d(sb + i * b_chunk_bytes + sg * p.n_seg * CK * 2, &tmB, bar_full + 8 * stage, tp.b_k0 + ch * CK,
+                              nt * p.n_tile_stride + tp.b_n0 + sg * p.n_seg, bb);
+              }
             }
             if (++stage == p.num_stages) { stage = 0; phase ^= 1; }
           }
@@ -529,42 +542,47 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     }
   } else if (warp == 1) {
     // ================================================================ MMA issuer (one elected thread: common.cuh elect_one)
+    // ncu r02: this single thread, not the tensor pipe, bounded the convolutions at C >= 128 (~140 instructions per 4-MMA chunk,
+    // among them an integer division for the "first write" test).  Which tap writes an accumulator segment first is a static
+    // property of the tap program (TapDesc::first_mask); descriptors are built from one constant high word plus 14-bit offsets.
     if (elect_one()) {
       const uint32_t idesc = make_idesc_bf16(kTileM, (uint32_t)p.n_seg);
+      const uint64_t desc_hi = make_kmajor_desc(0, GemmSmem<CK>::kSBO, GemmSmem<CK>::kSwizzle);
+      const int ntaps = p.ntaps, kps = p.kps, nstages = p.num_stages, nbufs = p.num_acc_bufs, n_acc = p.n_acc;
+      const uint32_t seg16 = (uint32_t)(p.n_seg * CK * 2) >> 4, bch16 = (uint32_t)b_chunk_bytes >> 4;
+      const uint32_t n_seg = (uint32_t)p.n_seg;
       int stage = 0;
       uint32_t phase = 0;
       int local = 0;
       for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++local) {
-        const int buf = local % p.num_acc_bufs;
-        const uint32_t use = (uint32_t)(local / p.num_acc_bufs);
+        const int buf = local % nbufs;
+        const uint32_t use = (uint32_t)(local / nbufs);
         mbar_wait(bar_tempty + 8 * buf, (use & 1) ^ 1, 2);
         tc_fence_after();
-        const uint32_t acc0 = tmem_base + (uint32_t)(buf * p.n_acc);
-        uint32_t written = 0;
-        for (int t = 0; t < p.ntaps; ++t) {
-          const TapDesc& tp = p.taps[t];
-          for (int ch0 = 0; ch0 < tp.nchunk; ch0 += p.kps) {
-            const int nch = min(p.kps, tp.nchunk - ch0);
+        const uint32_t acc0 = tmem_base + (uint32_t)(buf * n_acc);
+        for (int t = 0; t < ntaps; ++t) {
+          const int nchunk = p.taps[t].nchunk, nseg = p.taps[t].nseg;
+          const uint32_t col0 = acc0 + (uint32_t)p.taps[t].tmem_col0;
+          uint32_t first = (uint32_t)p.taps[t].first_mask;     // consumed by the tap's first chunk only
+          for (int ch0 = 0; ch0 < nchunk; ch0 += kps) {
+            const int nch = min(kps, nchunk - ch0);
             mbar_wait(bar_full + 8 * stage, phase, 3);
             tc_fence_after();
             const uint32_t sa = smem_base + stage * stage_bytes;
-            const uint32_t sb = sa + p.kps * GemmSmem<CK>::kABytes;
-            for (int i = 0; i < nch; ++i) {
-              const uint64_t adesc = make_kmajor_desc(sa + i * GemmSmem<CK>::kABytes, GemmSmem<CK>::kSBO, GemmSmem<CK>::kSwizzle);
-              for (int sg = 0; sg < tp.nseg; ++sg) {
-                const int col = tp.tmem_col0 + sg * p.n_seg;
-                const uint32_t bit = 1u << (col / p.n_seg);
-                const uint64_t bdesc = make_kmajor_desc(sb + i * b_chunk_bytes + sg * p.n_seg * CK * 2, GemmSmem<CK>::kSBO, GemmSmem<CK>::kSwizzle);
+            uint32_t a_lo = (sa & 0x3FFFFu) >> 4;
+            uint32_t b_lo0 = ((sa + kps * GemmSmem<CK>::kABytes) & 0x3FFFFu) >> 4;
+            for (int i = 0; i < nch; ++i, a_lo += (uint32_t)GemmSmem<CK>::kABytes >> 4, b_lo0 += bch16) {
+              uint32_t b_lo = b_lo0, col = col0;
+              for (int sg = 0; sg < nseg; ++sg, b_lo += seg16, col += n_seg) {
+                const uint32_t acc_first = ((first >> sg) & 1u) ^ 1u;
 #pragma unroll
-                for (int k = 0; k < CK / 16; ++k) {
-                  // +32 bytes along K inside the swizzle atom == +2 in the (addr >> 4) start-address field
-                  umma_bf16(acc0 + (uint32_t)col, adesc + 2 * k, bdesc + 2 * k, idesc, ((written & bit) != 0u) | (k > 0));
-                }
-                written |= bit;
+                for (int k = 0; k < CK / 16; ++k)   // +32 bytes along K inside the swizzle atom == +2 in the (addr >> 4) start-address field
+                  umma_bf16(col, desc_hi | (uint64_t)(a_lo + 2 * k), desc_hi | (uint64_t)(b_lo + 2 * k), idesc, k > 0 ? 1u : acc_first);
               }
+              first = 0u;
             }
             umma_commit(bar_empty + 8 * stage);   // smem slot is free once these MMAs have read it
-            if (++stage == p.num_stages) { stage = 0; phase ^= 1; }
+            if (++stage == nstages) { stage = 0; phase ^= 1; }
           }
         }
         umma_commit(bar_tfull + 8 * buf);         // accumulator complete
@@ -684,6 +702,28 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc(tmem_base, (uint32_t)p.tmem_cols);
+  }
+}
+
+// K-major bf16 weight w[row][ldw] -> the blocks of GemmParams' taps in consumption order, each block = n_seg rows x CK k in the
+// shared-memory image a TMA load of that box would produce (16-byte chunk j of row r at slot j ^ swizzle phase(r)).
+struct WimgParams {
+  int32_t ntaps, n_seg, ck, ldw, nblocks;
+  TapDesc taps[kMaxTaps];
+};
+__global__ void __launch_bounds__(256) wimg_generic_kernel(const __nv_bfloat16* __restrict__ w, uint8_t* __restrict__ img, const __grid_constant__ WimgParams p) {
+  const int blk = blockIdx.x;
+  int t = 0;
+  while (t + 1 < p.ntaps && p.taps[t + 1].img_blk <= blk) ++t;
+  const TapDesc& tp = p.taps[t];
+  const int rem = blk - tp.img_blk, ch = rem / tp.nseg, sg = rem - ch * tp.nseg;
+  const int cpr = p.ck >> 3;                                  // 16-byte chunks per row
+  uint8_t* dst = img + (int64_t)blk * p.n_seg * p.ck * 2;
+  for (int i = threadIdx.x; i < p.n_seg * cpr; i += blockDim.x) {
+    const int row = i / cpr, j = i - row * cpr;
+    const uint4 v = *reinterpret_cast<const uint4*>(w + (int64_t)(tp.b_n0 + sg * p.n_seg + row) * p.ldw + tp.b_k0 + ch * p.ck + j * 8);
+    const int ph = (p.ck == 64) ? (row & 7) : ((row >> 1) & 3);
+    *reinterpret_cast<uint4*>(dst + row * p.ck * 2 + ((j ^ ph) << 4)) = v;
   }
 }
 

@@ -229,6 +229,8 @@ class Model(nn.Module):
         runs the ConvTranspose kernel on the SAME weight tensor and vice versa."""
         bf = torch.bfloat16
         pk = {"train": train}
+        F0, nl = self.config.f_size, self.levels
+        img = ops.conv_wimg          # kernel-ready (swizzled) tile images, built here once per weight version: include/ddim_b200.h
 
         def c3(w):      # [Co, Ci, 3, 3] -> [Co, (ky*3+kx)*Ci + ci]
             return w.detach().permute(0, 2, 3, 1).reshape(w.shape[0], -1).to(bf).contiguous()
@@ -242,38 +244,52 @@ class Model(nn.Module):
         def as_convT(w):  # [I, O, 4, 4] -> [(ky*4+kx)*O + o, i]    (ddimb_conv_up4x4 operand)
             return w.detach().permute(2, 3, 1, 0).reshape(-1, w.shape[0]).to(bf).contiguous()
 
-        def rb(m, prefix):
+        def rb(m, prefix, W):
+            C = m.channels
             d = dict(g0=m.norm[0].weight, b0=m.norm[0].bias, g1=m.norm[1].weight, b1=m.norm[1].bias, g2=m.norm[2].weight,
-                     w0=c3(m.conv[0].weight), w1=c3(m.conv[1].weight), cb1=m.conv[1].bias, C=m.channels, prefix=prefix)
+                     w0=c3(m.conv[0].weight), w1=c3(m.conv[1].weight), cb1=m.conv[1].bias, C=C, prefix=prefix)
+            d["w0_img"], d["w1_img"] = img(ops.KIND_CONV3X3, d["w0"], C, C, W), img(ops.KIND_CONV3X3, d["w1"], C, C, W)
             if train:
                 d["w0d"], d["w1d"] = c3d(m.conv[0].weight), c3d(m.conv[1].weight)
+                d["w0d_img"], d["w1d_img"] = img(ops.KIND_CONV3X3, d["w0d"], C, C, W), img(ops.KIND_CONV3X3, d["w1d"], C, C, W)
             return d
 
         down = []
         for si, stage in enumerate(list(self.down_modules)[1:], start=1):
             ent = dict(down=None, blocks=[])
+            W = F0 >> (si - 1)                                                       # width of this level
             for mj, m in enumerate(stage):
                 prefix = f"down_modules.{si}.{mj}"
                 if isinstance(m, Downsample):
+                    co, ci = m.conv.weight.shape[:2]
                     ent["down"] = dict(w=as_conv(m.conv.weight), b=m.conv.bias, prefix=prefix)
+                    ent["down"]["w_img"] = img(ops.KIND_DOWN, ent["down"]["w"], ci, co, 2 * W)
                     if train:
-                        ent["down"]["wd"] = as_convT(m.conv.weight)
+                        ent["down"]["wd"] = as_convT(m.conv.weight)                  # data gradient: ConvTranspose co -> ci on the level's width
+                        ent["down"]["wd_img"] = img(ops.KIND_UP, ent["down"]["wd"], co, ci, W)
                 else:
-                    ent["blocks"].append(rb(m, prefix))
+                    ent["blocks"].append(rb(m, prefix, W))
             down.append(ent)
         up = []
         for si, stage in enumerate(list(self.up_modules)[:-1]):
             ent = dict(up=None, blocks=[])
+            W = F0 >> (nl - 1 - si)
             for mj, m in enumerate(stage):
                 prefix = f"up_modules.{si}.{mj}"
                 if isinstance(m, Upsample):
+                    ci, co = m.conv.weight.shape[:2]
                     ent["up"] = dict(w=as_convT(m.conv.weight), b=m.conv.bias, prefix=prefix)
+                    ent["up"]["w_img"] = img(ops.KIND_UP, ent["up"]["w"], ci, co, W)
                     if train:
-                        ent["up"]["wd"] = as_conv(m.conv.weight)
+                        ent["up"]["wd"] = as_conv(m.conv.weight)                     # data gradient: Conv2d 4x4 s2 co -> ci on the doubled width
+                        ent["up"]["wd_img"] = img(ops.KIND_DOWN, ent["up"]["wd"], co, ci, 2 * W)
                 else:
-                    ent["blocks"].append(rb(m, prefix))
+                    ent["blocks"].append(rb(m, prefix, W))
             up.append(ent)
         pk["down"], pk["up"] = down, up
+        cin, cout = self.down_modules[0], self.up_modules[-1]
+        pk["conv_in_img"] = img(ops.KIND_CONV_IN, cin.weight.detach(), cin.weight.shape[1], cin.weight.shape[0], F0)
+        pk["conv_out_img"] = img(ops.KIND_CONV_OUT, cout.weight.detach(), cout.weight.shape[1], cout.weight.shape[0], F0)
         tr = self.transformer
         pk["proj_w"] = tr.embedding.projection.weight.detach().to(bf).contiguous()
         pk["out_w"] = tr.compute_out.weight.detach().to(bf).contiguous()
@@ -287,6 +303,7 @@ class Model(nn.Module):
                 d["w2t"] = l.output.dense.weight.detach().t().to(bf).contiguous()
             w = self.up_modules[-1].weight.detach()                                  # conv_out [2, 32, 3, 3]
             pk["conv_out_wd"] = w.flip(2, 3).permute(1, 0, 2, 3).float().contiguous()  # conv_in-shaped data-gradient kernel
+            pk["conv_out_wd_img"] = img(ops.KIND_CONV_IN, pk["conv_out_wd"], 2, 32, F0)
         return pk
 
     def _packed_for(self, train):
@@ -314,9 +331,9 @@ class Model(nn.Module):
             out = ops.gn_apply(c1, s1, pb["g2"], None, 2, GN_EPS, res=h, stats_out=s2, out=c0)
             return out, s2
         a = ops.gn_apply(h, st_h, pb["g0"], pb["b0"], 1, GN_EPS)                                      # silu(GN0(h))
-        c0 = ops.conv3x3(a, pb["w0"], bias_b=tb, bias_b_stride=temb_stride, act=1, stats=s0)
+        c0 = ops.conv3x3(a, pb["w0"], bias_b=tb, bias_b_stride=temb_stride, act=1, stats=s0, wimg=pb["w0_img"])
         n1 = ops.gn_apply(c0, s0, pb["g1"], pb["b1"], 0, GN_EPS, out=a)                               # GN1(silu(conv0 + temb))
-        c1 = ops.conv3x3(n1, pb["w1"], bias=pb["cb1"], act=1, stats=s1, out=c0)                        # silu(conv1 + bias)
+        c1 = ops.conv3x3(n1, pb["w1"], bias=pb["cb1"], act=1, stats=s1, out=c0, wimg=pb["w1_img"])     # silu(conv1 + bias)
         out = ops.gn_apply(c1, s1, pb["g2"], None, 2, GN_EPS, res=h, stats_out=s2, out=n1)             # h + GN2(.)
         return out, s2
 
@@ -356,12 +373,12 @@ class Model(nn.Module):
         # ---- down path (:254-264)
         conv0 = self.down_modules[0]
         st = stats[nxt()]
-        h = ops.conv_in(x, conv0.weight, conv0.bias, st)
+        h = ops.conv_in(x, conv0.weight, conv0.bias, st, wimg=pk["conv_in_img"])
         hidden = [h]
         for l, ent in enumerate(pk["down"]):
             if ent["down"] is not None:
                 st = stats[nxt()]
-                h = ops.conv_down4x4(h, ent["down"]["w"], ent["down"]["b"], st)
+                h = ops.conv_down4x4(h, ent["down"]["w"], ent["down"]["b"], st, wimg=ent["down"]["w_img"])
             for pb in ent["blocks"]:
                 h, st = self._res_block(h, st, pb, temb, offs[rb_i], temb_stride, stats, nxt)
                 rb_i += 1
@@ -399,9 +416,9 @@ class Model(nn.Module):
                 rb_i += 1
             if ent["up"] is not None:
                 st = stats[nxt()]
-                h = ops.conv_up4x4(h, ent["up"]["w"], ent["up"]["b"], skip=hidden.pop(), stats=st)
+                h = ops.conv_up4x4(h, ent["up"]["w"], ent["up"]["b"], skip=hidden.pop(), stats=st, wimg=ent["up"]["w_img"])
         conv_last = self.up_modules[-1]
-        return ops.conv_out(h, hidden.pop(), conv_last.weight, conv_last.bias)
+        return ops.conv_out(h, hidden.pop(), conv_last.weight, conv_last.bias, wimg=pk["conv_out_img"])
 
     def forward(self, input, t):
         if torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters()):

@@ -40,9 +40,9 @@ def _block_fwd(h, st_h, pb, temb, temb_off, temb_stride, stats, nxt):
     in backward): a0 = silu(GN0(h)); u0 = conv0(a0) + temb; n1 = GN1(silu(u0)); u1 = conv1(n1) + b; out = h + GN2(silu(u1))."""
     s0, s1, s2 = stats[nxt()], stats[nxt()], stats[nxt()]
     a0 = ops.gn_apply(h, st_h, pb["g0"], pb["b0"], 1, GN_EPS)
-    u0 = ops.conv3x3(a0, pb["w0"], bias_b=temb[:, temb_off:], bias_b_stride=temb_stride, act=3, stats=s0)
+    u0 = ops.conv3x3(a0, pb["w0"], bias_b=temb[:, temb_off:], bias_b_stride=temb_stride, act=3, stats=s0, wimg=pb["w0_img"])
     n1 = ops.gn_apply(u0, s0, pb["g1"], pb["b1"], 3, GN_EPS)
-    u1 = ops.conv3x3(n1, pb["w1"], bias=pb["cb1"], act=3, stats=s1)
+    u1 = ops.conv3x3(n1, pb["w1"], bias=pb["cb1"], act=3, stats=s1, wimg=pb["w1_img"])
     out = ops.gn_apply(u1, s1, pb["g2"], None, 4, GN_EPS, res=h, stats_out=s2)
     return out, s2, dict(h=h, st_h=st_h, a0=a0, u0=u0, s0=s0, n1=n1, u1=u1, s1=s1, pb=pb, temb_off=temb_off)
 
@@ -82,14 +82,14 @@ def forward_train(model, x, t):
     # ---- down path
     conv0 = model.down_modules[0]
     st = stats[nxt()]
-    h = ops.conv_in(x, conv0.weight, conv0.bias, st)
+    h = ops.conv_in(x, conv0.weight, conv0.bias, st, wimg=pk["conv_in_img"])
     hidden = [h]
     sv.down = []
     for ent in pk["down"]:
         rec = dict(ent=ent, blocks=[], h_in=h)
         if ent["down"] is not None:
             st = stats[nxt()]
-            h = ops.conv_down4x4(h, ent["down"]["w"], ent["down"]["b"], st)
+            h = ops.conv_down4x4(h, ent["down"]["w"], ent["down"]["b"], st, wimg=ent["down"]["w_img"])
         for pb in ent["blocks"]:
             h, st, blk = _block_fwd(h, st, pb, temb, offs[rb_i], temb_stride, stats, nxt)
             rec["blocks"].append(blk)
@@ -147,12 +147,12 @@ def forward_train(model, x, t):
         if ent["up"] is not None:
             rec["h_in"] = h
             st = stats[nxt()]
-            h = ops.conv_up4x4(h, ent["up"]["w"], ent["up"]["b"], skip=hidden.pop(), stats=st)
+            h = ops.conv_up4x4(h, ent["up"]["w"], ent["up"]["b"], skip=hidden.pop(), stats=st, wimg=ent["up"]["w_img"])
         sv.up.append(rec)
     conv_last = model.up_modules[-1]
     sv.h_last, sv.skip0 = h, hidden.pop()
     sv.stats = stats
-    return ops.conv_out(h, sv.skip0, conv_last.weight, conv_last.bias), sv
+    return ops.conv_out(h, sv.skip0, conv_last.weight, conv_last.bias, wimg=pk["conv_out_img"]), sv
 
 
 # ------------------------------------------------------------------------------------------------ backward
@@ -169,7 +169,7 @@ def _block_bwd(blk, g, G, dtemb):
     ops.sums_scatter(sums1, out_c=G[pre + ".conv.1.bias"])
     # u1 = conv1(n1) + b
     ops.conv3x3_wgrad(blk["n1"], du1, G[pre + ".conv.1.weight"])
-    dn1 = ops.conv3x3(du1, pb["w1d"])
+    dn1 = ops.conv3x3(du1, pb["w1d"], wimg=pb["w1d_img"])
     # n1 = GN1(silu(u0))
     R1 = ops.gn_bwd_reduce(dn1, u0, blk["s0"], pb["g1"], pb["b1"], 1, GN_EPS)
     du0, sums0 = ops.gn_bwd_apply(dn1, u0, blk["s0"], R1, pb["g1"], pb["b1"], 1, GN_EPS, sums=True, out=dn1)
@@ -177,7 +177,7 @@ def _block_bwd(blk, g, G, dtemb):
     ops.sums_scatter(sums0, out_b=dtemb[:, blk["temb_off"]:], ldb=dtemb.shape[1])
     # u0 = conv0(a0) + temb
     ops.conv3x3_wgrad(blk["a0"], du0, G[pre + ".conv.0.weight"])
-    da0 = ops.conv3x3(du0, pb["w0d"], out=du1)
+    da0 = ops.conv3x3(du0, pb["w0d"], out=du1, wimg=pb["w0d_img"])
     # a0 = silu(GN0(h)); + residual path
     R0 = ops.gn_bwd_reduce(da0, h, blk["st_h"], pb["g0"], pb["b0"], 0, GN_EPS)
     dh, _ = ops.gn_bwd_apply(da0, h, blk["st_h"], R0, pb["g0"], pb["b0"], 0, GN_EPS, add=g, out=da0)
@@ -199,7 +199,7 @@ def backward_train(model, sv, gout):
     # ---- conv_out (:199-208,284)
     ops.conv_out_wgrad(sv.h_last, sv.skip0, gout, G[f"up_modules.{nup}.weight"], G[f"up_modules.{nup}.bias"])
     zero_b = model._const(("zero32", dev), lambda: torch.zeros(32, dtype=torch.float32, device=dev))
-    g = ops.conv_in(gout, pk["conv_out_wd"], zero_b, None)          # d(h + skip0), bf16 NHWC
+    g = ops.conv_in(gout, pk["conv_out_wd"], zero_b, None, wimg=pk["conv_out_wd_img"])          # d(h + skip0), bf16 NHWC
     skipgrad = {0: g}
 
     # ---- up path, reversed
@@ -212,7 +212,7 @@ def backward_train(model, sv, gout):
             k += 1
             ops.conv_up4x4_wgrad(rec["h_in"], g, G[pre + ".conv.weight"])
             ops.colsum(g, G[pre + ".conv.bias"])
-            g = ops.conv_down4x4(g, ent["up"]["wd"], None)
+            g = ops.conv_down4x4(g, ent["up"]["wd"], None, wimg=ent["up"]["wd_img"])
         for blk in reversed(rec["blocks"]):
             g = _block_bwd(blk, g, G, dtemb)
 
@@ -269,7 +269,7 @@ def backward_train(model, sv, gout):
             k -= 1
             ops.conv_down4x4_wgrad(rec["h_in"], g, G[pre + ".conv.weight"])
             ops.colsum(g, G[pre + ".conv.bias"])
-            g = ops.conv_up4x4(g, ent["down"]["wd"], None, skip=skipgrad[k])
+            g = ops.conv_up4x4(g, ent["down"]["wd"], None, skip=skipgrad[k], wimg=ent["down"]["wd_img"])
     assert k == 1
     ops.conv_in_wgrad(sv.x, g, skipgrad[0], G["down_modules.0.weight"], G["down_modules.0.bias"])
 

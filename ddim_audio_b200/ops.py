@@ -65,30 +65,53 @@ def denoise_2d(x, iters=5):
 
 
 # ---------------------------------------------------------------------------------------- convolutions
-def conv_in(x, w, bias, stats=None):
+KIND_CONV3X3, KIND_DOWN, KIND_UP, KIND_CONV_IN, KIND_CONV_OUT = 0, 1, 2, 3, 4
+
+
+def conv_wimg(kind, w, Cin, Cout, W):
+    """Kernel-ready weight image of one convolution (include/ddim_b200.h ``ddimb_conv_wimg``): a uint8 device tensor, or None
+    when the kernel for this shape reads ``w`` directly.  ``Model._pack`` builds these once per weight version; the op wrappers
+    below build one on the fly when the caller passes none (tests, one-off calls)."""
+    nbytes = int(_C.lib.ddimb_conv_wimg_bytes(int(kind), int(Cin), int(Cout), int(W)))
+    if nbytes < 0:
+        raise RuntimeError(f"ddim_audio_b200: no convolution kernel for kind {kind}, Cin {Cin}, Cout {Cout}, W {W}")
+    if nbytes == 0:
+        return None
+    img = torch.empty(nbytes, dtype=torch.uint8, device=w.device)
+    call("ddimb_conv_wimg", int(kind), ptr(w), ptr(img), int(Cin), int(Cout), int(W))
+    return img
+
+
+def conv_in(x, w, bias, stats=None, wimg=None):
     B, Cin, T, F = x.shape
     Cout = w.shape[0]
+    if wimg is None:
+        wimg = conv_wimg(KIND_CONV_IN, w, Cin, Cout, F)
     out = torch.empty((B, T, F, Cout), dtype=bf16, device=x.device)
-    call("ddimb_conv_in", ptr(x, f32), ptr(w, f32), ptr(bias, f32), ptr(out), ptr(stats, f64), B, Cin, T, F, Cout)
+    call("ddimb_conv_in", ptr(x, f32), ptr(w, f32), ptr(wimg), ptr(bias, f32), ptr(out), ptr(stats, f64), B, Cin, T, F, Cout)
     return out
 
 
-def conv_out(x, skip, w, bias):
+def conv_out(x, skip, w, bias, wimg=None):
     B, T, F, Cin = x.shape
     Cout = w.shape[0]
+    if wimg is None:
+        wimg = conv_wimg(KIND_CONV_OUT, w, Cin, Cout, F)
     out = torch.empty((B, Cout, T, F), dtype=f32, device=x.device)
-    call("ddimb_conv_out", ptr(x, bf16), ptr(skip, bf16), ptr(w, f32), ptr(bias, f32), ptr(out), B, T, F, Cin, Cout)
+    call("ddimb_conv_out", ptr(x, bf16), ptr(skip, bf16), ptr(w, f32), ptr(wimg), ptr(bias, f32), ptr(out), B, T, F, Cin, Cout)
     return out
 
 
-def conv3x3(x, w_packed, bias=None, bias_b=None, bias_b_stride=0, act=0, add=None, stats=None, out=None):
+def conv3x3(x, w_packed, bias=None, bias_b=None, bias_b_stride=0, act=0, add=None, stats=None, out=None, wimg=None):
     """x [B,T,W,Cin] bf16; w_packed bf16 [Cout, 9*Cin]; bias_b is a (possibly offset) fp32 view whose row b starts at
     ``bias_b.data_ptr() + 4*b*bias_b_stride``."""
     B, T, W, Cin = x.shape
     Cout = w_packed.shape[0]
+    if wimg is None:
+        wimg = conv_wimg(KIND_CONV3X3, w_packed, Cin, Cout, W)
     if out is None:
         out = torch.empty((B, T, W, Cout), dtype=bf16, device=x.device)
-    call("ddimb_conv3x3", ptr(x, bf16), ptr(w_packed, bf16), ptr(bias, f32), bias_b.data_ptr() if bias_b is not None else None,
+    call("ddimb_conv3x3", ptr(x, bf16), ptr(w_packed, bf16), ptr(wimg), ptr(bias, f32), bias_b.data_ptr() if bias_b is not None else None,
          int(bias_b_stride), int(act), ptr(add, bf16), ptr(out, bf16), ptr(stats, f64), B, T, W, Cin, Cout)
     return out
 
@@ -108,19 +131,23 @@ def conv3x3_gn(x, gn_stats, gamma, beta, eps, gn_mode, w_packed, bias=None, bias
     return out
 
 
-def conv_down4x4(x, w_packed, bias, stats=None):
+def conv_down4x4(x, w_packed, bias, stats=None, wimg=None):
     B, T, W, Cin = x.shape
     Cout = w_packed.shape[0]
+    if wimg is None:
+        wimg = conv_wimg(KIND_DOWN, w_packed, Cin, Cout, W)
     out = torch.empty((B, T // 2, W // 2, Cout), dtype=bf16, device=x.device)
-    call("ddimb_conv_down4x4", ptr(x, bf16), ptr(w_packed, bf16), ptr(bias, f32), ptr(out), ptr(stats, f64), B, T, W, Cin, Cout)
+    call("ddimb_conv_down4x4", ptr(x, bf16), ptr(w_packed, bf16), ptr(wimg), ptr(bias, f32), ptr(out), ptr(stats, f64), B, T, W, Cin, Cout)
     return out
 
 
-def conv_up4x4(x, w_packed, bias, skip=None, stats=None):
+def conv_up4x4(x, w_packed, bias, skip=None, stats=None, wimg=None):
     B, T, W, Cin = x.shape
     Cout = w_packed.shape[0] // 16
+    if wimg is None:
+        wimg = conv_wimg(KIND_UP, w_packed, Cin, Cout, W)
     out = torch.empty((B, 2 * T, 2 * W, Cout), dtype=bf16, device=x.device)
-    call("ddimb_conv_up4x4", ptr(x, bf16), ptr(w_packed, bf16), ptr(bias, f32), ptr(skip, bf16), ptr(out), ptr(stats, f64),
+    call("ddimb_conv_up4x4", ptr(x, bf16), ptr(w_packed, bf16), ptr(wimg), ptr(bias, f32), ptr(skip, bf16), ptr(out), ptr(stats, f64),
          B, T, W, Cin, Cout)
     return out
 

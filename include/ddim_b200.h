@@ -4,7 +4,8 @@
  * these are the entry points its Python layer binds through ctypes (ddim_audio_b200/_C.py; INTEGRATION.md shows the
  * stub a maintainer would add to the reference).  Every function
  *   - takes raw DEVICE pointers, explicit sizes and a cudaStream_t as its last argument; no torch types;
- *   - is asynchronous on that stream, re-entrant, and owns no device memory;
+ *   - is asynchronous on that stream, re-entrant, and owns no device memory (weight re-layouts live in caller-owned images,
+ *     ddimb_conv_wimg);
  *   - returns 0 on success, a negative DDIMB_ERR_* code for argument/driver errors or a positive cudaError_t;
  *     ddimb_last_error() returns a thread-local description.
  * There is no CPU path: on a machine without an sm_100 device the launches fail with a CUDA error.
@@ -94,22 +95,36 @@ int ddimb_grad_clip(const void* chunk_table, int nchunks, long long total_elems,
 int ddimb_optim_step(const void* chunk_table, int nchunks, long long total_elems, int kind, double lr, double beta1, double beta2,
                      double eps, double weight_decay, long long step, cudaStream_t stream);
 
-/* ---- network boundary convolutions (CUDA cores; K = 18 / N = 2 are not tensor-core shapes) -------------------- */
+/* ---- kernel-ready weight images -------------------------------------------------------------------------------- */
 
-/* models/diffusion.py:189-198 -- Conv2d(Cin=2 -> 32, k3 p1): x fp32 NCHW, w fp32 [32][Cin][3][3], out bf16 NHWC. */
-int ddimb_conv_in(const float* x, const float* w, const float* bias, void* out, double* stats, int B, int Cin, int T, int F,
-                  int Cout, cudaStream_t stream);
+/* Every convolution below reads its weights from a CALLER-OWNED device buffer ("image") that holds the weight tiles in the
+ * exact shared-memory (TMA-swizzle) layout of the kernel that runs for (kind, Cin, Cout, W) -- tiles reach shared memory by
+ * 1-D bulk copies, and nothing is re-laid out per call.  Build the image once per weight version (the reference's
+ * nn.Conv2d.weight changes only at optimizer.step / load_state_dict) and pass it as `wimg` next to `w`.
+ * kind: 0 Conv2d 3x3 (w bf16 [Cout][9*Cin]); 1 Conv2d 4x4 s2 (w bf16 [Cout][16*Cin]); 2 ConvTranspose2d 4x4 s2 (w bf16
+ * [16*Cout][Cin]); 3 conv_in (w fp32 [32][2][3][3]); 4 conv_out (w fp32 [2][32][3][3]).  W: width of the op's INPUT tensor.
+ * ddimb_conv_wimg_bytes: image size in bytes; 0 = this shape reads `w` directly (pass wimg NULL); < 0 = unsupported shape.
+ * wimg must be 16-byte aligned. */
+long long ddimb_conv_wimg_bytes(int kind, int Cin, int Cout, int W);
+int ddimb_conv_wimg(int kind, const void* w, void* wimg, int Cin, int Cout, int W, cudaStream_t stream);
+
+/* ---- network boundary convolutions ------------------------------------------------------------------------------ */
+
+/* models/diffusion.py:189-198 -- Conv2d(Cin=2 -> 32, k3 p1): x fp32 NCHW, w fp32 [32][Cin][3][3] (+ its image, kind 3, W = F),
+ * out bf16 NHWC. */
+int ddimb_conv_in(const float* x, const float* w, const void* wimg, const float* bias, void* out, double* stats, int B, int Cin, int T,
+                  int F, int Cout, cudaStream_t stream);
 /* models/diffusion.py:284,199-208 -- Conv2d(32 -> 2, k3 p1) of (x + skip): x, skip (nullable) bf16 NHWC,
- * w fp32 [2][32][3][3], out fp32 NCHW. */
-int ddimb_conv_out(const void* x, const void* skip, const float* w, const float* bias, float* out, int B, int T, int F, int Cin,
-                   int Cout, cudaStream_t stream);
+ * w fp32 [2][32][3][3] (+ its image, kind 4, W = F), out fp32 NCHW. */
+int ddimb_conv_out(const void* x, const void* skip, const float* w, const void* wimg, const float* bias, float* out, int B, int T, int F,
+                   int Cin, int Cout, cudaStream_t stream);
 
 /* ---- tcgen05 / TMEM / TMA implicit-GEMM convolutions and GEMMs ------------------------------------------------ */
 
 /* models/diffusion.py:28-40,49,52 -- Conv2d 3x3 s1 p1 on NHWC bf16.  w: bf16 [Cout][9*Cin], k = (ky*3+kx)*Cin + ci.
  * Epilogue: + bias[Cout] (nullable) + bias_b[b*bias_b_stride + co] (nullable; the temb slice of :49), act (0 none,
  * 1 SiLU of :50,53, 3 training: store the pre-activation but take the statistics of its SiLU), + add (nullable bf16, same shape as out), GroupNorm partial sums into stats (nullable). */
-int ddimb_conv3x3(const void* x, const void* w, const float* bias, const float* bias_b, int bias_b_stride, int act,
+int ddimb_conv3x3(const void* x, const void* w, const void* wimg, const float* bias, const float* bias_b, int bias_b_stride, int act,
                   const void* add, void* out, double* stats, int B, int T, int W, int Cin, int Cout, cudaStream_t stream);
 
 /* models/diffusion.py:42-56 -- GroupNorm(8, C, eps) [+ SiLU] of x from precomputed statistics gn_stats [B][8][2], then the
@@ -124,12 +139,12 @@ int ddimb_conv3x3_gn(const void* x, const double* gn_stats, const float* gn_gamm
 
 /* models/diffusion.py:70-78 -- Downsample Conv2d 4x4 s2 p1.  w: bf16 [Cout][16*Cin], k = (ky*4+kx)*Cin + ci.
  * x [B][T][W][Cin] -> out [B][T/2][W/2][Cout]. */
-int ddimb_conv_down4x4(const void* x, const void* w, const float* bias, void* out, double* stats, int B, int T, int W,
+int ddimb_conv_down4x4(const void* x, const void* w, const void* wimg, const float* bias, void* out, double* stats, int B, int T, int W,
                        int Cin, int Cout, cudaStream_t stream);
 
 /* models/diffusion.py:59-67 + :284 -- Upsample ConvTranspose2d 4x4 s2 p1, then "+ skip".
  * w: bf16 [16*Cout][Cin], row = (ky*4+kx)*Cout + co.  x [B][T][W][Cin] -> out [B][2T][2W][Cout]; skip nullable. */
-int ddimb_conv_up4x4(const void* x, const void* w, const float* bias, const void* skip, void* out, double* stats, int B,
+int ddimb_conv_up4x4(const void* x, const void* w, const void* wimg, const float* bias, const void* skip, void* out, double* stats, int B,
                      int T, int W, int Cin, int Cout, cudaStream_t stream);
 
 /* nn.Linear (models/diffusion.py:127-128,141,156,166; transformers modeling_fnet.py:204-231):
