@@ -9,7 +9,9 @@
 //     whose rows are zero where (s, dx) has no kernel column (dx = -1: s = 1; dx = +1: s = 0).
 //   * blocks ky = 0,1 complete with this input row, blocks ky = 2,3 receive their first contribution from it.
 // Warp roles (320 threads): 0 = TMA producer, 1 = MMA issuer, 2-9 = epilogue (two warps per TMEM lane quarter, alternating
-// output rows): bias, + skip, GroupNorm partial sums, bf16 NHWC store.
+// output rows): the skip tile of an output row ([32 pixel pairs][128 B] per warp) arrives by TMA into one of the warp's two
+// staging tiles a tile ahead, bias + skip are added in place, the tile leaves by ONE TMA store (r02: the per-thread staged
+// loads / stores of the skip and output rows kept this kernel at 0.38 of HBM).
 #pragma once
 #include "conv_wide.cuh"
 
@@ -18,11 +20,12 @@ namespace ddimb {
 constexpr int kUwThreads = 320;
 constexpr int kUwCin = 64, kUwCout = 32;
 constexpr int kUwSlotBytes = ((kWidePos * 128 + 1023) / 1024) * 1024;   // 17408
-constexpr int kUwSlots = 6;
+constexpr int kUwSlots = 3;
 constexpr int kUwNB = 8;                               // output rows in flight in TMEM (64 columns each)
 constexpr int kUwWTile = 256 * 128;                    // [4 ky][2 s][32 co] rows x 64 ci
 constexpr int kUwWBytes = 3 * kUwWTile;
-constexpr int kUwAux = 1024 + 4096 + 8 * 2048;         // barriers | 8 bias copies | 8 x store staging
+constexpr int kUwStage = 32 * 128;                     // one epilogue warp's tile: 32 pixel pairs x [s][co] (128 B), SWIZZLE_128B image
+constexpr int kUwAux = 1024 + 4096 + 8 * 2 * kUwStage; // barriers | 8 bias copies | 8 warps x 2 staging tiles
 constexpr int kUwSmem = 1024 + kUwWBytes + kUwSlots * kUwSlotBytes + kUwAux;
 
 struct UwParams {
@@ -63,7 +66,8 @@ struct UwUnit {
 };
 
 __global__ void __launch_bounds__(kUwThreads, 1)
-conv_up_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ UwParams p) {
+conv_up_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmS,
+                    const __grid_constant__ UwParams p) {
   constexpr int NS = kUwSlots, NB = kUwNB, NA = 2 * kUwCout;   // accumulator block width
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -72,8 +76,8 @@ conv_up_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   const uint32_t a_base = smem_base + kUwWBytes;
   const uint32_t aux = a_base + NS * kUwSlotBytes;
   uint8_t* aux_gen = smem_gen + kUwWBytes + NS * kUwSlotBytes;
-  // aux: full[8] @0, empty[8] @64, acc_full[8] @128, acc_empty[8] @192, wfull @256, tmem ptr @264
-  const uint32_t bar_full = aux, bar_empty = aux + 64, bar_afull = aux + 128, bar_aempty = aux + 192, bar_w = aux + 256;
+  // aux: full[8] @0, empty[8] @64, acc_full[8] @128, acc_empty[8] @192, wfull @256, tmem ptr @264, skip[8 warps][2] @320
+  const uint32_t bar_full = aux, bar_empty = aux + 64, bar_afull = aux + 128, bar_aempty = aux + 192, bar_w = aux + 256, bar_skip = aux + 320;
   volatile uint32_t* tmem_ptr_gen = reinterpret_cast<volatile uint32_t*>(aux_gen + 264);
   float* bias_smem = reinterpret_cast<float*>(aux_gen + 1024);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -89,6 +93,9 @@ conv_up_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       mbar_init(bar_aempty + 8 * b, 4);
     }
     mbar_init(bar_w, 1);
+    for (int i = 0; i < 16; ++i) mbar_init(bar_skip + 8 * i, 1);
+    tma_prefetch_desc(&tmO);
+    tma_prefetch_desc(&tmS);
     mbar_fence_init();
   }
   if (warp == 1) {
@@ -184,49 +191,129 @@ conv_up_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     // ================================================================ epilogue (TMEM lane quarter = warp % 4; group = output row parity)
     const int q = warp & 3;
     const uint32_t grp = (uint32_t)(warp - 2) >> 2;
-    const int m = q * 32 + lane;
     float* wb = bias_smem + (warp - 2) * 128;
-    uint8_t* stage = aux_gen + 1024 + 4096 + (warp - 2) * 2048;
+    uint8_t* stage_gen = aux_gen + 1024 + 4096 + (warp - 2) * 2 * kUwStage;
+    const uint32_t stage = smem_u32(stage_gen);
+    const uint32_t bsk = bar_skip + 16 * (warp - 2);
+    const uint32_t phase = (uint32_t)(lane & 7);
+    const bool has_skip = p.skip != nullptr, want_stats = p.stats != nullptr;
     ConvEpiState<kUwCout> st;
     st.reset();
     st.cur_batch = -1;
     if (grp == 0 && lane == 0) mbar_arrive(bar_aempty + 0);   // same for the "accumulator free" barrier of ring position 0 (4 arrivals)
-    const int To = 2 * p.T, Wo = 2 * p.W;
-    uint32_t g0 = 0;
-    UwUnit u;
-    for (int unit = blockIdx.x; unit < p.num_units; unit += gridDim.x) {
-      u.set(p, unit);
-      if (u.b != st.cur_batch) {
+
+    // this warp's tiles in order: (unit, local output row lo) with lo of this warp's parity group
+    struct Walk {
+      int unit, lo, nout;
+      uint32_t g0;
+      UwUnit u;
+      __device__ __forceinline__ void begin(const UwParams& p, uint32_t grp) {
+        unit = blockIdx.x; g0 = 0;
+        enter(p, grp);
+      }
+      __device__ __forceinline__ void enter(const UwParams& p, uint32_t grp) {
+        while (unit < p.num_units) {
+          u.set(p, unit);
+          nout = 2 * u.rows;
+          lo = (int)((grp - g0) & 1u);
+          if (lo < nout) return;
+          g0 += (uint32_t)nout;
+          unit += gridDim.x;
+        }
+      }
+      __device__ __forceinline__ bool valid(const UwParams& p) const { return unit < p.num_units; }
+      __device__ __forceinline__ void next(const UwParams& p, uint32_t grp) {
+        lo += 2;
+        if (lo >= nout) {
+          g0 += (uint32_t)nout;
+          unit += gridDim.x;
+          enter(p, grp);
+        }
+      }
+    };
+    Walk cur, nxt;
+    cur.begin(p, grp);
+    nxt = cur;
+    if (nxt.valid(p)) nxt.next(p, grp);
+    uint32_t it = 0;
+    auto load_skip = [&](const Walk& w, uint32_t b) {
+      if (has_skip && elect_one()) {
+        mbar_arrive_expect_tx(bsk + 8 * b, (uint32_t)kUwStage);
+        tma_load_4d(stage + b * kUwStage, &tmS, bsk + 8 * b, 0, w.u.w0 + q * 32, 2 * w.u.t0 + w.lo, w.u.b);
+      }
+    };
+    if (cur.valid(p)) load_skip(cur, 0);
+    for (; cur.valid(p); ++it) {
+      const uint32_t sb = it & 1u;
+      if (cur.u.b != st.cur_batch) {
         st.flush(p.stats, lane);
-        st.cur_batch = u.b;
-        conv_epilogue_bias<kUwCout>(wb, p.bias, nullptr, u.b, 0, 0, lane);
+        st.cur_batch = cur.u.b;
+        conv_epilogue_bias<kUwCout>(wb, p.bias, nullptr, cur.u.b, 0, 0, lane);
       }
-      const int nout = 2 * u.rows;
-      // the skip rows do not depend on the MMAs: this tile's words were requested one tile ago, the next tile's are requested
-      // before waiting for the accumulator (two batches of 8 x 16 B per thread in flight)
-      const int lo_first = (int)((grp - g0) & 1u);
-      const int64_t base0 = ((((int64_t)u.b * To + 2 * u.t0) * Wo) + 2 * (u.w0 + m)) * kUwCout;
-      const int64_t row_pitch = (int64_t)Wo * kUwCout;
-      uint4 cur[NA / 8], nxt[NA / 8];
-      conv_epilogue_prefetch_add<NA>(p.skip, base0 + lo_first * row_pitch, lo_first < nout, cur);
-      for (int lo = lo_first; lo < nout; lo += 2) {
-        const uint32_t g = g0 + (uint32_t)lo + 1;
-        const uint32_t buf = g % NB, use = g / NB;
-        const int64_t addr0 = base0 + lo * row_pitch;
-        conv_epilogue_prefetch_add<NA>(p.skip, addr0 + 2 * row_pitch, lo + 2 < nout, nxt);
-        mbar_wait(bar_afull + 8 * buf, use & 1, 65);
-        tc_fence_after();
-        const uint32_t trow = tmem_base + ((uint32_t)(q * 32) << 16) + buf * NA;
-        conv_epilogue_tile<NA, kUwCout>(trow, wb, 0, p.skip, p.out, addr0, true, p.stats != nullptr, st, stage, p.skip != nullptr ? cur : nullptr);
-#pragma unroll
-        for (int k = 0; k < NA / 8; ++k) cur[k] = nxt[k];
-        tc_fence_before();
+      // the other staging tile was the source of the previous tile's store: once that has been read, the next tile's skip may land in it
+      if (it > 0) {
+        bulk_wait_group_read<0>();
         __syncwarp();
-        if (lane == 0) mbar_arrive(bar_aempty + 8 * buf);
       }
-      g0 += (uint32_t)nout;
+      if (nxt.valid(p)) load_skip(nxt, sb ^ 1u);
+      const uint32_t g = cur.g0 + (uint32_t)cur.lo + 1;
+      const uint32_t buf = g % NB, use = g / NB;
+      mbar_wait(bar_afull + 8 * buf, use & 1, 65);
+      tc_fence_after();
+      const uint32_t trow = tmem_base + ((uint32_t)(q * 32) << 16) + buf * NA;
+      uint8_t* srow = stage_gen + sb * kUwStage + lane * 128;
+#pragma unroll
+      for (int c0 = 0; c0 < NA; c0 += 32) {
+        uint32_t v[32];
+        tmem_ld32(trow + (uint32_t)c0, v);
+        tmem_ld_wait();
+        if (c0 + 32 == NA) {
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(bar_aempty + 8 * buf);
+        }
+        uint64_t f[16];
+#pragma unroll
+        for (int j = 0; j < 16; j += 2) {
+          const ulonglong2 b4 = *reinterpret_cast<const ulonglong2*>(wb + ((c0 + 2 * j) % kUwCout));
+          f[j] = fadd2(pack2u(v[2 * j], v[2 * j + 1]), b4.x);
+          f[j + 1] = fadd2(pack2u(v[2 * j + 2], v[2 * j + 3]), b4.y);
+        }
+        if (has_skip) {
+          if (c0 == 0) {
+            mbar_wait(bsk + 8 * sb, (it >> 1) & 1u, 66);   // staging tile sb is used by every second tile
+          }
+#pragma unroll
+          for (int qq = 0; qq < 4; ++qq) {
+            const uint4 a = *reinterpret_cast<const uint4*>(srow + ((((uint32_t)(c0 >> 3) + qq) ^ phase) << 4));
+            f[4 * qq] = fadd2(f[4 * qq], bf16x2_to_f32x2(a.x));
+            f[4 * qq + 1] = fadd2(f[4 * qq + 1], bf16x2_to_f32x2(a.y));
+            f[4 * qq + 2] = fadd2(f[4 * qq + 2], bf16x2_to_f32x2(a.z));
+            f[4 * qq + 3] = fadd2(f[4 * qq + 3], bf16x2_to_f32x2(a.w));
+          }
+        }
+#pragma unroll
+        for (int qq = 0; qq < 4; ++qq)
+          *reinterpret_cast<uint4*>(srow + ((((uint32_t)(c0 >> 3) + qq) ^ phase) << 4)) =
+              make_uint4(f32x2_to_bf16x2(f[4 * qq]), f32x2_to_bf16x2(f[4 * qq + 1]), f32x2_to_bf16x2(f[4 * qq + 2]), f32x2_to_bf16x2(f[4 * qq + 3]));
+        if (want_stats) {
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            const int gi = ((c0 + 2 * j) % kUwCout) / (kUwCout / 8);   // compile-time after unrolling
+            st.s1[gi] = fadd2(st.s1[gi], f[j]);
+            st.s2[gi] = ffma2(f[j], f[j], st.s2[gi]);
+          }
+        }
+      }
+      fence_proxy_async_smem();
+      __syncwarp();
+      tma_store_4d_e(&tmO, stage + sb * kUwStage, 0, cur.u.w0 + q * 32, 2 * cur.u.t0 + cur.lo, cur.u.b);
+      bulk_commit_group();
+      cur = nxt;
+      if (nxt.valid(p)) nxt.next(p, grp);
     }
     st.flush(p.stats, lane);
+    bulk_wait_group<0>();
   }
 
   tc_fence_before();

@@ -602,10 +602,21 @@ static int launch_conv_up_wide(const void* x, const uint8_t* wimg, const float* 
     int r = make_tmap_bf16(&tmA, x, 4, dims, str, box, 64);
     if (r) return r;
   }
+  // output / skip as pixel pairs: pair f of output row o holds the 64 accumulator columns [s][co] (128 contiguous bytes)
+  CUtensorMap tmO, tmS;
+  {
+    uint64_t dims[4] = {64, (uint64_t)W, (uint64_t)2 * T, (uint64_t)B};
+    uint64_t str[3] = {64, (uint64_t)W * 64, (uint64_t)2 * T * W * 64};
+    uint32_t box[4] = {64, 32, 1, 1};
+    int r = make_tmap_bf16(&tmO, out, 4, dims, str, box, 64);
+    if (r) return r;
+    r = make_tmap_bf16(&tmS, skip ? skip : out, 4, dims, str, box, 64);
+    if (r) return r;
+  }
   static bool attr = false;
   if (!attr) { DDIMB_CUDA(cudaFuncSetAttribute(conv_up_wide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kUwSmem)); attr = true; }
   const int grid = p.num_units < ddimb_num_sms() ? p.num_units : ddimb_num_sms();
-  conv_up_wide_kernel<<<grid, kUwThreads, kUwSmem, stream>>>(tmA, p);
+  conv_up_wide_kernel<<<grid, kUwThreads, kUwSmem, stream>>>(tmA, tmO, tmS, p);
   DDIMB_LAUNCH_CHECK();
   return DDIMB_OK;
 }
