@@ -58,7 +58,7 @@ struct CiUnit {
   }
 };
 
-__global__ void __launch_bounds__(kCiThreads, 1) conv_in_tc_kernel(const __grid_constant__ CiParams p) {
+__global__ void __launch_bounds__(kCiThreads, 1) conv_in_tc_kernel(const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CiParams p) {
   constexpr int NS = kCiSlots, NB = kCiNB, CO = 32;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -107,7 +107,7 @@ __global__ void __launch_bounds__(kCiThreads, 1) conv_in_tc_kernel(const __grid_
       const float* xb = p.x + (int64_t)u.b * 2 * p.T * p.W;
       const int t_end = min(u.t0 + u.rows, p.T - 1);   // last input row this unit reads
       auto load6 = [&](int tt, float (&d)[2][3]) {
-        const bool ok = tt >= 0 && tt <= t_end && !(p.dbg & 2);
+        const bool ok = tt >= 0 && tt <= t_end;
 #pragma unroll
         for (int ci = 0; ci < 2; ++ci) {
           const float* xp = xb + ((int64_t)ci * p.T + tt) * p.W;
@@ -156,7 +156,7 @@ __global__ void __launch_bounds__(kCiThreads, 1) conv_in_tc_kernel(const __grid_
         *reinterpret_cast<uint4*>(dst + ((5 ^ sw) << 4)) = make_uint4(hw[2], hw[3], hw[4], hw[5]);
         *reinterpret_cast<uint4*>(dst + ((6 ^ sw) << 4)) = make_uint4(hw[6], hw[7], hw[8], 0u);
         *reinterpret_cast<uint4*>(dst + ((7 ^ sw) << 4)) = make_uint4(0u, 0u, 0u, 0u);
-        if (!(p.dbg & 1)) fence_proxy_async_smem();
+        fence_proxy_async_smem();
         __syncwarp();
         if (lane == 0) mbar_arrive(bar_full + 8 * slot);
         copy6(win[0], win[2]);
@@ -174,7 +174,12 @@ __global__ void __launch_bounds__(kCiThreads, 1) conv_in_tc_kernel(const __grid_
     const int q = warp & 3, g = (warp - 8) >> 2, ew = warp - 8;
     const int m = q * 32 + lane;
     float* wb = bias_smem + ew * 256;
-    uint8_t* stage = aux_gen + 1024 + 8192 + ew * 2048;
+    uint8_t* stage_gen = aux_gen + 1024 + 8192 + ew * 2048;     // [32 positions][64 B] in the SWIZZLE_64B image: the TMA store's source
+    const uint32_t stage = smem_u32(stage_gen);
+    const uint32_t phase = (uint32_t)((lane >> 1) & 3);
+    uint8_t* srow = stage_gen + lane * 64;
+    const bool want_stats = p.stats != nullptr;
+    bool pending = false;
     uint32_t total = 0;
     CiUnit u;
     for (int unit = blockIdx.x; unit < p.num_units; unit += gridDim.x) {
@@ -226,18 +231,47 @@ __global__ void __launch_bounds__(kCiThreads, 1) conv_in_tc_kernel(const __grid_
         const uint32_t cnt = base + (uint32_t)r;
         const uint32_t buf = cnt % NB;
         issue(cnt + 2);
-        const int64_t addr0 = ((((int64_t)u.b * p.T + (u.t0 + r)) * p.W) + u.w0 + m) * CO;
         mbar_wait(bar_afull + 8 * buf, (cnt / NB) & 1, 75);
         tc_fence_after();
         const uint32_t trow = tmem_base + ((uint32_t)(q * 32) << 16) + buf * CO;
-        if (!(p.dbg & 8)) conv_epilogue_tile<CO, CO>(trow, wb, 0, nullptr, p.out, addr0, !(p.dbg & 4), p.stats != nullptr, st, stage);
+        if (pending) {            // the previous tile's store has read the staging tile
+          bulk_wait_group_read<0>();
+          __syncwarp();
+        }
+        uint32_t v[32];
+        tmem_ld32(trow, v);
+        tmem_ld_wait();
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(bar_aempty + 8 * buf);
+        if (lane == 0) mbar_arrive(bar_aempty + 8 * buf);      // accumulators are in registers
+        uint64_t f[16];
+#pragma unroll
+        for (int j = 0; j < 16; j += 2) {
+          const ulonglong2 b4 = *reinterpret_cast<const ulonglong2*>(wb + 2 * j);
+          f[j] = fadd2(pack2u(v[2 * j], v[2 * j + 1]), b4.x);
+          f[j + 1] = fadd2(pack2u(v[2 * j + 2], v[2 * j + 3]), b4.y);
+        }
+#pragma unroll
+        for (int qq = 0; qq < 4; ++qq)
+          *reinterpret_cast<uint4*>(srow + (((uint32_t)qq ^ phase) << 4)) =
+              make_uint4(f32x2_to_bf16x2(f[4 * qq]), f32x2_to_bf16x2(f[4 * qq + 1]), f32x2_to_bf16x2(f[4 * qq + 2]), f32x2_to_bf16x2(f[4 * qq + 3]));
+        if (want_stats) {
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            st.s1[j >> 1] = fadd2(st.s1[j >> 1], f[j]);         // 4 channels per GroupNorm group
+            st.s2[j >> 1] = ffma2(f[j], f[j], st.s2[j >> 1]);
+          }
+        }
+        fence_proxy_async_smem();
+        __syncwarp();
+        tma_store_4d_e(&tmO, stage, 0, u.w0 + q * 32, u.t0 + r, u.b);
+        bulk_commit_group();
+        pending = true;
       }
       base += (uint32_t)u.rows;
     }
     st.flush(p.stats, lane);
+    bulk_wait_group<0>();
   }
 
   tc_fence_before();

@@ -367,7 +367,15 @@ int ddimb_conv_in_tc(const float* x, const uint8_t* wimg, const float* bias, voi
   static bool attr = false;
   if (!attr) { DDIMB_CUDA(cudaFuncSetAttribute(conv_in_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kCiSmem)); attr = true; }
   const int grid = p.num_units < ddimb_num_sms() ? p.num_units : ddimb_num_sms();
-  conv_in_tc_kernel<<<grid, kCiThreads, kCiSmem, stream>>>(p);
+  CUtensorMap tmO;
+  {
+    uint64_t dims[4] = {32, (uint64_t)F, (uint64_t)T, (uint64_t)B};
+    uint64_t str[3] = {32, (uint64_t)F * 32, (uint64_t)T * F * 32};
+    uint32_t box[4] = {32, 32, 1, 1};
+    int r = make_tmap_bf16(&tmO, out, 4, dims, str, box, 32);
+    if (r) return r;
+  }
+  conv_in_tc_kernel<<<grid, kCiThreads, kCiSmem, stream>>>(tmO, p);
   DDIMB_LAUNCH_CHECK();
   return DDIMB_OK;
 }
