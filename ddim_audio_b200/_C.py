@@ -44,6 +44,7 @@ SIGNATURES = {
     "ddimb_fourier_mix": [_vp, _ll, _vp, _vp, _vp, _vp, _i, _i, _i, _i],
     "ddimb_gn_apply": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _ll, _i, _f],
     "ddimb_linear_small": [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i],
+    "ddimb_gather_rows": [_vp, _vp, _vp, _i, _i, _i],
     "ddimb_tokens_ln": [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _f],
     "ddimb_tokens_to_nhwc": [_vp, _vp, _vp, _vp, _i, _i, _i, _i],
     "ddimb_layernorm512": [_vp, _vp, _vp, _vp, _vp, _vp, _ll, _i, _i, _f],

@@ -382,28 +382,18 @@ extern "C" int ddimb_gn_apply(const void* x, const void* res, void* y, const dou
   const int threads = (C % 96 == 0) ? 192 : 256;   // threads * 8 must be a multiple of C
   const int64_t items = a.per_sample / 8;
   int64_t bx = (items + threads * 4 - 1) / (threads * 4);
-  static const int env_cps = getenv("DDIMB_GN_CPS") ? atoi(getenv("DDIMB_GN_CPS")) : 0;
-  static const int env_unr = getenv("DDIMB_GN_UNR") ? atoi(getenv("DDIMB_GN_UNR")) : 0;
-  static const int env_old = getenv("DDIMB_GN_OLD") ? atoi(getenv("DDIMB_GN_OLD")) : 0;      // A/B: 1 = the 2-D grid kernel
-  static const int env_waves = getenv("DDIMB_GN_WAVES") ? atoi(getenv("DDIMB_GN_WAVES")) : 100;   // % of one resident wave
-  const int unr = env_unr > 0 ? env_unr : 4;
+  constexpr int unr = 4;
   // measured (tools/ab_gn.sh, B = 64, bench shapes): mode 2 -- ranges kernel +13 % at C = 96, +3 % at 128, +31 % at 192, but the
   // 2-D grid stays 4 % ahead at C = 32 / 64 (tensors large enough to hide its tail); modes 0 / 1 -- ranges +12 % (C = 64) to
-  // +31 % (C = 96, 192); UNR = 8 is no better than 4 anywhere
-  const bool ranges = env_old == 2 ? true : (env_old == 1 ? false : (mode != 2 || C >= 96));
+  // +31 % (C = 96, 192); an unroll of 8 is no better than 4 anywhere
+  const bool ranges = (mode != 2 || C >= 96);
   if (ranges && items % ((int64_t)threads * unr) == 0 && items / ((int64_t)threads * unr) >= 1) {
-    // balanced contiguous ranges, one resident wave
-    if (unr == 8) gn_ranges_launch<8>(a, B, threads, items, env_waves, stream);
-    else gn_ranges_launch<4>(a, B, threads, items, env_waves, stream);
+    gn_ranges_launch<unr>(a, B, threads, items, 100, stream);   // balanced contiguous ranges, one resident wave
   } else {
-    const int cps = env_cps > 0 ? env_cps : 8;
-    int64_t cap = (int64_t)ddimb_num_sms() * cps / B + 1;
+    int64_t cap = (int64_t)ddimb_num_sms() * 8 / B + 1;
     if (bx > cap) bx = cap;
     if (bx < 1) bx = 1;
-    if (unr == 8)
-      gn_apply_kernel<8><<<dim3((unsigned)bx, B), threads, 0, stream>>>(a);
-    else
-      gn_apply_kernel<4><<<dim3((unsigned)bx, B), threads, 0, stream>>>(a);
+    gn_apply_kernel<unr><<<dim3((unsigned)bx, B), threads, 0, stream>>>(a);
   }
   DDIMB_LAUNCH_CHECK();
   return DDIMB_OK;
@@ -447,6 +437,25 @@ extern "C" int ddimb_linear_small(const float* in, const long long* idx, const f
   DDIMB_CHECK_ARG(in && w && bias && out && rows >= 1 && K % 32 == 0 && K <= 512 && N >= 1);
   DDIMB_PROF(stream, "linear_small", N, K, 4.0 * ((double)N * K + (double)rows * (K + N)), 2.0 * rows * N * K);
   linear_small_kernel<<<(N + 7) / 8, 256, 0, stream>>>(in, reinterpret_cast<const int64_t*>(idx), w, bias, out, rows, K, N, act);
+  DDIMB_LAUNCH_CHECK();
+  return DDIMB_OK;
+}
+
+// out[r][:] = table[idx[r]][:] (fp32, width a multiple of 4): the per-step lookup into the precomputed timestep-embedding table
+// (models/diffusion.py:107-120 evaluated once for t = 0..999 in eval mode; during sampling every row of t is the same step).
+__global__ void __launch_bounds__(256) gather_rows_kernel(const float4* __restrict__ table, const int64_t* __restrict__ idx, float4* __restrict__ out,
+                                                          int width4, int table_rows) {
+  const int r = blockIdx.y;
+  int64_t src = idx[r];
+  src = src < 0 ? 0 : (src >= table_rows ? table_rows - 1 : src);
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < width4; i += gridDim.x * blockDim.x) out[(int64_t)r * width4 + i] = table[src * width4 + i];
+}
+
+extern "C" int ddimb_gather_rows(const float* table, const long long* idx, float* out, int rows, int width, int table_rows, cudaStream_t stream) {
+  DDIMB_CHECK_ARG(table && idx && out && rows >= 1 && rows <= 65535 && width >= 4 && width % 4 == 0 && table_rows >= 1);
+  DDIMB_PROF(stream, "gather_rows", width, rows, 8.0 * rows * width, 0.0);
+  gather_rows_kernel<<<dim3((width / 4 + 255) / 256, rows), 256, 0, stream>>>(reinterpret_cast<const float4*>(table), reinterpret_cast<const int64_t*>(idx),
+                                                                                reinterpret_cast<float4*>(out), width / 4, table_rows);
   DDIMB_LAUNCH_CHECK();
   return DDIMB_OK;
 }

@@ -82,7 +82,6 @@ static int launch_gemm(GemmParams& p, const CUtensorMap& tmA, const CUtensorMap&
     const int sbk = (ck == 64 ? GemmSmem<64>::stage_bytes(brows, k) : GemmSmem<32>::stage_bytes(brows, k));
     if ((max_smem - 1024 - kGemmAuxBytes) / sbk >= 3) kps = k;
   }
-  { const char* e = getenv("DDIMB_KPS"); if (e && atoi(e) >= 1) kps = atoi(e) < max_chunk ? atoi(e) : max_chunk; }
   p.kps = kps;
   const int stage_bytes = (ck == 64 ? GemmSmem<64>::stage_bytes(brows, kps) : GemmSmem<32>::stage_bytes(brows, kps));
   DDIMB_CHECK_ARG(stage_bytes % 1024 == 0);
@@ -291,9 +290,8 @@ static int win_smem_bytes(int W, int* nr, int* plane) {
 }
 
 static bool conv_window_supported(int Cin, int Cout, int W) {
-  static const bool off = getenv("DDIMB_NO_WINDOW") != nullptr;
   int nr, plane;
-  return !off && Cin == kWinC && Cout == kWinC && W + 2 <= 256 && win_smem_bytes(W, &nr, &plane) <= 232448 && nr <= 256;
+  return Cin == kWinC && Cout == kWinC && W + 2 <= 256 && win_smem_bytes(W, &nr, &plane) <= 232448 && nr <= 256;
 }
 
 static int launch_conv_window(const void* x, const uint8_t* wimg, const float* bias, const float* bias_b, int bias_b_stride, int act, const void* add,
@@ -503,8 +501,7 @@ extern "C" int ddimb_conv3x3(const void* x, const void* w, const void* wimg, con
 // ------------------------------------------------------------------------------------------------ wide Downsample (32 -> 64)
 // csrc/conv_down_wide.cuh; weights come from the caller's swizzled tile image (ddimb_conv_wimg, kind 1).
 static bool conv_down_wide_supported(int Cin, int Cout, int W) {
-  static const bool off = getenv("DDIMB_NO_DOWN_WIDE") != nullptr;
-  return !off && Cin == kDwCin && Cout == kDwCout && W % 256 == 0;
+  return Cin == kDwCin && Cout == kDwCout && W % 256 == 0;
 }
 
 static int launch_conv_down_wide(const void* x, const uint8_t* wimg, const float* bias, void* out, double* stats, int B, int T, int W, cudaStream_t stream) {
@@ -587,8 +584,7 @@ extern "C" int ddimb_conv_down4x4(const void* x, const void* w, const void* wimg
 // ------------------------------------------------------------------------------------------------ wide Upsample (64 -> 32)
 // csrc/conv_up_wide.cuh; weights come from the caller's swizzled tile image (ddimb_conv_wimg, kind 2).
 static bool conv_up_wide_supported(int Cin, int Cout, int W) {
-  static const bool off = getenv("DDIMB_NO_UP_WIDE") != nullptr;
-  return !off && Cin == kUwCin && Cout == kUwCout && W % 128 == 0;
+  return Cin == kUwCin && Cout == kUwCout && W % 128 == 0;
 }
 
 static int launch_conv_up_wide(const void* x, const uint8_t* wimg, const float* bias, const void* skip, void* out, double* stats, int B, int T, int W,

@@ -306,6 +306,16 @@ class Model(nn.Module):
             pk["conv_out_wd_img"] = img(ops.KIND_CONV_IN, pk["conv_out_wd"], 2, 32, F0)
         return pk
 
+    def _temb_table(self, pk):
+        """BetaEmbedding for every timestep at once (:95-120): the MLP sees only the table row te[t], so no-grad forwards just look
+        the result up (each row is computed exactly as the per-batch evaluation computes it).  Built on first use per weight version."""
+        if "temb_table" not in pk:
+            lin = self.temb.weight
+            e = ops.linear_small(self.temb.te, lin[0].weight, lin[0].bias, act=1)
+            e = ops.linear_small(e, lin[1].weight, lin[1].bias, act=1)
+            pk["temb_table"] = ops.linear_small(e, lin[2].weight, lin[2].bias, act=0)   # [num_timesteps, sum(embedding_size)]
+        return pk["temb_table"]
+
     def _packed_for(self, train):
         base, walk = self._pack_key(train)
         pk = self._packed
@@ -351,11 +361,8 @@ class Model(nn.Module):
         x = x.contiguous().float()
         t = t.to(device=dev, dtype=torch.int64).contiguous()
 
-        # ---- timestep embedding (:107-120), fp32
-        lin = self.temb.weight
-        e = ops.linear_small(self.temb.te, lin[0].weight, lin[0].bias, act=1, idx=t)
-        e = ops.linear_small(e, lin[1].weight, lin[1].bias, act=1)
-        temb = ops.linear_small(e, lin[2].weight, lin[2].bias, act=0)               # [B, sum(embedding_size)]
+        # ---- timestep embedding (:107-120), fp32: one row lookup into the table packed for this weight version
+        temb = ops.gather_rows(self._temb_table(pk), t)                             # [B, sum(embedding_size)]
         temb_stride = temb.shape[1]
         offs = [0]
         for w in self.embedding_size:

@@ -192,6 +192,14 @@ def linear_small(inp, w, bias, act=0, idx=None):
     return out
 
 
+def gather_rows(table, idx):
+    """out[r] = table[idx[r]] (fp32)."""
+    rows, width = idx.numel(), table.shape[1]
+    out = torch.empty((rows, width), dtype=f32, device=table.device)
+    call("ddimb_gather_rows", ptr(table, f32), ptr(idx, i64), ptr(out), rows, width, table.shape[0])
+    return out
+
+
 def tokens_ln(x, te, gamma, beta, eps):
     B, S, W, Cc = x.shape
     out = torch.empty((B * S, Cc * W), dtype=bf16, device=x.device)

@@ -172,6 +172,9 @@ int ddimb_gn_apply(const void* x, const void* res, void* y, const double* stats_
  * act bit 0: SiLU on the output; bit 1: SiLU on the input (training keeps the pre-activations). */
 int ddimb_linear_small(const float* in, const long long* idx, const float* w, const float* bias, float* out, int rows,
                        int K, int N, int act, cudaStream_t stream);
+/* out[r][:] = table[idx[r]][:] (fp32 rows of `width` values, width % 4 == 0): lookup into the timestep-embedding table
+ * [num_timesteps][sum(embedding_size)] that eval-mode models precompute once per weight version (models/diffusion.py:107-120,248). */
+int ddimb_gather_rows(const float* table, const long long* idx, float* out, int rows, int width, int table_rows, cudaStream_t stream);
 
 /* models/diffusion.py:273-275,130-142 -- NHWC [B][S][W][C] -> tokens [B*S][C*W] (+ positional table te) -> LayerNorm. */
 int ddimb_tokens_ln(const void* x, const float* te, const float* gamma, const float* beta, void* out, int B, int S, int W,

@@ -178,3 +178,47 @@ def test_generalized_steps_configs0_geometry(model, oracle_sd, golden_dir):
         assert r <= EPS_REL and m <= EPS_ABS_PER_STD
         xt.add_(et, alpha=-((1 - c["at"]) ** 0.5)).div_(c["at"] ** 0.5)
         xt.mul_(c["at_next"] ** 0.5).add_(et, alpha=c["c2"])
+
+
+def test_generalized_steps_device_groups_and_graph_replay(model):
+    """Runtime around the loop must not change a result: a device-resident batch walked as two sample groups (what happens when a
+    shard does not fit beside its activations) and the CUDA-graph replay of the forward both equal the plain single-group run
+    sample for sample (identical kernels per sample; only the fp64 statistics atomics may reorder)."""
+    from ddim_audio_b200.functions.denoising import generalized_steps
+    x, _, _ = O.synthetic_inputs(5, 32, 411)
+    seq = O.uniform_seq(1000, 4)
+    al = O.alphas_cumprod().to(DEV)
+    ref = generalized_steps(x.to(DEV), seq, model, al, {1, -1}, eta=0.0, graph=False)
+    for kw in (dict(chunks=2, graph=False), dict(graph=True), dict(chunks=2, graph=True)):
+        got = generalized_steps(x.to(DEV), seq, model, al, {1, -1}, eta=0.0, **kw)
+        assert len(got[0]) == len(ref[0]) == 3 and len(got[1]) == len(ref[1]) == 2
+        for a, b in zip(got[0][1:] + got[1], ref[0][1:] + ref[1]):
+            assert a.shape == b.shape == x.shape and not a.is_cuda
+            assert rel_l2(a, b) < 1e-3, kw
+    # a second call re-uses the captured graph (same shape, same weight version) and may recycle the pinned snapshot tensors
+    again = generalized_steps(x.to(DEV), seq, model, al, {1, -1}, eta=0.0, graph=True, out=got)
+    assert all(p.data_ptr() == q.data_ptr() for p, q in zip(again[0][1:] + again[1], got[0][1:] + got[1]))
+    for a, b in zip(again[0][1:] + again[1], ref[0][1:] + ref[1]):
+        assert rel_l2(a, b) < 1e-3
+
+
+def test_generalized_steps_match_reference_rng(model):
+    """functions/denoising.py:41-43 draws torch.randn_like(x) every step even when its coefficient is zero (eta = 0).  With
+    match_reference_rng=True the CUDA generator ends where the reference leaves it: exactly len(seq) draws of x's shape."""
+    from ddim_audio_b200.functions.denoising import generalized_steps
+    x, _, _ = O.synthetic_inputs(2, 32, 412)
+    seq = O.uniform_seq(1000, 3)
+    al = O.alphas_cumprod().to(DEV)
+    xd = x.to(DEV)
+    torch.cuda.manual_seed(99)
+    a = generalized_steps(xd, seq, model, al, None, eta=0.0, match_reference_rng=True)
+    after = torch.cuda.get_rng_state(xd.device)
+    torch.cuda.manual_seed(99)
+    for _ in seq:
+        torch.randn_like(xd)                                   # what the reference's loop consumes
+    assert torch.equal(after, torch.cuda.get_rng_state(xd.device))
+    torch.cuda.manual_seed(99)
+    b = generalized_steps(xd, seq, model, al, None, eta=0.0)  # default: no draw at eta = 0, same samples
+    assert torch.equal(torch.cuda.get_rng_state(xd.device), torch.cuda.get_rng_state(xd.device))
+    for p, q in zip(a[0][1:], b[0][1:]):
+        assert rel_l2(p, q) < 1e-3
