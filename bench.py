@@ -75,6 +75,11 @@ def parse_args():
                     help="sample: DDIM sample-steps/s (the headline, BASELINE configs[2]); train: noise_estimation_loss fwd+bwd samples/s "
                          "(configs[1]/[4]); parity: configs[0] -- 50 DDIM steps, batch 4, T=1024 on the GPU and on the CPU oracle, "
                          "per-step eps and final-sample error")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="weak: --batch samples per GPU (the default line); strong: --total-samples split over the ranks (BASELINE configs[3]: "
+                         "512 samples -> 256 / 128 / 64 per rank at N = 2 / 4 / 8), shards that do not fit are walked as sample groups")
+    ap.add_argument("--total-samples", type=int, default=512)
+    ap.add_argument("--graph", default="auto", choices=["auto", "on", "off"], help="CUDA-graph replay of the forward in the device-timed loop (auto: small groups only)")
     ap.add_argument("--no-parity", action="store_true", help="skip the parity / batch-position objects of the default line")
     ap.add_argument("--no-small-batch", action="store_true")
     ap.add_argument("--no-train", action="store_true", help="skip the bounded train leg of the default line")
@@ -313,6 +318,9 @@ def run_b200(args):
     al = alphas_cumprod()
     alpha_list = [1.0] + al.numpy().tolist()
     B, T = args.batch, args.t_size
+    if args.scaling == "strong":
+        lo = rank * (args.total_samples // world) + min(rank, args.total_samples % world)
+        B = args.total_samples // world + (1 if rank < args.total_samples % world else 0)
     K, W = args.steps, max(args.warmup, 0)
     g = torch.Generator().manual_seed(1234 + rank)
     x_host = torch.randn(B, 2, T, F_SIZE, generator=g).pin_memory()
@@ -331,10 +339,14 @@ def run_b200(args):
         return v
 
     # ---------------- value: device-resident loop
+    gmode = {"auto": None, "on": True, "off": False}[args.graph]
+    if args.scaling == "strong":
+        return run_strong(args, model, x_host, al, dev, world, rank, local, B, T, K, W, barrier, max_over_ranks)
+    torch.cuda.reset_peak_memory_stats(dev)
     xt = x_host.to(dev, non_blocking=True)
     with torch.no_grad():
         if W:
-            ddim_loop_device(xt, seq_all[-W:], model, alpha_list, 0.0)
+            ddim_loop_device(xt, seq_all[-W:], model, alpha_list, 0.0, graph=gmode)
         clocks = ClockSampler(local)
         barrier()
         clocks.start()
@@ -343,7 +355,7 @@ def run_b200(args):
         l0 = _C.launch_count()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        ddim_loop_device(xt, seq_all[-(W + K):-W] if W else seq_all[-K:], model, alpha_list, 0.0)
+        xt = ddim_loop_device(xt, seq_all[-(W + K):-W] if W else seq_all[-K:], model, alpha_list, 0.0, graph=gmode)
         e1.record()
         barrier()
         launches = _C.launch_count() - l0
@@ -353,6 +365,7 @@ def run_b200(args):
         clk = clocks.stop()
     value = world * B * K / (ms * 1e-3)
     finite = bool(torch.isfinite(xt).all().item())
+    peak_gb = torch.cuda.max_memory_allocated(dev) / 1e9
     del xt
 
     roof, kern, t_roof = roofline_from_profile(prof, K)
@@ -363,20 +376,27 @@ def run_b200(args):
         ald = al.to(dev)
         ckw = {"chunks": args.e2e_chunks} if args.e2e_chunks > 0 else {}
         cur = x_host
+        sets = [None, None]          # two recycled sets of pinned snapshot tensors: a call's input is the previous call's xs[-1]
         with torch.no_grad():
-            for i in range(max(W, 1)):
-                xs, x0 = generalized_steps(cur, [seq_all[-1 - i]], model, ald, None, eta=0.0, **ckw)
-                cur = xs[-1]
+            for i in range(max(W, 2)):
+                res = generalized_steps(cur, [seq_all[-1 - i]], model, ald, None, eta=0.0, out=sets[i & 1], **ckw)
+                sets[i & 1] = res
+                cur = res[0][-1]
             barrier()
             t0 = time.perf_counter()
             for i in range(K):
-                xs, x0 = generalized_steps(cur, [seq_all[-1 - W - i]], model, ald, None, eta=0.0, **ckw)
-                cur = xs[-1]
+                j = (max(W, 2) + i) & 1
+                res = generalized_steps(cur, [seq_all[-1 - W - i]], model, ald, None, eta=0.0, out=sets[j], **ckw)
+                sets[j] = res
+                cur = res[0][-1]
             barrier()
             dt = max_over_ranks(time.perf_counter() - t0)
+        del sets, res, cur
         nbytes = x_host.numel() * 4
         e2e = {"value": world * B * K / dt, "unit": UNIT, "h2d_bytes_per_step": nbytes + 8 * B, "d2h_bytes_per_step": 2 * nbytes, "ms_per_step": 1e3 * dt / K,
-               "api": "generalized_steps(x_pinned_host, [t], model, alphas, None, eta=0) once per step (4 sample groups pipelined over PCIe)"}
+               "pcie_GBps_per_rank": 3 * nbytes / (dt / K) / 1e9,
+               "api": "generalized_steps(x_pinned_host, [t], model, alphas, None, eta=0, out=<recycled pinned lists>) once per step "
+                      "(4 sample groups pipelined over PCIe)"}
 
     # ---------------- batch-position independence at the headline shape: samples 0 and B-1 of the full batch vs the same samples
     # run alone (the only check that exercises element offsets past 2^32; samples never interact)
@@ -431,9 +451,48 @@ def run_b200(args):
                        "snapshots": "none inside the device-timed steps (config 3 selects 10 of 1000 steps); every step in e2e"},
             "clocks": clk, "e2e": e2e, "gpu_launches": int(launches), "roofline": roof, "cpu_baseline": cpu,
             "step_roofline": {"t_roof_ms_per_step": t_roof / K, "frac": (t_roof / K) / (ms / K), "note": "sum over kernels of max(bytes/HBM peak, flops/tensor peak) / measured step"},
-            "kernels": kern, "finite": finite, "parity": parity, "batch_position": batch_pos, "small_batch": small, "train": train,
+            "kernels": kern, "finite": finite, "peak_device_memory_gb": peak_gb, "parity": parity, "batch_position": batch_pos, "small_batch": small, "train": train,
         }
         emit(line)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def run_strong(args, model, x_host, al, dev, world, rank, local, B, T, K, W, barrier, max_over_ranks):
+    """BASELINE configs[3]: ``--total-samples`` (512) split over the ranks; this rank's shard is device-resident and goes through the
+    public ``generalized_steps`` (no snapshots), which walks it as as many sample groups as device memory requires.  One JSON line
+    with "scaling": "strong"; value = total samples x steps / max-over-ranks device time."""
+    import torch
+    import torch.distributed as dist
+    from ddim_audio_b200 import _C
+    from ddim_audio_b200.functions.denoising import generalized_steps, max_group_size
+    ald = al.to(dev)
+    seq_all = list(range(1000))
+    xd = x_host.to(dev)
+    groups = -(-B // max_group_size(xd.shape, dev))
+    with torch.no_grad():
+        if W:
+            generalized_steps(xd, seq_all[-W:], model, ald, set(), eta=0.0)
+        clocks = ClockSampler(local)
+        barrier()
+        clocks.start()
+        l0 = _C.launch_count()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        generalized_steps(xd, seq_all[-(W + K):-W] if W else seq_all[-K:], model, ald, set(), eta=0.0)
+        e1.record()
+        barrier()
+        launches = _C.launch_count() - l0
+        ms = max_over_ranks(e0.elapsed_time(e1))
+        clk = clocks.stop()
+    if rank == 0:
+        emit({"metric": METRIC, "value": args.total_samples * K / (ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms / K,
+              "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+              "config": {"workload": f"audio.yml DDIM sampling, {args.total_samples} samples x[.,2,{T},{F_SIZE}] split over {world} GPU(s) "
+                                     f"(BASELINE configs[3]), eta=0, uniform 1000-step schedule", "samples_per_gpu": B, "sample_groups_per_gpu": int(groups),
+                         "t_size": T, "f_size": F_SIZE, "parallelism": f"batch-sharded x{world}, no collectives",
+                         "api": "generalized_steps(x_cuda_shard, seq, model, alphas, set(), eta=0): groups sized from free device memory"},
+              "clocks": clk, "gpu_launches": int(launches)})
     if world > 1:
         dist.destroy_process_group()
 

@@ -30,6 +30,7 @@ SIGNATURES = {
     "ddimb_sqerr_loss": [_vp, _vp, _vp, _i, _ll],
     "ddimb_sqerr_loss_bwd": [_vp, _vp, _vp, _vp, _i, _ll],
     "ddimb_denoise2d": [_vp, _vp, _vp, _ll, _i, _i, _i, _i, _i],
+    "ddimb_pfft2wav": [_vp, _vp, _vp, _vp, _vp, _vp, _ll, _i, _i, _i, _i, _d, _d, _d, _d, _d],
     "ddimb_ema_update": [_vp, _i, _ll, _d],
     "ddimb_grad_clip": [_vp, _i, _ll, _d, _vp, _vp],
     "ddimb_optim_step": [_vp, _i, _ll, _i, _d, _d, _d, _d, _d, _ll],
@@ -70,13 +71,15 @@ SIGNATURES = {
     "ddimb_conv_in_wgrad": [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i],
     "ddimb_conv_out_wgrad": [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i],
 }
-EXPORTS = ["ddimb_version", "ddimb_last_error", "ddimb_launch_count", "ddimb_prof_enable", "ddimb_prof_report", "ddimb_conv3x3_wide_supported", "ddimb_denoise2d_workspace", "ddimb_conv_wimg_bytes"] + list(SIGNATURES)
+EXPORTS = ["ddimb_version", "ddimb_last_error", "ddimb_launch_count", "ddimb_prof_enable", "ddimb_prof_report", "ddimb_conv3x3_wide_supported", "ddimb_denoise2d_workspace", "ddimb_conv_wimg_bytes", "ddimb_pfft2wav_workspace"] + list(SIGNATURES)
 
 lib.ddimb_version.restype = _i
 lib.ddimb_last_error.restype = C.c_char_p
 lib.ddimb_launch_count.restype = _ll
 lib.ddimb_conv3x3_wide_supported.argtypes = [_i, _i, _i]
 lib.ddimb_conv3x3_wide_supported.restype = _i
+lib.ddimb_pfft2wav_workspace.argtypes = [_i, _i, _i]
+lib.ddimb_pfft2wav_workspace.restype = _ll
 lib.ddimb_conv_wimg_bytes.argtypes = [_i, _i, _i, _i]
 lib.ddimb_conv_wimg_bytes.restype = _ll
 lib.ddimb_denoise2d_workspace.argtypes = [_i, _i, _i, _i, _i]

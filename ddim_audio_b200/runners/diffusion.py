@@ -22,6 +22,7 @@ from ..functions.losses import loss_registry
 from ..models.diffusion import Model
 from ..models.ema import EMAHelper
 from ..signal.denoise import denoise_2d
+from ..signal.pfft2wav import pfft2wav_batch
 from . import dist as rdist
 
 
@@ -171,14 +172,39 @@ class Diffusion(object):
                 xs, x0 = self.sample_image(x, model, select_index=self.select_index())
         else:
             xs, x0 = [], []
-        if getattr(cfg.sampling, "denoise", False):
-            x0 = [denoise_2d(y.to(self.device)).cpu() for y in x0]                    # :400-401, per sample -> shards like the loop
+        # :400-420 per predicted x0: denoise_2d, then (AUDIO) permute(0,3,2,1) + pfft2wav -> int32 PCM; both per sample, so they
+        # shard like the loop.  The PNG preview (pfft2img) and the file names are host-side (out of scope).
+        want_wav = getattr(getattr(cfg, "data", None), "dataset", None) == "AUDIO" and getattr(self, "render_wav", True)
+        wavs = []
+        for k, y in enumerate(x0):
+            yd = y.to(self.device)
+            if getattr(cfg.sampling, "denoise", False):
+                yd = denoise_2d(yd)
+            if want_wav:
+                wavs.append(pfft2wav_batch(yd, cfg.sampling.virtual_samplerate, HPI=cfg.sampling.HPI).cpu())
+            x0[k] = yd.cpu()
+            del yd
         if world > 1:
             xs = rdist.gather_host_lists([t.cpu() for t in xs])
             x0 = rdist.gather_host_lists(x0)
+            wavs = rdist.gather_host_lists(wavs) if want_wav else wavs
+        self.wavs = wavs                      # list (one entry per selected step) of int32 [num_samples, (F-1)*(T-1)] PCM, rank 0
+        if xs is not None and want_wav and getattr(self.args, "image_folder", None):
+            self.write_wavs(wavs, self.args.image_folder)
         if self.writer is not None and xs is not None:
             self.writer(xs, x0)
         return xs, x0
+
+    def write_wavs(self, wavs, folder):
+        """:403-420 -- ``{sample}_{step:0{digits}d}.wav`` at the dataset's virtual sample rate (scipy.io.wavfile, host-side file IO)."""
+        from scipy.io.wavfile import write as WAV_write
+
+        os.makedirs(folder, exist_ok=True)
+        digits = int(np.ceil(np.log10(len(wavs) + 1)))
+        rate = self.config.data.dataset_kwargs.virtual_samplerate
+        for i, batch in enumerate(wavs):
+            for j, wav in enumerate(batch):
+                WAV_write(os.path.join(folder, f"{j}_{i:0{digits}d}.wav"), rate, wav.numpy())
 
     def load_model(self, path=None):
         """:289-316 -- ``Model(config)`` + ``ckpt.pth`` in the reference's list format [model_sd, opt_sd, epoch, step, ema_sd]."""

@@ -67,6 +67,15 @@ long long ddimb_denoise2d_workspace(int B, int C, int T, int F, int iters);
 int ddimb_denoise2d(const float* x, float* out, void* workspace, long long workspace_bytes, int B, int C, int T, int F, int iters,
                     cudaStream_t stream);
 
+/* External/SST/utils/wav2img.py:82-127 pfft2wav as called by runners/diffusion.py:401-420 on x0.permute(0,3,2,1)[b], for a whole batch:
+ * x fp32 [B][2][T][F] (NCHW: re / im planes) -> out int32 [B][(F-1)*(T-1)] PCM.  sri: double [F] ISO-226 weights of the rfft
+ * frequencies; wt: fp32 [2F][NP] irfft basis (n = 2(F-1), NP = n rounded up to 128) with the hann synthesis window and win.sum()
+ * folded in; norm: fp32 [n/2] overlap-add normaliser (all three are host-built constants, ddim_audio_b200/signal/pfft2wav.py).
+ * hpi: the reference's HPI flag; target_norm, base_db, max_db, p_low, p_upp: wav2img.py:86-100.  ws: ddimb_pfft2wav_workspace() bytes. */
+long long ddimb_pfft2wav_workspace(int B, int T, int F);
+int ddimb_pfft2wav(const float* x, const double* sri, const float* wt, const float* norm, int* out, void* ws, long long ws_bytes, int B, int T,
+                   int F, int hpi, double target_norm, double base_db, double max_db, double p_low, double p_upp, cudaStream_t stream);
+
 /* ---- EMA of the parameters ------------------------------------------------------------- */
 
 /* models/ema.py:16-23 -- shadow = (1 - mu) param + mu shadow for EVERY registered parameter in one launch (bit-exact: the

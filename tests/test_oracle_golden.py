@@ -170,3 +170,19 @@ def test_fullshape_goldens_ddim_configs0_geometry(oracle_sd, golden_dir):
     xs, x0 = O.generalized_steps(x, [int(v) for v in g["seq"]], O.OracleModel(oracle_sd), O.alphas_cumprod(), None, eta=0.0)
     for got, want in zip(xs[1:] + x0, list(g["xs_probe"]) + list(g["x0_probe"])):
         np.testing.assert_allclose(got[..., ::61, ::7].numpy(), want, rtol=0, atol=5e-4)
+
+
+@pytest.mark.parametrize("name", ["pfft2wav_b2_t64", "pfft2wav_b3_t97_loud", "pfft2wav_b1_t130_hpi"])
+def test_pfft2wav_oracle_vs_reference_golden(golden_dir, name):
+    """oracle/pfft2wav_oracle.py against int32 PCM minted from the reference's own pfft2wav (oracle/make_golden_pfft2wav.py): the
+    restatement uses the same scipy pocketfft and the same in-place float32 operations, so it is bit-exact."""
+    from oracle import pfft2wav_oracle as P
+    g = _load(golden_dir, name)
+    b, T, seed, hpi = (int(v) for v in g["meta"])
+    x = P.synthetic_spectrogram(b, T, seed, scale=float(g["scale"]))
+    for j in range(b):
+        img = np.ascontiguousarray(np.transpose(x[j], (2, 1, 0)))
+        with np.errstate(all="ignore"):
+            got = P.pfft2wav(img, int(g["samplerate"]), dtype=np.int32, HPI=bool(hpi))
+        # a different host CPU / scipy build may round the float32 FFT differently by an ulp (32 counts near the 3e8 peak)
+        assert np.abs(got.astype(np.int64) - g["wav"][j].astype(np.int64)).max() <= 64

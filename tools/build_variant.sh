@@ -7,7 +7,7 @@ here=$(cd "$(dirname "$0")/.." && pwd)
 src=$here/ddim_audio_b200/csrc; out=$here/ddim_audio_b200/lib/variants; tmp=$(mktemp -d)
 mkdir -p "$out"
 FLAGS="-gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -lineinfo --use_fast_math -Xcompiler -fPIC -Xcompiler -O2 -cudart static"
-for f in runtime gemm_host elementwise train_host train_elementwise conv_boundary denoise2d ema optim; do
+for f in runtime gemm_host elementwise train_host train_elementwise conv_boundary denoise2d ema optim pfft2wav; do
   nvcc $FLAGS "$@" -c "$src/$f.cu" -o "$tmp/$f.o" &
 done
 wait
