@@ -117,6 +117,10 @@ def ptr(t, dtype=None):
         raise RuntimeError(f"ddim_audio_b200: expected {dtype}, got {t.dtype}")
     if not t.is_contiguous():
         raise RuntimeError("ddim_audio_b200: expected a contiguous tensor")
+    if t.device.index != torch.cuda.current_device():
+        # launches go to torch.cuda.current_stream() of the CURRENT device; a tensor of another GPU would be launched on the wrong one
+        raise RuntimeError(f"ddim_audio_b200: tensor on {t.device} but the current CUDA device is {torch.cuda.current_device()} "
+                           "(wrap the call in torch.cuda.device(tensor.device))")
     return t.data_ptr()
 
 

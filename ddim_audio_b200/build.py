@@ -18,8 +18,12 @@ SOURCES = ["runtime.cu", "gemm_host.cu", "elementwise.cu", "train_host.cu", "tra
 HEADERS = ["common.cuh", "umma_gemm.cuh", "conv_wide.cuh", "conv_window.cuh", "conv_out_tc.cuh", "conv_in_tc.cuh", "conv_down_wide.cuh", "conv_up_wide.cuh", "gemm_tn.cuh", "tmap.cuh", os.path.join("..", "..", "include", "ddim_b200.h")]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo",
-    "--use_fast_math", "-Xcompiler", "-fPIC", "-Xcompiler", "-O2", "-cudart", "static", "-Xptxas", "-v",
+    "-Xcompiler", "-fPIC", "-Xcompiler", "-O2", "-cudart", "static", "-Xptxas", "-v",
 ]
+# --use_fast_math (approximate division / sqrt, flush-to-zero) only for the translation units whose arithmetic is bf16-storage GEMM
+# epilogues and activation passes; the fp32 kernels that promise the reference's operation order or bit-exactness (DDIM update,
+# q-sample, loss, optimizers, EMA, denoise_2d, the WAV codec) are compiled with IEEE division / sqrt and denormals
+FAST_MATH = {"gemm_host.cu", "train_host.cu", "train_elementwise.cu", "conv_boundary.cu"}
 
 
 def _nvcc() -> str:
@@ -34,7 +38,7 @@ def _digest() -> str:
     for f in SOURCES + HEADERS:
         with open(os.path.join(CSRC, f), "rb") as fh:
             h.update(fh.read())
-    h.update(" ".join(NVCC_FLAGS).encode())
+    h.update((" ".join(NVCC_FLAGS) + " fast:" + ",".join(sorted(FAST_MATH))).encode())
     return h.hexdigest()
 
 
@@ -48,7 +52,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
     log = []
     for src in SOURCES:
         obj = os.path.join(LIBDIR, src.replace(".cu", ".o"))
-        cmd = [_nvcc(), *NVCC_FLAGS, "-c", os.path.join(CSRC, src), "-o", obj]
+        cmd = [_nvcc(), *NVCC_FLAGS, *(["--use_fast_math"] if src in FAST_MATH else []), "-c", os.path.join(CSRC, src), "-o", obj]
         r = subprocess.run(cmd, capture_output=True, text=True)
         log.append(r.stderr)
         if r.returncode != 0:

@@ -50,15 +50,25 @@ struct DdimbProfScope {
     }                                                                                          \
   } while (0)
 
+// per-device caches (a process may drive several GPUs): SM count, and "this kernel's dynamic shared-memory opt-in has been set"
 static inline int ddimb_num_sms() {
-  static int n = 0;
-  if (n == 0) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
-  }
-  return n;
+  static int n[64] = {0};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 0 || dev >= 64) return 148;
+  if (n[dev] == 0 && (cudaDeviceGetAttribute(&n[dev], cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n[dev] <= 0)) n[dev] = 148;
+  return n[dev];
 }
+#define DDIMB_SMEM_ATTR(kernel, bytes)                                                                          \
+  do {                                                                                                          \
+    static bool done__[64] = {false};                                                                           \
+    int dev__ = 0;                                                                                              \
+    cudaGetDevice(&dev__);                                                                                      \
+    if (dev__ < 0 || dev__ >= 64 || !done__[dev__]) {                                                           \
+      DDIMB_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));             \
+      if (dev__ >= 0 && dev__ < 64) done__[dev__] = true;                                                       \
+    }                                                                                                           \
+  } while (0)
 
 #ifdef __CUDACC__
 namespace ddimb {

@@ -234,11 +234,8 @@ extern "C" int ddimb_conv_out(const void* x, const void* skip, const float* w, c
   const int strips = (F + 127) / 128;
   const int units = strips * ((T + kStripRows - 1) / kStripRows);
   const int smem = 3 * kRingRowFloats * (int)sizeof(float);
-  static bool attr = false;
-  if (!attr) {
-    DDIMB_CUDA(cudaFuncSetAttribute(conv_out_strip_kernel<32, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    attr = true;
-  }
+  auto strip_kernel = conv_out_strip_kernel<32, 2>;
+  DDIMB_SMEM_ATTR(strip_kernel, smem);
   conv_out_strip_kernel<32, 2><<<dim3(units, B), 128, smem, stream>>>(reinterpret_cast<const __nv_bfloat16*>(x),
                                                                       reinterpret_cast<const __nv_bfloat16*>(skip), out, T, F, strips);
   DDIMB_LAUNCH_CHECK();

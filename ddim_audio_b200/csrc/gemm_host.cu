@@ -99,11 +99,8 @@ static int launch_gemm(GemmParams& p, const CUtensorMap& tmA, const CUtensorMap&
   // (CK, accumulator columns, channels) instantiations: every convolution shape of audio.yml (ch 32..256), plus the generic GEMM
 #define DDIMB_GEMM_CASE(CKV, NACCV, CMODV)                                                                                       \
   if (ck == CKV && nacc_t == NACCV && cmod_t == CMODV) {                                                                         \
-    static bool attr = false;                                                                                                    \
-    if (!attr) {                                                                                                                 \
-      DDIMB_CUDA(cudaFuncSetAttribute(umma_gemm_kernel<CKV, NACCV, CMODV>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem)); \
-      attr = true;                                                                                                               \
-    }                                                                                                                            \
+    auto kernel__ = umma_gemm_kernel<CKV, NACCV, CMODV>;                                                                         \
+    DDIMB_SMEM_ATTR(kernel__, max_smem);                                                                                         \
     umma_gemm_kernel<CKV, NACCV, CMODV><<<grid, kGemmThreads, smem, stream>>>(tmA, tmB, tmO, tmS, p);                            \
     launched = true;                                                                                                             \
   }
@@ -255,12 +252,10 @@ static int launch_conv_wide(const void* x, const double* gn_stats, const float* 
   p.bias = bias; p.bias_b = bias_b; p.stats = stats; p.bias_b_stride = bias_b_stride; p.act = act;
   const int grid = p.num_units < ddimb_num_sms() ? p.num_units : ddimb_num_sms();
   if (C == 32) {
-    static bool attr = false;
-    if (!attr) { DDIMB_CUDA(cudaFuncSetAttribute(conv3x3_wide_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, WideCfg<32>::kSmemBytes)); attr = true; }
+    DDIMB_SMEM_ATTR(conv3x3_wide_kernel<32>, WideCfg<32>::kSmemBytes);
     conv3x3_wide_kernel<32><<<grid, kWideThreads, WideCfg<32>::kSmemBytes, stream>>>(tmA, tmB, tmO, p);
   } else {
-    static bool attr = false;
-    if (!attr) { DDIMB_CUDA(cudaFuncSetAttribute(conv3x3_wide_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, WideCfg<64>::kSmemBytes)); attr = true; }
+    DDIMB_SMEM_ATTR(conv3x3_wide_kernel<64>, WideCfg<64>::kSmemBytes);
     conv3x3_wide_kernel<64><<<grid, kWideThreads, WideCfg<64>::kSmemBytes, stream>>>(tmA, tmB, tmO, p);
   }
   DDIMB_LAUNCH_CHECK();
@@ -313,8 +308,7 @@ static int launch_conv_window(const void* x, const uint8_t* wimg, const float* b
     int r = make_tmap_bf16(&tmA, x, 4, dims, str, box, 32);
     if (r) return r;
   }
-  static bool attr = false;
-  if (!attr) { DDIMB_CUDA(cudaFuncSetAttribute(conv3x3_window_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448)); attr = true; }
+  DDIMB_SMEM_ATTR(conv3x3_window_kernel, 232448);
   const int grid = p.num_units < ddimb_num_sms() ? p.num_units : ddimb_num_sms();
   conv3x3_window_kernel<<<grid, kWinThreads, smem, stream>>>(tmA, p);
   DDIMB_LAUNCH_CHECK();
@@ -342,8 +336,7 @@ int ddimb_conv_out_tc(const void* x, const void* skip, const uint8_t* wimg, cons
   if (r) return r;
   r = make_tmap_bf16(&tmS, skip ? skip : x, 4, dims, str, box, 32);
   if (r) return r;
-  static bool attr = false;
-  if (!attr) { DDIMB_CUDA(cudaFuncSetAttribute(conv_out_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kCoSmem)); attr = true; }
+  DDIMB_SMEM_ATTR(conv_out_tc_kernel, kCoSmem);
   const int grid = p.num_units < ddimb_num_sms() ? p.num_units : ddimb_num_sms();
   conv_out_tc_kernel<<<grid, kCoThreads, kCoSmem, stream>>>(tmX, tmS, p);
   DDIMB_LAUNCH_CHECK();
@@ -362,8 +355,7 @@ int ddimb_conv_in_tc(const float* x, const uint8_t* wimg, const float* bias, voi
   while (rt > 8 && (long long)B * (F / 128) * ceil_div(T, rt) < 4LL * ddimb_num_sms()) rt /= 2;
   p.RT = rt; p.units_t = ceil_div(T, rt); p.num_units = B * (F / 128) * p.units_t;
   p.x = x; p.wimg = wimg; p.bias = bias; p.out = reinterpret_cast<__nv_bfloat16*>(out); p.stats = stats;
-  static bool attr = false;
-  if (!attr) { DDIMB_CUDA(cudaFuncSetAttribute(conv_in_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kCiSmem)); attr = true; }
+  DDIMB_SMEM_ATTR(conv_in_tc_kernel, kCiSmem);
   const int grid = p.num_units < ddimb_num_sms() ? p.num_units : ddimb_num_sms();
   CUtensorMap tmO;
   {
@@ -521,8 +513,7 @@ static int launch_conv_down_wide(const void* x, const uint8_t* wimg, const float
     int r = make_tmap_bf16(&tmA, x, 4, dims, str, box, 64);
     if (r) return r;
   }
-  static bool attr = false;
-  if (!attr) { DDIMB_CUDA(cudaFuncSetAttribute(conv_down_wide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kDwSmem)); attr = true; }
+  DDIMB_SMEM_ATTR(conv_down_wide_kernel, kDwSmem);
   const int grid = p.num_units < ddimb_num_sms() ? p.num_units : ddimb_num_sms();
   conv_down_wide_kernel<<<grid, kDwThreads, kDwSmem, stream>>>(tmA, p);
   DDIMB_LAUNCH_CHECK();
@@ -617,8 +608,7 @@ static int launch_conv_up_wide(const void* x, const uint8_t* wimg, const float* 
     r = make_tmap_bf16(&tmS, skip ? skip : out, 4, dims, str, box, 64);
     if (r) return r;
   }
-  static bool attr = false;
-  if (!attr) { DDIMB_CUDA(cudaFuncSetAttribute(conv_up_wide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kUwSmem)); attr = true; }
+  DDIMB_SMEM_ATTR(conv_up_wide_kernel, kUwSmem);
   const int grid = p.num_units < ddimb_num_sms() ? p.num_units : ddimb_num_sms();
   conv_up_wide_kernel<<<grid, kUwThreads, kUwSmem, stream>>>(tmA, tmO, tmS, p);
   DDIMB_LAUNCH_CHECK();

@@ -55,7 +55,10 @@ __global__ void __launch_bounds__(256) grad_clip_kernel(const OptChunk* __restri
                                                         float* __restrict__ norm_out) {
   const float total = (float)sqrt(*sqnorm);
   if (blockIdx.x == 0 && threadIdx.x == 0 && norm_out) *norm_out = total;
-  const float coef = fminf(__fdiv_rn(max_norm, total + 1e-6f), 1.0f);
+  // torch clamps with max=1.0, which lets a NaN total norm through to every gradient (the divergence shows up loudly); fminf would
+  // silently return 1
+  const float c0 = __fdiv_rn(max_norm, total + 1e-6f);
+  const float coef = (c0 < 1.0f || c0 != c0) ? c0 : 1.0f;
   const OptChunk c = table[blockIdx.x];
   const int n4 = vec4_count(c);
   float4* g4 = reinterpret_cast<float4*>(c.g);

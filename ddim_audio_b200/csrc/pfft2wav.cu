@@ -186,11 +186,7 @@ extern "C" int ddimb_pfft2wav(const float* x, const double* sri, const float* wt
   const int lo = (int)(T * p_low), hi = (int)(T * p_upp);      // wav2img.py:112 int(len(s_HPI) * p)
   DDIMB_CHECK_ARG(hi < T && lo <= hi);
   const int smem = npow2 * 8;
-  static int attr_smem = 0;   // largest opt-in requested so far (per process; the attribute is sticky per device context)
-  if (smem > 48 * 1024 && smem > attr_smem) {
-    DDIMB_CUDA(cudaFuncSetAttribute(window_gain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    attr_smem = smem;
-  }
+  DDIMB_SMEM_ATTR(window_gain_kernel, kMaxT * 8);
   window_gain_kernel<<<B, 1024, smem, stream>>>(s, gain, T, npow2, lo, hi, target_norm, base_db, max_db);
   DDIMB_LAUNCH_CHECK();
   const int64_t M = (int64_t)B * T;

@@ -35,11 +35,7 @@ static int launch_tn(TnParams& p, const CUtensorMap& tmX, const CUtensorMap& tmY
   p.num_stages = stages;
   int smem = 1024 + stages * stage_bytes + 1024;
   if (smem < 120 * 1024) smem = 120 * 1024;   // one CTA per SM: TMEM allocation never contends
-  static bool attr = false;
-  if (!attr) {
-    DDIMB_CUDA(cudaFuncSetAttribute(gemm_tn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
-    attr = true;
-  }
+  DDIMB_SMEM_ATTR(gemm_tn_kernel, max_smem);
   gemm_tn_kernel<<<p.njobs * p.splits, kTnThreads, smem, stream>>>(tmX, tmY, p);
   DDIMB_LAUNCH_CHECK();
   return DDIMB_OK;

@@ -74,13 +74,15 @@ def clip_grad_norm_(parameters, max_norm, norm_type=2.0):
         raise NotImplementedError("ddim_audio_b200.clip_grad_norm_: only the L2 norm the reference uses")
     if isinstance(parameters, torch.Tensor):
         parameters = [parameters]
+    parameters = list(parameters)
     grads = [p.grad for p in parameters if p.grad is not None]
     if not grads:
         return torch.tensor(0.0)
     if not grads[0].is_cuda:
         raise RuntimeError("ddim_audio_b200.optim: gradients must be CUDA tensors (there is no CPU path)")
     dev = grads[0].device
-    slot = _clip_tables.setdefault((dev, len(grads)), (ChunkTable(), torch.zeros(1, dtype=torch.float64, device=dev)))
+    key = (dev, tuple(id(p) for p in parameters))        # one table per parameter list: two groups of equal length must not share (and rebuild) one
+    slot = _clip_tables.setdefault(key, (ChunkTable(), torch.zeros(1, dtype=torch.float64, device=dev)))
     table, total = slot[0].get([None, grads, None, None], dev, check=lambda: _check(grads, "gradients"))
     norm = torch.empty((), dtype=torch.float32, device=dev)
     _C.call("ddimb_grad_clip", _C.ptr(table), table.shape[0], total, float(max_norm), _C.ptr(slot[1]), _C.ptr(norm))
