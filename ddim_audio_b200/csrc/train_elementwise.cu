@@ -277,9 +277,48 @@ __global__ void __launch_bounds__(256) colsum_kernel(const T* __restrict__ x, in
   }
 }
 
+// Contiguous bf16 [rows][C] with C in {32, 64, 96, 128, 192, 256}: the tensor is walked as a flat vector of 16-byte chunks; the block
+// size (256, or 192 when 96 divides C) makes a thread's stride a multiple of C, so a thread always meets the same 8 columns and keeps
+// 8 register sums; shared-memory atomics fold the block, one global atomicAdd per column per block.  (r02: the generic kernel above
+// used 32 of 256 lanes at C = 32 with 2-byte loads: 0.04 of HBM on the bias gradients of the level-0 Upsample.)
+template <int THREADS>
+__global__ void __launch_bounds__(THREADS) colsum_flat_bf16_kernel(const uint4* __restrict__ x, int64_t nchunks, int C, float* __restrict__ out) {
+  __shared__ float s_acc[256];
+  for (int c = threadIdx.x; c < C; c += THREADS) s_acc[c] = 0.f;
+  __syncthreads();
+  float acc[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+  for (int64_t i = (int64_t)blockIdx.x * THREADS + threadIdx.x; i < nchunks; i += (int64_t)gridDim.x * THREADS) {
+    const uint4 v = ddimb::ldg_nc_v4(x + i);
+    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float2 f = ddimb::unpack_bf16x2(w[j]);
+      acc[2 * j] += f.x;
+      acc[2 * j + 1] += f.y;
+    }
+  }
+  const int c0 = (threadIdx.x * 8) % C;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) atomicAdd(&s_acc[c0 + j], acc[j]);
+  __syncthreads();
+  for (int c = threadIdx.x; c < C; c += THREADS) atomicAdd(out + c, s_acc[c]);
+}
+
 extern "C" int ddimb_colsum(const void* x, int is_bf16, long long ld, long long rows, int C, float* out, cudaStream_t stream) {
   DDIMB_CHECK_ARG(x && out && rows >= 1 && C >= 1 && ld >= C);
   DDIMB_PROF(stream, "colsum", C, is_bf16, (double)rows * C * (is_bf16 ? 2 : 4), 0.0);
+  if (is_bf16 && ld == C && C % 32 == 0 && C <= 256 && (reinterpret_cast<uintptr_t>(x) & 15) == 0) {
+    const int64_t nchunks = rows * C / 8;
+    const int threads = (C % 96 == 0) ? 192 : 256;               // threads * 8 is a multiple of C
+    int64_t blocks = (nchunks + threads * 8 - 1) / (threads * 8);
+    if (blocks > 8 * ddimb_num_sms()) blocks = 8 * ddimb_num_sms();
+    if (threads == 192) colsum_flat_bf16_kernel<192><<<(unsigned)blocks, 192, 0, stream>>>(reinterpret_cast<const uint4*>(x), nchunks, C, out);
+    else colsum_flat_bf16_kernel<256><<<(unsigned)blocks, 256, 0, stream>>>(reinterpret_cast<const uint4*>(x), nchunks, C, out);
+    DDIMB_LAUNCH_CHECK();
+    return DDIMB_OK;
+  }
   int rpb = (int)((rows + 4 * ddimb_num_sms() - 1) / (4 * ddimb_num_sms()));
   if (rpb < 8) rpb = 8;
   const dim3 grid((unsigned)((rows + rpb - 1) / rpb), (unsigned)((C + 255) / 256));

@@ -251,6 +251,11 @@ def test_conv_in_out_wgrad_and_colsum(ops):
     out = torch.zeros(32, device=DEV)
     ops.colsum(g1, out)
     assert rel_l2(out, g1.float().sum(dim=(0, 1, 2))) < 1e-4
+    for C in (64, 96, 192, 256):                                   # flat 16-byte-chunk kernel: block size keeps a thread on the same 8 columns
+        gc = _bf(torch.randn(3, 7, 33, C, device=DEV, generator=g))
+        oc = torch.zeros(C, device=DEV)
+        ops.colsum(gc, oc)
+        assert rel_l2(oc, gc.float().sum(dim=(0, 1, 2))) < 1e-4, C
     f = torch.randn(1000, 512, device=DEV, generator=g)
     o2 = torch.zeros(512, device=DEV)
     ops.colsum(f, o2)
