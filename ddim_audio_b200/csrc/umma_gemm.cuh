@@ -711,7 +711,7 @@ struct WimgParams {
   int32_t ntaps, n_seg, ck, ldw, nblocks;
   TapDesc taps[kMaxTaps];
 };
-__global__ void __launch_bounds__(256) wimg_generic_kernel(const __nv_bfloat16* __restrict__ w, uint8_t* __restrict__ img, const __grid_constant__ WimgParams p) {
+static __global__ void __launch_bounds__(256) wimg_generic_kernel(const __nv_bfloat16* __restrict__ w, uint8_t* __restrict__ img, const __grid_constant__ WimgParams p) {
   const int blk = blockIdx.x;
   int t = 0;
   while (t + 1 < p.ntaps && p.taps[t + 1].img_blk <= blk) ++t;
