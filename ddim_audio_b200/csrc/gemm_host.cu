@@ -110,7 +110,7 @@ static int launch_gemm(GemmParams& p, const CUtensorMap& tmA, const CUtensorMap&
   DDIMB_GEMM_CASE(64, 192, 192) DDIMB_GEMM_CASE(64, 256, 256)
   DDIMB_GEMM_CASE(32, 64, 64) DDIMB_GEMM_CASE(64, 96, 96) DDIMB_GEMM_CASE(32, 128, 128)
   DDIMB_GEMM_CASE(64, 384, 192) DDIMB_GEMM_CASE(64, 256, 128) DDIMB_GEMM_CASE(64, 192, 96) DDIMB_GEMM_CASE(32, 128, 64)
-  DDIMB_GEMM_CASE(64, 64, 32)
+  DDIMB_GEMM_CASE(64, 64, 32) DDIMB_GEMM_CASE(64, 128, 64)
 #undef DDIMB_GEMM_CASE
   if (!launched) {
     ddimb_set_error("no tcgen05 kernel instantiation for CK=%d accumulator columns=%d channels=%d (audio.yml channel widths only)", ck, nacc_t, cmod_t);
@@ -126,6 +126,11 @@ static void init_params(GemmParams& p) {
   p.num_n_tiles = 1;
 }
 
+// K chunk of the convolution kernels.  Measured (r02, tools/ab_generic.sh): TMA delivers ~40 B/clk/SM into shared memory with
+// 128-byte box rows and ~30 with 64-byte rows, and the generic kernel is bound by that rate (every tile re-streams its taps' A boxes
+// and the whole weight image); running Cin = 96 as two zero-padded 64-channel chunks moves 33 % more bytes at the higher rate -- a
+// wash (Upsample 96->64: 3.96 -> 4.25 ms) -- so chunks stay exact divisors of Cin.  (TapDesc::k_valid keeps the padded form available.)
+static inline int conv_ck(int c) { return (c % 64 == 0) ? 64 : 32; }
 static inline int pick_ck(int c) { return (c % 64 == 0) ? 64 : 32; }
 
 // spatial tile of 128 positions inside one [T, W] image: full-width rows when W < 128, else a 128-wide strip
@@ -144,7 +149,7 @@ static void conv3x3_taps(GemmParams& p, int Cin, int Cout, int ck) {
       TapDesc& tp = p.taps[ky * 3 + kx];
       tp.da[0] = (int16_t)(kx - 1); tp.da[1] = (int16_t)(ky - 1); tp.da[2] = 0; tp.da[3] = 0;
       tp.a_c0 = 0; tp.b_k0 = (ky * 3 + kx) * Cin; tp.b_n0 = 0;
-      tp.nchunk = (int16_t)(Cin / ck); tp.nseg = 1; tp.tmem_col0 = 0;
+      tp.nchunk = (int16_t)ceil_div(Cin, ck); tp.k_valid = Cin; tp.nseg = 1; tp.tmem_col0 = 0;
     }
 }
 
@@ -161,7 +166,7 @@ static void down_taps(GemmParams& p, int Cin, int Cout, int ck) {
       TapDesc& tp = p.taps[nt++];
       tp.da[0] = (int16_t)grp[g][0]; tp.da[1] = (int16_t)kR[ky]; tp.da[2] = (int16_t)kDy[ky]; tp.da[3] = 0;
       tp.a_c0 = grp[g][1]; tp.b_k0 = (ky * 4 + grp[g][2]) * Cin; tp.b_n0 = 0;
-      tp.nchunk = (int16_t)(grp[g][3] * Cin / ck); tp.nseg = 1; tp.tmem_col0 = 0;
+      tp.nchunk = (int16_t)ceil_div(grp[g][3] * Cin, ck); tp.k_valid = grp[g][3] * Cin; tp.nseg = 1; tp.tmem_col0 = 0;
     }
   }
   p.ntaps = nt;
@@ -180,7 +185,7 @@ static void up_taps(GemmParams& p, int r, int Cin, int Cout, int ck) {
       const int dx = dxs[ix];
       TapDesc& tp = p.taps[nt++];
       tp.da[0] = (int16_t)dx; tp.da[1] = (int16_t)dy; tp.da[2] = 0; tp.da[3] = 0;
-      tp.a_c0 = 0; tp.b_k0 = 0; tp.nchunk = (int16_t)(Cin / ck);
+      tp.a_c0 = 0; tp.b_k0 = 0; tp.nchunk = (int16_t)ceil_div(Cin, ck); tp.k_valid = Cin;
       if (dx == 0) { tp.nseg = 2; tp.b_n0 = (ky * 4 + 1) * Cout; tp.tmem_col0 = 0; }        // s=0 -> kx=1, s=1 -> kx=2
       else if (dx < 0) { tp.nseg = 1; tp.b_n0 = (ky * 4 + 3) * Cout; tp.tmem_col0 = 0; }    // s=0, kx=3
       else { tp.nseg = 1; tp.b_n0 = (ky * 4 + 0) * Cout; tp.tmem_col0 = Cout; }             // s=1, kx=0
@@ -387,13 +392,17 @@ extern "C" long long ddimb_conv_wimg_bytes(int kind, int Cin, int Cout, int W) {
       if (Cin % 32 || Cout % 32 || Cin > 256 || Cout > 256) return -1;
       if (ddimb_conv3x3_wide_supported(Cin, Cout, W)) return 0;          // nine tiles, loaded once per CTA straight from w
       if (conv_window_supported(Cin, Cout, W)) return 9LL * kWinChunks * kWinBStage;
-      return 9LL * Cin * Cout * 2;
+      return 9LL * ceil_div(Cin, conv_ck(Cin)) * conv_ck(Cin) * Cout * 2;
     case 1:
       if (Cin % 32 || Cout % 32 || Cin > 256 || Cout > 256) return -1;
-      return conv_down_wide_supported(Cin, Cout, W) ? (long long)kDwWBytes : 16LL * Cin * Cout * 2;
+      if (conv_down_wide_supported(Cin, Cout, W)) return (long long)kDwWBytes;
+      {   // per kernel row: one two-block slab + two single blocks, each padded to whole chunks
+        const int ck = conv_ck(Cin);
+        return 4LL * (ceil_div(2 * Cin, ck) + 2 * ceil_div(Cin, ck)) * ck * Cout * 2;
+      }
     case 2:
       if (Cin % 32 || Cout % 32 || Cin > 256 || Cout > 256) return -1;
-      return conv_up_wide_supported(Cin, Cout, W) ? (long long)kUwWBytes : 16LL * Cin * Cout * 2;
+      return conv_up_wide_supported(Cin, Cout, W) ? (long long)kUwWBytes : 16LL * ceil_div(Cin, conv_ck(Cin)) * conv_ck(Cin) * Cout * 2;
     case 3: return (Cin == 2 && Cout == 32) ? (W % 128 == 0 ? (long long)kCiWBytes : 0) : -1;
     case 4: return (Cin == 32 && Cout == 2) ? (W % 128 == 0 ? (long long)kCoWBytes : 0) : -1;
     default: return -1;
@@ -413,18 +422,18 @@ extern "C" int ddimb_conv_wimg(int kind, const void* w, void* wimg, int Cin, int
   init_params(p);
   if (kind == 0) {
     if (conv_window_supported(Cin, Cout, W)) { win_swizzle_weights_kernel<<<9 * kWinChunks, 256, 0, stream>>>(wb, img); DDIMB_LAUNCH_CHECK(); return DDIMB_OK; }
-    const int ck = pick_ck(Cin);
+    const int ck = conv_ck(Cin);
     conv3x3_taps(p, Cin, Cout, ck);
     return build_generic_wimg(p, w, img, ck, 9 * Cin, 0, assign_img_blocks(p, 0), stream);
   }
   if (kind == 1) {
     if (conv_down_wide_supported(Cin, Cout, W)) { dw_weight_image_kernel<<<4, 256, 0, stream>>>(wb, img); DDIMB_LAUNCH_CHECK(); return DDIMB_OK; }
-    const int ck = pick_ck(Cin);
+    const int ck = conv_ck(Cin);
     down_taps(p, Cin, Cout, ck);
     return build_generic_wimg(p, w, img, ck, 16 * Cin, 0, assign_img_blocks(p, 0), stream);
   }
   if (conv_up_wide_supported(Cin, Cout, W)) { uw_weight_image_kernel<<<3, 256, 0, stream>>>(wb, img); DDIMB_LAUNCH_CHECK(); return DDIMB_OK; }
-  const int ck = pick_ck(Cin);
+  const int ck = conv_ck(Cin);
   int first = 0;
   for (int r = 0; r < 2; ++r) {
     up_taps(p, r, Cin, Cout, ck);
@@ -451,7 +460,7 @@ extern "C" int ddimb_conv3x3(const void* x, const void* w, const void* wimg, con
     return launch_conv_wide(x, nullptr, nullptr, nullptr, 0.f, 0, w, bias, bias_b, bias_b_stride, act, add, out, stats, B, T, W, Cin, stream);
   if (conv_window_supported(Cin, Cout, W))
     return launch_conv_window(x, reinterpret_cast<const uint8_t*>(wimg), bias, bias_b, bias_b_stride, act, add, out, stats, B, T, W, stream);
-  const int ck = pick_ck(Cin);
+  const int ck = conv_ck(Cin);
   int bw, bt;
   spatial_tile(T, W, &bw, &bt);
   CUtensorMap tmA, tmB;
@@ -532,7 +541,7 @@ extern "C" int ddimb_conv_down4x4(const void* x, const void* w, const void* wimg
   DDIMB_CHECK_ARG(W >= 16 && W <= 256 && (W & (W - 1)) == 0);
   DDIMB_CHECK_ARG(Cin % 32 == 0 && Cout % 32 == 0 && Cout <= 256 && Cin <= 256);
   if (conv_down_wide_supported(Cin, Cout, W)) return launch_conv_down_wide(x, reinterpret_cast<const uint8_t*>(wimg), bias, out, stats, B, T, W, stream);
-  const int ck = pick_ck(Cin);
+  const int ck = conv_ck(Cin);
   const int To = T / 2, Wo = W / 2;
   int bw, bt;
   spatial_tile(To, Wo, &bw, &bt);
@@ -628,7 +637,7 @@ extern "C" int ddimb_conv_up4x4(const void* x, const void* w, const void* wimg, 
   DDIMB_CHECK_ARG(W >= 8 && W <= 128 && (W & (W - 1)) == 0);
   DDIMB_CHECK_ARG(Cin % 32 == 0 && Cout % 32 == 0 && Cout <= 256 && Cin <= 256);
   if (conv_up_wide_supported(Cin, Cout, W)) return launch_conv_up_wide(x, reinterpret_cast<const uint8_t*>(wimg), bias, skip, out, stats, B, T, W, stream);
-  const int ck = pick_ck(Cin);
+  const int ck = conv_ck(Cin);
   int bw, bt;
   spatial_tile(T, W, &bw, &bt);
   CUtensorMap tmA, tmB;

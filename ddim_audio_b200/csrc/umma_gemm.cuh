@@ -29,6 +29,7 @@ struct TapDesc {
   int32_t tmem_col0;  // accumulator column of segment 0
   int32_t img_blk;    // first block of this tap in the pre-swizzled weight image (block = one (chunk, segment) B tile)
   int32_t first_mask; // bit sg: this tap is the first writer of accumulator segment sg's columns in a tile (launch_gemm fills it)
+  int32_t k_valid;    // K elements of this tap that exist (0 = all nchunk * CK); the weight image is zero beyond
 };
 
 struct GemmParams {
@@ -721,7 +722,9 @@ static __global__ void __launch_bounds__(256) wimg_generic_kernel(const __nv_bfl
   uint8_t* dst = img + (int64_t)blk * p.n_seg * p.ck * 2;
   for (int i = threadIdx.x; i < p.n_seg * cpr; i += blockDim.x) {
     const int row = i / cpr, j = i - row * cpr;
-    const uint4 v = *reinterpret_cast<const uint4*>(w + (int64_t)(tp.b_n0 + sg * p.n_seg + row) * p.ldw + tp.b_k0 + ch * p.ck + j * 8);
+    const int koff = ch * p.ck + j * 8;
+    uint4 v = make_uint4(0u, 0u, 0u, 0u);
+    if (tp.k_valid == 0 || koff < tp.k_valid) v = *reinterpret_cast<const uint4*>(w + (int64_t)(tp.b_n0 + sg * p.n_seg + row) * p.ldw + tp.b_k0 + koff);
     const int ph = (p.ck == 64) ? (row & 7) : ((row >> 1) & 3);
     *reinterpret_cast<uint4*>(dst + row * p.ck * 2 + ((j ^ ph) << 4)) = v;
   }
