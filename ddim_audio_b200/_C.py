@@ -38,7 +38,7 @@ SIGNATURES = {
     "ddimb_conv_in": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i],
     "ddimb_conv_out": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i],
     "ddimb_conv3x3": [_vp, _vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _i, _i, _i, _i, _i],
-    "ddimb_conv3x3_gn": [_vp, _vp, _vp, _vp, _f, _i, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _i, _i, _i, _i],
+    "ddimb_conv3x3_gn": [_vp, _vp, _vp, _vp, _f, _i, _vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _i, _i, _i, _i],
     "ddimb_conv_down4x4": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i],
     "ddimb_conv_up4x4": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i],
     "ddimb_linear": [_vp, _ll, _vp, _ll, _vp, _i, _vp, _ll, _i, _ll, _i, _i, _i],
@@ -71,13 +71,15 @@ SIGNATURES = {
     "ddimb_conv_in_wgrad": [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i],
     "ddimb_conv_out_wgrad": [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i],
 }
-EXPORTS = ["ddimb_version", "ddimb_last_error", "ddimb_launch_count", "ddimb_prof_enable", "ddimb_prof_report", "ddimb_conv3x3_wide_supported", "ddimb_denoise2d_workspace", "ddimb_conv_wimg_bytes", "ddimb_pfft2wav_workspace"] + list(SIGNATURES)
+EXPORTS = ["ddimb_version", "ddimb_last_error", "ddimb_launch_count", "ddimb_prof_enable", "ddimb_prof_report", "ddimb_conv3x3_wide_supported", "ddimb_conv3x3_gn_supported", "ddimb_denoise2d_workspace", "ddimb_conv_wimg_bytes", "ddimb_pfft2wav_workspace"] + list(SIGNATURES)
 
 lib.ddimb_version.restype = _i
 lib.ddimb_last_error.restype = C.c_char_p
 lib.ddimb_launch_count.restype = _ll
 lib.ddimb_conv3x3_wide_supported.argtypes = [_i, _i, _i]
 lib.ddimb_conv3x3_wide_supported.restype = _i
+lib.ddimb_conv3x3_gn_supported.argtypes = [_i, _i]
+lib.ddimb_conv3x3_gn_supported.restype = _i
 lib.ddimb_pfft2wav_workspace.argtypes = [_i, _i, _i]
 lib.ddimb_pfft2wav_workspace.restype = _ll
 lib.ddimb_conv_wimg_bytes.argtypes = [_i, _i, _i, _i]

@@ -331,13 +331,14 @@ class Model(nn.Module):
 
     # ------------------------------------------------------------------ forward
     def _res_block(self, h, st_h, pb, temb, temb_off, temb_stride, stats, nxt):
-        """models/diffusion.py:42-56; returns (h', stats of h').  Wide levels: 3 launches (GroupNorm+SiLU fused into the
-        convolutions' operand path); other levels: 5 launches with materialised activations."""
+        """models/diffusion.py:42-56; returns (h', stats of h').  Levels 0-3 (C = 32 / 64 row-walking kernel, C = 96 / 128 window
+        kernel): 3 launches, GroupNorm(+SiLU) fused into the convolutions' operand path; levels 4-5: 5 launches with materialised
+        activations."""
         tb = temb[:, temb_off:]
         s0, s1, s2 = stats[nxt()], stats[nxt()], stats[nxt()]
         if ops.conv3x3_gn_supported(pb["C"], h.shape[2]):
-            c0 = ops.conv3x3_gn(h, st_h, pb["g0"], pb["b0"], GN_EPS, 2, pb["w0"], bias_b=tb, bias_b_stride=temb_stride, act=1, stats=s0)
-            c1 = ops.conv3x3_gn(c0, s0, pb["g1"], pb["b1"], GN_EPS, 1, pb["w1"], bias=pb["cb1"], act=1, stats=s1)
+            c0 = ops.conv3x3_gn(h, st_h, pb["g0"], pb["b0"], GN_EPS, 2, pb["w0"], bias_b=tb, bias_b_stride=temb_stride, act=1, stats=s0, wimg=pb["w0_img"])
+            c1 = ops.conv3x3_gn(c0, s0, pb["g1"], pb["b1"], GN_EPS, 1, pb["w1"], bias=pb["cb1"], act=1, stats=s1, wimg=pb["w1_img"])
             out = ops.gn_apply(c1, s1, pb["g2"], None, 2, GN_EPS, res=h, stats_out=s2, out=c0)
             return out, s2
         a = ops.gn_apply(h, st_h, pb["g0"], pb["b0"], 1, GN_EPS)                                      # silu(GN0(h))

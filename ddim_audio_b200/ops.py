@@ -117,15 +117,18 @@ def conv3x3(x, w_packed, bias=None, bias_b=None, bias_b_stride=0, act=0, add=Non
 
 
 def conv3x3_gn_supported(C, W) -> bool:
-    return bool(_C.lib.ddimb_conv3x3_wide_supported(int(C), int(C), int(W)))
+    return bool(_C.lib.ddimb_conv3x3_gn_supported(int(C), int(W)))
 
 
-def conv3x3_gn(x, gn_stats, gamma, beta, eps, gn_mode, w_packed, bias=None, bias_b=None, bias_b_stride=0, act=0, add=None, stats=None, out=None):
+def conv3x3_gn(x, gn_stats, gamma, beta, eps, gn_mode, w_packed, bias=None, bias_b=None, bias_b_stride=0, act=0, add=None, stats=None, out=None,
+               wimg=None):
     """GroupNorm(+SiLU) of ``x`` from ``gn_stats`` fused into the 3x3 convolution (models/diffusion.py:47-52)."""
     B, T, W, C = x.shape
+    if wimg is None:
+        wimg = conv_wimg(KIND_CONV3X3, w_packed, C, C, W)
     if out is None:
         out = torch.empty((B, T, W, C), dtype=bf16, device=x.device)
-    call("ddimb_conv3x3_gn", ptr(x, bf16), ptr(gn_stats, f64), ptr(gamma, f32), ptr(beta, f32), float(eps), int(gn_mode), ptr(w_packed, bf16),
+    call("ddimb_conv3x3_gn", ptr(x, bf16), ptr(gn_stats, f64), ptr(gamma, f32), ptr(beta, f32), float(eps), int(gn_mode), ptr(w_packed, bf16), ptr(wimg),
          ptr(bias, f32), bias_b.data_ptr() if bias_b is not None else None, int(bias_b_stride), int(act), ptr(add, bf16), ptr(out, bf16),
          ptr(stats, f64), B, T, W, C)
     return out

@@ -139,12 +139,13 @@ int ddimb_conv3x3(const void* x, const void* w, const void* wimg, const float* b
 /* models/diffusion.py:42-56 -- GroupNorm(8, C, eps) [+ SiLU] of x from precomputed statistics gn_stats [B][8][2], then the
  * Conv2d 3x3 of ddimb_conv3x3 with the same epilogue, in ONE pass over x (no materialised activation).  gn_mode 1: affine
  * only (norm[1] -> conv[1]); 2: affine + SiLU (norm[0], silu -> conv[0]).  gn_beta nullable.  Available for the shapes
- * ddimb_conv3x3_wide_supported() reports (C = Cin = Cout in {32, 64}, W a multiple of 128); other levels compose
- * ddimb_gn_apply + ddimb_conv3x3. */
+ * ddimb_conv3x3_gn_supported() reports: C in {32, 64} with W a multiple of 128 (row-walking kernel, reads w directly) and C in
+ * {96, 128} with 32 <= W <= 254 (window kernel, needs wimg; add must be NULL); other levels compose ddimb_gn_apply + ddimb_conv3x3. */
 int ddimb_conv3x3_wide_supported(int Cin, int Cout, int W);
+int ddimb_conv3x3_gn_supported(int C, int W);
 int ddimb_conv3x3_gn(const void* x, const double* gn_stats, const float* gn_gamma, const float* gn_beta, float gn_eps, int gn_mode,
-                     const void* w, const float* bias, const float* bias_b, int bias_b_stride, int act, const void* add, void* out,
-                     double* stats, int B, int T, int W, int C, cudaStream_t stream);
+                     const void* w, const void* wimg, const float* bias, const float* bias_b, int bias_b_stride, int act, const void* add,
+                     void* out, double* stats, int B, int T, int W, int C, cudaStream_t stream);
 
 /* models/diffusion.py:70-78 -- Downsample Conv2d 4x4 s2 p1.  w: bf16 [Cout][16*Cin], k = (ky*4+kx)*Cin + ci.
  * x [B][T][W][Cin] -> out [B][T/2][W/2][Cout]. */

@@ -61,8 +61,9 @@ def test_linear_strided_operand_and_lo_plane(ops):
 CONV_CASES = [  # (C, W, T, B)
     (32, 256, 8, 1), (32, 256, 5, 2), (64, 128, 16, 3), (96, 64, 8, 1), (128, 32, 12, 2), (192, 16, 10, 1), (256, 8, 4, 3),
     (256, 8, 1, 1), (128, 32, 1, 1),
-    # C = 96 runs the flattened-window kernel (csrc/conv_window.cuh): unit boundaries inside a row, ragged last unit, tiny images
+    # C = 96 / 128 run the flattened-window kernel (csrc/conv_window.cuh): unit boundaries inside a row, ragged last unit, tiny images
     (96, 64, 33, 3), (96, 64, 1, 2), (96, 64, 130, 2), (96, 32, 7, 2), (96, 16, 5, 1),
+    (128, 32, 33, 3), (128, 32, 130, 2), (128, 64, 9, 1), (128, 128, 5, 1),
 ]
 
 
@@ -150,7 +151,12 @@ WIDE_CASES = [(32, 256, 8, 1), (32, 256, 70, 2), (32, 128, 33, 3), (64, 128, 16,
               (64, 128, 4096, 6), (32, 256, 2048, 5)]
 
 
-@pytest.mark.parametrize("C,W,T,B", WIDE_CASES)
+# the window kernel (C = 96 / 128): ragged last unit, T = 1, several samples, long images (many units per CTA), other widths
+WINDOW_GN_CASES = [(96, 64, 8, 1), (96, 64, 33, 3), (96, 64, 1, 2), (128, 32, 12, 2), (128, 32, 1, 1), (128, 32, 257, 3), (96, 64, 2048, 4),
+                   (128, 32, 1024, 6), (96, 32, 7, 2), (128, 64, 9, 1)]
+
+
+@pytest.mark.parametrize("C,W,T,B", WIDE_CASES + WINDOW_GN_CASES)
 @pytest.mark.parametrize("gn_mode", [1, 2])
 def test_conv3x3_gn_fused(ops, C, W, T, B, gn_mode):
     """models/diffusion.py:47-52: conv(silu(GN(x))) / conv(GN(x)) in one kernel vs torch group_norm + conv2d in fp32."""
