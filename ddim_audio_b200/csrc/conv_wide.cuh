@@ -193,9 +193,11 @@ __device__ __forceinline__ void wide_epilogue_lean(const WideParams& p, const CU
   constexpr int NB = Cfg::kAccBufs;
   constexpr uint32_t kGrpMask = kWideEpiWarps / 4 - 1;
   constexpr int CG = C / 8;
-  // C = 32: a tensor store costs the TMA engine ~4 cycles per 64-byte box row (as the loads do) and the engine, not HBM, bounded the
-  // kernel; the warp's 32 positions x 64 B are contiguous in global memory, so they leave as ONE 1-D bulk copy instead
+  // C = 32: the warp's 32 positions x 64 B are contiguous in global memory, so they leave as ONE 1-D bulk copy of a linear tile (C = 64:
+  // a tensor store of the swizzled tile).  Measured equal to the tensor store at C = 32 (profiles/r02_experiments.md section 1); straight
+  // 16-byte stores from registers (no staging tile) measured 3 % (C = 32) and 11 % (C = 64) slower.
   constexpr bool kBulk = (C == 32) && (DDIMB_WIDE_BULKST != 0);
+
   const int q = warp & 3;
   const uint32_t grp = (uint32_t)(warp - 2) >> 2;
   const uint32_t stage = smem_u32(stage_gen);
@@ -287,10 +289,8 @@ __device__ __forceinline__ void wide_epilogue_lean(const WideParams& p, const CU
       }
       fence_proxy_async_smem();   // generic-proxy writes of every lane -> visible to the TMA engine
       __syncwarp();
-#ifndef DDIMB_WIDE_NOSTORE
       if (kBulk) bulk_store_s2g_e(p.out + ((((int64_t)u.b * p.T + (u.t0 + ot)) * p.W) + wq) * C, stage, 32 * C * 2);
       else tma_store_4d_e(tmO, stage, 0, wq, u.t0 + ot, u.b);
-#endif
       bulk_commit_group();
       pending = true;
     }
