@@ -43,7 +43,7 @@ SIGNATURES = {
     "ddimb_conv_up4x4": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i],
     "ddimb_linear": [_vp, _ll, _vp, _ll, _vp, _i, _vp, _ll, _i, _ll, _i, _i, _i],
     "ddimb_fourier_mix": [_vp, _ll, _vp, _vp, _vp, _vp, _i, _i, _i, _i],
-    "ddimb_gn_apply": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _ll, _i, _f],
+    "ddimb_gn_apply": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _ll, _i, _f],
     "ddimb_linear_small": [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i],
     "ddimb_gather_rows": [_vp, _vp, _vp, _i, _i, _i],
     "ddimb_tokens_ln": [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _f],

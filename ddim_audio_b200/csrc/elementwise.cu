@@ -155,6 +155,7 @@ extern "C" int ddimb_sqerr_loss_bwd(const float* e, const float* output, const f
 struct GnArgs {
   const __nv_bfloat16* x;
   const __nv_bfloat16* res;
+  const __nv_bfloat16* res2;   // optional second residual (mode 2): y = res + res2 + gn(x) -- the last block also adds conv_out's skip operand
   __nv_bfloat16* y;
   const double* stats_in;
   double* stats_out;
@@ -167,7 +168,9 @@ struct GnArgs {
   float eps;
 };
 
-template <int UNR>
+// RES2: compile-time presence of the second residual, so the common instantiation keeps its register count / loads in flight
+// (as a run-time branch the extra UNR x 16 B registers cost every mode-2 call 10-20 %)
+template <int UNR, bool RES2>
 __global__ void __launch_bounds__(256) gn_apply_kernel(const GnArgs a) {
   __shared__ float s_scale[256], s_shift[256];
   const int b = blockIdx.y, C = a.C, cg = C >> 3;
@@ -191,19 +194,21 @@ __global__ void __launch_bounds__(256) gn_apply_kernel(const GnArgs a) {
   const int64_t items = a.per_sample / 8;
   const uint4* xp = reinterpret_cast<const uint4*>(a.x + (int64_t)b * a.per_sample);
   const uint4* rp = a.res ? reinterpret_cast<const uint4*>(a.res + (int64_t)b * a.per_sample) : nullptr;
+  const uint4* r2p = a.res2 ? reinterpret_cast<const uint4*>(a.res2 + (int64_t)b * a.per_sample) : nullptr;
   uint4* yp = reinterpret_cast<uint4*>(a.y + (int64_t)b * a.per_sample);
   float sa1 = 0.f, sa2 = 0.f, sb1 = 0.f, sb2 = 0.f;   // channels c0..c0+3 and c0+4..c0+7 (group width is a multiple of 4)
   // UNR items per iteration with every load issued before the first use: ~8 x 16 B in flight per thread keeps HBM busy
   // (UNR = 8 for the one-operand modes, 4 for mode 2 which also loads the residual)
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t i0 = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i0 < items; i0 += UNR * stride) {
-    uint4 xv[UNR], rv[UNR];
+    uint4 xv[UNR], rv[UNR], qv[RES2 ? UNR : 1];
 #pragma unroll
     for (int u = 0; u < UNR; ++u) {
       const int64_t i = i0 + u * stride;
       if (i < items) {
         xv[u] = ldg_nc_v4(xp + i);
         if (a.mode == 2) rv[u] = ldg_nc_v4(rp + i);
+        if (RES2) qv[u] = ldg_nc_v4(r2p + i);
       }
     }
 #pragma unroll
@@ -228,6 +233,14 @@ __global__ void __launch_bounds__(256) gn_apply_kernel(const GnArgs a) {
         for (int j = 0; j < 4; ++j) {
           const float2 t = unpack_bf16x2(rw[j]);
           f[2 * j] += t.x; f[2 * j + 1] += t.y;
+        }
+        if (RES2) {
+          const uint32_t qw[4] = {qv[u].x, qv[u].y, qv[u].z, qv[u].w};
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const float2 t = unpack_bf16x2(qw[j]);
+            f[2 * j] += t.x; f[2 * j + 1] += t.y;
+          }
         }
 #pragma unroll
         for (int j = 0; j < 4; ++j) { sa1 += f[j]; sa2 = fmaf(f[j], f[j], sa2); sb1 += f[4 + j]; sb2 = fmaf(f[4 + j], f[4 + j], sb2); }
@@ -257,7 +270,7 @@ __global__ void __launch_bounds__(256) gn_apply_kernel(const GnArgs a) {
 // one sample), one CTA per range and exactly as many CTAs as are resident at once -- no partial second wave (the 2-D grid above
 // ran 2.7 waves at 3 CTAs / SM and lost 10-30 % to the tail at C >= 96).  A CTA crosses at most a few sample boundaries; there
 // it flushes its statistics and reloads the per-channel scale / shift.
-template <int UNR>
+template <int UNR, bool RES2>
 __global__ void __launch_bounds__(256) gn_apply_ranges_kernel(const GnArgs a, int64_t tiles_per_sample, int64_t tiles_total) {
   __shared__ float s_scale[256], s_shift[256];
   __shared__ float s_part[256][4];
@@ -268,7 +281,7 @@ __global__ void __launch_bounds__(256) gn_apply_ranges_kernel(const GnArgs a, in
   float sc[8], sh[8];
   float sa1 = 0.f, sa2 = 0.f, sb1 = 0.f, sb2 = 0.f;
   int cur_b = -1;
-  const uint4 *xp = nullptr, *rp = nullptr;
+  const uint4 *xp = nullptr, *rp = nullptr, *r2p = nullptr;
   uint4* yp = nullptr;
 
   auto flush = [&](int b) {
@@ -309,15 +322,17 @@ __global__ void __launch_bounds__(256) gn_apply_ranges_kernel(const GnArgs a, in
       for (int j = 0; j < 8; ++j) { sc[j] = s_scale[c0 + j]; sh[j] = s_shift[c0 + j]; }
       xp = reinterpret_cast<const uint4*>(a.x + (int64_t)b * a.per_sample);
       rp = a.res ? reinterpret_cast<const uint4*>(a.res + (int64_t)b * a.per_sample) : nullptr;
+      r2p = a.res2 ? reinterpret_cast<const uint4*>(a.res2 + (int64_t)b * a.per_sample) : nullptr;
       yp = reinterpret_cast<uint4*>(a.y + (int64_t)b * a.per_sample);
       cur_b = b;
     }
     const int64_t base = (tile - (int64_t)b * tiles_per_sample) * ((int64_t)blockDim.x * UNR) + threadIdx.x;
-    uint4 xv[UNR], rv[UNR];
+    uint4 xv[UNR], rv[UNR], qv[RES2 ? UNR : 1];
 #pragma unroll
     for (int u = 0; u < UNR; ++u) {
       xv[u] = ldg_nc_v4(xp + base + u * (int64_t)blockDim.x);
       if (a.mode == 2) rv[u] = ldg_nc_v4(rp + base + u * (int64_t)blockDim.x);
+      if (RES2) qv[u] = ldg_nc_v4(r2p + base + u * (int64_t)blockDim.x);
     }
 #pragma unroll
     for (int u = 0; u < UNR; ++u) {
@@ -340,6 +355,14 @@ __global__ void __launch_bounds__(256) gn_apply_ranges_kernel(const GnArgs a, in
           const float2 t = unpack_bf16x2(rw[j]);
           f[2 * j] += t.x; f[2 * j + 1] += t.y;
         }
+        if (RES2) {
+          const uint32_t qw[4] = {qv[u].x, qv[u].y, qv[u].z, qv[u].w};
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const float2 t = unpack_bf16x2(qw[j]);
+            f[2 * j] += t.x; f[2 * j + 1] += t.y;
+          }
+        }
 #pragma unroll
         for (int j = 0; j < 4; ++j) { sa1 += f[j]; sa2 = fmaf(f[j], f[j], sa2); sb1 += f[4 + j]; sb2 = fmaf(f[4 + j], f[4 + j], sb2); }
       }
@@ -351,20 +374,20 @@ __global__ void __launch_bounds__(256) gn_apply_ranges_kernel(const GnArgs a, in
   if (cur_b >= 0 && a.mode == 2 && a.stats_out) flush(cur_b);
 }
 
-template <int UNR>
+template <int UNR, bool RES2>
 static int gn_ranges_launch(const GnArgs& a, int B, int threads, int64_t items, int waves_pct, cudaStream_t stream) {
   const int64_t tile = (int64_t)threads * UNR;
   const int64_t tps = items / tile, total = tps * B;
   int occ = 0;
-  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, gn_apply_ranges_kernel<UNR>, threads, 0) != cudaSuccess || occ < 1) occ = 1;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, gn_apply_ranges_kernel<UNR, RES2>, threads, 0) != cudaSuccess || occ < 1) occ = 1;
   int64_t grid = (int64_t)ddimb_num_sms() * occ * waves_pct / 100;
   if (grid > total) grid = total;
   if (grid < 1) grid = 1;
-  gn_apply_ranges_kernel<UNR><<<(unsigned)grid, threads, 0, stream>>>(a, tps, total);
+  gn_apply_ranges_kernel<UNR, RES2><<<(unsigned)grid, threads, 0, stream>>>(a, tps, total);
   return 0;
 }
 
-extern "C" int ddimb_gn_apply(const void* x, const void* res, void* y, const double* stats_in, double* stats_out, const float* gamma,
+extern "C" int ddimb_gn_apply(const void* x, const void* res, const void* res2, void* y, const double* stats_in, double* stats_out, const float* gamma,
                               const float* beta, int mode, int B, long long positions, int C, float eps, cudaStream_t stream) {
   DDIMB_CHECK_ARG(x && y && stats_in && gamma && B >= 1 && positions >= 1);
   DDIMB_CHECK_ARG(C % 32 == 0 && C <= 256 && mode >= 0 && mode <= 4);
@@ -373,9 +396,11 @@ extern "C" int ddimb_gn_apply(const void* x, const void* res, void* y, const dou
   if (mode == 3) mode = 0;
   if (mode == 4) mode = 2;
   DDIMB_CHECK_ARG(mode != 2 || res);
-  DDIMB_PROF(stream, "gn_apply", C, mode, 2.0 * B * positions * C * (mode == 2 ? 3 : 2), 0.0);
+  DDIMB_CHECK_ARG(res2 == nullptr || mode == 2);
+  DDIMB_PROF(stream, "gn_apply", C, mode, 2.0 * B * positions * C * (mode == 2 ? (res2 ? 4 : 3) : 2), 0.0);
   GnArgs a;
   a.x = reinterpret_cast<const __nv_bfloat16*>(x); a.res = reinterpret_cast<const __nv_bfloat16*>(res);
+  a.res2 = reinterpret_cast<const __nv_bfloat16*>(res2);
   a.y = reinterpret_cast<__nv_bfloat16*>(y);
   a.stats_in = stats_in; a.stats_out = stats_out; a.gamma = gamma; a.beta = beta;
   a.per_sample = positions * C; a.C = C; a.mode = mode; a.pre_silu = pre_silu; a.eps = eps;
@@ -388,12 +413,14 @@ extern "C" int ddimb_gn_apply(const void* x, const void* res, void* y, const dou
   // +31 % (C = 96, 192); an unroll of 8 is no better than 4 anywhere
   const bool ranges = (mode != 2 || C >= 96);
   if (ranges && items % ((int64_t)threads * unr) == 0 && items / ((int64_t)threads * unr) >= 1) {
-    gn_ranges_launch<unr>(a, B, threads, items, 100, stream);   // balanced contiguous ranges, one resident wave
+    if (a.res2) gn_ranges_launch<unr, true>(a, B, threads, items, 100, stream);
+    else gn_ranges_launch<unr, false>(a, B, threads, items, 100, stream);   // balanced contiguous ranges, one resident wave
   } else {
     int64_t cap = (int64_t)ddimb_num_sms() * 8 / B + 1;
     if (bx > cap) bx = cap;
     if (bx < 1) bx = 1;
-    gn_apply_kernel<unr><<<dim3((unsigned)bx, B), threads, 0, stream>>>(a);
+    if (a.res2) gn_apply_kernel<unr, true><<<dim3((unsigned)bx, B), threads, 0, stream>>>(a);
+    else gn_apply_kernel<unr, false><<<dim3((unsigned)bx, B), threads, 0, stream>>>(a);
   }
   DDIMB_LAUNCH_CHECK();
   return DDIMB_OK;

@@ -330,7 +330,7 @@ class Model(nn.Module):
         return self._consts[key]
 
     # ------------------------------------------------------------------ forward
-    def _res_block(self, h, st_h, pb, temb, temb_off, temb_stride, stats, nxt):
+    def _res_block(self, h, st_h, pb, temb, temb_off, temb_stride, stats, nxt, res2=None):
         """models/diffusion.py:42-56; returns (h', stats of h').  Levels 0-3 (C = 32 / 64 row-walking kernel, C = 96 / 128 window
         kernel): 3 launches, GroupNorm(+SiLU) fused into the convolutions' operand path; levels 4-5: 5 launches with materialised
         activations."""
@@ -339,13 +339,13 @@ class Model(nn.Module):
         if ops.conv3x3_gn_supported(pb["C"], h.shape[2]):
             c0 = ops.conv3x3_gn(h, st_h, pb["g0"], pb["b0"], GN_EPS, 2, pb["w0"], bias_b=tb, bias_b_stride=temb_stride, act=1, stats=s0, wimg=pb["w0_img"])
             c1 = ops.conv3x3_gn(c0, s0, pb["g1"], pb["b1"], GN_EPS, 1, pb["w1"], bias=pb["cb1"], act=1, stats=s1, wimg=pb["w1_img"])
-            out = ops.gn_apply(c1, s1, pb["g2"], None, 2, GN_EPS, res=h, stats_out=s2, out=c0)
+            out = ops.gn_apply(c1, s1, pb["g2"], None, 2, GN_EPS, res=h, stats_out=s2, out=c0, res2=res2)
             return out, s2
         a = ops.gn_apply(h, st_h, pb["g0"], pb["b0"], 1, GN_EPS)                                      # silu(GN0(h))
         c0 = ops.conv3x3(a, pb["w0"], bias_b=tb, bias_b_stride=temb_stride, act=1, stats=s0, wimg=pb["w0_img"])
         n1 = ops.gn_apply(c0, s0, pb["g1"], pb["b1"], 0, GN_EPS, out=a)                               # GN1(silu(conv0 + temb))
         c1 = ops.conv3x3(n1, pb["w1"], bias=pb["cb1"], act=1, stats=s1, out=c0, wimg=pb["w1_img"])     # silu(conv1 + bias)
-        out = ops.gn_apply(c1, s1, pb["g2"], None, 2, GN_EPS, res=h, stats_out=s2, out=n1)             # h + GN2(.)
+        out = ops.gn_apply(c1, s1, pb["g2"], None, 2, GN_EPS, res=h, stats_out=s2, out=n1, res2=res2)  # h + GN2(.)
         return out, s2
 
     @torch.no_grad()
@@ -418,15 +418,20 @@ class Model(nn.Module):
         h = ops.tokens_to_nhwc(tok_out, hidden.pop(), st)                                          # + first additive skip (:284)
 
         # ---- up path (:282-292)
+        n_blocks = len(self.embedding_size)
         for ent in pk["up"]:
             for pb in ent["blocks"]:
-                h, st = self._res_block(h, st, pb, temb, offs[rb_i], temb_stride, stats, nxt)
+                # the very last block also adds the final additive skip (:284 before conv_out): conv(h + skip) then reads ONE tensor
+                # (conv_out is bound by the TMA delivery rate of its two 64-byte-row input planes)
+                last = rb_i == n_blocks - 1
+                h, st = self._res_block(h, st, pb, temb, offs[rb_i], temb_stride, stats, nxt, res2=hidden[0] if last else None)
                 rb_i += 1
             if ent["up"] is not None:
                 st = stats[nxt()]
                 h = ops.conv_up4x4(h, ent["up"]["w"], ent["up"]["b"], skip=hidden.pop(), stats=st, wimg=ent["up"]["w_img"])
         conv_last = self.up_modules[-1]
-        return ops.conv_out(h, hidden.pop(), conv_last.weight, conv_last.bias, wimg=pk["conv_out_img"])
+        hidden.pop()
+        return ops.conv_out(h, None, conv_last.weight, conv_last.bias, wimg=pk["conv_out_img"])
 
     def forward(self, input, t):
         if torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters()):

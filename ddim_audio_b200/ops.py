@@ -177,12 +177,12 @@ def fourier_mix(xbf, ldx, wh, a2, ut, B, S, H, split):
 
 
 # ---------------------------------------------------------------------------------------- norms / repacks
-def gn_apply(x, stats_in, gamma, beta, mode, eps, res=None, stats_out=None, out=None):
+def gn_apply(x, stats_in, gamma, beta, mode, eps, res=None, stats_out=None, out=None, res2=None):
     B, C = x.shape[0], x.shape[-1]
     positions = x.numel() // (B * C)
     if out is None:
         out = torch.empty_like(x)
-    call("ddimb_gn_apply", ptr(x, bf16), ptr(res, bf16), ptr(out, bf16), ptr(stats_in, f64), ptr(stats_out, f64), ptr(gamma, f32),
+    call("ddimb_gn_apply", ptr(x, bf16), ptr(res, bf16), ptr(res2, bf16), ptr(out, bf16), ptr(stats_in, f64), ptr(stats_out, f64), ptr(gamma, f32),
          ptr(beta, f32), int(mode), B, positions, C, float(eps))
     return out
 

@@ -172,10 +172,11 @@ int ddimb_fourier_mix(const void* x, long long ldx, const void* wh, const void* 
 /* ---- GroupNorm / LayerNorm / token repacks -------------------------------------------------------------------- */
 
 /* models/diffusion.py:17-26,47-56 -- GroupNorm(8, C, eps) applied from precomputed statistics.
- * mode 0: y = gn(x); mode 1: y = silu(gn(x)); mode 2: y = res + gn(x) and accumulate stats_out of y;
+ * mode 0: y = gn(x); mode 1: y = silu(gn(x)); mode 2: y = res (+ res2) + gn(x) and accumulate stats_out of y;
  * modes 3 / 4 (training, x is a stored pre-activation): as 0 / 2 on silu(x).
- * beta nullable (norm[2] has no bias, :26). */
-int ddimb_gn_apply(const void* x, const void* res, void* y, const double* stats_in, double* stats_out, const float* gamma,
+ * beta nullable (norm[2] has no bias, :26).  res2 (nullable, mode 2): a second residual -- the last block of the network also
+ * adds the skip operand of conv_out (:284), which then reads one tensor instead of two. */
+int ddimb_gn_apply(const void* x, const void* res, const void* res2, void* y, const double* stats_in, double* stats_out, const float* gamma,
                    const float* beta, int mode, int B, long long positions, int C, float eps, cudaStream_t stream);
 
 /* models/diffusion.py:107-120 -- BetaEmbedding layers in fp32: out[r][n] = act(in[idx?idx[r]:r] . w[n] + bias[n]);

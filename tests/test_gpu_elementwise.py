@@ -83,6 +83,13 @@ def test_gn_apply(ops, C, P, mode):
     assert_close_bf16(y, ref, f"gn C={C} mode={mode}")
     if mode == 2:
         assert_stats(so, ref, f"gn stats C={C}")
+        # second residual (the last block also adds conv_out's skip operand): y = res + res2 + gn(x), statistics of that sum
+        res2 = torch.randn(B, P, 1, C, device=DEV, generator=g).to(torch.bfloat16)
+        so2 = torch.zeros(B, 8, 2, dtype=torch.float64, device=DEV)
+        y2 = ops.gn_apply(x, st, gamma, beta, mode, 1e-6, res=res, stats_out=so2, res2=res2)
+        ref2 = ref + res2.float()
+        assert_close_bf16(y2, ref2, f"gn C={C} mode=2 + res2")
+        assert_stats(so2, ref2, f"gn stats C={C} + res2")
 
 
 @pytest.mark.parametrize("B,T,F", [(1, 32, 256), (3, 64, 256), (2, 1, 256), (1, 77, 256), (2, 300, 256), (2, 45, 128), (70, 9, 256), (2, 33, 96)])
