@@ -5,13 +5,13 @@
 // row-shifted tcgen05 A descriptors, an input row feeds the accumulators of three output rows through ONE MMA of N = 48.
 // An accumulator block is 16 columns (the minimum UMMA N): columns 0,1 carry the bf16 high parts of the two output channels'
 // weights, columns 2,3 the low parts (w = hi + lo to 2^-17), which the epilogue adds -- fp32-class weights for free, since the
-// 14 spare columns exist anyway.  Warp roles (192 threads): 0 = TMA producer, 1 = MMA issuer, 2-5 = epilogue.
+// 14 spare columns exist anyway.  Warp roles (320 threads): 0 = TMA producer, 1 = MMA issuer, 2-9 = epilogue (two groups, alternate rows).
 #pragma once
 #include "conv_wide.cuh"
 
 namespace ddimb {
 
-constexpr int kCoThreads = 192;
+constexpr int kCoThreads = 320;                     // TMA producer, MMA issuer, 2 x 4 epilogue warps (alternating output rows)
 constexpr int kCoSlots = 10;                       // input rows in flight (x and skip planes each)
 constexpr int kCoPlane = 9216;                     // 130 x 64 B rounded to 1024
 constexpr int kCoSlotBytes = 2 * kCoPlane;
@@ -172,15 +172,18 @@ conv_out_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constan
       }
     }
   } else {
-    // ================================================================ epilogue (TMEM lane quarter = warp % 4): hi + lo + bias -> fp32 NCHW
+    // ================================================================ epilogue (TMEM lane quarter = warp % 4; the two warp groups take alternate
+    // output rows -- one row is a short dependent chain (wait, tcgen05.ld, two stores), so a single group was latency-bound): hi + lo + bias -> fp32 NCHW
     const int q = warp & 3;
+    const uint32_t grp = (uint32_t)(warp - 2) >> 2;
     const int m = q * 32 + lane;
     const float bias0 = p.bias[0], bias1 = p.bias[1];
-    uint32_t tile = 0;
+    uint32_t tile0 = 0;
     CoUnit u;
     for (int unit = blockIdx.x; unit < p.num_units; unit += gridDim.x) {
       u.set(p, unit);
-      for (int ot = 0; ot < u.rows; ++ot, ++tile) {
+      for (int ot = (int)((grp - tile0) & 1u); ot < u.rows; ot += 2) {
+        const uint32_t tile = tile0 + (uint32_t)ot;
         const uint32_t buf = tile % NB, use = tile / NB;
         mbar_wait(bar_afull + 8 * buf, use & 1, 45);
         tc_fence_after();
@@ -194,6 +197,7 @@ conv_out_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constan
         p.out[o] = __uint_as_float(v[0]) + __uint_as_float(v[2]) + bias0;
         p.out[o + (int64_t)p.T * p.W] = __uint_as_float(v[1]) + __uint_as_float(v[3]) + bias1;
       }
+      tile0 += (uint32_t)u.rows;
     }
   }
 

@@ -66,7 +66,8 @@ struct WideCfg {
   static constexpr int kXfTabBytes = ((kWideXfWarps * C * 8 + 1023) / 1024) * 1024;
   static constexpr bool kStage = (C == 32);           // the legacy (skip-add) epilogue's smem-staged stores need 2 KB per warp: C = 32 only
   static constexpr int kStageBytes = 32 * C * 2;      // one epilogue warp's output tile (32 positions x C channels): the TMA store's source
-  static constexpr int kAuxBytes = 1024 + 4096 + kXfTabBytes + kWideEpiWarps * kStageBytes;   // barriers | epilogue bias copies | transform scale/shift copies | store staging
+  static constexpr int kStageBufs = (C == 32) ? 2 : 1;  // C = 32 has room for two tiles per warp: a tile is never rewritten while the TMA engine may still read it
+  static constexpr int kAuxBytes = 1024 + 4096 + kXfTabBytes + kWideEpiWarps * kStageBufs * kStageBytes;   // barriers | epilogue bias copies | transform scale/shift copies | store staging
   static constexpr int kSmemBytes = 1024 + kWBytes + kSlots * kSlotBytes + kAuxBytes;
 };
 
@@ -200,15 +201,15 @@ __device__ __forceinline__ void wide_epilogue_lean(const WideParams& p, const CU
 
   const int q = warp & 3;
   const uint32_t grp = (uint32_t)(warp - 2) >> 2;
-  const uint32_t stage = smem_u32(stage_gen);
+  constexpr int NSB = Cfg::kStageBufs;
+  const uint32_t stage0 = smem_u32(stage_gen);
   const uint32_t phase = (C == 64) ? (uint32_t)(lane & 7) : (uint32_t)((lane >> 1) & 3);
-  uint8_t* srow = stage_gen + lane * (C * 2);
+  uint32_t nstore = 0;
   const uint64_t s2x = (ACT == 1) ? pack2(0.5f, 0.5f) : pack2(1.0f, 1.0f);
   ConvEpiState<C> st;
   st.reset();
   st.cur_batch = -1;
   uint32_t tile = 0;
-  bool pending = false;
   WideUnit u;
   for (int unit = blockIdx.x; unit < p.num_units; unit += gridDim.x) {
     u.set(p, unit);
@@ -223,10 +224,9 @@ __device__ __forceinline__ void wide_epilogue_lean(const WideParams& p, const CU
       mbar_wait(bar_afull + 8 * buf, use & 1, 15);
       tc_fence_after();
       const uint32_t trow = tmem_base + ((uint32_t)(q * 32) << 16) + buf * C;
-      if (pending) {            // the previous tile's store has read the staging tile
-        bulk_wait_group_read<0>();
-        __syncwarp();
-      }
+      const uint32_t sb = (NSB == 2) ? (nstore & 1u) : 0u;
+      const uint32_t stage = stage0 + sb * Cfg::kStageBytes;
+      uint8_t* srow = stage_gen + sb * Cfg::kStageBytes + lane * (C * 2);
 #pragma unroll
       for (int c0 = 0; c0 < C; c0 += 32) {
         uint32_t v[32];
@@ -247,6 +247,12 @@ __device__ __forceinline__ void wide_epilogue_lean(const WideParams& p, const CU
         if (ACT == 1) {
 #pragma unroll
           for (int j = 0; j < 16; ++j) f[j] = silu2_from_half(f[j]);
+        }
+        if (c0 == 0 && nstore >= (uint32_t)NSB) {
+          // the staging tile about to be rewritten was the source of the store issued NSB tiles ago: waited for only now, after this
+          // tile's tcgen05.ld and arithmetic, so the TMA engine's read overlaps them
+          bulk_wait_group_read<NSB - 1>();
+          __syncwarp();
         }
         if (kBulk) {
           // linear [32 positions][64 B] tile for a 1-D bulk store: lane writes its chunks in the rotated order (i + phase) & 3 so the 8
@@ -292,7 +298,7 @@ __device__ __forceinline__ void wide_epilogue_lean(const WideParams& p, const CU
       if (kBulk) bulk_store_s2g_e(p.out + ((((int64_t)u.b * p.T + (u.t0 + ot)) * p.W) + wq) * C, stage, 32 * C * 2);
       else tma_store_4d_e(tmO, stage, 0, wq, u.t0 + ot, u.b);
       bulk_commit_group();
-      pending = true;
+      ++nstore;
     }
     tile += (uint32_t)u.rows;
   }
@@ -441,7 +447,7 @@ conv3x3_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   } else if (warp < 2 + kWideEpiWarps) {
     // ================================================================ epilogue (TMEM lane quarter = warp % 4; group = output row parity)
     float* wb = bias_smem + (warp - 2) * 128;
-    uint8_t* stage = aux_gen + 1024 + 4096 + Cfg::kXfTabBytes + (warp - 2) * Cfg::kStageBytes;
+    uint8_t* stage = aux_gen + 1024 + 4096 + Cfg::kXfTabBytes + (warp - 2) * Cfg::kStageBufs * Cfg::kStageBytes;
     if (p.add == nullptr) {
       const bool want = p.stats != nullptr;
 #define DDIMB_WIDE_EPI_CASE(A)                                                                                        \

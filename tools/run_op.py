@@ -63,6 +63,10 @@ elif a.op == "conv_out":
     b = torch.randn(2, device=dev, generator=g)
     sk = torch.randn(B, T, W, 32, device=dev, generator=g).to(bf)
     fn = lambda: ops.conv_out(x, sk, w, b)
+elif a.op == "conv_out1":                       # one input plane (the denoiser folds the last skip into the preceding gn_apply)
+    w = torch.randn(2, 32, 3, 3, device=dev, generator=g) / 17
+    b = torch.randn(2, device=dev, generator=g)
+    fn = lambda: ops.conv_out(x, None, w, b)
 elif a.op == "conv_in":
     xi = torch.randn(B, 2, T, W, device=dev, generator=g)
     w = torch.randn(32, 2, 3, 3, device=dev, generator=g) / 4
