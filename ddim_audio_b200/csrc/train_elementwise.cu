@@ -672,132 +672,183 @@ extern "C" int ddimb_linear_small_dgrad(const float* g, const float* w, const fl
 }
 
 // ------------------------------------------------------------------------------------------------ conv_in / conv_out parameter gradients
-// conv_in (models/diffusion.py:189-198): dw[co][ci][ky][kx] += sum g[b,t,f,co] * x[b,ci,t+ky-1,f+kx-1], db[co] += sum g;
-// g = g1 + g2 (bf16 NHWC: conv_in's output feeds the first residual block AND the last additive skip).  lane = co.
-template <int CIN>
-__global__ void __launch_bounds__(256) conv_in_wgrad_kernel(const float* __restrict__ x, const __nv_bfloat16* __restrict__ g1,
-                                                           const __nv_bfloat16* __restrict__ g2, float* __restrict__ dw, float* __restrict__ db,
-                                                           int T, int F) {
-  constexpr int NA = CIN * 9 + 1;
-  __shared__ float s_acc[8][NA][32];
-  const int b = blockIdx.y, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int t = blockIdx.x * 8 + warp;
-  float acc[NA];
+// Both boundary convolutions pair a 32-channel bf16 NHWC tensor V (a sum of two) with a 2-plane fp32 NCHW image P through a 3x3 stencil:
+//   conv_in  (models/diffusion.py:189-198): dw[co][ci][ky][kx] += sum g[b,t,f,co] * x[b,ci,t+ky-1,f+kx-1], db[co] += sum g;  V = g1 + g2, P = x
+//   conv_out (models/diffusion.py:199-208,284): dw[co][ci][ky][kx] += sum dout[b,co,t,f] * hs[b,t+ky-1,f+kx-1,ci], db[co] += sum dout;
+//            V = h + skip, P = dout, i.e. hs[q] meets dout[q - (ky-1, kx-1)]
+// so one kernel accumulates  acc[c][pl][dy][dx] = sum_q V[q][c] * P[pl][q + (dy, dx)]  and the two ops differ only in where an accumulator
+// lands (conv_out mirrors the tap).  HBM-bound on reading V once (P is 1/16 of it).  A CTA takes 8 rows of one sample per unit (warp = row):
+// the 10 P rows it meets sit in shared memory with zeroed halo columns; a lane owns 4 channels (one 8-byte load per position and tensor)
+// and a quarter of the row, and keeps its 4 x 18 sums in registers across all units of a grid-stride loop; one reduction and one set of
+// atomics per CTA at the end.
+constexpr int kBwRows = 8, kBwThreads = 256;
+__device__ __forceinline__ int bw_sidx(int c) { return c + ((c >> 6) << 3); }   // row segments of 64 land on different banks
+
+template <bool CONV_OUT>
+__global__ void __launch_bounds__(kBwThreads, 2) boundary_wgrad_kernel(const __nv_bfloat16* __restrict__ v1, const __nv_bfloat16* __restrict__ v2,
+                                                                       const float* __restrict__ img, float* __restrict__ dw, float* __restrict__ db,
+                                                                       int B, int T, int F, int units_t, int num_units, int pitch) {
+  extern __shared__ float s_p[];                           // [10 rows][2 planes][pitch]; reused as [8 warps][76][8] at the end
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int cg = lane & 7, seg = lane >> 3;
+  const int L = (F + 3) >> 2;
+  const int f_lo = seg * L, f_hi = min(F, f_lo + L);
+  float acc[4][18];
 #pragma unroll
-  for (int i = 0; i < NA; ++i) acc[i] = 0.f;
-  if (t < T) {
-    const __nv_bfloat16* gp1 = g1 + (((int64_t)b * T + t) * F) * 32 + lane;
-    const __nv_bfloat16* gp2 = g2 ? g2 + (((int64_t)b * T + t) * F) * 32 + lane : nullptr;
-    for (int f = 0; f < F; ++f) {
-      float gv = __bfloat162float(gp1[(int64_t)f * 32]);
-      if (gp2) gv += __bfloat162float(gp2[(int64_t)f * 32]);
-      acc[NA - 1] += gv;
+  for (int c = 0; c < 4; ++c)
 #pragma unroll
-      for (int ci = 0; ci < CIN; ++ci) {
-        const float* xp = x + ((int64_t)(b * CIN + ci) * T) * F;
+    for (int i = 0; i < 18; ++i) acc[c][i] = 0.f;
+  float vsum[4] = {0.f, 0.f, 0.f, 0.f};
+  float psum[2] = {0.f, 0.f};
+
+  for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x) {
+    const int b = unit / units_t;
+    const int t0 = (unit - b * units_t) * kBwRows;
+    __syncthreads();                                       // the previous unit's readers are done with s_p
+    for (int r = warp; r < kBwRows + 2; r += kBwThreads / 32) {
+      const int t = t0 - 1 + r;
+      const bool in_t = t >= 0 && t < T;
 #pragma unroll
-        for (int ky = 0; ky < 3; ++ky) {
-          const int tt = t + ky - 1;
-          if (tt < 0 || tt >= T) continue;
+      for (int pl = 0; pl < 2; ++pl) {
+        const float* src = img + ((int64_t)(b * 2 + pl) * T + t) * F;
+        float* dst = s_p + (r * 2 + pl) * pitch;
+        float own = 0.f;
+        for (int c = lane; c < F + 2; c += 32) {
+          const int f = c - 1;
+          const float val = (in_t && f >= 0 && f < F) ? __ldg(src + f) : 0.f;
+          dst[bw_sidx(c)] = val;
+          own += val;
+        }
+        if (CONV_OUT && r >= 1 && r <= kBwRows) psum[pl] += own;
+      }
+    }
+    __syncthreads();
+    const int t = t0 + warp;
+    if (t < T) {
+      const int64_t rowoff = (((int64_t)b * T + t) * F) * 32 + cg * 4;
+      const float* p0 = s_p + (warp * 2) * pitch;          // rows t-1, t, t+1 = warp, warp+1, warp+2
+      for (int f0 = f_lo; f0 < f_hi; f0 += 4) {
+        uint2 q1[4], q2[4];
 #pragma unroll
-          for (int kx = 0; kx < 3; ++kx) {
-            const int ff = f + kx - 1;
-            if (ff < 0 || ff >= F) continue;
-            acc[ci * 9 + ky * 3 + kx] = fmaf(gv, __ldg(xp + (int64_t)tt * F + ff), acc[ci * 9 + ky * 3 + kx]);
+        for (int u = 0; u < 4; ++u) {
+          const int f = min(f0 + u, f_hi - 1);
+          q1[u] = *reinterpret_cast<const uint2*>(v1 + rowoff + (int64_t)f * 32);
+          if (v2) q2[u] = *reinterpret_cast<const uint2*>(v2 + rowoff + (int64_t)f * 32);
+        }
+        // stencil columns f0-1 .. f0+4 of the three rows and two planes
+        float win[2][3][6];
+#pragma unroll
+        for (int pl = 0; pl < 2; ++pl)
+#pragma unroll
+          for (int dy = 0; dy < 3; ++dy)
+#pragma unroll
+            for (int j = 0; j < 6; ++j) {
+              const int c = min(f0 + j, F + 1);            // halo-shifted column of f0 - 1 + j
+              win[pl][dy][j] = p0[(dy * 2 + pl) * pitch + bw_sidx(c)];
+            }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          if (f0 + u >= f_hi) break;
+          float2 a = unpack_bf16x2(q1[u].x), c2 = unpack_bf16x2(q1[u].y);
+          float v[4] = {a.x, a.y, c2.x, c2.y};
+          if (v2) {
+            a = unpack_bf16x2(q2[u].x); c2 = unpack_bf16x2(q2[u].y);
+            v[0] += a.x; v[1] += a.y; v[2] += c2.x; v[3] += c2.y;
+          }
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            if (!CONV_OUT) vsum[c] += v[c];
+#pragma unroll
+            for (int pl = 0; pl < 2; ++pl)
+#pragma unroll
+              for (int dy = 0; dy < 3; ++dy)
+#pragma unroll
+                for (int dx = 0; dx < 3; ++dx) acc[c][(pl * 3 + dy) * 3 + dx] = fmaf(v[c], win[pl][dy][u + dx], acc[c][(pl * 3 + dy) * 3 + dx]);
           }
         }
       }
     }
   }
-#pragma unroll
-  for (int i = 0; i < NA; ++i) s_acc[warp][i][lane] = acc[i];
-  __syncthreads();
-  for (int o = threadIdx.x; o < NA * 32; o += blockDim.x) {
-    const int i = o >> 5, co = o & 31;
-    float s = 0.f;
-#pragma unroll
-    for (int w = 0; w < 8; ++w) s += s_acc[w][i][co];
-    if (i == NA - 1) atomicAdd(db + co, s);
-    else atomicAdd(dw + (int64_t)co * CIN * 9 + i, s);
-  }
-}
 
-extern "C" int ddimb_conv_in_wgrad(const float* x, const void* g1, const void* g2, float* dw, float* db, int B, int Cin, int T, int F,
-                                   int Cout, cudaStream_t stream) {
-  DDIMB_CHECK_ARG(x && g1 && dw && db && B >= 1 && Cin == 2 && Cout == 32);
-  DDIMB_PROF(stream, "conv_in_wgrad", Cin, Cout, (double)B * T * F * (4.0 * Cin + 2.0 * Cout * (g2 ? 2 : 1)), 18.0 * Cin * Cout * B * T * F);
-  conv_in_wgrad_kernel<2><<<dim3((T + 7) / 8, B), 256, 0, stream>>>(x, reinterpret_cast<const __nv_bfloat16*>(g1),
-                                                                    reinterpret_cast<const __nv_bfloat16*>(g2), dw, db, T, F);
-  DDIMB_LAUNCH_CHECK();
-  return DDIMB_OK;
-}
-
-// conv_out (models/diffusion.py:199-208,284): out[b,co,t,f] = bias + sum w[co][ci][ky][kx] * (h + skip)[b,t+ky-1,f+kx-1,ci].
-// dw[co][ci][ky][kx] += sum dout[b,co,t,f] * hs[b,t+ky-1,f+kx-1,ci], db[co] += sum dout.  lane = ci; a warp walks one row of hs.
-template <int CO>
-__global__ void __launch_bounds__(256) conv_out_wgrad_kernel(const __nv_bfloat16* __restrict__ h, const __nv_bfloat16* __restrict__ skip,
-                                                            const float* __restrict__ dout, float* __restrict__ dw, float* __restrict__ db,
-                                                            int T, int F) {
-  constexpr int NA = CO * 9;
-  __shared__ float s_acc[8][NA][32];
-  __shared__ float s_b[8][CO];
-  const int b = blockIdx.y, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int tq = blockIdx.x * 8 + warp;   // row of hs
-  float acc[NA];
+  // reduce the four row quarters (lanes 8 apart), then the eight warps, then one atomic per accumulator
 #pragma unroll
-  for (int i = 0; i < NA; ++i) acc[i] = 0.f;
-  float bacc = 0.f;
-  if (tq < T) {
-    const int64_t rowoff = (((int64_t)b * T + tq) * F) * 32 + lane;
-    for (int fq = 0; fq < F; ++fq) {
-      float v = __bfloat162float(h[rowoff + (int64_t)fq * 32]);
-      if (skip) v += __bfloat162float(skip[rowoff + (int64_t)fq * 32]);
+  for (int c = 0; c < 4; ++c) {
 #pragma unroll
-      for (int co = 0; co < CO; ++co) {
-        const float* dp = dout + ((int64_t)(b * CO + co) * T) * F;
-#pragma unroll
-        for (int ky = 0; ky < 3; ++ky) {
-          const int t = tq - ky + 1;
-          if (t < 0 || t >= T) continue;
-#pragma unroll
-          for (int kx = 0; kx < 3; ++kx) {
-            const int f = fq - kx + 1;
-            if (f < 0 || f >= F) continue;
-            acc[co * 9 + ky * 3 + kx] = fmaf(v, __ldg(dp + (int64_t)t * F + f), acc[co * 9 + ky * 3 + kx]);
-          }
-        }
-      }
+    for (int i = 0; i < 18; ++i) {
+      float s = acc[c][i];
+      s += __shfl_xor_sync(0xffffffffu, s, 8);
+      s += __shfl_xor_sync(0xffffffffu, s, 16);
+      acc[c][i] = s;
     }
-    if (lane < CO) {
-      const float* dp = dout + ((int64_t)(b * CO + lane) * T + tq) * F;
-      for (int f = 0; f < F; ++f) bacc += dp[f];
+    vsum[c] += __shfl_xor_sync(0xffffffffu, vsum[c], 8);
+    vsum[c] += __shfl_xor_sync(0xffffffffu, vsum[c], 16);
+  }
+#pragma unroll
+  for (int pl = 0; pl < 2; ++pl)
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) psum[pl] += __shfl_xor_sync(0xffffffffu, psum[pl], o);
+  __syncthreads();
+  float* red = s_p;                                        // [8 warps][32 channels][19] + [8][2]
+  if (seg == 0) {
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+#pragma unroll
+      for (int i = 0; i < 18; ++i) red[(warp * 32 + cg * 4 + c) * 19 + i] = acc[c][i];
+      red[(warp * 32 + cg * 4 + c) * 19 + 18] = vsum[c];
     }
   }
-#pragma unroll
-  for (int i = 0; i < NA; ++i) s_acc[warp][i][lane] = acc[i];
-  if (lane < CO) s_b[warp][lane] = bacc;
+  if (lane == 0) { red[8 * 32 * 19 + warp * 2] = psum[0]; red[8 * 32 * 19 + warp * 2 + 1] = psum[1]; }
   __syncthreads();
-  for (int o = threadIdx.x; o < NA * 32; o += blockDim.x) {
-    const int i = o >> 5, ci = o & 31;
-    const int co = i / 9, tap = i - co * 9;
+  for (int o = threadIdx.x; o < 32 * 19; o += blockDim.x) {
+    const int ch = o / 19, i = o - ch * 19;
     float s = 0.f;
 #pragma unroll
-    for (int w = 0; w < 8; ++w) s += s_acc[w][i][ci];
-    atomicAdd(dw + ((int64_t)co * 32 + ci) * 9 + tap, s);
+    for (int w = 0; w < 8; ++w) s += red[(w * 32 + ch) * 19 + i];
+    if (i == 18) {
+      if (!CONV_OUT) atomicAdd(db + ch, s);
+      continue;
+    }
+    const int pl = i / 9, dy = (i - pl * 9) / 3, dx = i - pl * 9 - dy * 3;
+    if (CONV_OUT) atomicAdd(dw + ((int64_t)pl * 32 + ch) * 9 + (2 - dy) * 3 + (2 - dx), s);   // hs[q] meets dout[q + d]  <=>  tap k = 1 - d
+    else atomicAdd(dw + ((int64_t)ch * 2 + pl) * 9 + dy * 3 + dx, s);                       // g[q] meets x[q + d]      <=>  tap k = 1 + d
   }
-  if (threadIdx.x < CO) {
+  if (CONV_OUT && threadIdx.x < 2) {
     float s = 0.f;
-    for (int w = 0; w < 8; ++w) s += s_b[w][threadIdx.x];
+    for (int w = 0; w < 8; ++w) s += red[8 * 32 * 19 + w * 2 + threadIdx.x];
     atomicAdd(db + threadIdx.x, s);
   }
 }
 
-extern "C" int ddimb_conv_out_wgrad(const void* h, const void* skip, const float* dout, float* dw, float* db, int B, int T, int F, int Cin,
-                                    int Cout, cudaStream_t stream) {
-  DDIMB_CHECK_ARG(h && dout && dw && db && B >= 1 && Cin == 32 && Cout == 2);
-  DDIMB_PROF(stream, "conv_out_wgrad", Cin, Cout, (double)B * T * F * (2.0 * Cin * (skip ? 2 : 1) + 4.0 * Cout), 18.0 * Cin * Cout * B * T * F);
-  conv_out_wgrad_kernel<2><<<dim3((T + 7) / 8, B), 256, 0, stream>>>(reinterpret_cast<const __nv_bfloat16*>(h), reinterpret_cast<const __nv_bfloat16*>(skip),
-                                                                     dout, dw, db, T, F);
+template <bool CONV_OUT>
+static int boundary_wgrad_launch(const void* v1, const void* v2, const float* img, float* dw, float* db, int B, int T, int F, cudaStream_t stream) {
+  const int c_max = F + 1;
+  const int pitch = ((c_max + ((c_max >> 6) << 3) + 1) + 7) & ~7;
+  size_t smem = (size_t)(kBwRows + 2) * 2 * pitch * sizeof(float);
+  const size_t red = (size_t)(8 * 32 * 19 + 16) * sizeof(float);
+  if (smem < red) smem = red;
+  DDIMB_SMEM_ATTR((boundary_wgrad_kernel<CONV_OUT>), smem);
+  const int units_t = (T + kBwRows - 1) / kBwRows;
+  const int64_t units = (int64_t)B * units_t;
+  int64_t grid = (int64_t)ddimb_num_sms() * 2;
+  if (grid > units) grid = units;
+  boundary_wgrad_kernel<CONV_OUT><<<(unsigned)grid, kBwThreads, smem, stream>>>(reinterpret_cast<const __nv_bfloat16*>(v1), reinterpret_cast<const __nv_bfloat16*>(v2),
+                                                                               img, dw, db, B, T, F, units_t, (int)units, pitch);
   DDIMB_LAUNCH_CHECK();
   return DDIMB_OK;
+}
+
+extern "C" int ddimb_conv_in_wgrad(const float* x, const void* g1, const void* g2, float* dw, float* db, int B, int Cin, int T, int F,
+                                   int Cout, cudaStream_t stream) {
+  DDIMB_CHECK_ARG(x && g1 && dw && db && B >= 1 && T >= 1 && F >= 1 && Cin == 2 && Cout == 32);
+  DDIMB_CHECK_ARG((int64_t)B * ((T + kBwRows - 1) / kBwRows) < (1ll << 31));
+  DDIMB_PROF(stream, "conv_in_wgrad", Cin, Cout, (double)B * T * F * (4.0 * Cin + 2.0 * Cout * (g2 ? 2 : 1)), 18.0 * Cin * Cout * B * T * F);
+  return boundary_wgrad_launch<false>(g1, g2, x, dw, db, B, T, F, stream);
+}
+
+extern "C" int ddimb_conv_out_wgrad(const void* h, const void* skip, const float* dout, float* dw, float* db, int B, int T, int F, int Cin,
+                                    int Cout, cudaStream_t stream) {
+  DDIMB_CHECK_ARG(h && dout && dw && db && B >= 1 && T >= 1 && F >= 1 && Cin == 32 && Cout == 2);
+  DDIMB_CHECK_ARG((int64_t)B * ((T + kBwRows - 1) / kBwRows) < (1ll << 31));
+  DDIMB_PROF(stream, "conv_out_wgrad", Cin, Cout, (double)B * T * F * (2.0 * Cin * (skip ? 2 : 1) + 4.0 * Cout), 18.0 * Cin * Cout * B * T * F);
+  return boundary_wgrad_launch<true>(h, skip, dout, dw, db, B, T, F, stream);
 }
