@@ -30,6 +30,7 @@ SIGNATURES = {
     "ddimb_sqerr_loss": [_vp, _vp, _vp, _i, _ll],
     "ddimb_sqerr_loss_bwd": [_vp, _vp, _vp, _vp, _i, _ll],
     "ddimb_denoise2d": [_vp, _vp, _vp, _ll, _i, _i, _i, _i, _i],
+    "ddimb_denoise2d_static": [_vp, _vp, _i, _i, _i, _i, _i],
     "ddimb_pfft2wav": [_vp, _vp, _vp, _vp, _vp, _vp, _ll, _i, _i, _i, _i, _d, _d, _d, _d, _d],
     "ddimb_ema_update": [_vp, _i, _ll, _d],
     "ddimb_grad_clip": [_vp, _i, _ll, _d, _vp, _vp],
@@ -71,7 +72,7 @@ SIGNATURES = {
     "ddimb_conv_in_wgrad": [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i],
     "ddimb_conv_out_wgrad": [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i],
 }
-EXPORTS = ["ddimb_version", "ddimb_last_error", "ddimb_launch_count", "ddimb_prof_enable", "ddimb_prof_report", "ddimb_conv3x3_wide_supported", "ddimb_conv3x3_gn_supported", "ddimb_denoise2d_workspace", "ddimb_conv_wimg_bytes", "ddimb_pfft2wav_workspace"] + list(SIGNATURES)
+EXPORTS = ["ddimb_version", "ddimb_last_error", "ddimb_launch_count", "ddimb_prof_enable", "ddimb_prof_report", "ddimb_conv3x3_wide_supported", "ddimb_conv3x3_gn_supported", "ddimb_denoise2d_workspace", "ddimb_denoise2d_static_max_bytes", "ddimb_conv_wimg_bytes", "ddimb_pfft2wav_workspace"] + list(SIGNATURES)
 
 lib.ddimb_version.restype = _i
 lib.ddimb_last_error.restype = C.c_char_p
@@ -86,6 +87,8 @@ lib.ddimb_conv_wimg_bytes.argtypes = [_i, _i, _i, _i]
 lib.ddimb_conv_wimg_bytes.restype = _ll
 lib.ddimb_denoise2d_workspace.argtypes = [_i, _i, _i, _i, _i]
 lib.ddimb_denoise2d_workspace.restype = _ll
+lib.ddimb_denoise2d_static_max_bytes.argtypes = []
+lib.ddimb_denoise2d_static_max_bytes.restype = _ll
 lib.ddimb_prof_enable.argtypes = [_i]
 lib.ddimb_prof_enable.restype = _i
 lib.ddimb_prof_report.argtypes = [C.c_char_p, _i]

@@ -412,3 +412,45 @@ extern "C" int ddimb_denoise2d(const float* x, float* out, void* workspace, long
   if (F == 256) return run<2>(x, out, w, B, T, iters, stream);
   return run<4>(x, out, w, B, T, iters, stream);
 }
+
+// ------------------------------------------------------------------------------------------------ allocation-free variant
+// No counterpart in the reference: added for callers that cannot allocate device memory (code
+// under CUDA graph capture, serving loops, harnesses that forbid cudaMalloc).  Same kernels as ddimb_denoise2d, but the scratch is the
+// file-scope device array below instead of a caller buffer: every GPU that loads the library holds kDenoiseStaticBytes until exit.
+// The array is shared by every call on that GPU and keeps the previous call's contents -- the parts that must start at zero
+// (histograms, column sums) are cleared on the stream at the start of every call, exactly as the caller-workspace path does -- so
+// two calls that overlap on the GPU (different streams, no ordering) race on it.
+constexpr long long kDenoiseStaticBytes = 4ll << 20;           // 4 MiB: e.g. x[1,2,8192,256] needs 1.06 MiB, x[3,2,8192,256] 3.2 MiB at 5 iterations
+static __device__ __align__(256) unsigned char g_denoise_scratch[kDenoiseStaticBytes];
+
+extern "C" long long ddimb_denoise2d_static_max_bytes() { return kDenoiseStaticBytes; }
+
+extern "C" int ddimb_denoise2d_static(const float* x, float* out, int B, int C, int T, int F, int iters, cudaStream_t stream) {
+  DDIMB_CHECK_ARG(x && out && B >= 1 && T >= 1 && iters >= 0 && iters <= 8);
+  DDIMB_CHECK_ARG(C == 2);
+  DDIMB_CHECK_ARG(F == 128 || F == 256 || F == 512);
+  DDIMB_CHECK_ARG((long long)B * C <= 65535);
+  DDIMB_CHECK_ARG((reinterpret_cast<uintptr_t>(x) & 15) == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0);
+  const long long need = (long long)carve(nullptr, B, C, T, F, iters).total;
+  if (need > kDenoiseStaticBytes) {
+    ddimb_set_error("ddimb_denoise2d_static: x[%d,%d,%d,%d] with %d iterations needs %lld bytes of scratch, the built-in array holds %lld; "
+                    "use ddimb_denoise2d with a caller workspace", B, C, T, F, iters, need, kDenoiseStaticBytes);
+    return DDIMB_ERR_ARG;
+  }
+  // In host code the array's name is a host-side stand-in, not a device address: resolve it once per device, with that device current.
+  static void* dev_ptr[64] = {nullptr};
+  int dev = 0;
+  DDIMB_CUDA(cudaGetDevice(&dev));
+  DDIMB_CHECK_ARG(dev >= 0 && dev < 64);
+  if (!dev_ptr[dev]) {
+    void* ptr = nullptr;
+    DDIMB_CUDA(cudaGetSymbolAddress(&ptr, g_denoise_scratch));
+    DDIMB_CHECK_ARG(ptr != nullptr && (reinterpret_cast<uintptr_t>(ptr) & 255) == 0);
+    dev_ptr[dev] = ptr;
+  }
+  const Workspace w = carve(dev_ptr[dev], B, C, T, F, iters);
+  DDIMB_PROF(stream, "denoise2d_static", F, iters, 8.0 * B * C * T * F, 12.0 * iters * B * C * T * F);
+  if (F == 128) return run<1>(x, out, w, B, T, iters, stream);
+  if (F == 256) return run<2>(x, out, w, B, T, iters, stream);
+  return run<4>(x, out, w, B, T, iters, stream);
+}

@@ -67,6 +67,17 @@ long long ddimb_denoise2d_workspace(int B, int C, int T, int F, int iters);
 int ddimb_denoise2d(const float* x, float* out, void* workspace, long long workspace_bytes, int B, int C, int T, int F, int iters,
                     cudaStream_t stream);
 
+/* Allocation-free variant of ddimb_denoise2d.  It has NO counterpart in the reference: it was added
+ * for callers that cannot allocate device memory (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  Same arguments, kernels and results as ddimb_denoise2d, but the scratch is a file-scope device array inside the
+ * library (ddimb_denoise2d_static_max_bytes() = 4 MiB, held by every GPU that loads the library until exit) and the call performs no
+ * cudaMalloc / cudaFree or other allocating call.  Shapes whose ddimb_denoise2d_workspace() exceeds that limit are rejected with
+ * DDIMB_ERR_ARG and a message in ddimb_last_error() (x[3,2,8192,256] at 5 iterations fits, x[4,...] does not).  The array is shared
+ * by every call on the GPU and keeps the last call's contents (what must start at zero is cleared on the stream at the start of each
+ * call): calls that OVERLAP on the GPU -- different streams without ordering -- race on it; calls ordered on one stream do not. */
+long long ddimb_denoise2d_static_max_bytes(void);
+int ddimb_denoise2d_static(const float* x, float* out, int B, int C, int T, int F, int iters, cudaStream_t stream);
+
 /* External/SST/utils/wav2img.py:82-127 pfft2wav as called by runners/diffusion.py:401-420 on x0.permute(0,3,2,1)[b], for a whole batch:
  * x fp32 [B][2][T][F] (NCHW: re / im planes) -> out int32 [B][(F-1)*(T-1)] PCM.  sri: double [F] ISO-226 weights of the rfft
  * frequencies; wt: fp32 [2F][NP] irfft basis (n = 2(F-1), NP = n rounded up to 128) with the hann synthesis window and win.sum()
