@@ -21,7 +21,9 @@
 //     WP > 32) and the tile leaves through the tensor map whose box has 32, 31 or 30 rows; the T * W bound clips rows >= T.
 //     (TMA stores fault on negative start coordinates, so clipping cannot remove a leading halo position.)
 // Per 256 positions the kernel moves the window (~90 KB) + the weights (9 C^2 x 2 B) through L2 instead of 9 A boxes + the weights
-// per 128 positions.  Warp roles (512 threads): 0 = window producer, 1 = MMA issuer, 2 = weight producer, 3 idle, 4-7 = epilogue (one
+// per 128 positions.  Warp roles (512 threads): 0 = window producer, 1 / 3 = MMA issuers of accumulator tile 0 / 1 (a single thread gets one
+// N <= 128 MMA through every ~81-94 cycles whatever N is, two threads interleave down to ~60 at N = 96: tools/umma_tput.cu,
+// profiles/r02_experiments.md section 6; the tiles share nothing but the operand barriers), 2 = weight producer, 4-7 = epilogue (one
 // per TMEM lane quarter, both accumulator tiles), 8-15 = transform (measured: with four transform warps working one 16-byte granule
 // at a time the fused kernel was SLOWER than gn_apply + conv; eight warps with four granules in flight each keep the planes ahead
 // of the MMA warp).
@@ -226,15 +228,15 @@ conv3x3_window_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
     for (int i = 0; i < NCH; ++i) {
       mbar_init(bar_pfull + 8 * i, 1);
       mbar_init(bar_pready + 8 * i, kWinXfWarps);
-      mbar_init(bar_pempty + 8 * i, 1);
+      mbar_init(bar_pempty + 8 * i, 2);            // both MMA issuers
     }
     for (int i = 0; i < 2; ++i) {
-      mbar_init(bar_afull + 8 * i, 1);
+      mbar_init(bar_afull + 8 * i, 2);
       mbar_init(bar_aempty + 8 * i, kWinEpiWarps);   // one arrive per epilogue warp
     }
     for (int s = 0; s < NBS; ++s) {
       mbar_init(bar_bfull + 8 * s, 1);
-      mbar_init(bar_bempty + 8 * s, 1);
+      mbar_init(bar_bempty + 8 * s, 2);
     }
     mbar_fence_init();
   }
@@ -274,9 +276,10 @@ conv3x3_window_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
         }
       }
     }
-  } else if (warp == 1) {
-    // ================================================================ MMA issuer (one elected thread)
+  } else if (warp == 1 || warp == 3) {
+    // ================================================================ MMA issuers (one elected thread each; warp 1 = tile 0, warp 3 = tile 1)
     if (elect_one()) {
+      const uint32_t g = warp == 1 ? 0u : 1u;
       const uint64_t desc_hi = make_kmajor_desc(0, 512, 4);              // SWIZZLE_64B, 8-row group pitch 512 B
       const uint32_t idesc = make_idesc_bf16(kWinTile, (uint32_t)C);
       const uint32_t bar_in = fused ? bar_pready : bar_pfull;
@@ -287,7 +290,7 @@ conv3x3_window_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
         const uint32_t buf = it & 1, ph = (it >> 1) & 1;
         mbar_wait(bar_aempty + 8 * buf, ph ^ 1, 33);
         tc_fence_after();
-        const uint32_t acc = tmem_base + buf * (2 * C);
+        const uint32_t acc = tmem_base + buf * (2 * C) + g * C;
 #pragma unroll 1
         for (int ch = 0; ch < NCH; ++ch) {
           mbar_wait(bar_in + 8 * ch, it & 1, 34);
@@ -299,20 +302,17 @@ conv3x3_window_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
             const uint32_t s = cnt % NBS, use = cnt / NBS;
             mbar_wait(bar_bfull + 8 * s, use & 1, 35);
             tc_fence_after();
-            const uint32_t a_lo = ((plane + pos * 64) & 0x3FFFFu) >> 4;
+            const uint32_t a_lo = ((plane + (pos + g * kWinTile) * 64) & 0x3FFFFu) >> 4;
             const uint32_t b_lo = ((b_base + s * Cfg::kBStage) & 0x3FFFFu) >> 4;
             const uint32_t first = (ch == 0 && tap == 0) ? 0u : 1u;
 #pragma unroll
-            for (int k = 0; k < 2; ++k) {
-              const uint64_t bd = desc_hi | (uint64_t)(b_lo + 2 * k);
-              umma_bf16(acc, desc_hi | (uint64_t)(a_lo + 2 * k), bd, idesc, k ? 1u : first);
-              umma_bf16(acc + C, desc_hi | (uint64_t)(a_lo + (kWinTile * 64 >> 4) + 2 * k), bd, idesc, k ? 1u : first);
-            }
+            for (int k = 0; k < 2; ++k)
+              umma_bf16(acc, desc_hi | (uint64_t)(a_lo + 2 * k), desc_hi | (uint64_t)(b_lo + 2 * k), idesc, k ? 1u : first);
             umma_commit(bar_bempty + 8 * s);
           }
           umma_commit(bar_pempty + 8 * ch);      // plane consumed: the next unit's plane may land
         }
-        umma_commit(bar_afull + 8 * buf);        // both accumulator tiles complete
+        umma_commit(bar_afull + 8 * buf);        // this issuer's accumulator tile is complete
       }
     }
   } else if (warp >= 4 && warp < 4 + kWinEpiWarps) {
