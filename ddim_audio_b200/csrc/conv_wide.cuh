@@ -15,17 +15,16 @@
 
 namespace ddimb {
 
-#ifndef DDIMB_WIDE_EPI
-#define DDIMB_WIDE_EPI 8
-#endif
 #ifndef DDIMB_WIDE_BULKST
 #define DDIMB_WIDE_BULKST 1
 #endif
-#ifndef DDIMB_WIDE_XF
-#define DDIMB_WIDE_XF 6
+// C = 32 accumulator protocol: the epilogue warps hand every accumulator block back ZEROED (tcgen05.st after their tcgen05.ld), so every
+// MMA accumulates and the block an input row opens needs no separate overwriting MMA: 6 MMAs per row instead of 7 (one thread gets an
+// N <= 128 MMA through every ~81-94 cycles whatever N is: tools/umma_tput.cu).  Measured -3 % (profiles/r02_experiments.md section 6;
+// a second issuing warp in place of a transform warp gained 8 % without the GroupNorm prologue and nothing with GroupNorm + SiLU).
+#ifndef DDIMB_WIDE32_ZERO
+#define DDIMB_WIDE32_ZERO 1
 #endif
-constexpr int kWideEpiWarps = DDIMB_WIDE_EPI, kWideXfWarps = DDIMB_WIDE_XF;   // 4 or 8 epilogue warps
-constexpr int kWideThreads = 32 * (2 + kWideEpiWarps + kWideXfWarps);
 constexpr int kWidePos = 130;   // positions per row strip: 128 + 2 halo columns
 
 struct WideParams {
@@ -53,21 +52,27 @@ struct WideCfg {
   static constexpr int kRowBytes = C * 2;
   static constexpr int kSlotBytes = ((kWidePos * kRowBytes + 1023) / 1024) * 1024;
   // rows in flight (HBM latency x bandwidth needs > 60 KB per SM).  MUST be a multiple of the transform warp count: a transform
-  // warp owns rows r = tw (mod kWideXfWarps), so with kSlots % kWideXfWarps == 0 it is also the only warp that ever waits on the
+  // warp owns rows r = tw (mod kXfWarps), so with kSlots % kXfWarps == 0 it is also the only warp that ever waits on the
   // "raw" barrier of a given slot, and it cannot run a whole phase ahead of it.  With 8 slots and 6 warps a fast warp (affine-only
   // prologue) could reach a slot before the PREVIOUS row of that slot had landed, its parity wait aliased to the phase before, and
   // the CTA deadlocked (seen at T = 4096).
-  static constexpr int kSlots = (C == 32) ? 3 * kWideXfWarps : kWideXfWarps;
-  static constexpr int kAccBufs = 8;                // output rows in flight in TMEM
-  static constexpr int kTmemCols = 8 * C;           // 256 / 512 columns
+  static constexpr bool kZeroAcc = (C == 32) && (DDIMB_WIDE32_ZERO != 0);
+  static constexpr int kIssuers = 1;
+  static constexpr int kEpiWarps = 8;                                     // two warps per TMEM lane quarter
+  static constexpr int kXfWarps = 6;
+  static constexpr int kXfWarp0 = 2 + kEpiWarps;
+  static constexpr int kThreads = 32 * (kXfWarp0 + kXfWarps);             // 512: a 17th warp would leave a scheduler's five warps 102 registers each
+  static constexpr int kSlots = (C == 32) ? 3 * kXfWarps : kXfWarps;
+  static constexpr int kAccBufs = (C == 32) ? 16 : 8;   // output rows in flight in TMEM (the ring wraps inside an input row's three blocks on 2 of kAccBufs rows: those rows cost two MMAs per step)
+  static constexpr int kTmemCols = kAccBufs * C;    // 512 columns
   static constexpr int kWBytes = 9 * C * C * 2;
   static constexpr int kSwizzle = (C == 64) ? 2 : 4;
   static constexpr int kSBO = 8 * kRowBytes;
-  static constexpr int kXfTabBytes = ((kWideXfWarps * C * 8 + 1023) / 1024) * 1024;
+  static constexpr int kXfTabBytes = ((kXfWarps * C * 8 + 1023) / 1024) * 1024;
   static constexpr bool kStage = (C == 32);           // the legacy (skip-add) epilogue's smem-staged stores need 2 KB per warp: C = 32 only
   static constexpr int kStageBytes = 32 * C * 2;      // one epilogue warp's output tile (32 positions x C channels): the TMA store's source
   static constexpr int kStageBufs = (C == 32) ? 2 : 1;  // C = 32 has room for two tiles per warp: a tile is never rewritten while the TMA engine may still read it
-  static constexpr int kAuxBytes = 1024 + 4096 + kXfTabBytes + kWideEpiWarps * kStageBufs * kStageBytes;   // barriers | epilogue bias copies | transform scale/shift copies | store staging
+  static constexpr int kAuxBytes = 1024 + 4096 + kXfTabBytes + kEpiWarps * kStageBufs * kStageBytes;   // barriers | epilogue bias copies | transform scale/shift copies | store staging
   static constexpr int kSmemBytes = 1024 + kWBytes + kSlots * kSlotBytes + kAuxBytes;
 };
 
@@ -94,7 +99,7 @@ struct WideUnit {
 };
 
 // Transform warp of conv3x3_wide_kernel: GroupNorm affine (MODE 1) or affine + SiLU (MODE 2) applied in place to the row
-// strips this warp owns (every kWideXfWarps-th).  Lane -> (position p0 + 32/CH * k, 16-byte chunk j): consecutive k are 512 B
+// strips this warp owns (every WideCfg<C>::kXfWarps-th).  Lane -> (position p0 + 32/CH * k, 16-byte chunk j): consecutive k are 512 B
 // apart for both channel counts.  The loop body is branch-free (mode is a template parameter, only the 2-position tail and the
 // two image-edge halo positions are special) so the independent pair chains of a batch interleave: the branchy version spent
 // ~1040 warp instructions per row at 6 cycles each, most of them control flow around 16-byte granules.
@@ -147,9 +152,9 @@ __device__ __forceinline__ void wide_transform_warp(const WideParams& p, uint8_t
       for (int e = 0; e < 4; ++e) { sc2[e] = pack2(tab[8 * j + 2 * e], tab[8 * j + 2 * e + 1]); sh2[e] = pack2(tab[C + 8 * j + 2 * e], tab[C + 8 * j + 2 * e + 1]); }
     }
     const bool left_edge = (u.w0 == 0), right_edge = (u.w0 + 128 == p.W);
-    // first row of this unit owned by this warp, then every kWideXfWarps-th
-    int rr = (int)((uint32_t)(tw + kWideXfWarps - (int)(cnt % kWideXfWarps)) % kWideXfWarps);
-    for (; rr < u.rows + 2; rr += kWideXfWarps) {
+    // first row of this unit owned by this warp, then every WideCfg<C>::kXfWarps-th
+    int rr = (int)((uint32_t)(tw + WideCfg<C>::kXfWarps - (int)(cnt % WideCfg<C>::kXfWarps)) % WideCfg<C>::kXfWarps);
+    for (; rr < u.rows + 2; rr += WideCfg<C>::kXfWarps) {
       const uint32_t c2 = cnt + (uint32_t)rr;
       const uint32_t slot = c2 % NS, use = c2 / NS;
       const int t = u.t0 - 1 + rr;
@@ -192,7 +197,7 @@ __device__ __forceinline__ void wide_epilogue_lean(const WideParams& p, const CU
                                                    uint32_t bar_aempty, float* wb, uint8_t* stage_gen, int warp, int lane) {
   using Cfg = WideCfg<C>;
   constexpr int NB = Cfg::kAccBufs;
-  constexpr uint32_t kGrpMask = kWideEpiWarps / 4 - 1;
+  constexpr uint32_t kGrpMask = WideCfg<C>::kEpiWarps / 4 - 1;
   constexpr int CG = C / 8;
   // C = 32: the warp's 32 positions x 64 B are contiguous in global memory, so they leave as ONE 1-D bulk copy of a linear tile (C = 64:
   // a tensor store of the swizzled tile).  Measured equal to the tensor store at C = 32 (profiles/r02_experiments.md section 1); straight
@@ -233,6 +238,11 @@ __device__ __forceinline__ void wide_epilogue_lean(const WideParams& p, const CU
         tmem_ld32(trow + (uint32_t)c0, v);
         tmem_ld_wait();
         if (c0 + 32 == C) {     // accumulators are in registers: the MMA warp may overwrite the buffer
+          if (Cfg::kZeroAcc) {  // ... which it only ever accumulates into: hand it back zeroed
+#pragma unroll
+            for (int z0 = 0; z0 < C; z0 += 32) tmem_st_zero32(trow + (uint32_t)z0);
+            tmem_st_wait();
+          }
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(bar_aempty + 8 * buf);
@@ -307,7 +317,7 @@ __device__ __forceinline__ void wide_epilogue_lean(const WideParams& p, const CU
 }
 
 template <int C>
-__global__ void __launch_bounds__(kWideThreads, 1)
+__global__ void __launch_bounds__(WideCfg<C>::kThreads, 1)
 conv3x3_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmO,
                     const __grid_constant__ WideParams p) {
   using Cfg = WideCfg<C>;
@@ -320,10 +330,10 @@ conv3x3_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   uint8_t* a_gen = smem_gen + Cfg::kWBytes;
   const uint32_t aux = a_base + NS * Cfg::kSlotBytes;
   uint8_t* aux_gen = a_gen + NS * Cfg::kSlotBytes;
-  // aux: raw_full[24] @0, ready[24] @192, empty[24] @384, acc_full[8] @576, acc_empty[8] @640, wfull @704, tmem ptr @712
-  static_assert(NS <= 24 && NS % kWideXfWarps == 0, "ring slots: a multiple of the transform warp count");
-  const uint32_t bar_raw = aux, bar_ready = aux + 192, bar_empty = aux + 384, bar_afull = aux + 576, bar_aempty = aux + 640, bar_w = aux + 704;
-  volatile uint32_t* tmem_ptr_gen = reinterpret_cast<volatile uint32_t*>(aux_gen + 712);
+  // aux: raw_full[24] @0, ready[24] @192, empty[24] @384, acc_full[16] @576, acc_empty[16] @704, wfull @832, tmem ptr @840
+  static_assert(NS <= 24 && NS % WideCfg<C>::kXfWarps == 0, "ring slots: a multiple of the transform warp count");
+  const uint32_t bar_raw = aux, bar_ready = aux + 192, bar_empty = aux + 384, bar_afull = aux + 576, bar_aempty = aux + 704, bar_w = aux + 832;
+  volatile uint32_t* tmem_ptr_gen = reinterpret_cast<volatile uint32_t*>(aux_gen + 840);
   float* bias_smem = reinterpret_cast<float*>(aux_gen + 1024);
   float* gn_smem = reinterpret_cast<float*>(aux_gen + 1024 + 4096);
 
@@ -337,17 +347,17 @@ conv3x3_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     for (int s = 0; s < NS; ++s) {
       mbar_init(bar_raw + 8 * s, 1);
       mbar_init(bar_ready + 8 * s, 1);    // the transform warp that owns the row
-      mbar_init(bar_empty + 8 * s, 1);
+      mbar_init(bar_empty + 8 * s, Cfg::kIssuers);
     }
     for (int b = 0; b < NB; ++b) {
-      mbar_init(bar_afull + 8 * b, 1);
+      mbar_init(bar_afull + 8 * b, Cfg::kIssuers);
       mbar_init(bar_aempty + 8 * b, 4);   // one arrive per epilogue warp
     }
     mbar_init(bar_w, 1);
     mbar_fence_init();
   }
   if (warp == 1) {
-    tmem_alloc(aux + 712, (uint32_t)Cfg::kTmemCols);
+    tmem_alloc(aux + 840, (uint32_t)Cfg::kTmemCols);
     tmem_relinquish();
   }
   tc_fence_before();
@@ -415,10 +425,22 @@ conv3x3_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           const uint32_t iai = make_idesc_bf16(kTileM, (uint32_t)(has_ai ? spl_i - fb : 1) * C);
           const uint32_t ibi = make_idesc_bf16(kTileM, (uint32_t)(has_bi ? lbi - split + 1 : 1) * C);
           mbar_wait(bar_in + 8 * slot, ((cnt + rr) / NS) & 1, 13);
-          if (v2) mbar_wait(bar_aempty + 8 * b2, (((otile + rr) / NB) & 1) ^ 1, 14);
+          if (v2) mbar_wait(bar_aempty + 8 * b2, ((((otile + rr) / NB) & 1) ^ 1) ^ (Cfg::kZeroAcc ? 1u : 0u), 14);   // zeroed mode: phase 0 = the initial zeroing
           tc_fence_after();
           const uint32_t a_lo = ((a_base + slot * Cfg::kSlotBytes) & 0x3FFFFu) >> 4;
-          {
+          if (Cfg::kZeroAcc) {
+            // every block fb..lb accumulates in every step
+#pragma unroll
+            for (int kx = 0; kx < 3; ++kx) {
+#pragma unroll
+              for (int k = 0; k < C / 16; ++k) {
+                const uint64_t ad = desc_hi | (uint64_t)(a_lo + (uint32_t)(kx * (Cfg::kRowBytes >> 4) + 2 * k));
+                const uint32_t wl = w_lo + (uint32_t)(kx * 3) * kTile16 + 2 * k;
+                umma_bf16(ta, ad, desc_hi | (uint64_t)(wl + wa), ia, 1u);
+                if (has_b) umma_bf16(tmem_base, ad, desc_hi | (uint64_t)(wl + wb2), ib, 1u);
+              }
+            }
+          } else {
             {
               const uint64_t ad = desc_hi | (uint64_t)a_lo;
               if (has_ai) umma_bf16(ta, ad, desc_hi | (uint64_t)(w_lo + wa), iai, 1u);
@@ -444,10 +466,20 @@ conv3x3_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         otile += u.rows;
       }
     }
-  } else if (warp < 2 + kWideEpiWarps) {
+  } else if (warp < 2 + WideCfg<C>::kEpiWarps) {
     // ================================================================ epilogue (TMEM lane quarter = warp % 4; group = output row parity)
     float* wb = bias_smem + (warp - 2) * 128;
     uint8_t* stage = aux_gen + 1024 + 4096 + Cfg::kXfTabBytes + (warp - 2) * Cfg::kStageBufs * Cfg::kStageBytes;
+    if (Cfg::kZeroAcc && warp < 6) {
+      // every accumulator block starts zeroed; this completes phase 0 of the "empty" barriers the issuers wait on before a block's first use
+#pragma unroll
+      for (int z0 = 0; z0 < Cfg::kTmemCols; z0 += 32) tmem_st_zero32(tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)z0);
+      tmem_st_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0)
+        for (int b = 0; b < NB; ++b) mbar_arrive(bar_aempty + 8 * b);
+    }
     if (p.add == nullptr) {
       const bool want = p.stats != nullptr;
 #define DDIMB_WIDE_EPI_CASE(A)                                                                                        \
@@ -461,7 +493,7 @@ conv3x3_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       // ---- legacy path: skip operand added after the activation (generic tile epilogue, direct / smem-staged stores)
       const int q = warp & 3;
       const uint32_t grp = (uint32_t)(warp - 2) >> 2;
-      constexpr uint32_t kGrpMask = kWideEpiWarps / 4 - 1;
+      constexpr uint32_t kGrpMask = WideCfg<C>::kEpiWarps / 4 - 1;
       const int row = q * 32 + lane;
       ConvEpiState<C> st;
       st.reset();
@@ -482,6 +514,11 @@ conv3x3_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           tc_fence_after();
           const uint32_t trow = tmem_base + ((uint32_t)(q * 32) << 16) + buf * C;
           conv_epilogue_tile<C, C>(trow, wb, p.act, p.add, p.out, addr0, true, p.stats != nullptr, st, Cfg::kStage ? stage : nullptr);
+          if (Cfg::kZeroAcc) {
+#pragma unroll
+            for (int z0 = 0; z0 < C; z0 += 32) tmem_st_zero32(trow + (uint32_t)z0);
+            tmem_st_wait();
+          }
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(bar_aempty + 8 * buf);
@@ -490,11 +527,11 @@ conv3x3_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       }
       st.flush(p.stats, lane);
     }
-  } else if (fused) {
+  } else if (fused && warp >= Cfg::kXfWarp0) {
     // ================================================================ transform: GroupNorm affine (+SiLU) in place
-    float* tab = gn_smem + (warp - (2 + kWideEpiWarps)) * 2 * C;
-    if (p.prologue == 2) wide_transform_warp<C, 2>(p, a_gen, bar_raw, bar_ready, tab, warp - (2 + kWideEpiWarps), lane);
-    else wide_transform_warp<C, 1>(p, a_gen, bar_raw, bar_ready, tab, warp - (2 + kWideEpiWarps), lane);
+    float* tab = gn_smem + (warp - Cfg::kXfWarp0) * 2 * C;
+    if (p.prologue == 2) wide_transform_warp<C, 2>(p, a_gen, bar_raw, bar_ready, tab, warp - Cfg::kXfWarp0, lane);
+    else wide_transform_warp<C, 1>(p, a_gen, bar_raw, bar_ready, tab, warp - Cfg::kXfWarp0, lane);
   }
 
   tc_fence_before();

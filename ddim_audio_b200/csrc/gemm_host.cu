@@ -258,10 +258,10 @@ static int launch_conv_wide(const void* x, const double* gn_stats, const float* 
   const int grid = p.num_units < ddimb_num_sms() ? p.num_units : ddimb_num_sms();
   if (C == 32) {
     DDIMB_SMEM_ATTR(conv3x3_wide_kernel<32>, WideCfg<32>::kSmemBytes);
-    conv3x3_wide_kernel<32><<<grid, kWideThreads, WideCfg<32>::kSmemBytes, stream>>>(tmA, tmB, tmO, p);
+    conv3x3_wide_kernel<32><<<grid, WideCfg<32>::kThreads, WideCfg<32>::kSmemBytes, stream>>>(tmA, tmB, tmO, p);
   } else {
     DDIMB_SMEM_ATTR(conv3x3_wide_kernel<64>, WideCfg<64>::kSmemBytes);
-    conv3x3_wide_kernel<64><<<grid, kWideThreads, WideCfg<64>::kSmemBytes, stream>>>(tmA, tmB, tmO, p);
+    conv3x3_wide_kernel<64><<<grid, WideCfg<64>::kThreads, WideCfg<64>::kSmemBytes, stream>>>(tmA, tmB, tmO, p);
   }
   DDIMB_LAUNCH_CHECK();
   return DDIMB_OK;
