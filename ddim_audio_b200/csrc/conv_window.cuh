@@ -23,7 +23,7 @@
 // Per 256 positions the kernel moves the window (~90 KB) + the weights (9 C^2 x 2 B) through L2 instead of 9 A boxes + the weights
 // per 128 positions.  Warp roles (512 threads): 0 = window producer, 1 / 3 = MMA issuers of accumulator tile 0 / 1 (a single thread gets one
 // N <= 128 MMA through every ~81-94 cycles whatever N is, two threads interleave down to ~60 at N = 96: tools/umma_tput.cu,
-// profiles/r02_experiments.md section 6; the tiles share nothing but the operand barriers), 2 = weight producer, 4-7 = epilogue (one
+// profiles/r02_experiments.md section 8; the tiles share nothing but the operand barriers), 2 = weight producer, 4-7 = epilogue (one
 // per TMEM lane quarter, both accumulator tiles), 8-15 = transform (measured: with four transform warps working one 16-byte granule
 // at a time the fused kernel was SLOWER than gn_apply + conv; eight warps with four granules in flight each keep the planes ahead
 // of the MMA warp).
