@@ -20,7 +20,7 @@ namespace ddimb {
 #endif
 // C = 32 accumulator protocol: the epilogue warps hand every accumulator block back ZEROED (tcgen05.st after their tcgen05.ld), so every
 // MMA accumulates and the block an input row opens needs no separate overwriting MMA: 6 MMAs per row instead of 7 (one thread gets an
-// N <= 128 MMA through every ~81-94 cycles whatever N is: tools/umma_tput.cu).  Measured -3 % (profiles/r02_experiments.md section 6;
+// N <= 128 MMA through every ~81-94 cycles whatever N is: tools/umma_tput.cu).  Measured -3 % (profiles/r02_experiments.md section 8;
 // a second issuing warp in place of a transform warp gained 8 % without the GroupNorm prologue and nothing with GroupNorm + SiLU).
 #ifndef DDIMB_WIDE32_ZERO
 #define DDIMB_WIDE32_ZERO 1

@@ -168,6 +168,30 @@ struct GnArgs {
   float eps;
 };
 
+// Block reduction of the per-thread GroupNorm partial sums (sa1, sa2: channels c0..c0+3; sb1, sb2: c0+4..c0+7) into the 8 x (sum, sumsq)
+// of the sample, then one fp64 atomic per statistic.  Fixed order (run-to-run reproducible per CTA): thread (slot, part) adds the
+// partials of threads part, part + 16, ... that belong to group slot / 2 in increasing order, then a fixed shuffle tree joins the 16
+// parts.  (The first version had 16 threads walk all 256 partials with a division per step: ~13 us per call, which is most of a
+// mode-2 call on the small tensors of the deep levels / small sampling batches.)
+__device__ __forceinline__ void gn_block_stats_flush(float (*s_part)[4], unsigned char (*s_grp)[2], float sa1, float sa2, float sb1, float sb2,
+                                                     double* stats_out_b) {
+  s_part[threadIdx.x][0] = sa1; s_part[threadIdx.x][1] = sa2; s_part[threadIdx.x][2] = sb1; s_part[threadIdx.x][3] = sb2;
+  __syncthreads();
+  const int part = threadIdx.x & 15;
+  // slot = group * 2 + which; a half warp per slot, whole warps per pass (blocks of 192 threads take slots 12..15 in a second pass)
+  for (int slot = threadIdx.x >> 4; slot < 16; slot += (int)(blockDim.x >> 4)) {
+    const int g = slot >> 1, which = slot & 1;
+    float acc = 0.f;
+    for (int t = part; t < (int)blockDim.x; t += 16) {
+      if (s_grp[t][0] == g) acc += s_part[t][which];
+      if (s_grp[t][1] == g) acc += s_part[t][2 + which];
+    }
+#pragma unroll
+    for (int o = 8; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o, 16);
+    if (part == 0) atomicAdd(stats_out_b + slot, (double)acc);
+  }
+}
+
 // RES2: compile-time presence of the second residual, so the common instantiation keeps its register count / loads in flight
 // (as a run-time branch the extra UNR x 16 B registers cost every mode-2 call 10-20 %)
 template <int UNR, bool RES2>
@@ -249,20 +273,10 @@ __global__ void __launch_bounds__(256) gn_apply_kernel(const GnArgs a) {
     }
   }
   if (a.mode == 2 && a.stats_out) {
-    // fixed-order block reduction (run-to-run reproducible): per-thread partials -> shared -> 16 threads sum them in thread order
     __shared__ float s_part[256][4];
-    s_part[threadIdx.x][0] = sa1; s_part[threadIdx.x][1] = sa2; s_part[threadIdx.x][2] = sb1; s_part[threadIdx.x][3] = sb2;
-    __syncthreads();
-    if (threadIdx.x < 16) {
-      const int g = threadIdx.x >> 1, which = threadIdx.x & 1;
-      float acc = 0.f;
-      for (int t = 0; t < (int)blockDim.x; ++t) {
-        const int tc = (t * 8) % C;
-        if (tc / cg == g) acc += s_part[t][which];
-        if ((tc + 4) / cg == g) acc += s_part[t][2 + which];
-      }
-      atomicAdd(a.stats_out + b * 16 + threadIdx.x, (double)acc);
-    }
+    __shared__ unsigned char s_grp[256][2];
+    s_grp[threadIdx.x][0] = (unsigned char)(c0 / cg); s_grp[threadIdx.x][1] = (unsigned char)((c0 + 4) / cg);
+    gn_block_stats_flush(s_part, s_grp, sa1, sa2, sb1, sb2, a.stats_out + b * 16);
   }
 }
 
@@ -284,20 +298,10 @@ __global__ void __launch_bounds__(256) gn_apply_ranges_kernel(const GnArgs a, in
   const uint4 *xp = nullptr, *rp = nullptr, *r2p = nullptr;
   uint4* yp = nullptr;
 
+  __shared__ unsigned char s_grp[256][2];
+  s_grp[threadIdx.x][0] = (unsigned char)(c0 / cg); s_grp[threadIdx.x][1] = (unsigned char)((c0 + 4) / cg);
   auto flush = [&](int b) {
-    // fixed-order block reduction, as in gn_apply_kernel
-    s_part[threadIdx.x][0] = sa1; s_part[threadIdx.x][1] = sa2; s_part[threadIdx.x][2] = sb1; s_part[threadIdx.x][3] = sb2;
-    __syncthreads();
-    if (threadIdx.x < 16) {
-      const int g = threadIdx.x >> 1, which = threadIdx.x & 1;
-      float acc = 0.f;
-      for (int t = 0; t < (int)blockDim.x; ++t) {
-        const int tc = (t * 8) % C;
-        if (tc / cg == g) acc += s_part[t][which];
-        if ((tc + 4) / cg == g) acc += s_part[t][2 + which];
-      }
-      atomicAdd(a.stats_out + b * 16 + threadIdx.x, (double)acc);
-    }
+    gn_block_stats_flush(s_part, s_grp, sa1, sa2, sb1, sb2, a.stats_out + b * 16);
     sa1 = sa2 = sb1 = sb2 = 0.f;
   };
 

@@ -742,6 +742,9 @@ extern "C" int ddimb_linear(const void* a, long long lda, const void* w, long lo
     nseg_w = 256;
     while (N % nseg_w != 0) nseg_w -= 16;
   }
+  // few rows (small sampling batches: 128 token rows at x[4,2,1024,256]): a CTA streams its whole [n_seg x K] weight slice at the TMA
+  // delivery rate (~40 B/clk), so 8 CTAs of 256 columns took 32 us for a 0.27 GFLOP GEMM; halve the segments until the grid fills the SMs
+  while ((long long)ceil_div(M, kTileM) * (N / nseg_w) < ddimb_num_sms() && nseg_w % 32 == 0 && nseg_w / 2 >= 32) nseg_w /= 2;
   CUtensorMap tmA, tmB;
   {
     uint64_t dims[5] = {(uint64_t)K, (uint64_t)M, 1, 1, 1};
