@@ -329,6 +329,12 @@ __device__ __forceinline__ void tmem_st_zero32(uint32_t taddr) {
       "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], {z,z,z,z,z,z,z,z,z,z,z,z,z,z,z,z,z,z,z,z,z,z,z,z,z,z,z,z,z,z,z,z};\n\t}" ::"r"(taddr)
       : "memory");
 }
+__device__ __forceinline__ void tmem_st_zero16(uint32_t taddr) {
+  asm volatile(
+      "{\n\t.reg .b32 z;\n\tmov.b32 z, 0;\n\t"
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {z,z,z,z,z,z,z,z,z,z,z,z,z,z,z,z};\n\t}" ::"r"(taddr)
+      : "memory");
+}
 __device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 
 // K-major shared-memory matrix descriptor (PTX ISA "tcgen05 shared memory descriptor"):

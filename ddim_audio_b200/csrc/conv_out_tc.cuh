@@ -5,13 +5,17 @@
 // row-shifted tcgen05 A descriptors, an input row feeds the accumulators of three output rows through ONE MMA of N = 48.
 // An accumulator block is 16 columns (the minimum UMMA N): columns 0,1 carry the bf16 high parts of the two output channels'
 // weights, columns 2,3 the low parts (w = hi + lo to 2^-17), which the epilogue adds -- fp32-class weights for free, since the
-// 14 spare columns exist anyway.  Warp roles (320 threads): 0 = TMA producer, 1 = MMA issuer, 2-9 = epilogue (two groups, alternate rows).
+// 14 spare columns exist anyway.  Warp roles (352 threads): 0 = TMA producer, 1 and 10 = MMA issuers, 2-9 = epilogue (two groups, alternate rows).
+// The kernel is bound by the rate at which ONE thread can issue small MMAs (~81-94 cycles each whatever N is; 7 per 8 KB input row;
+// with the MMAs compiled out it ran at 6.3 TB/s, profiles/r02_experiments.md section 8): two issuing warps take alternate (kx, k) steps.
+// Every MMA accumulates (the epilogue hands each accumulator block back zeroed) and each issuer owns its own ring of blocks (TMEM columns
+// 0..127 / 128..255), which the epilogue adds: the summation order stays fixed, results are run-to-run identical.
 #pragma once
 #include "conv_wide.cuh"
 
 namespace ddimb {
 
-constexpr int kCoThreads = 320;                     // TMA producer, MMA issuer, 2 x 4 epilogue warps (alternating output rows)
+constexpr int kCoThreads = 352;                     // TMA producer, MMA issuer, 2 x 4 epilogue warps (alternating output rows), second MMA issuer
 constexpr int kCoSlots = 10;                       // input rows in flight (x and skip planes each)
 constexpr int kCoPlane = 9216;                     // 130 x 64 B rounded to 1024
 constexpr int kCoSlotBytes = 2 * kCoPlane;
@@ -75,17 +79,17 @@ conv_out_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constan
     tma_prefetch_desc(&tmS);
     for (int s = 0; s < NS; ++s) {
       mbar_init(bar_full + 8 * s, 1);
-      mbar_init(bar_empty + 8 * s, 1);
+      mbar_init(bar_empty + 8 * s, 2);   // both issuers
     }
     for (int b = 0; b < NB; ++b) {
-      mbar_init(bar_afull + 8 * b, 1);
+      mbar_init(bar_afull + 8 * b, 2);
       mbar_init(bar_aempty + 8 * b, 4);
     }
     mbar_init(bar_w, 1);
     mbar_fence_init();
   }
   if (warp == 1) {
-    tmem_alloc(aux + 392, 128u);
+    tmem_alloc(aux + 392, 256u);
     tmem_relinquish();
   }
   tc_fence_before();
@@ -111,9 +115,10 @@ conv_out_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constan
         }
       }
     }
-  } else if (warp == 1) {
-    // ================================================================ MMA issuer (one elected thread; same segment logic as conv_wide.cuh)
+  } else if (warp == 1 || warp == 10) {
+    // ================================================================ MMA issuers (one elected thread each; same segment logic as conv_wide.cuh)
     if (elect_one()) {
+      const uint32_t me = warp == 1 ? 0u : 1u;
       mbar_wait(bar_w, 0, 42);
       tc_fence_after();
       constexpr uint32_t kTile16 = (16 * 64) >> 4;                       // one 16-row weight block, in descriptor units
@@ -132,35 +137,25 @@ conv_out_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constan
           if (fb < 1 && 1 <= lb && b1 == 0) split = 1;
           else if (fb < 2 && 2 <= lb && b2 == 0) split = 2;
           const bool has_b = split <= lb;
-          const uint32_t ta = tmem_base + ((b0 + (uint32_t)fb) % NB) * 16;
+          const uint32_t tm = tmem_base + me * 128u;                     // this issuer's ring of accumulator blocks
+          const uint32_t ta = tm + ((b0 + (uint32_t)fb) % NB) * 16;
           const uint32_t wa = (uint32_t)fb * kTile16, wb2 = (uint32_t)split * kTile16;
           const uint32_t ia = make_idesc_bf16(kTileM, (uint32_t)(split - fb) * 16), ib = make_idesc_bf16(kTileM, (uint32_t)(lb - split + 1) * 16);
-          const int lbi = v2 ? 1 : lb;
-          const int spl_i = split < lbi + 1 ? split : lbi + 1;
-          const bool has_ai = fb <= lbi, has_bi = split <= lbi;
-          const uint32_t iai = make_idesc_bf16(kTileM, (uint32_t)(has_ai ? spl_i - fb : 1) * 16);
-          const uint32_t ibi = make_idesc_bf16(kTileM, (uint32_t)(has_bi ? lbi - split + 1 : 1) * 16);
           mbar_wait(bar_full + 8 * slot, ((cnt + rr) / NS) & 1, 43);
-          if (v2) mbar_wait(bar_aempty + 8 * b2, (((otile + rr) / NB) & 1) ^ 1, 44);
+          if (v2) mbar_wait(bar_aempty + 8 * b2, ((otile + rr) / NB) & 1, 44);   // phase 0 = the initial zeroing
           tc_fence_after();
           const uint32_t a_lo0 = ((a_base + slot * kCoSlotBytes) & 0x3FFFFu) >> 4;
-          {
-            const uint64_t ad = desc_hi | (uint64_t)a_lo0;
-            if (has_ai) umma_bf16(ta, ad, desc_hi | (uint64_t)(w_lo + wa), iai, 1u);
-            if (has_bi) umma_bf16(tmem_base, ad, desc_hi | (uint64_t)(w_lo + wb2), ibi, 1u);
-            if (v2) umma_bf16(tmem_base + b2 * 16, ad, desc_hi | (uint64_t)(w_lo + 2 * kTile16), make_idesc_bf16(kTileM, 16u), 0u);
-          }
           for (int pl = 0; pl < p.planes; ++pl) {
             const uint32_t a_lo = a_lo0 + (uint32_t)pl * (kCoPlane >> 4);
 #pragma unroll
             for (int kx = 0; kx < 3; ++kx) {
 #pragma unroll
               for (int k = 0; k < 2; ++k) {
-                if (pl == 0 && kx == 0 && k == 0) continue;
+                if ((uint32_t)((kx * 2 + k) & 1) != me) continue;
                 const uint64_t ad = desc_hi | (uint64_t)(a_lo + (uint32_t)(kx * 4 + 2 * k));
                 const uint32_t wl = w_lo + (uint32_t)(kx * 3) * kTile16 + 2 * k;
                 umma_bf16(ta, ad, desc_hi | (uint64_t)(wl + wa), ia, 1u);
-                if (has_b) umma_bf16(tmem_base, ad, desc_hi | (uint64_t)(wl + wb2), ib, 1u);
+                if (has_b) umma_bf16(tm, ad, desc_hi | (uint64_t)(wl + wb2), ib, 1u);
               }
             }
           }
@@ -178,6 +173,16 @@ conv_out_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constan
     const uint32_t grp = (uint32_t)(warp - 2) >> 2;
     const int m = q * 32 + lane;
     const float bias0 = p.bias[0], bias1 = p.bias[1];
+    if (grp == 0) {
+      // every accumulator block starts zeroed; the arrivals complete phase 0 of the "empty" barriers
+#pragma unroll
+      for (int b = 0; b < 2 * NB; ++b) tmem_st_zero16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)b * 16);
+      tmem_st_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0)
+        for (int b = 0; b < NB; ++b) mbar_arrive(bar_aempty + 8 * b);
+    }
     uint32_t tile0 = 0;
     CoUnit u;
     for (int unit = blockIdx.x; unit < p.num_units; unit += gridDim.x) {
@@ -187,15 +192,19 @@ conv_out_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constan
         const uint32_t buf = tile % NB, use = tile / NB;
         mbar_wait(bar_afull + 8 * buf, use & 1, 45);
         tc_fence_after();
-        uint32_t v[16];
+        uint32_t v[16], v1[16];
         tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + buf * 16, v);
+        tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + 128u + buf * 16, v1);
         tmem_ld_wait();
+        tmem_st_zero16(tmem_base + ((uint32_t)(q * 32) << 16) + buf * 16);
+        tmem_st_zero16(tmem_base + ((uint32_t)(q * 32) << 16) + 128u + buf * 16);
+        tmem_st_wait();
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(bar_aempty + 8 * buf);
         const int64_t o = (((int64_t)u.b * 2) * p.T + (u.t0 + ot)) * p.W + u.w0 + m;
-        p.out[o] = __uint_as_float(v[0]) + __uint_as_float(v[2]) + bias0;
-        p.out[o + (int64_t)p.T * p.W] = __uint_as_float(v[1]) + __uint_as_float(v[3]) + bias1;
+        p.out[o] = (__uint_as_float(v[0]) + __uint_as_float(v1[0])) + (__uint_as_float(v[2]) + __uint_as_float(v1[2])) + bias0;
+        p.out[o + (int64_t)p.T * p.W] = (__uint_as_float(v[1]) + __uint_as_float(v1[1])) + (__uint_as_float(v[3]) + __uint_as_float(v1[3])) + bias1;
       }
       tile0 += (uint32_t)u.rows;
     }
@@ -205,7 +214,7 @@ conv_out_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constan
   __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, 128u);
+    tmem_dealloc(tmem_base, 256u);
   }
 }
 
