@@ -89,8 +89,8 @@ extern "C" int ddimb_conv3x3_wgrad(const void* x, const void* dy, float* dw, int
   const double npos = (double)B * T * W;
   DDIMB_PROF(stream, "wgrad3x3", Cin, W, npos * (Cin + Cout) * 2 + 36.0 * Cin * Cout, 18.0 * Cin * Cout * npos);
   DDIMB_CHECK_ARG(W >= 8 && W <= 256 && (W & (W - 1)) == 0 && Cin % 32 == 0 && Cout % 32 == 0 && Cin <= 256 && Cout <= 256);
-  if (Cin == kWgC && Cout == kWgC && W % 128 == 0) {
-    // widest level: x and dy are read once, the nine [ci][co] accumulators stay in tensor memory (csrc/wgrad_wide.cuh)
+  if (Cin == Cout && (Cin == 32 || Cin == 64) && W % 128 == 0) {
+    // two widest levels: x and dy are read once, the accumulators of all nine taps stay in tensor memory (csrc/wgrad_wide.cuh)
     WgParams q;
     memset(&q, 0, sizeof(q));
     q.B = B; q.T = T; q.W = W; q.dw = dw;
@@ -98,16 +98,21 @@ extern "C" int ddimb_conv3x3_wgrad(const void* x, const void* dy, float* dw, int
     while (rt > 8 && (long long)B * (W / 128) * ceil_div(T, rt) < 2LL * ddimb_num_sms()) rt /= 2;
     q.RT = rt; q.units_t = ceil_div(T, rt); q.num_units = B * (W / 128) * q.units_t;
     CUtensorMap tmX, tmY;
-    uint64_t dims[4] = {(uint64_t)kWgC, (uint64_t)W, (uint64_t)T, (uint64_t)B};
-    uint64_t str[3] = {(uint64_t)kWgC, (uint64_t)W * kWgC, (uint64_t)T * W * kWgC};
-    uint32_t bx[4] = {(uint32_t)kWgC, (uint32_t)kWgXRows, 1, 1}, by[4] = {(uint32_t)kWgC, 128, 1, 1};
-    int r = make_tmap_bf16(&tmX, x, 4, dims, str, bx, kWgC);
+    uint64_t dims[4] = {(uint64_t)Cin, (uint64_t)W, (uint64_t)T, (uint64_t)B};
+    uint64_t str[3] = {(uint64_t)Cin, (uint64_t)W * Cin, (uint64_t)T * W * Cin};
+    uint32_t bx[4] = {(uint32_t)Cin, (uint32_t)kWgXPos, 1, 1}, by[4] = {(uint32_t)Cin, 128, 1, 1};
+    int r = make_tmap_bf16(&tmX, x, 4, dims, str, bx, Cin);
     if (r) return r;
-    r = make_tmap_bf16(&tmY, dy, 4, dims, str, by, kWgC);
+    r = make_tmap_bf16(&tmY, dy, 4, dims, str, by, Cin);
     if (r) return r;
-    DDIMB_SMEM_ATTR(wgrad_wide_kernel, kWgSmem);
     const int grid = q.num_units < ddimb_num_sms() ? q.num_units : ddimb_num_sms();
-    wgrad_wide_kernel<<<grid, kWgThreads, kWgSmem, stream>>>(tmX, tmY, q);
+    if (Cin == 32) {
+      DDIMB_SMEM_ATTR(wgrad_wide_kernel<32>, WgCfg<32>::kSmem);
+      wgrad_wide_kernel<32><<<grid, kWgThreads, WgCfg<32>::kSmem, stream>>>(tmX, tmY, q);
+    } else {
+      DDIMB_SMEM_ATTR(wgrad_wide_kernel<64>, WgCfg<64>::kSmem);
+      wgrad_wide_kernel<64><<<grid, kWgThreads, WgCfg<64>::kSmem, stream>>>(tmX, tmY, q);
+    }
     DDIMB_LAUNCH_CHECK();
     return DDIMB_OK;
   }

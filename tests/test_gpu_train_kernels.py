@@ -26,7 +26,7 @@ def _nchw(t):
     return t.float().permute(0, 3, 1, 2)
 
 
-WG_CASES = [(32, 256, 8, 1), (32, 256, 5, 2), (64, 128, 16, 3), (96, 64, 8, 1), (128, 32, 12, 2), (192, 16, 10, 1), (256, 8, 4, 3), (256, 8, 1, 1)]
+WG_CASES = [(32, 256, 8, 1), (32, 256, 5, 2), (32, 256, 1, 1), (32, 256, 2, 1), (32, 256, 131, 2), (64, 128, 1, 2), (64, 128, 77, 2), (64, 256, 9, 1), (32, 128, 300, 1), (64, 128, 16, 3), (96, 64, 8, 1), (128, 32, 12, 2), (192, 16, 10, 1), (256, 8, 4, 3), (256, 8, 1, 1)]
 
 
 @pytest.mark.parametrize("C,W,T,B", WG_CASES)

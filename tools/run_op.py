@@ -38,6 +38,10 @@ elif a.op == "conv3x3_gn":
     bet = torch.randn(C, device=dev, generator=g)
     sti = torch.stack([x.double().reshape(B, -1, 8, C // 8).sum(dim=(1, 3)), (x.double() ** 2).reshape(B, -1, 8, C // 8).sum(dim=(1, 3))], -1).contiguous()
     fn = lambda: ops.conv3x3_gn(x, sti, gam, bet, 1e-6, int(os.environ.get("GN_MODE", "2")), w, bias_b=temb, bias_b_stride=4416, act=1, stats=st)
+elif a.op == "wgrad":
+    dy = torch.randn(B, T, W, C, device=dev, generator=g).to(bf)
+    dw = torch.zeros(C, C, 3, 3, device=dev)
+    fn = lambda: ops.conv3x3_wgrad(x, dy, dw)
 elif a.op == "down":
     w = (torch.randn(Co, 16 * C, device=dev, generator=g) / math.sqrt(16 * C)).to(bf)
     b = torch.randn(Co, device=dev, generator=g)
