@@ -189,7 +189,12 @@ wgrad_wide_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
     if (lane == 0) mbar_arrive(bar_zero);
     mbar_wait(bar_done, 0, 85);
     tc_fence_after();
-    // TMEM lane (q, lane) of pass ps = D row (kx, ci): kx = ps * kAtoms + (q * 32 + lane) / C, ci = (q * 32 + lane) % C
+    // TMEM lane (q, lane) of pass ps = D row (kx, ci): kx = ps * kAtoms + (q * 32 + lane) / C, ci = (q * 32 + lane) % C.
+    // The accumulators are laid out in shared memory as dw is ([co][ci][ky][kx], 9 C^2 floats over the idle x / dy rings: every MMA has
+    // completed) and then added to dw with consecutive lanes on consecutive addresses: 4 sectors per warp atomic instead of the 32 a
+    // lane-per-ci pattern touches (148 CTAs x 9 C^2 scattered atomics were a fixed 40-60 us of every call).
+    float* stage = reinterpret_cast<float*>(smem_gen);
+    static_assert(9 * C * C * 4 <= NX * Cfg::kXSlot + NY * Cfg::kYSlot, "staging tile fits in the rings");
     const int row = q * 32 + lane;
     const int ci = row % C;
 #pragma unroll 1
@@ -203,9 +208,11 @@ wgrad_wide_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
         tmem_ld_wait();
         const int ky = 2 - c0 / C, co0 = c0 % C;
 #pragma unroll
-        for (int i = 0; i < 16; ++i) atomicAdd(p.dw + ((int64_t)(co0 + i) * C + ci) * 9 + ky * 3 + kx, __uint_as_float(v[i]));
+        for (int i = 0; i < 16; ++i) stage[((co0 + i) * C + ci) * 9 + ky * 3 + kx] = __uint_as_float(v[i]);
       }
     }
+    asm volatile("bar.sync 1, 128;" ::: "memory");          // the four reduction warps
+    for (int i = (warp - 4) * 32 + lane; i < 9 * C * C; i += 128) atomicAdd(p.dw + i, stage[i]);
   }
 
   tc_fence_before();
