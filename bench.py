@@ -657,7 +657,7 @@ def train_leg(sd, dev, world, rank, local, B, T, K, W, prof_kernels=True, tail=F
                               "what": "clip x groups + AdaBelief + AdamW + LambdaLR + EMA, device time between events"},
            "gpu_launches": int(launches), "roofline": roof,
            "step_roofline": {"t_roof_ms_per_step": t_roof / K, "frac": (t_roof / K) / (ms / K)} if prof else None,
-           "kernels": kern[:12], "clocks": clk, "finite": finite, "last_loss": float(loss.item()), "dtype": "bf16",
+           "kernels": kern[:int(os.environ.get("DDIMB_BENCH_TRAIN_KERNELS", "12"))], "clocks": clk, "finite": finite, "last_loss": float(loss.item()), "dtype": "bf16",
            "timing": "CUDA events around K full steps, barrier + synchronize both sides, max over ranks"}
 
     # e2e: pinned host batch in, loss scalar out, every step (the runner's own train_step does exactly this)

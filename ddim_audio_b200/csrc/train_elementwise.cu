@@ -189,22 +189,31 @@ __global__ void __launch_bounds__(256) gn_bwd_apply_kernel(const GnBwdArgs a) {
   if (a.sums_out) block_channel_sums<1>(acc, a.sums_out + (int64_t)b * C, C, s_dyn);
 }
 
-// d gamma[c] += sum_b rstd (R1 - mean R0);  d beta[c] += sum_b R0
-__global__ void gn_bwd_param_kernel(const double* __restrict__ R, const double* __restrict__ stats, float* __restrict__ dgamma,
-                                    float* __restrict__ dbeta, int B, int C, double n, float eps) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+// d gamma[c] += sum_b rstd (R1 - mean R0);  d beta[c] += sum_b R0.  A warp per channel: lanes take samples b = lane, lane + 32, ...
+// (each term costs an fp64 division and square root: the first version walked the samples serially, 20-30 us per call x 96 calls per
+// train step), joined by a fixed shuffle tree.
+__global__ void __launch_bounds__(256) gn_bwd_param_kernel(const double* __restrict__ R, const double* __restrict__ stats, float* __restrict__ dgamma,
+                                                           float* __restrict__ dbeta, int B, int C, double n, float eps) {
+  const int c = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
   if (c >= C) return;
   const int g = c / (C >> 3);
   double dg = 0, db = 0;
-  for (int b = 0; b < B; ++b) {
+  for (int b = lane; b < B; b += 32) {
     float mean, rstd;
     gn_group_stats(stats, b, g, n, eps, mean, rstd);
     const double r0 = R[((int64_t)b * C + c) * 2], r1 = R[((int64_t)b * C + c) * 2 + 1];
     dg += (double)rstd * (r1 - (double)mean * r0);
     db += r0;
   }
-  dgamma[c] += (float)dg;
-  if (dbeta) dbeta[c] += (float)db;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    dg += __shfl_xor_sync(0xffffffffu, dg, o);
+    db += __shfl_xor_sync(0xffffffffu, db, o);
+  }
+  if (lane == 0) {
+    dgamma[c] += (float)dg;
+    if (dbeta) dbeta[c] += (float)db;
+  }
 }
 
 int gn_bwd_grid(int64_t per_sample, int B, int threads) {
@@ -255,7 +264,7 @@ extern "C" int ddimb_gn_bwd_param(const double* R, const double* stats, float* d
                                   float eps, cudaStream_t stream) {
   DDIMB_CHECK_ARG(R && stats && dgamma && B >= 1 && C % 8 == 0);
   DDIMB_PROF(stream, "gn_bwd_param", C, 0, 16.0 * B * C, 0.0);
-  gn_bwd_param_kernel<<<(C + 63) / 64, 64, 0, stream>>>(R, stats, dgamma, dbeta, B, C, (double)positions * (C / 8), eps);
+  gn_bwd_param_kernel<<<(C + 7) / 8, 256, 0, stream>>>(R, stats, dgamma, dbeta, B, C, (double)positions * (C / 8), eps);
   DDIMB_LAUNCH_CHECK();
   return DDIMB_OK;
 }
@@ -418,11 +427,21 @@ __global__ void __launch_bounds__(256) layernorm512_bwd_kernel(const float* __re
       }
     }
   }
+  // the block's warps are joined in shared memory first (fixed order), then one atomic per column and block: with an atomic per
+  // column and WARP, 1024 rows meant 1024-way contention on each of the 1024 addresses (60 us for a 4 MB problem)
+  __shared__ float s_red[8][2][H];
+  const int w = threadIdx.x >> 5;
 #pragma unroll
   for (int j = 0; j < 4; ++j) {
-    const int c = (j * 32 + lane) * 4;
-    atomicAdd(dgamma + c, dgacc[j].x); atomicAdd(dgamma + c + 1, dgacc[j].y); atomicAdd(dgamma + c + 2, dgacc[j].z); atomicAdd(dgamma + c + 3, dgacc[j].w);
-    atomicAdd(dbeta + c, dbacc[j].x); atomicAdd(dbeta + c + 1, dbacc[j].y); atomicAdd(dbeta + c + 2, dbacc[j].z); atomicAdd(dbeta + c + 3, dbacc[j].w);
+    reinterpret_cast<float4*>(&s_red[w][0][0])[j * 32 + lane] = dgacc[j];
+    reinterpret_cast<float4*>(&s_red[w][1][0])[j * 32 + lane] = dbacc[j];
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < 2 * H; i += blockDim.x) {
+    const int which = i / H, c = i - which * H;
+    float acc = 0.f;
+    for (int k = 0; k < wpb; ++k) acc += s_red[k][which][c];
+    atomicAdd((which ? dbeta : dgamma) + c, acc);
   }
 }
 
@@ -432,7 +451,7 @@ extern "C" int ddimb_layernorm512_bwd(const float* a, const float* b, const floa
   DDIMB_CHECK_ARG(a && dy1 && gamma && ds && dgamma && dbeta && rows >= 1);
   DDIMB_CHECK_ARG(!dsbf || (ldy % 4 == 0 && ldy >= (write_lo ? 1024 : 512)));
   DDIMB_PROF(stream, "layernorm512_bwd", write_lo, 0, 512.0 * rows * 4.0 * (2 + (b ? 1 : 0) + (dy2 ? 1 : 0)), 0.0);
-  int blocks = (rows + 7) / 8;
+  int blocks = (rows + 15) / 16;                 // two rows per warp at least: halves the atomics against one more 1 us row per warp
   if (blocks > 2 * ddimb_num_sms()) blocks = 2 * ddimb_num_sms();
   layernorm512_bwd_kernel<<<blocks, 256, 0, stream>>>(a, b, dy1, dy2, gamma, ds, reinterpret_cast<__nv_bfloat16*>(dsbf), ldy, write_lo, dgamma,
                                                       dbeta, rows, eps);
