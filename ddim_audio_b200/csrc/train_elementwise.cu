@@ -667,25 +667,60 @@ extern "C" int ddimb_linear_small_wgrad(const float* g, const float* in, const l
   return DDIMB_OK;
 }
 
-// out[r][k] = (z ? silu'(z[r][k]) : 1) * sum_n g[r][n] * w[n][k]
-__global__ void __launch_bounds__(512) linear_small_dgrad_kernel(const float* __restrict__ g, const float* __restrict__ w,
-                                                                const float* __restrict__ z, float* __restrict__ out, int K, int N) {
-  extern __shared__ float s_g[];
-  const int r = blockIdx.x;
-  for (int n = threadIdx.x; n < N; n += blockDim.x) s_g[n] = g[(int64_t)r * N + n];
+// out[r][k] = (z ? silu'(z[r][k]) : 1) * sum_n g[r][n] * w[n][k].  A CTA owns 32 columns k (lane = k) and up to 8 rows; its warps
+// split n, every w element is read ONCE per CTA and meets all the CTA's rows from registers (g is staged in shared memory, broadcast
+// reads).  (The first version ran one CTA per row with a serial loop over n of dependent loads: 313 us at [32 x 4416] x [4416 x 512].)
+constexpr int kLsdRows = 8, kLsdWarps = 16;
+__global__ void __launch_bounds__(32 * kLsdWarps) linear_small_dgrad_kernel(const float* __restrict__ g, const float* __restrict__ w,
+                                                                          const float* __restrict__ z, float* __restrict__ out, int rows, int K, int N) {
+  extern __shared__ float s_g[];                           // [N][kLsdRows] (row-minor: one 32-byte broadcast read per n), then the warps' partials
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int k = blockIdx.x * 32 + lane, r0 = blockIdx.y * kLsdRows;
+  const int nr = min(kLsdRows, rows - r0);
+  for (int i = threadIdx.x; i < N * kLsdRows; i += blockDim.x) {
+    const int n = i / kLsdRows, r = i - n * kLsdRows;
+    s_g[i] = r < nr ? g[(int64_t)(r0 + r) * N + n] : 0.f;
+  }
   __syncthreads();
-  for (int k = threadIdx.x; k < K; k += blockDim.x) {
-    float acc = 0.f;
-    for (int n = 0; n < N; ++n) acc = fmaf(s_g[n], w[(int64_t)n * K + k], acc);
-    if (z) acc *= dsilu_exact(z[(int64_t)r * K + k]);
-    out[(int64_t)r * K + k] = acc;
+  float acc[kLsdRows];
+#pragma unroll
+  for (int r = 0; r < kLsdRows; ++r) acc[r] = 0.f;
+  if (k < K) {
+    for (int n = warp; n < N; n += kLsdWarps) {
+      const float wv = __ldg(w + (int64_t)n * K + k);
+      const float4* gp = reinterpret_cast<const float4*>(s_g + n * kLsdRows);
+#pragma unroll
+      for (int q = 0; q < kLsdRows / 4; ++q) {
+        const float4 gv = gp[q];
+        acc[4 * q] = fmaf(gv.x, wv, acc[4 * q]); acc[4 * q + 1] = fmaf(gv.y, wv, acc[4 * q + 1]);
+        acc[4 * q + 2] = fmaf(gv.z, wv, acc[4 * q + 2]); acc[4 * q + 3] = fmaf(gv.w, wv, acc[4 * q + 3]);
+      }
+    }
+  }
+  __syncthreads();                                         // s_g is reused for the partial sums [warp][row][lane]
+#pragma unroll
+  for (int r = 0; r < kLsdRows; ++r) s_g[(warp * kLsdRows + r) * 32 + lane] = acc[r];
+  __syncthreads();
+  for (int i = threadIdx.x; i < kLsdRows * 32; i += blockDim.x) {
+    const int r = i >> 5, l = i & 31, kk = blockIdx.x * 32 + l;
+    if (r >= nr || kk >= K) continue;
+    float sum = 0.f;
+#pragma unroll
+    for (int wq = 0; wq < kLsdWarps; ++wq) sum += s_g[(wq * kLsdRows + r) * 32 + l];   // fixed order
+    if (z) sum *= dsilu_exact(z[(int64_t)(r0 + r) * K + kk]);
+    out[(int64_t)(r0 + r) * K + kk] = sum;
   }
 }
 
 extern "C" int ddimb_linear_small_dgrad(const float* g, const float* w, const float* z, float* out, int rows, int K, int N, cudaStream_t stream) {
-  DDIMB_CHECK_ARG(g && w && out && rows >= 1 && K >= 1 && N >= 1 && N <= 8192);
+  DDIMB_CHECK_ARG(g && w && out && rows >= 1 && K >= 1 && N >= 1 && N <= 6400);   // g rows staged in shared memory: N x 8 floats
   DDIMB_PROF(stream, "linear_small_dgrad", N, K, 4.0 * ((double)N * K + (double)rows * (2 * K + N)), 2.0 * rows * N * K);
-  linear_small_dgrad_kernel<<<rows, K < 512 ? K : 512, N * sizeof(float), stream>>>(g, w, z, out, K, N);
+  size_t smem = (size_t)N * kLsdRows * sizeof(float);
+  const size_t red = (size_t)kLsdWarps * kLsdRows * 32 * sizeof(float);
+  if (smem < red) smem = red;
+  DDIMB_CHECK_ARG(smem <= 200 * 1024);
+  DDIMB_SMEM_ATTR(linear_small_dgrad_kernel, 200 * 1024);
+  linear_small_dgrad_kernel<<<dim3((K + 31) / 32, (rows + kLsdRows - 1) / kLsdRows), 32 * kLsdWarps, smem, stream>>>(g, w, z, out, rows, K, N);
   DDIMB_LAUNCH_CHECK();
   return DDIMB_OK;
 }

@@ -191,7 +191,7 @@ int ddimb_gn_apply(const void* x, const void* res, const void* res2, void* y, co
                    const float* beta, int mode, int B, long long positions, int C, float eps, cudaStream_t stream);
 
 /* models/diffusion.py:107-120 -- BetaEmbedding layers in fp32: out[r][n] = act(in[idx?idx[r]:r] . w[n] + bias[n]);
- * act bit 0: SiLU on the output; bit 1: SiLU on the input (training keeps the pre-activations). */
+ * act bit 0: SiLU on the output; bit 1: SiLU on the input (training keeps the pre-activations).  Any number of rows (chunks of 64). */
 int ddimb_linear_small(const float* in, const long long* idx, const float* w, const float* bias, float* out, int rows,
                        int K, int N, int act, cudaStream_t stream);
 /* out[r][:] = table[idx[r]][:] (fp32 rows of `width` values, width % 4 == 0): lookup into the timestep-embedding table
