@@ -9,7 +9,10 @@
 
 using namespace ddimb;
 
-static int launch_tn(TnParams& p, const CUtensorMap& tmX, const CUtensorMap& tmY, cudaStream_t stream) {
+// ctas_per_sm: split-K CTAs per SM over all jobs.  Every split adds its whole [M x N] tile to the gradient with scattered atomics (tap stride
+// 9 floats), so more splits trade shorter K loops for more atomic traffic: measured on the 3x3 gradients at C = 96 .. 256, one CTA per SM
+// beats two by 5-37 % and half a CTA per SM is slower again (profiles/r02_experiments.md section 10).
+static int launch_tn(TnParams& p, const CUtensorMap& tmX, const CUtensorMap& tmY, cudaStream_t stream, int ctas_per_sm = 2) {
   DDIMB_CHECK_ARG(p.njobs >= 1 && p.njobs <= kTnMaxJobs);
   DDIMB_CHECK_ARG((p.x_at == 32 || p.x_at == 64) && (p.y_at == 32 || p.y_at == 64));
   int max_n = 0;
@@ -23,7 +26,7 @@ static int launch_tn(TnParams& p, const CUtensorMap& tmX, const CUtensorMap& tmY
   p.y_bytes = max_n * kTnChunk * 2;
   p.num_chunks = p.nchunk[0] * p.nchunk[1] * p.nchunk[2];
   DDIMB_CHECK_ARG(p.num_chunks >= 1);
-  int splits = (2 * ddimb_num_sms()) / p.njobs;
+  int splits = (ctas_per_sm * ddimb_num_sms()) / p.njobs;
   if (splits < 1) splits = 1;
   if (splits > p.num_chunks) splits = p.num_chunks;
   p.splits = splits;
@@ -140,7 +143,7 @@ extern "C" int ddimb_conv3x3_wgrad(const void* x, const void* dy, float* dw, int
       jb.out_off = (int64_t)m0 * 9 + tap;
     }
   p.njobs = nj;
-  return launch_tn(p, tmX, tmY, stream);
+  return launch_tn(p, tmX, tmY, stream, 1);
 }
 
 // taps of a 4x4 stride-2 pad-1 kernel on the space-to-depth view: kernel column kx reads pixel pair (w' + pdx) half ph,
