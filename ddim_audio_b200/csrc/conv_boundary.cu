@@ -209,7 +209,7 @@ extern "C" int ddimb_conv_in(const float* x, const float* w, const void* wimg, c
                              int F, int Cout, cudaStream_t stream) {
   DDIMB_CHECK_ARG(x && w && bias && out && B >= 1 && Cin == 2 && Cout == 32 && B <= 65535);
   DDIMB_PROF(stream, "conv_in", Cin, Cout, (double)B * T * F * (4.0 * Cin + 2.0 * Cout), 18.0 * Cin * Cout * B * T * F);
-  if (F % 128 == 0)   // tensor-core path (csrc/conv_in_tc.cuh); the strip kernel below covers ragged F
+  if (F % 128 == 0)   // tensor-core path (prologue 3 of csrc/conv_wide.cuh); the strip kernel below covers ragged F
     return ddimb_conv_in_tc(x, reinterpret_cast<const uint8_t*>(wimg), bias, out, stats, B, T, F, stream);
   DDIMB_CUDA(cudaMemcpyToSymbolAsync(c_w_in, w, sizeof(float) * 32 * 2 * 9, 0, cudaMemcpyDeviceToDevice, stream));
   DDIMB_CUDA(cudaMemcpyToSymbolAsync(c_w_in, bias, sizeof(float) * 32, sizeof(float) * 32 * 2 * 9, cudaMemcpyDeviceToDevice, stream));

@@ -32,7 +32,9 @@ struct WideParams {
   int32_t RT;             // output rows per work unit
   int32_t units_t;        // ceil(T / RT)
   int32_t num_units;      // B * (W / 128) * units_t
-  int32_t prologue;       // 0: x is already activated; 1: GroupNorm affine; 2: GroupNorm affine + SiLU
+  int32_t prologue;       // 0: x is already activated; 1: GroupNorm affine; 2: GroupNorm affine + SiLU; 3 (C = 32): conv_in -- rows built from src_f32
+  int32_t ksteps;         // K = 16 steps per tap that hold data (C / 16; 1 for conv_in)
+  const float* src_f32;   // prologue 3: fp32 NCHW network input [B][2][T][W]
   float eps;
   const double* gn_stats; // [B][8][2] (sum, sumsq) of x
   const float* gn_gamma;  // [C]
@@ -179,6 +181,58 @@ __device__ __forceinline__ void wide_transform_warp(const WideParams& p, uint8_t
         }
       }
       fence_proxy_async_smem();     // generic-proxy writes -> visible to the tensor core's async-proxy reads
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_ready + 8 * slot);
+    }
+    cnt += (uint32_t)(u.rows + 2);
+  }
+}
+
+// conv_in (reference models/diffusion.py:189-198, Conv2d(2 -> 32, k3 p1) of the fp32 NCHW input) as prologue 3 of the C = 32 kernel: the
+// "transform" warps BUILD the row strips instead of normalising TMA-delivered ones.  A position's 64-byte row holds
+// [x0_hi x1_hi x0_lo x1_lo x0_hi x1_hi 0 0 | 0 ...] (x = hi + lo to 2^-17) against weight rows [w_hi w_hi . w_hi w_hi . w_lo w_lo | 0] per tap
+// (ddimb_conv_wimg kind 3), i.e. w.x = w_hi x_hi + w_hi x_lo + w_lo x_hi with fp32 accumulation: fp32-class accuracy from ONE K = 16 step
+// per tap; taps and output rows are the wide kernel's row-shifted descriptors and N = 3 C MMAs.  Only the first 16 bytes of a row are ever
+// written (the slots are zeroed once when the kernel starts).  (The kernel this replaces built a 128-byte im2col row of all 18 taps per
+// position: 9 x the shared-memory writes and conversions, 0.37-0.40 of HBM.)
+template <int C>
+__device__ __forceinline__ void wide_convert_warp(const WideParams& p, uint8_t* a_gen, uint32_t bar_empty, uint32_t bar_ready, int tw, int lane) {
+  using Cfg = WideCfg<C>;
+  constexpr int NS = Cfg::kSlots, XF = Cfg::kXfWarps;
+  uint32_t cnt = 0;
+  WideUnit u;
+  for (int unit = blockIdx.x; unit < p.num_units; unit += gridDim.x) {
+    u.set(p, unit);
+    int rr = (int)((uint32_t)(tw + XF - (int)(cnt % XF)) % XF);
+    for (; rr < u.rows + 2; rr += XF) {
+      const uint32_t c2 = cnt + (uint32_t)rr;
+      const uint32_t slot = c2 % NS, use = c2 / NS;
+      const int t = u.t0 - 1 + rr;
+      uint8_t* sb = a_gen + slot * Cfg::kSlotBytes;
+      const bool row_in = t >= 0 && t < p.T;
+      const float* x0 = p.src_f32 + (((int64_t)u.b * 2) * p.T + (row_in ? t : 0)) * p.W;
+      const float* x1 = x0 + (int64_t)p.T * p.W;
+      float v0[5], v1[5];
+#pragma unroll
+      for (int i = 0; i < 5; ++i) {                          // positions lane, lane + 32, ... of the 130 (w = w0 - 1 + position)
+        const int pos = lane + 32 * i, w = u.w0 - 1 + pos;
+        const bool in = row_in && pos < kWidePos && w >= 0 && w < p.W;
+        v0[i] = in ? __ldg(x0 + w) : 0.f;
+        v1[i] = in ? __ldg(x1 + w) : 0.f;
+      }
+      mbar_wait(bar_empty + 8 * slot, (use & 1) ^ 1, 17);    // the MMAs of the row that used this slot have completed
+#pragma unroll
+      for (int i = 0; i < 5; ++i) {
+        const int pos = lane + 32 * i;
+        if (pos < kWidePos) {
+          const __nv_bfloat16 h0 = __float2bfloat16_rn(v0[i]), h1 = __float2bfloat16_rn(v1[i]);
+          const __nv_bfloat16 l0 = __float2bfloat16_rn(v0[i] - __bfloat162float(h0)), l1 = __float2bfloat16_rn(v1[i] - __bfloat162float(h1));
+          const uint32_t hh = (uint32_t)__bfloat16_as_ushort(h0) | ((uint32_t)__bfloat16_as_ushort(h1) << 16);
+          const uint32_t ll = (uint32_t)__bfloat16_as_ushort(l0) | ((uint32_t)__bfloat16_as_ushort(l1) << 16);
+          *reinterpret_cast<uint4*>(sb + pos * 64 + (((pos >> 1) & 3) << 4)) = make_uint4(hh, ll, hh, 0u);   // logical chunk 0 of a SWIZZLE_64B row
+        }
+      }
+      fence_proxy_async_smem();
       __syncwarp();
       if (lane == 0) mbar_arrive(bar_ready + 8 * slot);
     }
@@ -339,6 +393,11 @@ conv3x3_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const bool fused = p.prologue != 0;
+  const bool from_f32 = (C == 32) && p.prologue == 3;
+  if (from_f32) {     // rows are built by the converter warps, 16 bytes per position: everything else in a slot stays zero
+    for (int i = threadIdx.x; i < NS * Cfg::kSlotBytes / 16; i += blockDim.x) reinterpret_cast<uint4*>(a_gen)[i] = make_uint4(0u, 0u, 0u, 0u);
+    fence_proxy_async_smem();
+  }
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
@@ -374,7 +433,7 @@ conv3x3_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         for (int kx = 0; kx < 3; ++kx) tma_load_3d(w_base + (kx * 3 + (2 - ky)) * C * C * 2, &tmB, bar_w, (ky * 3 + kx) * C, 0, 0);
       uint32_t cnt = 0;
       WideUnit u;
-      for (int unit = blockIdx.x; unit < p.num_units; unit += gridDim.x) {
+      for (int unit = blockIdx.x; unit < p.num_units && !from_f32; unit += gridDim.x) {
         u.set(p, unit);
         for (int rr = 0; rr < u.rows + 2; ++rr, ++cnt) {
           const uint32_t slot = cnt % NS, use = cnt / NS;
@@ -434,6 +493,7 @@ conv3x3_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             for (int kx = 0; kx < 3; ++kx) {
 #pragma unroll
               for (int k = 0; k < C / 16; ++k) {
+                if (k >= p.ksteps) continue;                 // conv_in: one K = 16 step per tap holds data
                 const uint64_t ad = desc_hi | (uint64_t)(a_lo + (uint32_t)(kx * (Cfg::kRowBytes >> 4) + 2 * k));
                 const uint32_t wl = w_lo + (uint32_t)(kx * 3) * kTile16 + 2 * k;
                 umma_bf16(ta, ad, desc_hi | (uint64_t)(wl + wa), ia, 1u);
@@ -530,7 +590,8 @@ conv3x3_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   } else if (fused && warp >= Cfg::kXfWarp0) {
     // ================================================================ transform: GroupNorm affine (+SiLU) in place
     float* tab = gn_smem + (warp - Cfg::kXfWarp0) * 2 * C;
-    if (p.prologue == 2) wide_transform_warp<C, 2>(p, a_gen, bar_raw, bar_ready, tab, warp - Cfg::kXfWarp0, lane);
+    if (from_f32) wide_convert_warp<C>(p, a_gen, bar_empty, bar_ready, warp - Cfg::kXfWarp0, lane);
+    else if (p.prologue == 2) wide_transform_warp<C, 2>(p, a_gen, bar_raw, bar_ready, tab, warp - Cfg::kXfWarp0, lane);
     else wide_transform_warp<C, 1>(p, a_gen, bar_raw, bar_ready, tab, warp - Cfg::kXfWarp0, lane);
   }
 

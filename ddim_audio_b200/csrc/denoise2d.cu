@@ -357,11 +357,7 @@ int run(const float* x, float* out, const Workspace& w, int B, int T, int iters,
   DDIMB_CUDA(cudaMemsetAsync(w.colsum, 0, w.colsum_bytes, stream));
   col_select_init_kernel<<<(unsigned)((ncols + 255) / 256), 256, 0, stream>>>(w.prefix, w.krem, ncols, (uint32_t)((T - 1) / 2));
   DDIMB_LAUNCH_CHECK();
-  static bool hist_attr = false;
-  if (!hist_attr) {
-    DDIMB_CUDA(cudaFuncSetAttribute(col_hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kHistSmem));
-    hist_attr = true;
-  }
+  DDIMB_SMEM_ATTR(col_hist_kernel, kHistSmem);   // once per device
   for (int shift = 24; shift >= 0; shift -= 8) {
     col_hist_kernel<<<dim3(F / 128, (T + kHistRows - 1) / kHistRows, B * C), 256, kHistSmem, stream>>>(x, w.rowoff, w.prefix, w.hist, T, F, shift);
     DDIMB_LAUNCH_CHECK();

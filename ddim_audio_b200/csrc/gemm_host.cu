@@ -8,7 +8,6 @@
 #include "conv_wide.cuh"
 #include "conv_window.cuh"
 #include "conv_out_tc.cuh"
-#include "conv_in_tc.cuh"
 #include "conv_down_wide.cuh"
 #include "conv_up_wide.cuh"
 
@@ -222,13 +221,14 @@ extern "C" int ddimb_conv3x3_wide_supported(int Cin, int Cout, int W) {
 static int launch_conv_wide(const void* x, const double* gn_stats, const float* gn_gamma, const float* gn_beta, float gn_eps, int gn_mode,
                             const void* w, const float* bias, const float* bias_b, int bias_b_stride, int act, const void* add, void* out,
                             double* stats, int B, int T, int W, int C, cudaStream_t stream) {
-  DDIMB_CHECK_ARG(gn_mode >= 0 && gn_mode <= 2 && (gn_mode == 0 || (gn_stats && gn_gamma)));
+  // gn_mode 3 (C = 32): conv_in -- x is the fp32 NCHW network input [B][2][T][W], w the [32][9 * 32] hi / hi / lo weight image
+  DDIMB_CHECK_ARG(gn_mode >= 0 && gn_mode <= 3 && (gn_mode == 0 || gn_mode == 3 || (gn_stats && gn_gamma)) && (gn_mode != 3 || C == 32));
   CUtensorMap tmA, tmB;
   {
     uint64_t dims[4] = {(uint64_t)C, (uint64_t)W, (uint64_t)T, (uint64_t)B};
     uint64_t str[3] = {(uint64_t)C, (uint64_t)W * C, (uint64_t)T * W * C};
     uint32_t box[4] = {(uint32_t)C, (uint32_t)kWidePos, 1, 1};
-    int r = make_tmap_bf16(&tmA, x, 4, dims, str, box, C);
+    int r = make_tmap_bf16(&tmA, gn_mode == 3 ? out : x, 4, dims, str, box, C);   // conv_in reads x through the converter warps, not TMA
     if (r) return r;
   }
   {
@@ -253,6 +253,7 @@ static int launch_conv_wide(const void* x, const double* gn_stats, const float* 
   while (rt > 8 && (long long)B * (W / 128) * ceil_div(T, rt) < 4LL * ddimb_num_sms()) rt /= 2;
   p.RT = rt; p.units_t = ceil_div(T, rt); p.num_units = B * (W / 128) * p.units_t;
   p.prologue = gn_mode; p.eps = gn_eps; p.gn_stats = gn_stats; p.gn_gamma = gn_gamma; p.gn_beta = gn_beta;
+  p.ksteps = gn_mode == 3 ? 1 : C / 16; p.src_f32 = gn_mode == 3 ? reinterpret_cast<const float*>(x) : nullptr;
   p.out = reinterpret_cast<__nv_bfloat16*>(out); p.add = reinterpret_cast<const __nv_bfloat16*>(add);
   p.bias = bias; p.bias_b = bias_b; p.stats = stats; p.bias_b_stride = bias_b_stride; p.act = act;
   const int grid = p.num_units < ddimb_num_sms() ? p.num_units : ddimb_num_sms();
@@ -383,30 +384,27 @@ int ddimb_conv_out_tc(const void* x, const void* skip, const uint8_t* wimg, cons
 }
 
 // ------------------------------------------------------------------------------------------------ conv_in on the tensor cores
-// csrc/conv_in_tc.cuh; called by ddimb_conv_in (conv_boundary.cu) when F is a multiple of 128.  wimg: the bf16 [hi | hi | lo] tile
-// image of the fp32 parameter [32][2][3][3] (ddimb_conv_wimg, kind 3).
+// Prologue 3 of the C = 32 wide kernel (csrc/conv_wide.cuh: wide_convert_warp); called by ddimb_conv_in (conv_boundary.cu) when F is a
+// multiple of 128.  wimg: the bf16 hi / hi / lo image of the fp32 parameter [32][2][3][3] (ddimb_conv_wimg, kind 3), shaped like a C = 32
+// 3x3 weight.
+constexpr int kCiWideWBytes = 32 * 9 * 32 * 2;   // bf16 [32 co][9 taps][32 k]: k 0,1 = hi(w), 2,3 = hi(w), 4,5 = lo(w), else 0
+
+__global__ void __launch_bounds__(256) ci_wide_weight_image_kernel(const float* __restrict__ w, __nv_bfloat16* __restrict__ dst) {
+  for (int i = threadIdx.x; i < 32 * 9 * 32; i += blockDim.x) {
+    const int k = i & 31, tap = (i >> 5) % 9, co = i / (9 * 32);
+    float v = 0.f;
+    if (k < 6) {
+      const float full = w[(co * 2 + (k & 1)) * 9 + tap];
+      const float hi = __bfloat162float(__float2bfloat16_rn(full));
+      v = (k < 4) ? hi : full - hi;
+    }
+    dst[i] = __float2bfloat16_rn(v);
+  }
+}
+
 int ddimb_conv_in_tc(const float* x, const uint8_t* wimg, const float* bias, void* out, double* stats, int B, int T, int F, cudaStream_t stream) {
   DDIMB_CHECK_ARG(F % 128 == 0 && wimg != nullptr);
-  CiParams p;
-  memset(&p, 0, sizeof(p));
-  p.B = B; p.T = T; p.W = F;
-  int rt = kCiStripRows;
-  while (rt > 8 && (long long)B * (F / 128) * ceil_div(T, rt) < 4LL * ddimb_num_sms()) rt /= 2;
-  p.RT = rt; p.units_t = ceil_div(T, rt); p.num_units = B * (F / 128) * p.units_t;
-  p.x = x; p.wimg = wimg; p.bias = bias; p.out = reinterpret_cast<__nv_bfloat16*>(out); p.stats = stats;
-  DDIMB_SMEM_ATTR(conv_in_tc_kernel, kCiSmem);
-  const int grid = p.num_units < ddimb_num_sms() ? p.num_units : ddimb_num_sms();
-  CUtensorMap tmO;
-  {
-    uint64_t dims[4] = {32, (uint64_t)F, (uint64_t)T, (uint64_t)B};
-    uint64_t str[3] = {32, (uint64_t)F * 32, (uint64_t)T * F * 32};
-    uint32_t box[4] = {32, 32, 1, 1};
-    int r = make_tmap_bf16(&tmO, out, 4, dims, str, box, 32);
-    if (r) return r;
-  }
-  conv_in_tc_kernel<<<grid, kCiThreads, kCiSmem, stream>>>(tmO, p);
-  DDIMB_LAUNCH_CHECK();
-  return DDIMB_OK;
+  return launch_conv_wide(x, nullptr, nullptr, nullptr, 0.f, 3, wimg, bias, nullptr, 0, 0, nullptr, out, stats, B, T, F, 32, stream);
 }
 
 // ------------------------------------------------------------------------------------------------ kernel-ready weight images
@@ -436,7 +434,7 @@ extern "C" long long ddimb_conv_wimg_bytes(int kind, int Cin, int Cout, int W) {
     case 2:
       if (Cin % 32 || Cout % 32 || Cin > 256 || Cout > 256) return -1;
       return conv_up_wide_supported(Cin, Cout, W) ? (long long)kUwWBytes : 16LL * ceil_div(Cin, conv_ck(Cin)) * conv_ck(Cin) * Cout * 2;
-    case 3: return (Cin == 2 && Cout == 32) ? (W % 128 == 0 ? (long long)kCiWBytes : 0) : -1;
+    case 3: return (Cin == 2 && Cout == 32) ? (W % 128 == 0 ? (long long)kCiWideWBytes : 0) : -1;
     case 4: return (Cin == 32 && Cout == 2) ? (W % 128 == 0 ? (long long)kCoWBytes : 0) : -1;
     default: return -1;
   }
@@ -449,7 +447,11 @@ extern "C" int ddimb_conv_wimg(int kind, const void* w, void* wimg, int Cin, int
   DDIMB_CHECK_ARG(wimg != nullptr && (reinterpret_cast<uintptr_t>(wimg) & 15) == 0);
   uint8_t* img = reinterpret_cast<uint8_t*>(wimg);
   const __nv_bfloat16* wb = reinterpret_cast<const __nv_bfloat16*>(w);
-  if (kind == 3) { ci_weight_image_kernel<<<1, 256, 0, stream>>>(reinterpret_cast<const float*>(w), img); DDIMB_LAUNCH_CHECK(); return DDIMB_OK; }
+  if (kind == 3) {
+    ci_wide_weight_image_kernel<<<1, 256, 0, stream>>>(reinterpret_cast<const float*>(w), reinterpret_cast<__nv_bfloat16*>(img));
+    DDIMB_LAUNCH_CHECK();
+    return DDIMB_OK;
+  }
   if (kind == 4) { co_weight_image_kernel<<<1, 256, 0, stream>>>(reinterpret_cast<const float*>(w), img); DDIMB_LAUNCH_CHECK(); return DDIMB_OK; }
   GemmParams p;
   init_params(p);

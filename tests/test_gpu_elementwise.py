@@ -94,7 +94,7 @@ def test_gn_apply(ops, C, P, mode):
 
 @pytest.mark.parametrize("B,T,F", [(1, 32, 256), (3, 64, 256), (2, 1, 256), (1, 77, 256), (2, 300, 256), (2, 45, 128), (70, 9, 256), (2, 33, 96)])
 def test_conv_in_out(ops, B, T, F):
-    """F % 128 == 0 runs the tensor-core kernels (conv_in_tc.cuh / conv_out_tc.cuh), ragged F the strip kernels."""
+    """F % 128 == 0 runs the tensor-core kernels (conv_wide.cuh prologue 3 / conv_out_tc.cuh), ragged F the strip kernels."""
     g = torch.Generator(device=DEV).manual_seed(7)
     x = torch.randn(B, 2, T, F, device=DEV, generator=g)
     w = torch.randn(32, 2, 3, 3, device=DEV, generator=g) * 0.3

@@ -11,4 +11,4 @@ for k in t['kernels'][:40]:
 python tools/run_op.py conv_out1 --T 8192 --B 16 --iters 3 | tail -1
 python tools/run_op.py conv_in --T 8192 --B 16 --iters 3 | tail -1
 ncu --set full --clock-control none --import-source on -k regex:conv_out_tc -c 1 -s 1 -o gpurun_out/r02_convout -f python tools/run_op.py conv_out1 --T 8192 --B 16 --iters 2 > gpurun_out/ncu_co.log 2>&1
-ncu --set full --clock-control none --import-source on -k regex:conv_in_tc -c 1 -s 1 -o gpurun_out/r02_convin -f python tools/run_op.py conv_in --T 8192 --B 16 --iters 2 > gpurun_out/ncu_ci.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:conv3x3_wide -c 1 -s 1 -o gpurun_out/r02_convin -f python tools/run_op.py conv_in --T 8192 --B 16 --iters 2 > gpurun_out/ncu_ci.log 2>&1
