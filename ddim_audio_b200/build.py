@@ -15,7 +15,7 @@ CSRC = os.path.join(HERE, "csrc")
 LIBDIR = os.path.join(HERE, "lib")
 LIB = os.path.join(LIBDIR, "libddim_b200.so")
 SOURCES = ["runtime.cu", "gemm_host.cu", "elementwise.cu", "train_host.cu", "train_elementwise.cu", "conv_boundary.cu", "denoise2d.cu", "ema.cu", "optim.cu", "pfft2wav.cu"]
-HEADERS = ["common.cuh", "umma_gemm.cuh", "conv_wide.cuh", "conv_window.cuh", "conv_out_tc.cuh", "conv_down_wide.cuh", "conv_up_wide.cuh", "gemm_tn.cuh", "wgrad_wide.cuh", "tmap.cuh", os.path.join("..", "..", "include", "ddim_b200.h")]
+HEADERS = ["common.cuh", "umma_gemm.cuh", "conv_wide.cuh", "conv_window.cuh", "conv_out_tc.cuh", "conv_down_wide.cuh", "conv_up_wide.cuh", "gemm_tn.cuh", "wgrad_wide.cuh", "wgrad_updown_wide.cuh", "tmap.cuh", os.path.join("..", "..", "include", "ddim_b200.h")]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo",
     "-Xcompiler", "-fPIC", "-Xcompiler", "-O2", "-cudart", "static", "-Xptxas", "-v",

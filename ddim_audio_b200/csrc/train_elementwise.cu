@@ -216,10 +216,16 @@ __global__ void __launch_bounds__(256) gn_bwd_param_kernel(const double* __restr
   }
 }
 
-int gn_bwd_grid(int64_t per_sample, int B, int threads) {
+// CTAs per sample: at most ONE resident wave over all samples (occ = CTAs of this kernel an SM holds: 3 at 78 registers).  The first
+// version sized the grid for 8 CTAs per SM: 2.7 waves at x[32,2,1024,256], the last one a third full.
+template <typename K>
+int gn_bwd_grid(K kernel, int64_t per_sample, int B, int threads, size_t smem) {
   const int64_t items = per_sample / 8;
   int64_t bx = (items + threads * 4 - 1) / (threads * 4);
-  const int64_t cap = (int64_t)ddimb_num_sms() * 8 / B + 1;
+  int occ = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, threads, smem) != cudaSuccess || occ < 1) occ = 1;
+  int64_t cap = (int64_t)ddimb_num_sms() * occ / B;
+  if (cap < 1) cap = 1;
   if (bx > cap) bx = cap;
   return bx < 1 ? 1 : (int)bx;
 }
@@ -236,7 +242,7 @@ extern "C" int ddimb_gn_bwd_reduce(const void* g, const void* z, const double* s
   a.g = reinterpret_cast<const __nv_bfloat16*>(g); a.z = reinterpret_cast<const __nv_bfloat16*>(z);
   a.stats = stats; a.R = R; a.gamma = gamma; a.beta = beta; a.per_sample = positions * C; a.C = C; a.type = type; a.eps = eps;
   const int threads = (C % 96 == 0) ? 192 : 256;
-  gn_bwd_reduce_kernel<<<dim3(gn_bwd_grid(a.per_sample, B, threads), B), threads, threads * 16 * sizeof(float), stream>>>(a);
+  gn_bwd_reduce_kernel<<<dim3(gn_bwd_grid(gn_bwd_reduce_kernel, a.per_sample, B, threads, threads * 16 * sizeof(float)), B), threads, threads * 16 * sizeof(float), stream>>>(a);
   DDIMB_LAUNCH_CHECK();
   return DDIMB_OK;
 }
@@ -254,7 +260,7 @@ extern "C" int ddimb_gn_bwd_apply(const void* g, const void* z, const void* add,
   a.stats = stats; a.R = const_cast<double*>(R); a.sums_out = sums_out; a.gamma = gamma; a.beta = beta;
   a.per_sample = positions * C; a.C = C; a.type = type; a.eps = eps;
   const int threads = (C % 96 == 0) ? 192 : 256;
-  gn_bwd_apply_kernel<<<dim3(gn_bwd_grid(a.per_sample, B, threads), B), threads, threads * 8 * sizeof(float), stream>>>(a);
+  gn_bwd_apply_kernel<<<dim3(gn_bwd_grid(gn_bwd_apply_kernel, a.per_sample, B, threads, threads * 8 * sizeof(float)), B), threads, threads * 8 * sizeof(float), stream>>>(a);
   DDIMB_LAUNCH_CHECK();
   return DDIMB_OK;
 }

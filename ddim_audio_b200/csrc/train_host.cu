@@ -5,6 +5,7 @@
 #include "../../include/ddim_b200.h"
 #include "gemm_tn.cuh"
 #include "wgrad_wide.cuh"
+#include "wgrad_updown_wide.cuh"
 #include "tmap.cuh"
 
 using namespace ddimb;
@@ -150,6 +151,38 @@ extern "C" int ddimb_conv3x3_wgrad(const void* x, const void* dy, float* dw, int
 // kernel row ky reads row pair (t' + pdy) sub-row pr
 static const int kPairShift[4] = {-1, 0, 0, 1}, kPairHalf[4] = {1, 0, 1, 0};
 
+// csrc/wgrad_updown_wide.cuh: H = high-resolution 32-channel tensor [B][T][W][32], L = low-resolution 64-channel tensor [B][T/2][W/2][64],
+// g = fp32 [64][32][4][4] (Downsample: dw[co][ci], Upsample: dw[ci][co]).
+static int launch_wgrad_updown_wide(const void* h, const void* l, float* g, int B, int T, int W, cudaStream_t stream) {
+  UdParams q;
+  memset(&q, 0, sizeof(q));
+  q.B = B; q.T = T; q.W = W; q.g = g;
+  const int To = T / 2, Wo = W / 2;
+  int rt = 64;
+  while (rt > 4 && (long long)B * (Wo / 128) * ceil_div(To, rt) < 2LL * ddimb_num_sms()) rt /= 2;
+  q.RT = rt; q.units_t = ceil_div(To, rt); q.num_units = B * (Wo / 128) * q.units_t;
+  CUtensorMap tmH, tmL;
+  {
+    uint64_t dims[4] = {64, (uint64_t)Wo, (uint64_t)T, (uint64_t)B};                      // pixel pairs: 64 contiguous channels
+    uint64_t str[3] = {64, (uint64_t)W * 32, (uint64_t)T * W * 32};
+    uint32_t box[4] = {64, (uint32_t)kUdHPairs, 1, 1};
+    int r = make_tmap_bf16(&tmH, h, 4, dims, str, box, 64);
+    if (r) return r;
+  }
+  {
+    uint64_t dims[4] = {64, (uint64_t)Wo, (uint64_t)To, (uint64_t)B};
+    uint64_t str[3] = {64, (uint64_t)Wo * 64, (uint64_t)To * Wo * 64};
+    uint32_t box[4] = {64, 128, 1, 1};
+    int r = make_tmap_bf16(&tmL, l, 4, dims, str, box, 64);
+    if (r) return r;
+  }
+  DDIMB_SMEM_ATTR(wgrad_updown_wide_kernel, kUdSmem);
+  const int grid = q.num_units < ddimb_num_sms() ? q.num_units : ddimb_num_sms();
+  wgrad_updown_wide_kernel<<<grid, kUdThreads, kUdSmem, stream>>>(tmH, tmL, q);
+  DDIMB_LAUNCH_CHECK();
+  return DDIMB_OK;
+}
+
 // ------------------------------------------------------------------------------------------------ Downsample weight gradient
 // dw[co][ci][ky][kx] += sum dy[b,t',w',co] * x[b,2t'+ky-1,2w'+kx-1,ci]   (autograd of models/diffusion.py:70-78)
 extern "C" int ddimb_conv_down4x4_wgrad(const void* x, const void* dy, float* dw, int B, int T, int W, int Cin, int Cout,
@@ -158,6 +191,7 @@ extern "C" int ddimb_conv_down4x4_wgrad(const void* x, const void* dy, float* dw
   const double npos = (double)B * (T / 2) * (W / 2);
   DDIMB_PROF(stream, "wgrad_down4x4", Cin, W, npos * (4.0 * Cin + Cout) * 2 + 64.0 * Cin * Cout, 32.0 * Cin * Cout * npos);
   DDIMB_CHECK_ARG(W >= 16 && W <= 256 && (W & (W - 1)) == 0 && Cin % 32 == 0 && Cout % 32 == 0 && Cin <= 256 && Cout <= 256);
+  if (Cin == 32 && Cout == 64 && (W / 2) % 128 == 0) return launch_wgrad_updown_wide(x, dy, dw, B, T, W, stream);   // level 0 -> 1
   const int To = T / 2, Wo = W / 2;
   int bw, bt;
   tile_128(Wo, &bw, &bt);
@@ -197,6 +231,7 @@ extern "C" int ddimb_conv_up4x4_wgrad(const void* x, const void* dy, float* dw, 
   const double npos = (double)B * T * W;
   DDIMB_PROF(stream, "wgrad_up4x4", Cin, W, npos * (Cin + 4.0 * Cout) * 2 + 64.0 * Cin * Cout, 32.0 * Cin * Cout * npos);
   DDIMB_CHECK_ARG(W >= 8 && W <= 128 && (W & (W - 1)) == 0 && Cin % 32 == 0 && Cout % 32 == 0 && Cin <= 256 && Cout <= 256);
+  if (Cin == 64 && Cout == 32 && W % 128 == 0) return launch_wgrad_updown_wide(dy, x, dw, B, 2 * T, 2 * W, stream);   // level 1 -> 0
   int bw, bt;
   tile_128(W, &bw, &bt);
   TnParams p;

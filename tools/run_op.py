@@ -42,6 +42,14 @@ elif a.op == "wgrad":
     dy = torch.randn(B, T, W, C, device=dev, generator=g).to(bf)
     dw = torch.zeros(C, C, 3, 3, device=dev)
     fn = lambda: ops.conv3x3_wgrad(x, dy, dw)
+elif a.op == "wgrad_down":                     # x [B,T,W,C] -> dy [B,T/2,W/2,Co]
+    dy = torch.randn(B, T // 2, W // 2, Co, device=dev, generator=g).to(bf)
+    dw = torch.zeros(Co, C, 4, 4, device=dev)
+    fn = lambda: ops.conv_down4x4_wgrad(x, dy, dw)
+elif a.op == "wgrad_up":                       # x [B,T,W,C] -> dy [B,2T,2W,Co]
+    dy = torch.randn(B, 2 * T, 2 * W, Co, device=dev, generator=g).to(bf)
+    dw = torch.zeros(C, Co, 4, 4, device=dev)
+    fn = lambda: ops.conv_up4x4_wgrad(x, dy, dw)
 elif a.op == "down":
     w = (torch.randn(Co, 16 * C, device=dev, generator=g) / math.sqrt(16 * C)).to(bf)
     b = torch.randn(Co, device=dev, generator=g)
