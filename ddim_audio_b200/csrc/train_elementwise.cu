@@ -100,17 +100,30 @@ __global__ void __launch_bounds__(256) gn_bwd_reduce_kernel(const GnBwdArgs a) {
   float acc[2][8];
 #pragma unroll
   for (int j = 0; j < 8; ++j) { acc[0][j] = 0.f; acc[1][j] = 0.f; }
-  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < items; i += (int64_t)gridDim.x * blockDim.x) {
-    float g[8], z[8];
-    unpack8(ldg_nc_v4(gp + i), g);
-    unpack8(ldg_nc_v4(zp + i), z);
+  // four items per iteration with every load issued before the first use (one item at a time left 32 bytes per thread in flight:
+  // 0.65 of HBM at 3 resident CTAs per SM)
+  const int64_t S = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i0 = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i0 < items; i0 += 4 * S) {
+    uint4 gv[4], zv[4];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      float gh, zin;
-      if (a.type == 0) { gh = g[j] * dsilu_fast(fmaf(z[j], sc[j], sh[j])); zin = z[j]; }
-      else { gh = g[j]; zin = silu_fast(z[j]); }
-      acc[0][j] += gh;
-      acc[1][j] = fmaf(gh, zin, acc[1][j]);
+    for (int u = 0; u < 4; ++u) {
+      const int64_t i = i0 + u * S;
+      if (i < items) { gv[u] = ldg_nc_v4(gp + i); zv[u] = ldg_nc_v4(zp + i); }
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      if (i0 + u * S >= items) break;
+      float g[8], z[8];
+      unpack8(gv[u], g);
+      unpack8(zv[u], z);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float gh, zin;
+        if (a.type == 0) { gh = g[j] * dsilu_fast(fmaf(z[j], sc[j], sh[j])); zin = z[j]; }
+        else { gh = g[j]; zin = silu_fast(z[j]); }
+        acc[0][j] += gh;
+        acc[1][j] = fmaf(gh, zin, acc[1][j]);
+      }
     }
   }
   block_channel_sums<2>(acc, a.R + (int64_t)b * C * 2, C, s_dyn);
@@ -160,30 +173,47 @@ __global__ void __launch_bounds__(256) gn_bwd_apply_kernel(const GnBwdArgs a) {
   float acc[1][8];
 #pragma unroll
   for (int j = 0; j < 8; ++j) acc[0][j] = 0.f;
-  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < items; i += (int64_t)gridDim.x * blockDim.x) {
-    float g[8], z[8], ad[8], o[8];
-    unpack8(ldg_nc_v4(gp + i), g);
-    unpack8(ldg_nc_v4(zp + i), z);
-    if (ap) unpack8(ldg_nc_v4(ap + i), ad);
+  const int64_t S = (int64_t)gridDim.x * blockDim.x;     // four items per iteration, loads first (see gn_bwd_reduce_kernel)
+  for (int64_t i0 = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i0 < items; i0 += 4 * S) {
+    uint4 gv[4], zv[4], av[4];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const float cB = j < 4 ? cB0 : cB1, cC = j < 4 ? cC0 : cC1;
-      if (a.type == 0) {
-        const float gh = g[j] * dsilu_fast(fmaf(z[j], sc[j], sh[j]));
-        o[j] = fmaf(cA[j], gh, fmaf(cB, z[j], cC));
-      } else {
-        const float zin = silu_fast(z[j]);
-        o[j] = fmaf(cA[j], g[j], fmaf(cB, zin, cC)) * dsilu_fast(z[j]);
+    for (int u = 0; u < 4; ++u) {
+      const int64_t i = i0 + u * S;
+      if (i < items) {
+        gv[u] = ldg_nc_v4(gp + i);
+        zv[u] = ldg_nc_v4(zp + i);
+        if (ap) av[u] = ldg_nc_v4(ap + i);
       }
-      if (ap) o[j] += ad[j];
     }
-    const uint4 ov = pack8(o);
-    stg_v4(op + i, ov);
-    if (a.sums_out) {
-      float r[8];
-      unpack8(ov, r);   // sums of the STORED (bf16) values: what the weight-gradient GEMM of the same tensor sees
 #pragma unroll
-      for (int j = 0; j < 8; ++j) acc[0][j] += r[j];
+    for (int u = 0; u < 4; ++u) {
+      const int64_t i = i0 + u * S;
+      if (i >= items) break;
+      float g[8], z[8], ad[8], o[8];
+      unpack8(gv[u], g);
+      unpack8(zv[u], z);
+      if (ap) unpack8(av[u], ad);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float cB = j < 4 ? cB0 : cB1, cC = j < 4 ? cC0 : cC1;
+        if (a.type == 0) {
+          const float gh = g[j] * dsilu_fast(fmaf(z[j], sc[j], sh[j]));
+          o[j] = fmaf(cA[j], gh, fmaf(cB, z[j], cC));
+        } else {
+          const float sg = sigmoid_fast(z[j]);              // one tanh serves silu(u) and silu'(u)
+          const float zin = z[j] * sg;
+          o[j] = fmaf(cA[j], g[j], fmaf(cB, zin, cC)) * (sg * fmaf(z[j], 1.0f - sg, 1.0f));
+        }
+        if (ap) o[j] += ad[j];
+      }
+      const uint4 ov = pack8(o);
+      stg_v4(op + i, ov);
+      if (a.sums_out) {
+        float r[8];
+        unpack8(ov, r);   // sums of the STORED (bf16) values: what the weight-gradient GEMM of the same tensor sees
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[0][j] += r[j];
+      }
     }
   }
   if (a.sums_out) block_channel_sums<1>(acc, a.sums_out + (int64_t)b * C, C, s_dyn);
