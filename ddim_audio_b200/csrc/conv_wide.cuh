@@ -33,7 +33,6 @@ struct WideParams {
   int32_t units_t;        // ceil(T / RT)
   int32_t num_units;      // B * (W / 128) * units_t
   int32_t prologue;       // 0: x is already activated; 1: GroupNorm affine; 2: GroupNorm affine + SiLU; 3 (C = 32): conv_in -- rows built from src_f32
-  int32_t ksteps;         // K = 16 steps per tap that hold data (C / 16; 1 for conv_in)
   const float* src_f32;   // prologue 3: fp32 NCHW network input [B][2][T][W]
   float eps;
   const double* gn_stats; // [B][8][2] (sum, sumsq) of x
@@ -370,7 +369,9 @@ __device__ __forceinline__ void wide_epilogue_lean(const WideParams& p, const CU
   bulk_wait_group<0>();
 }
 
-template <int C>
+// FROM_F32: the conv_in instantiation (prologue 3).  A template parameter, not a run-time mode: as a run-time branch in the issuing
+// thread's step loop and the producer it cost every C = 32 call 6 %.
+template <int C, bool FROM_F32 = false>
 __global__ void __launch_bounds__(WideCfg<C>::kThreads, 1)
 conv3x3_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmO,
                     const __grid_constant__ WideParams p) {
@@ -393,7 +394,8 @@ conv3x3_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const bool fused = p.prologue != 0;
-  const bool from_f32 = (C == 32) && p.prologue == 3;
+  constexpr bool from_f32 = FROM_F32;
+  static_assert(!FROM_F32 || C == 32, "conv_in is a C = 32 instantiation");
   if (from_f32) {     // rows are built by the converter warps, 16 bytes per position: everything else in a slot stays zero
     for (int i = threadIdx.x; i < NS * Cfg::kSlotBytes / 16; i += blockDim.x) reinterpret_cast<uint4*>(a_gen)[i] = make_uint4(0u, 0u, 0u, 0u);
     fence_proxy_async_smem();
@@ -493,7 +495,7 @@ conv3x3_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             for (int kx = 0; kx < 3; ++kx) {
 #pragma unroll
               for (int k = 0; k < C / 16; ++k) {
-                if (k >= p.ksteps) continue;                 // conv_in: one K = 16 step per tap holds data
+                if (FROM_F32 && k >= 1) continue;            // conv_in: one K = 16 step per tap holds data
                 const uint64_t ad = desc_hi | (uint64_t)(a_lo + (uint32_t)(kx * (Cfg::kRowBytes >> 4) + 2 * k));
                 const uint32_t wl = w_lo + (uint32_t)(kx * 3) * kTile16 + 2 * k;
                 umma_bf16(ta, ad, desc_hi | (uint64_t)(wl + wa), ia, 1u);
@@ -590,7 +592,7 @@ conv3x3_wide_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   } else if (fused && warp >= Cfg::kXfWarp0) {
     // ================================================================ transform: GroupNorm affine (+SiLU) in place
     float* tab = gn_smem + (warp - Cfg::kXfWarp0) * 2 * C;
-    if (from_f32) wide_convert_warp<C>(p, a_gen, bar_empty, bar_ready, warp - Cfg::kXfWarp0, lane);
+    if constexpr (from_f32) wide_convert_warp<C>(p, a_gen, bar_empty, bar_ready, warp - Cfg::kXfWarp0, lane);
     else if (p.prologue == 2) wide_transform_warp<C, 2>(p, a_gen, bar_raw, bar_ready, tab, warp - Cfg::kXfWarp0, lane);
     else wide_transform_warp<C, 1>(p, a_gen, bar_raw, bar_ready, tab, warp - Cfg::kXfWarp0, lane);
   }

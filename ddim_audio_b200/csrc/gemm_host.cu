@@ -253,11 +253,14 @@ static int launch_conv_wide(const void* x, const double* gn_stats, const float* 
   while (rt > 8 && (long long)B * (W / 128) * ceil_div(T, rt) < 4LL * ddimb_num_sms()) rt /= 2;
   p.RT = rt; p.units_t = ceil_div(T, rt); p.num_units = B * (W / 128) * p.units_t;
   p.prologue = gn_mode; p.eps = gn_eps; p.gn_stats = gn_stats; p.gn_gamma = gn_gamma; p.gn_beta = gn_beta;
-  p.ksteps = gn_mode == 3 ? 1 : C / 16; p.src_f32 = gn_mode == 3 ? reinterpret_cast<const float*>(x) : nullptr;
+  p.src_f32 = gn_mode == 3 ? reinterpret_cast<const float*>(x) : nullptr;
   p.out = reinterpret_cast<__nv_bfloat16*>(out); p.add = reinterpret_cast<const __nv_bfloat16*>(add);
   p.bias = bias; p.bias_b = bias_b; p.stats = stats; p.bias_b_stride = bias_b_stride; p.act = act;
   const int grid = p.num_units < ddimb_num_sms() ? p.num_units : ddimb_num_sms();
-  if (C == 32) {
+  if (gn_mode == 3) {
+    DDIMB_SMEM_ATTR((conv3x3_wide_kernel<32, true>), WideCfg<32>::kSmemBytes);
+    conv3x3_wide_kernel<32, true><<<grid, WideCfg<32>::kThreads, WideCfg<32>::kSmemBytes, stream>>>(tmA, tmB, tmO, p);
+  } else if (C == 32) {
     DDIMB_SMEM_ATTR(conv3x3_wide_kernel<32>, WideCfg<32>::kSmemBytes);
     conv3x3_wide_kernel<32><<<grid, WideCfg<32>::kThreads, WideCfg<32>::kSmemBytes, stream>>>(tmA, tmB, tmO, p);
   } else {
