@@ -304,6 +304,10 @@ def run_b200(args):
     dev = torch.device("cuda", local)
     if world > 1:
         os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")   # keep stdout to the one JSON line
+        if os.environ.get("DDIMB_NO_NUMA_BIND") is None:
+            from ddim_audio_b200.runners.dist import bind_to_gpu_numa
+            ok = bind_to_gpu_numa(local)                           # pinned host buffers land on the GPU's own NUMA node
+            print(f"[bench] rank {rank}: NUMA binding {'on' if ok else 'unavailable'} ({len(os.sched_getaffinity(0))} cores)", file=sys.stderr)
         dist.init_process_group("nccl", device_id=dev)
 
     from ddim_audio_b200 import _C, ops
