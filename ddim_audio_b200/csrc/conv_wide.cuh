@@ -18,12 +18,13 @@ namespace ddimb {
 #ifndef DDIMB_WIDE_BULKST
 #define DDIMB_WIDE_BULKST 1
 #endif
-// C = 32 accumulator protocol: the epilogue warps hand every accumulator block back ZEROED (tcgen05.st after their tcgen05.ld), so every
-// MMA accumulates and the block an input row opens needs no separate overwriting MMA: 6 MMAs per row instead of 7 (one thread gets an
-// N <= 128 MMA through every ~81-94 cycles whatever N is: tools/umma_tput.cu).  Measured -3 % (profiles/r02_experiments.md section 8;
-// a second issuing warp in place of a transform warp gained 8 % without the GroupNorm prologue and nothing with GroupNorm + SiLU).
-#ifndef DDIMB_WIDE32_ZERO
-#define DDIMB_WIDE32_ZERO 1
+// Accumulator protocol: the epilogue warps hand every accumulator block back ZEROED (tcgen05.st after their tcgen05.ld), so every MMA
+// accumulates and the block an input row opens needs no separate overwriting MMA: 6 MMAs per row instead of 7 at C = 32, 12 instead of
+// 13-14 at C = 64 (one thread gets an N <= 128 MMA through every ~81-94 cycles whatever N is: tools/umma_tput.cu).  Measured -3 % at
+// C = 32, -2.4 % at C = 64 (profiles/r02_experiments.md section 8; a second issuing warp in place of a transform warp gained 8 % without
+// the GroupNorm prologue and nothing with GroupNorm + SiLU).
+#ifndef DDIMB_WIDE_ZERO
+#define DDIMB_WIDE_ZERO 1
 #endif
 constexpr int kWidePos = 130;   // positions per row strip: 128 + 2 halo columns
 
@@ -57,7 +58,7 @@ struct WideCfg {
   // "raw" barrier of a given slot, and it cannot run a whole phase ahead of it.  With 8 slots and 6 warps a fast warp (affine-only
   // prologue) could reach a slot before the PREVIOUS row of that slot had landed, its parity wait aliased to the phase before, and
   // the CTA deadlocked (seen at T = 4096).
-  static constexpr bool kZeroAcc = (C == 32) && (DDIMB_WIDE32_ZERO != 0);
+  static constexpr bool kZeroAcc = DDIMB_WIDE_ZERO != 0;
   static constexpr int kIssuers = 1;
   static constexpr int kEpiWarps = 8;                                     // two warps per TMEM lane quarter
   static constexpr int kXfWarps = 6;
