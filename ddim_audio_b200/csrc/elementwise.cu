@@ -305,8 +305,11 @@ __global__ void __launch_bounds__(256) gn_apply_ranges_kernel(const GnArgs a, in
     sa1 = sa2 = sb1 = sb2 = 0.f;
   };
 
-  for (int64_t tile = t_begin; tile < t_end; ++tile) {
-    const int b = (int)(tile / tiles_per_sample);
+  // (sample, tile inside the sample) advance incrementally: a 64-bit division per tile cost the loop ~10 % at four items per thread
+  int b = (int)(t_begin / tiles_per_sample);
+  int64_t tin = t_begin - (int64_t)b * tiles_per_sample;
+  for (int64_t tile = t_begin; tile < t_end; ++tile, ++tin) {
+    if (tin == tiles_per_sample) { tin = 0; ++b; }
     if (b != cur_b) {   // uniform across the CTA
       if (cur_b >= 0 && a.mode == 2 && a.stats_out) flush(cur_b);
       __syncthreads();
@@ -330,7 +333,7 @@ __global__ void __launch_bounds__(256) gn_apply_ranges_kernel(const GnArgs a, in
       yp = reinterpret_cast<uint4*>(a.y + (int64_t)b * a.per_sample);
       cur_b = b;
     }
-    const int64_t base = (tile - (int64_t)b * tiles_per_sample) * ((int64_t)blockDim.x * UNR) + threadIdx.x;
+    const int64_t base = tin * ((int64_t)blockDim.x * UNR) + threadIdx.x;
     uint4 xv[UNR], rv[UNR], qv[RES2 ? UNR : 1];
 #pragma unroll
     for (int u = 0; u < UNR; ++u) {
