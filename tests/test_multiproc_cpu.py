@@ -87,3 +87,16 @@ def test_gloo_world2_shard_gather_and_allreduce(runner_mod, tmp_path):
     port = 29500 + (os.getpid() % 2000)
     mp.spawn(_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
     assert os.path.exists(tmp_path / "ok0") and os.path.exists(tmp_path / "ok1")
+
+
+def test_numa_binding_is_a_noop_without_a_gpu():
+    """runners/dist.py::bind_to_gpu_numa must never raise and never shrink the affinity mask when NVML / the GPU is unavailable."""
+    import os
+
+    from ddim_audio_b200.runners.dist import bind_to_gpu_numa
+
+    before = os.sched_getaffinity(0)
+    ok = bind_to_gpu_numa(0)
+    after = os.sched_getaffinity(0)
+    assert ok in (True, False)
+    assert after == before or (ok and after and after <= before)
