@@ -809,14 +809,18 @@ extern "C" int ddimb_fourier_mix(const void* x, long long ldx, const void* wh, c
     if (r) return r;
     uint64_t bd[3] = {(uint64_t)(split == 3 ? 2 * H : H), (uint64_t)S, (uint64_t)B};
     uint64_t bs[2] = {(uint64_t)ldx, (uint64_t)ldx * S};
-    uint32_t bb[3] = {(uint32_t)ck, (uint32_t)nS, 1};
+    // few samples (small sampling batches): cut the S columns into segments until the grid fills the SMs (as ddimb_linear does)
+    int seg1 = nS;
+    while ((long long)(2 * H / kTileM) * B * (nS / seg1) < ddimb_num_sms() && seg1 % 32 == 0 && seg1 / 2 >= 32) seg1 /= 2;
+    uint32_t bb[3] = {(uint32_t)ck, (uint32_t)seg1, 1};
     r = make_tmap_bf16(&tmB, x, 3, bd, bs, bb, ck);
     if (r) return r;
     GemmParams p;
     init_params(p);
     p.box[0] = kTileM;
     p.ntile[0] = 2 * H / kTileM; p.ntile[3] = B;
-    p.n_seg = nS; p.n_acc = nS; p.b_batched = 1;
+    p.num_n_tiles = nS / seg1; p.n_tile_stride = seg1;
+    p.n_seg = seg1; p.n_acc = seg1; p.b_batched = 1;
     p.ntaps = split;
     const int bk[3] = {0, H, 0};   // x: hi, lo, hi
     for (int t = 0; t < split; ++t) {
@@ -841,14 +845,16 @@ extern "C" int ddimb_fourier_mix(const void* x, long long ldx, const void* wh, c
     if (r) return r;
     uint64_t bd[3] = {(uint64_t)2 * Sp, (uint64_t)2 * H, (uint64_t)B};
     uint64_t bs[2] = {(uint64_t)2 * Sp, (uint64_t)2 * Sp * 2 * H};
-    uint32_t bb[3] = {(uint32_t)ck, 256, 1};
+    int seg2 = 256;
+    while ((long long)ceil_div(S, kTileM) * B * (H / seg2) < ddimb_num_sms() && seg2 / 2 >= 32) seg2 /= 2;
+    uint32_t bb[3] = {(uint32_t)ck, (uint32_t)seg2, 1};
     r = make_tmap_bf16(&tmB, ut, 3, bd, bs, bb, ck);
     if (r) return r;
     GemmParams p;
     init_params(p);
     p.box[0] = kTileM;
     p.ntile[0] = ceil_div(S, kTileM); p.ntile[3] = B;
-    p.num_n_tiles = H / 256; p.n_seg = 256; p.n_acc = 256; p.n_tile_stride = 256; p.b_batched = 1;
+    p.num_n_tiles = H / seg2; p.n_seg = seg2; p.n_acc = seg2; p.n_tile_stride = seg2; p.b_batched = 1;
     int nt = 0;
     for (int half = 0; half < 2; ++half) {
       // (A block, Ut plane): hi*hi, hi*lo, lo*hi
