@@ -92,7 +92,7 @@ def test_gn_apply(ops, C, P, mode):
         assert_stats(so2, ref2, f"gn stats C={C} + res2")
 
 
-@pytest.mark.parametrize("B,T,F", [(1, 32, 256), (3, 64, 256), (2, 1, 256), (1, 77, 256), (2, 300, 256), (2, 45, 128), (70, 9, 256), (2, 33, 96)])
+@pytest.mark.parametrize("B,T,F", [(1, 32, 256), (3, 64, 256), (2, 1, 256), (1, 77, 256), (2, 300, 256), (2, 45, 128), (70, 9, 256), (2, 33, 96), (1, 2500, 256)])
 def test_conv_in_out(ops, B, T, F):
     """F % 128 == 0 runs the tensor-core kernels (conv_wide.cuh prologue 3 / conv_out_tc.cuh), ragged F the strip kernels."""
     g = torch.Generator(device=DEV).manual_seed(7)

@@ -42,7 +42,7 @@ def test_conv3x3_wgrad(ops, C, W, T, B):
     assert rel_l2(dw, 2 * ref) < 1e-3
 
 
-@pytest.mark.parametrize("Cin,Cout,W,T,B", [(32, 64, 256, 8, 2), (32, 64, 256, 2, 1), (32, 64, 256, 70, 2), (64, 96, 128, 16, 1), (96, 128, 64, 8, 2), (128, 192, 32, 4, 1), (192, 256, 16, 2, 3)])
+@pytest.mark.parametrize("Cin,Cout,W,T,B", [(32, 64, 256, 8, 2), (32, 64, 256, 2, 1), (32, 64, 256, 70, 2), (32, 64, 256, 4, 3), (64, 96, 128, 16, 1), (96, 128, 64, 8, 2), (128, 192, 32, 4, 1), (192, 256, 16, 2, 3)])
 def test_down_up_wgrad(ops, Cin, Cout, W, T, B):
     g = torch.Generator(device=DEV).manual_seed(Cin + W)
     # Downsample: x [B,T,W,Cin] -> y [B,T/2,W/2,Cout]
