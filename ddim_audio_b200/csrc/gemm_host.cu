@@ -488,6 +488,25 @@ extern "C" int ddimb_conv_wimg(int kind, const void* w, void* wimg, int Cin, int
   return DDIMB_OK;
 }
 
+// Many weight images in one call: `records` is a HOST array of n {int kind, Cin, Cout, W; const void* w; void* img} (32 bytes each).
+// The training step rebuilds ~126 images per step; one library call instead of 126 saves the per-call host cost of the binding.
+struct WimgBatchRec {
+  int32_t kind, Cin, Cout, W;
+  const void* w;
+  void* img;
+};
+static_assert(sizeof(WimgBatchRec) == 32, "WimgBatchRec layout is part of the ABI");
+
+extern "C" int ddimb_conv_wimg_batch(const void* records, int n, cudaStream_t stream) {
+  DDIMB_CHECK_ARG(records && n >= 1);
+  const WimgBatchRec* r = static_cast<const WimgBatchRec*>(records);
+  for (int i = 0; i < n; ++i) {
+    const int rc = ddimb_conv_wimg(r[i].kind, r[i].w, r[i].img, r[i].Cin, r[i].Cout, r[i].W, stream);
+    if (rc != DDIMB_OK) return rc;
+  }
+  return DDIMB_OK;
+}
+
 // ------------------------------------------------------------------------------------------------ Conv2d 3x3 s1 p1
 // reference: models/diffusion.py:28-40 (Residual_Block.conv), evaluated on NHWC bf16.
 extern "C" int ddimb_conv3x3(const void* x, const void* w, const void* wimg, const float* bias, const float* bias_b, int bias_b_stride, int act,

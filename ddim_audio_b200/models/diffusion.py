@@ -153,6 +153,63 @@ def _fourier_operands(S: int, H: int, device) -> tuple:
     return wh_op.to(device), a2.to(device), Sp
 
 
+def _gather_torch(w: torch.Tensor, dims, strides, off: int) -> torch.Tensor:
+    """dst[i0][i1][i2][i3] = w.flat[off + sum_k i_k strides_k] (negative strides = flips): the torch statement of one operand layout."""
+    idx = torch.full((1, 1, 1, 1), int(off), dtype=torch.int64, device=w.device)
+    for k, (d, s_) in enumerate(zip(dims, strides)):
+        shape = [1, 1, 1, 1]
+        shape[k] = int(d)
+        idx = idx + (torch.arange(int(d), dtype=torch.int64, device=w.device) * int(s_)).reshape(shape)
+    return w.reshape(-1)[idx.reshape(-1)].reshape([int(d) for d in dims])
+
+
+class _RepackPlan:
+    """Everything ``Model._pack(train=True)`` derived from the fp32 masters, as data: strided-gather records for ONE ``ddimb_repack``
+    launch (include/ddim_b200.h) and the argument lists of the weight-image calls.  ``refresh`` rewrites all copies in place."""
+
+    CHUNK = 16384
+
+    def __init__(self):
+        self.records, self.images = [], []
+        self.table, self.nchunks, self.total, self.param_ptrs = None, 0, 0, ()
+
+    def add(self, w, dst, dims, strides, off, f32):
+        self.records.append((w, dst, tuple(int(d) for d in dims), tuple(int(x) for x in strides), int(off), bool(f32)))
+
+    def add_image(self, kind, src, img, Cin, Cout, W):
+        self.images.append((int(kind), src, img, int(Cin), int(Cout), int(W)))
+
+    def finish(self, model):
+        import numpy as np
+
+        dt = np.dtype([("src", "<u8"), ("dst", "<u8"), ("start", "<i8"), ("n", "<i8"), ("d1", "<i4"), ("d2", "<i4"), ("d3", "<i4"),
+                       ("f32", "<i4"), ("s0", "<i8"), ("s1", "<i8"), ("s2", "<i8"), ("s3", "<i8")])
+        assert dt.itemsize == 80
+        rows = []
+        for w, dst, dims, strides, off, f32 in self.records:
+            n = dst.numel()
+            for start in range(0, n, self.CHUNK):
+                rows.append((w.data_ptr() + 4 * off, dst.data_ptr(), start, min(self.CHUNK, n - start), dims[1], dims[2], dims[3], int(f32),
+                             strides[0], strides[1], strides[2], strides[3]))
+            self.total += n
+        arr = np.array(rows, dtype=dt)
+        dev = self.records[0][1].device
+        self.table = torch.from_numpy(arr.view(np.uint8).reshape(-1).copy()).to(dev)
+        self.nchunks = len(rows)
+        self.param_ptrs = tuple(p.data_ptr() for p in model._params())
+        idt = np.dtype([("kind", "<i4"), ("Cin", "<i4"), ("Cout", "<i4"), ("W", "<i4"), ("w", "<u8"), ("img", "<u8")])
+        assert idt.itemsize == 32
+        self._img_recs = np.array([(k, ci, co, W, _C.ptr(src), _C.ptr(img)) for k, src, img, ci, co, W in self.images], dtype=idt)
+
+    def matches(self, model) -> bool:
+        return self.table is not None and self.param_ptrs == tuple(p.data_ptr() for p in model._params())
+
+    def refresh(self):
+        _C.call("ddimb_repack", _C.ptr(self.table), self.nchunks, self.total)
+        if len(self._img_recs):
+            _C.call("ddimb_conv_wimg_batch", self._img_recs.ctypes.data, len(self._img_recs))
+
+
 class Model(nn.Module):
     """Drop-in for the reference ``Model`` (models/diffusion.py:170-294): same constructor argument (the full config
     namespace), same parameter names and shapes, same ``forward(input[B,C,T,F], t[B]) -> [B,C,T,F]`` fp32."""
@@ -214,13 +271,25 @@ class Model(nn.Module):
 
     def _apply(self, fn, *args, **kwargs):
         self.mark_params_dirty()
-        return super()._apply(fn, *args, **kwargs)
+        r = super()._apply(fn, *args, **kwargs)
+        self.__dict__.pop("_param_list", None)       # .to() / .type() may replace the Parameter objects
+        return r
+
+    def _params(self):
+        """The module's parameters as a cached list: ``nn.Module.parameters()`` walks the module tree (~3 ms per call for this network)
+        and the train step needs the list several times per step.  Parameter OBJECTS only change through module surgery / ``_apply``,
+        which drops the cache."""
+        pl = self.__dict__.get("_param_list")
+        if pl is None:
+            pl = self.__dict__["_param_list"] = list(self.parameters())
+            self.__dict__["_param_names"] = [n for n, _ in self.named_parameters()]
+        return pl
 
     def _pack_key(self, train):
         """Sampling: two counters (no walk over the 389 parameters per forward).  Training adds the (pointer, version) walk so a
         stock torch optimizer's in-place update is seen too (100 us next to an 85 ms step)."""
         base = (_C.param_epoch[0], self._gen)
-        return (base, tuple((p.data_ptr(), p._version) for p in self.parameters()) if train else None)
+        return (base, tuple((p.data_ptr(), p._version) for p in self._params()) if train else None)
 
     @torch.no_grad()
     def _pack(self, train=False):
@@ -230,19 +299,50 @@ class Model(nn.Module):
         bf = torch.bfloat16
         pk = {"train": train}
         F0, nl = self.config.f_size, self.levels
-        img = ops.conv_wimg          # kernel-ready (swizzled) tile images, built here once per weight version: include/ddim_b200.h
+
+        # Every operand copy is a strided gather of its fp32 master (negative strides = flips).  The first train pack builds the copies
+        # with torch AND records (master, copy, dims, strides) plus every weight-image call; later packs of the same parameters rewrite
+        # the copies in place with one library launch (``_refresh``): ~600 torch calls were 25 ms of host time per train step.
+        plan = _RepackPlan() if train else None
+
+        def gather(w, dims, strides, off=0, out_shape=None, f32=False):
+            w = w.detach()
+            dst = _gather_torch(w, dims, strides, off).to(torch.float32 if f32 else bf).contiguous()
+            if out_shape is not None:
+                dst = dst.reshape(out_shape)
+            if plan is not None:
+                plan.add(w, dst, dims, strides, off, f32)
+            return dst
 
         def c3(w):      # [Co, Ci, 3, 3] -> [Co, (ky*3+kx)*Ci + ci]
-            return w.detach().permute(0, 2, 3, 1).reshape(w.shape[0], -1).to(bf).contiguous()
+            Co, Ci = w.shape[:2]
+            return gather(w, (Co, 3, 3, Ci), (Ci * 9, 3, 1, 9), 0, (Co, 9 * Ci))
 
         def c3d(w):     # data-gradient operand: [Ci, (ky*3+kx)*Co + co] of the flipped kernel
-            return w.detach().flip(2, 3).permute(1, 2, 3, 0).reshape(w.shape[1], -1).to(bf).contiguous()
+            Co, Ci = w.shape[:2]
+            return gather(w, (Ci, 3, 3, Co), (9, -3, -1, Ci * 9), 8, (Ci, 9 * Co))
 
         def as_conv(w):   # [O, I, 4, 4] -> [O, (ky*4+kx)*I + i]   (ddimb_conv_down4x4 operand)
-            return w.detach().permute(0, 2, 3, 1).reshape(w.shape[0], -1).to(bf).contiguous()
+            O, I = w.shape[:2]
+            return gather(w, (O, 4, 4, I), (I * 16, 4, 1, 16), 0, (O, 16 * I))
 
         def as_convT(w):  # [I, O, 4, 4] -> [(ky*4+kx)*O + o, i]    (ddimb_conv_up4x4 operand)
-            return w.detach().permute(2, 3, 1, 0).reshape(-1, w.shape[0]).to(bf).contiguous()
+            I, O = w.shape[:2]
+            return gather(w, (4, 4, O, I), (4, 1, 16, O * 16), 0, (16 * O, I))
+
+        def lin(w):       # [N, K] -> bf16 copy
+            N, K = w.shape
+            return gather(w, (1, 1, N, K), (0, 0, K, 1), 0, (N, K))
+
+        def lin_t(w):     # [N, K] -> [K, N]
+            N, K = w.shape
+            return gather(w, (1, 1, K, N), (0, 0, 1, K), 0, (K, N))
+
+        def img(kind, w, Cin, Cout, W):
+            im = ops.conv_wimg(kind, w, Cin, Cout, W)
+            if plan is not None and im is not None:
+                plan.add_image(kind, w, im, Cin, Cout, W)
+            return im
 
         def rb(m, prefix, W):
             C = m.channels
@@ -291,19 +391,22 @@ class Model(nn.Module):
         pk["conv_in_img"] = img(ops.KIND_CONV_IN, cin.weight.detach(), cin.weight.shape[1], cin.weight.shape[0], F0)
         pk["conv_out_img"] = img(ops.KIND_CONV_OUT, cout.weight.detach(), cout.weight.shape[1], cout.weight.shape[0], F0)
         tr = self.transformer
-        pk["proj_w"] = tr.embedding.projection.weight.detach().to(bf).contiguous()
-        pk["out_w"] = tr.compute_out.weight.detach().to(bf).contiguous()
-        pk["fnet"] = [dict(w1=l.intermediate.dense.weight.detach().to(bf).contiguous(),
-                           w2=l.output.dense.weight.detach().to(bf).contiguous()) for l in tr.encoder.layer]
+        pk["proj_w"] = lin(tr.embedding.projection.weight)
+        pk["out_w"] = lin(tr.compute_out.weight)
+        pk["fnet"] = [dict(w1=lin(l.intermediate.dense.weight), w2=lin(l.output.dense.weight)) for l in tr.encoder.layer]
         if train:
-            pk["proj_wt"] = tr.embedding.projection.weight.detach().t().to(bf).contiguous()
-            pk["out_wt"] = tr.compute_out.weight.detach().t().to(bf).contiguous()
+            pk["proj_wt"] = lin_t(tr.embedding.projection.weight)
+            pk["out_wt"] = lin_t(tr.compute_out.weight)
             for d, l in zip(pk["fnet"], tr.encoder.layer):
-                d["w1t"] = l.intermediate.dense.weight.detach().t().to(bf).contiguous()
-                d["w2t"] = l.output.dense.weight.detach().t().to(bf).contiguous()
-            w = self.up_modules[-1].weight.detach()                                  # conv_out [2, 32, 3, 3]
-            pk["conv_out_wd"] = w.flip(2, 3).permute(1, 0, 2, 3).float().contiguous()  # conv_in-shaped data-gradient kernel
+                d["w1t"] = lin_t(l.intermediate.dense.weight)
+                d["w2t"] = lin_t(l.output.dense.weight)
+            w = self.up_modules[-1].weight                                           # conv_out [2, 32, 3, 3]
+            # conv_in-shaped data-gradient kernel: [ci, co, ky, kx] = w[co, ci, 2 - ky, 2 - kx], kept in fp32
+            pk["conv_out_wd"] = gather(w, (32, 2, 3, 3), (9, 288, -3, -1), 8, (32, 2, 3, 3), f32=True)
             pk["conv_out_wd_img"] = img(ops.KIND_CONV_IN, pk["conv_out_wd"], 2, 32, F0)
+            # conv_in / conv_out images are built from the fp32 masters themselves
+            plan.finish(self)
+            pk["_plan"] = plan
         return pk
 
     def _temb_table(self, pk):
@@ -321,7 +424,13 @@ class Model(nn.Module):
         pk = self._packed
         fresh = pk is not None and self._packed_key[0] == base and (not train or (pk["train"] and self._packed_key[1] == walk))
         if not fresh:
-            self._packed, self._packed_key = self._pack(train), (base, walk)
+            plan = pk.get("_plan") if (pk is not None and train and pk["train"]) else None
+            if plan is not None and plan.matches(self):
+                plan.refresh()                                   # same parameter storage, new values: rewrite the copies in place
+                pk.pop("temb_table", None)
+                self._packed_key = (base, walk)
+            else:
+                self._packed, self._packed_key = self._pack(train), (base, walk)
         return self._packed
 
     def _const(self, key, build):
@@ -434,7 +543,7 @@ class Model(nn.Module):
         return ops.conv_out(h, None, conv_last.weight, conv_last.bias, wimg=pk["conv_out_img"])
 
     def forward(self, input, t):
-        if torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters()):
+        if torch.is_grad_enabled() and any(p.requires_grad for p in self._params()):
             # training: one autograd node over the whole network (models/training.py); backward runs in library kernels
             from .training import DenoiserFn
             if not input.is_cuda:
@@ -445,5 +554,5 @@ class Model(nn.Module):
                 raise RuntimeError(f"ddim_audio_b200: unsupported input shape {tuple(input.shape)}")
             x = input.detach().contiguous().float()
             tt = t.to(device=x.device, dtype=torch.int64).contiguous()
-            return DenoiserFn.apply(self, x, tt, *self.parameters())
+            return DenoiserFn.apply(self, x, tt, *self._params())
         return self._forward_impl(input, t)

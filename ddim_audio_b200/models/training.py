@@ -25,10 +25,12 @@ class _Saved:
 def _flat_views(model, device):
     # every view starts on a 16-byte boundary (128-bit accesses in the optimizer / clip kernels); the <= 3 zero floats of
     # padding per parameter ride along in the data-parallel all-reduce
-    total = sum((p.numel() + 3) // 4 * 4 for p in model.parameters())
+    params = model._params()
+    names = model.__dict__["_param_names"]
+    total = sum((p.numel() + 3) // 4 * 4 for p in params)
     flat = torch.zeros(total, dtype=torch.float32, device=device)
     views, off = {}, 0
-    for name, p in model.named_parameters():
+    for name, p in zip(names, params):
         views[name] = flat[off:off + p.numel()].view(p.shape)
         off += (p.numel() + 3) // 4 * 4
     return flat, views
@@ -298,6 +300,7 @@ class DenoiserFn(torch.autograd.Function):
         ctx.sv = None
         flat, G = backward_train(model, sv, gout.contiguous().float())
         model.flat_grad = flat
-        grads = tuple(G[name] for name, _ in model.named_parameters())
+        model._params()
+        grads = tuple(G[name] for name in model.__dict__["_param_names"])
         del G
         return (None, None, None) + grads

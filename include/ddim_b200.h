@@ -87,6 +87,15 @@ long long ddimb_pfft2wav_workspace(int B, int T, int F);
 int ddimb_pfft2wav(const float* x, const double* sri, const float* wt, const float* norm, int* out, void* ws, long long ws_bytes, int B, int T,
                    int F, int hpi, double target_norm, double base_db, double max_db, double p_low, double p_upp, cudaStream_t stream);
 
+/* ---- bf16 operand copies of the fp32 master weights, rebuilt in one launch (training: the masters change every step) ---------------- */
+
+/* models/diffusion.py:28-78 weights in the operand layouts of the entry points below (tap-major 3x3 / 4x4 kernels, their flipped and
+ * transposed data-gradient twins, Linear weights and transposes): each is a strided gather dst[i0][i1][i2][i3] = src[i0 s0 + i1 s1 +
+ * i2 s2 + i3 s3] (negative strides = flips) with a cast to bf16.  chunk_table: DEVICE array of nchunks 80-byte records
+ * {const float* src; void* dst; long long start, n; int d1, d2, d3, dst_f32; long long s0, s1, s2, s3} -- dst elements [start, start+n)
+ * of a contiguous [d0][d1][d2][d3] copy (dst_f32: keep fp32); one CTA per record.  total_elems: profiler bookkeeping. */
+int ddimb_repack(const void* chunk_table, int nchunks, long long total_elems, cudaStream_t stream);
+
 /* ---- EMA of the parameters ------------------------------------------------------------- */
 
 /* models/ema.py:16-23 -- shadow = (1 - mu) param + mu shadow for EVERY registered parameter in one launch (bit-exact: the
@@ -127,6 +136,8 @@ int ddimb_optim_step(const void* chunk_table, int nchunks, long long total_elems
  * wimg must be 16-byte aligned. */
 long long ddimb_conv_wimg_bytes(int kind, int Cin, int Cout, int W);
 int ddimb_conv_wimg(int kind, const void* w, void* wimg, int Cin, int Cout, int W, cudaStream_t stream);
+/* The same for n convolutions in one call: records = HOST array of n {int kind, Cin, Cout, W; const void* w; void* img} (32 bytes each). */
+int ddimb_conv_wimg_batch(const void* records, int n, cudaStream_t stream);
 
 /* ---- network boundary convolutions ------------------------------------------------------------------------------ */
 
