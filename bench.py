@@ -83,6 +83,7 @@ def parse_args():
     ap.add_argument("--no-parity", action="store_true", help="skip the parity / batch-position objects of the default line")
     ap.add_argument("--no-small-batch", action="store_true")
     ap.add_argument("--no-train", action="store_true", help="skip the bounded train leg of the default line")
+    ap.add_argument("--no-train-graph", action="store_true", help="train leg: issue forward + backward eagerly instead of replaying the captured step")
     ap.add_argument("--train-batch", type=int, default=32)
     ap.add_argument("--train-t-size", type=int, default=1024)
     ap.add_argument("--train-steps", type=int, default=5)
@@ -442,7 +443,7 @@ def run_b200(args):
     if not args.no_train:
         del x_host
         torch.cuda.empty_cache()
-        train = train_leg(sd, dev, world, rank, local, args.train_batch, args.train_t_size, args.train_steps, max(args.train_warmup, 3),
+        train = train_leg(sd, dev, world, rank, local, args.train_batch, args.train_t_size, args.train_steps, max(args.train_warmup, 3), train_graph=not args.no_train_graph,
                           prof_kernels=True, tail=False, cpu=False)
 
     if rank == 0:
@@ -550,7 +551,7 @@ def small_batch_leg(model, al, dev, steps=10, warm=3):
 
 
 # ------------------------------------------------------------------------------------------------ training arm (--mode train)
-def train_leg(sd, dev, world, rank, local, B, T, K, W, prof_kernels=True, tail=False, cpu=False, e2e=True):
+def train_leg(sd, dev, world, rank, local, B, T, K, W, prof_kernels=True, tail=False, cpu=False, e2e=True, train_graph=True):
     """BASELINE configs[1] / [4]: K full train steps of audio.yml at x[B,2,T,256] per GPU, dropout 0.1 active -- per step:
     zero_grad, noise_estimation_loss forward + backward (functions/losses.py:4-18), NCCL all-reduce of the flat gradient buffer
     when N > 1, clip_grad_norm_ per group, AdaBelief + AdamW, LambdaLR, EMA (runners/diffusion.py:130-183), and the re-pack of the
@@ -597,13 +598,18 @@ def train_leg(sd, dev, world, rank, local, B, T, K, W, prof_kernels=True, tail=F
             return float(tns.item())
         return v
 
+    graphed = [None]
+
     def step(x0, e, t, ev=None):
         if ev:
             ev[0].record()
-        for o in optimizers.values():
-            o.zero_grad(set_to_none=True)
-        loss = noise_estimation_loss(model, x0, t, e, al)
-        (loss / world if world > 1 else loss).backward()
+        if graphed[0] is not None:
+            loss = graphed[0](x0, t, e)                      # captured re-pack + forward + backward (models/training.py)
+        else:
+            for o in optimizers.values():
+                o.zero_grad(set_to_none=True)
+            loss = noise_estimation_loss(model, x0, t, e, al)
+            (loss / world if world > 1 else loss).backward()
         if ev:
             ev[1].record()
         rdist.allreduce_gradients(params, model.flat_grad)
@@ -622,6 +628,10 @@ def train_leg(sd, dev, world, rank, local, B, T, K, W, prof_kernels=True, tail=F
         return loss
 
     x0, e, t = x_host.to(dev), e_host.to(dev), t_host.to(dev)
+    step(x0, e, t)
+    if train_graph:
+        from ddim_audio_b200.models.training import GraphedLossBackward
+        graphed[0] = GraphedLossBackward(model, al, x0, t, e, world)
     for _ in range(W):
         step(x0, e, t)
     clocks = ClockSampler(local)
@@ -641,6 +651,7 @@ def train_leg(sd, dev, world, rank, local, B, T, K, W, prof_kernels=True, tail=F
     # launches of a step costs the step ~3 ms: 57.1 against 54.0 ms); the throughput figures above are from the unprofiled pass
     prof = []
     if prof_kernels:
+        held, graphed[0] = graphed[0], None     # the library profiler records at launch time: the profiled pass issues the step eagerly
         _C.prof_enable(True)
         _C.prof_report()
         for k in range(K):
@@ -648,6 +659,7 @@ def train_leg(sd, dev, world, rank, local, B, T, K, W, prof_kernels=True, tail=F
         torch.cuda.synchronize()
         prof = _C.prof_report()
         _C.prof_enable(False)
+        graphed[0] = held
     clk = clocks.stop()
     fb_ms = max_over_ranks(sum(v[0].elapsed_time(v[2]) for v in evs) / K)
     ar_ms = max_over_ranks(sum(v[1].elapsed_time(v[2]) for v in evs) / K)
@@ -667,7 +679,8 @@ def train_leg(sd, dev, world, rank, local, B, T, K, W, prof_kernels=True, tail=F
            "gpu_launches": int(launches), "roofline": roof,
            "step_roofline": {"t_roof_ms_per_step": t_roof / K, "frac": (t_roof / K) / (ms / K)} if prof else None,
            "kernels": kern[:int(os.environ.get("DDIMB_BENCH_TRAIN_KERNELS", "12"))], "clocks": clk, "finite": finite, "last_loss": float(loss.item()), "dtype": "bf16",
-           "timing": "CUDA events around K full steps, barrier + synchronize both sides, max over ranks; kernel table / roofline from a second, profiled pass of K steps"}
+           "timing": "CUDA events around K full steps, barrier + synchronize both sides, max over ranks; kernel table / roofline from a second, profiled pass of K eagerly issued steps",
+           "graph": bool(graphed[0] is not None)}
 
     # e2e: pinned host batch in, loss scalar out, every step (the runner's own train_step does exactly this)
     if e2e:
@@ -748,7 +761,7 @@ def run_train(args):
         os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=dev)
     sd = synthetic_state_dict()
-    tr = train_leg(sd, dev, world, rank, local, args.batch, args.t_size, args.steps, max(args.warmup, 0), prof_kernels=True, tail=True,
+    tr = train_leg(sd, dev, world, rank, local, args.batch, args.t_size, args.steps, max(args.warmup, 0), prof_kernels=True, tail=True, train_graph=not args.no_train_graph,
                    cpu=not args.no_cpu_baseline, e2e=not args.no_e2e)
     if rank == 0:
         B, T = args.batch, args.t_size

@@ -66,7 +66,7 @@ SIGNATURES = {
     "ddimb_layernorm512_bwd": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _ll, _i, _vp, _vp, _i, _f],
     "ddimb_gelu": [_vp, _vp, _vp, _ll],
     "ddimb_add_split_bf16": [_vp, _vp, _vp, _vp, _ll, _i, _i, _ll],
-    "ddimb_dropout": [_vp, _vp, _ll, _f, C.c_ulonglong],
+    "ddimb_dropout": [_vp, _vp, _ll, _f, C.c_ulonglong, _vp],
     "ddimb_tokens_ln_bwd": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _f],
     "ddimb_nhwc_to_tokens": [_vp, _vp, _i, _i, _i, _i],
     "ddimb_linear_small_wgrad": [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i],

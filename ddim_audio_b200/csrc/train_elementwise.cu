@@ -568,17 +568,19 @@ __device__ __forceinline__ uint32_t mix32(uint64_t x) {
   return (uint32_t)x;
 }
 __global__ void __launch_bounds__(256) dropout_kernel(const float* __restrict__ x, float* __restrict__ y, int64_t n, uint32_t thresh, float scale,
-                                                      uint64_t seed) {
+                                                      uint64_t seed, const unsigned long long* __restrict__ seed_dev) {
+  if (seed_dev) seed += *seed_dev;     // a captured launch (CUDA graph) takes the step's seed from device memory
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
     y[i] = mix32(seed + (uint64_t)i * 0x9E3779B97F4A7C15ULL) >= thresh ? x[i] * scale : 0.f;
 }
 
-extern "C" int ddimb_dropout(const float* x, float* y, long long n, float p, unsigned long long seed, cudaStream_t stream) {
+extern "C" int ddimb_dropout(const float* x, float* y, long long n, float p, unsigned long long seed, const unsigned long long* seed_dev,
+                             cudaStream_t stream) {
   DDIMB_CHECK_ARG(x && y && n > 0 && p >= 0.f && p < 1.f);
   DDIMB_PROF(stream, "dropout", 0, 0, 8.0 * n, 0.0);
   int64_t blocks = (n + 255) / 256;
   if (blocks > 8LL * ddimb_num_sms()) blocks = 8LL * ddimb_num_sms();
-  dropout_kernel<<<(int)blocks, 256, 0, stream>>>(x, y, n, (uint32_t)((double)p * 4294967296.0), 1.0f / (1.0f - p), seed);
+  dropout_kernel<<<(int)blocks, 256, 0, stream>>>(x, y, n, (uint32_t)((double)p * 4294967296.0), 1.0f / (1.0f - p), seed, seed_dev);
   DDIMB_LAUNCH_CHECK();
   return DDIMB_OK;
 }

@@ -61,7 +61,9 @@ def forward_train(model, x, t):
     sv.x, sv.t, sv.pk = x, t, pk
     p_drop = model.transformer.embedding.dropout_p if model.training else 0.0
     sv.p_drop = p_drop
-    sv.seed = int(torch.randint(0, 2 ** 62, (1,)).item()) if p_drop > 0 else 0
+    # the step's seed: drawn on the host, or (captured steps: GraphedLossBackward) read from device memory by the kernels
+    sv.seed_dev = model.__dict__.get("_seed_dev")
+    sv.seed = (int(torch.randint(0, 2 ** 62, (1,)).item()) if sv.seed_dev is None else 0) if p_drop > 0 else 0
 
     # ---- timestep embedding, pre-activations kept (:107-120)
     lin = model.temb.weight
@@ -113,7 +115,7 @@ def forward_train(model, x, t):
     xr = ops.linear(sv.tok, pk["proj_w"], tr.embedding.projection.bias, out_f32=True)
     site = 0
     if p_drop > 0:
-        xr = ops.dropout(xr, p_drop, sv.seed + site * _SEED_STRIDE, out=xr)
+        xr = ops.dropout(xr, p_drop, sv.seed + site * _SEED_STRIDE, out=xr, seed_dev=sv.seed_dev)
     xbf = torch.empty((rows, 2 * H), dtype=torch.bfloat16, device=dev)
     ops.split_bf16(xr, xbf, True)
     sv.layers = []
@@ -127,7 +129,7 @@ def forward_train(model, x, t):
         gact = ops.gelu(u)
         v = ops.linear(gact, pw["w2"], lay.output.dense.bias, out_f32=True)
         if p_drop > 0:
-            v = ops.dropout(v, p_drop, sv.seed + site * _SEED_STRIDE, out=v)
+            v = ops.dropout(v, p_drop, sv.seed + site * _SEED_STRIDE, out=v, seed_dev=sv.seed_dev)
         ln2 = lay.output.LayerNorm
         xbf = torch.empty((rows, 2 * H), dtype=torch.bfloat16, device=dev)
         xr_next = ops.layernorm512(v, hr, ln2.weight, ln2.bias, tr.ln_eps, xbf, True)
@@ -235,7 +237,7 @@ def backward_train(model, sv, gout):
                                    G[pre + ".output.LayerNorm.bias"], tr.ln_eps, dsbf=dvbf, write_lo=False)
         dv = ds2
         if sv.p_drop > 0:
-            dv = ops.dropout(ds2, sv.p_drop, sv.seed + rec["site"] * _SEED_STRIDE)
+            dv = ops.dropout(ds2, sv.p_drop, sv.seed + rec["site"] * _SEED_STRIDE, seed_dev=sv.seed_dev)
             ops.add_split_bf16(dv, None, dvbf, False)
         ops.colsum(dv, G[pre + ".output.dense.bias"])
         ops.linear_wgrad(rec["gact"], dvbf, G[pre + ".output.dense.weight"])
@@ -252,7 +254,7 @@ def backward_train(model, sv, gout):
     dxr = torch.empty_like(dy1)
     ops.add_split_bf16(dy1, dy2, dxbf, False, sum_out=dxr)
     if sv.p_drop > 0:
-        dxr = ops.dropout(dxr, sv.p_drop, sv.seed, out=dxr)
+        dxr = ops.dropout(dxr, sv.p_drop, sv.seed, out=dxr, seed_dev=sv.seed_dev)
         ops.add_split_bf16(dxr, None, dxbf, False)
     ops.colsum(dxr, G["transformer.embedding.projection.bias"])
     ops.linear_wgrad(sv.tok, dxbf, G["transformer.embedding.projection.weight"])
@@ -304,3 +306,75 @@ class DenoiserFn(torch.autograd.Function):
         grads = tuple(G[name] for name in model.__dict__["_param_names"])
         del G
         return (None, None, None) + grads
+
+
+# ------------------------------------------------------------------------------------------------ captured loss + backward
+def loss_and_grads(model, x0, t, e, a, world=1):
+    """noise_estimation_loss forward + backward WITHOUT the autograd engine (functions/losses.py:4-18 and its derivative): returns
+    (loss, flat gradient buffer, {parameter name: view into it}) of loss / world.  The same library calls as the autograd path
+    (functions/losses.py, DenoiserFn) in the same order."""
+    x0 = x0.contiguous().float()
+    e = e.contiguous().float()
+    t = t.long().contiguous()
+    x = ops.qsample(x0, e, a, t)                                                      # :12-13
+    out, sv = forward_train(model, x, t)                                              # :14
+    out = out.contiguous()
+    per = ops.sqerr_loss(e, out).to(torch.float32)                                    # :15-18
+    loss = per.mean(dim=0)
+    g = torch.full((per.numel(),), 1.0 / (per.numel() * world), dtype=torch.float32, device=x0.device)
+    gout = ops.sqerr_loss_bwd(e, out, g)
+    flat, G = backward_train(model, sv, gout.contiguous().float())
+    return loss, flat, G
+
+
+class GraphedLossBackward:
+    """``loss = noise_estimation_loss(model, x, t, e, alphas); (loss / world).backward()`` for ONE batch shape, captured in a CUDA graph
+    and replayed per step.  A train step at x[32,2,1024,256] is ~1100 launches of 8-400 us: issued from Python the short ones (FNet, the
+    deep levels, the GroupNorm parameter sums) leave the GPU waiting for the host; a replay does not.
+
+    What the capture contains: the re-pack of the bf16 operand copies from the fp32 masters (``_RepackPlan.refresh``: the optimizer
+    changes the masters between replays), forward diffusion, the whole forward and backward (``loss_and_grads``: the library calls of
+    the autograd path without the autograd engine, whose AccumulateGrad nodes are tied to the stream they were created on), the zeroing
+    of the flat gradient buffer.  What stays outside: drawing t / e (copied into static input buffers), the dropout seed (a device word
+    the kernels read: ``ddimb_dropout`` seed_dev), the data-parallel all-reduce, clipping, optimizers, EMA.  After the capture every
+    ``p.grad`` is a static view into ``model.flat_grad``: callers must not ``zero_grad(set_to_none=True)`` (``keep_grads`` puts the
+    tensors back if they did)."""
+
+    def __init__(self, model, alphas, x, t, e, world=1):
+        dev = x.device
+        self.model, self.world = model, world
+        self.params = model._params()
+        self.a = alphas.to(device=dev, dtype=torch.float32).contiguous()
+        self.x, self.t, self.e = x.detach().float().clone(), t.detach().long().clone(), e.detach().float().clone()
+        self.seed = torch.zeros(1, dtype=torch.int64, device=dev)
+        model.__dict__["_seed_dev"] = self.seed
+        cur = torch.cuda.current_stream(dev)
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(cur)
+        with torch.cuda.stream(side), torch.no_grad():
+            for _ in range(2):                  # builds the re-pack plan, sets the kernels' shared-memory attributes, sizes the allocator pools
+                loss_and_grads(model, self.x, self.t, self.e, self.a, world)
+        cur.wait_stream(side)
+        torch.cuda.synchronize(dev)
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph), torch.no_grad():
+            model.mark_params_dirty()           # the re-pack launches belong to every replay
+            self.loss, self.flat_grad, G = loss_and_grads(model, self.x, self.t, self.e, self.a, world)
+        model._params()
+        self.grads = [G[name] for name in model.__dict__["_param_names"]]
+        self.keep_grads()
+
+    def keep_grads(self):
+        for p, g in zip(self.params, self.grads):
+            if p.grad is not g:
+                p.grad = g
+        self.model.flat_grad = self.flat_grad
+
+    def __call__(self, x, t, e):
+        self.x.copy_(x, non_blocking=True)
+        self.t.copy_(t, non_blocking=True)
+        self.e.copy_(e, non_blocking=True)
+        self.seed.random_(0, 2 ** 62)
+        self.keep_grads()
+        self.graph.replay()
+        return self.loss

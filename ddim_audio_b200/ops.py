@@ -313,10 +313,11 @@ def add_split_bf16(a, b, ybf, write_lo, sum_out=None):
     return ybf
 
 
-def dropout(x, p, seed, out=None):
+def dropout(x, p, seed, out=None, seed_dev=None):
+    """``seed_dev``: optional int64 device tensor added to ``seed`` inside the kernel (CUDA-graph replays: models/training.py)."""
     if out is None:
         out = torch.empty_like(x)
-    call("ddimb_dropout", ptr(x, f32), ptr(out, f32), x.numel(), float(p), int(seed) & 0xFFFFFFFFFFFFFFFF)
+    call("ddimb_dropout", ptr(x, f32), ptr(out, f32), x.numel(), float(p), int(seed) & 0xFFFFFFFFFFFFFFFF, ptr(seed_dev))
     return out
 
 

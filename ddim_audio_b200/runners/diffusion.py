@@ -109,6 +109,8 @@ def antithetic_timesteps(n, num_timesteps, generator=None):
 class Diffusion(object):
     def __init__(self, args, config, device=None):
         self.args = args
+        # extension: --train_graph replays one captured (re-pack + forward + backward) per train step (fixed batch shape)
+        self.train_graph = bool(getattr(args, "train_graph", False))
         self.config = config
         if device is None:
             if not torch.cuda.is_available():
@@ -251,8 +253,19 @@ class Diffusion(object):
         if t is None:
             t = antithetic_timesteps(n, self.num_timesteps)
         t = t.to(self.device)
-        loss = loss_registry[self.config.model.type](model, x, t, e, self.alphas)
-        (loss / world if world > 1 else loss).backward()
+        loss_fn = loss_registry[self.config.model.type]
+        if getattr(self, "train_graph", False) and model.training:
+            # one captured (re-pack + forward + backward) per batch shape, replayed per step (models/training.py::GraphedLossBackward)
+            from ..models.training import GraphedLossBackward
+            cache = model.__dict__.setdefault("_train_graphs", {})
+            key = (tuple(x.shape), str(x.device), world)
+            gl = cache.get(key)
+            if gl is None:
+                gl = cache[key] = GraphedLossBackward(model, self.alphas, x, t, e, world)
+            loss = gl(x, t, e)
+        else:
+            loss = loss_fn(model, x, t, e, self.alphas)
+            (loss / world if world > 1 else loss).backward()
         if world > 1:
             rdist.allreduce_gradients(list(model.parameters()), getattr(model, "flat_grad", None))
         return loss
@@ -260,9 +273,11 @@ class Diffusion(object):
     def train_step(self, model, x, optimizers, schedulers, grad_group, ema_helper, step, epoch, t=None, e=None):
         """:130-199.  ``t`` / ``e`` (extension, default None = drawn as the reference draws them, :137-142) inject the timesteps
         and the noise for reproducible runs."""
-        model.train()
-        for opt in optimizers.values():
-            opt.zero_grad(set_to_none=True)
+        if not model.training:
+            model.train()
+        if not getattr(self, "train_graph", False):        # a captured step owns static gradient tensors and overwrites them
+            for opt in optimizers.values():
+                opt.zero_grad(set_to_none=True)
         loss = self.loss_and_backward(model, x, t=t, e=e)
         loggings = {"step": step, "loss": float(loss.item())}
         for g in grad_group.values():

@@ -264,8 +264,10 @@ int ddimb_gelu(const void* u, const void* dact, void* out, long long n, cudaStre
 int ddimb_add_split_bf16(const float* a, const float* b, float* sum_out, void* ybf, long long ldy, int H, int write_lo, long long rows,
                          cudaStream_t stream);
 /* nn.Dropout (models/diffusion.py:129,144; hf modeling_fnet.py:226-231): counter-based mask from (seed, index); the backward
- * is the same call on the gradient. */
-int ddimb_dropout(const float* x, float* y, long long n, float p, unsigned long long seed, cudaStream_t stream);
+ * is the same call on the gradient.  seed_dev (nullable, DEVICE): added to seed at run time -- a launch captured in a CUDA graph takes each
+ * replay's seed from device memory. */
+int ddimb_dropout(const float* x, float* y, long long n, float p, unsigned long long seed, const unsigned long long* seed_dev,
+                  cudaStream_t stream);
 /* backward of ddimb_tokens_ln (+ add: gradient of the additive skip reading the same tensor); dgamma / dbeta accumulated. */
 int ddimb_tokens_ln_bwd(const void* x, const float* te, const float* gamma, const float* dtok, const void* add, void* dx, float* dgamma,
                         float* dbeta, int B, int S, int W, int C, float eps, cudaStream_t stream);
