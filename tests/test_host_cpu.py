@@ -124,3 +124,26 @@ def test_fourier_operands_reproduce_fft():
     y = cs @ u[:H].T + ss @ u[H:].T                  # a2 stores -sin
     ref = torch.fft.fftn(x, dim=(0, 1)).real
     assert float((y - ref).abs().max()) < 1e-3
+
+
+def test_operand_layouts_are_strided_gathers_of_the_masters():
+    """models/diffusion.py::_gather_torch with the (dims, strides, offset) Model._pack records for ddimb_repack must equal the torch
+    statements of the operand layouts (tap-major 3x3 / 4x4 kernels, flipped + transposed data-gradient twins, Linear transposes)."""
+    import torch
+
+    from ddim_audio_b200.models.diffusion import _gather_torch as G
+
+    g = torch.Generator().manual_seed(11)
+    Co, Ci = 5, 7
+    w = torch.randn(Co, Ci, 3, 3, generator=g)
+    assert torch.equal(G(w, (Co, 3, 3, Ci), (Ci * 9, 3, 1, 9), 0).reshape(Co, -1), w.permute(0, 2, 3, 1).reshape(Co, -1))
+    assert torch.equal(G(w, (Ci, 3, 3, Co), (9, -3, -1, Ci * 9), 8).reshape(Ci, -1), w.flip(2, 3).permute(1, 2, 3, 0).reshape(Ci, -1))
+    O, I = 6, 4
+    w4 = torch.randn(O, I, 4, 4, generator=g)
+    assert torch.equal(G(w4, (O, 4, 4, I), (I * 16, 4, 1, 16), 0).reshape(O, -1), w4.permute(0, 2, 3, 1).reshape(O, -1))
+    assert torch.equal(G(w4, (4, 4, I, O), (4, 1, 16, I * 16), 0).reshape(16 * I, O), w4.permute(2, 3, 1, 0).reshape(-1, O))
+    l = torch.randn(9, 4, generator=g)
+    assert torch.equal(G(l, (1, 1, 9, 4), (0, 0, 4, 1), 0).reshape(9, 4), l)
+    assert torch.equal(G(l, (1, 1, 4, 9), (0, 0, 1, 4), 0).reshape(4, 9), l.t())
+    wo = torch.randn(2, 32, 3, 3, generator=g)
+    assert torch.equal(G(wo, (32, 2, 3, 3), (9, 288, -3, -1), 8), wo.flip(2, 3).permute(1, 0, 2, 3))
