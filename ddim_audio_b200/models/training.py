@@ -61,9 +61,11 @@ def forward_train(model, x, t):
     sv.x, sv.t, sv.pk = x, t, pk
     p_drop = model.transformer.embedding.dropout_p if model.training else 0.0
     sv.p_drop = p_drop
-    # the step's seed: drawn on the host, or (captured steps: GraphedLossBackward) read from device memory by the kernels
+    # the step's seed: drawn on the host (a CPU draw: legal under stream capture, where its value is baked into the launches) plus, once a
+    # captured step exists (GraphedLossBackward), a device word the kernels add -- that word is what changes between replays, the host
+    # part is what changes between eagerly issued steps
     sv.seed_dev = model.__dict__.get("_seed_dev")
-    sv.seed = (int(torch.randint(0, 2 ** 62, (1,)).item()) if sv.seed_dev is None else 0) if p_drop > 0 else 0
+    sv.seed = int(torch.randint(0, 2 ** 62, (1,)).item()) if p_drop > 0 else 0
 
     # ---- timestep embedding, pre-activations kept (:107-120)
     lin = model.temb.weight
